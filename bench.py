@@ -1,0 +1,386 @@
+#!/usr/bin/env python
+"""bench.py -- Lloyd-iteration throughput of the B200 k-means path (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c3|c2|c1|c4] [--impl reference]
+
+N > 1 is launched by the driver as ``python -m torch.distributed.run --nproc-per-node N ...``
+(one rank per GPU, NCCL).  Rank 0 prints ONE JSON line.
+
+A *step* is one Lloyd iteration over the rank's resident row shard: pack centres -> K1 fused
+distance/argmin (+ fp64 re-decision of flagged rows) -> K2 sums/counts/inertia -> one allreduce of
+the packed [k*d | k | 1] float64 buffer -> K3 finalize -> 8-byte shift read (the reference's one
+``compute()`` per iteration, dask_ml/cluster/k_means.py:602).
+
+Workloads (BASELINE.json configs).  The metric is quoted on C3 (N=1e9, d=64, k=1024, float32):
+256 GB of X does not fit one 180 GB B200, so the default per-GPU workload is the C3 shard of the
+8-GPU run (N/8 = 1.25e8 rows per GPU; WEAK scaling: at --gpus 8 the job IS C3).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+WORKLOADS = {
+    # name: (rows per GPU, d, k, dtype, description)
+    "c3": (125_000_000, 64, 1024, "float32", "C3 shard: N=1e9/8=1.25e8 rows per GPU, d=64, k=1024, float32 blobs"),
+    "c2": (100_000_000, 32, 256, "float32", "C2: N=1e8 rows per GPU, d=32, k=256, float32 blobs"),
+    "c1": (1_000_000, 16, 8, "float64", "C1: N=1e6 rows per GPU, d=16, k=8, float64 blobs"),
+    "c4": (25_000_000, 128, 8192, "float32", "C4 shard: N=2e8/8=2.5e7 rows per GPU, d=128, k=8192, float32 blobs"),
+}
+METRIC = "lloyd_points_per_sec"
+UNIT = "points/s"
+
+
+def _peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            p = json.load(f)
+        return float(p["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clock / throttle-reason sampling DURING the timed region (profiling recipe)."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.gpu_index = gpu_index
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200",
+                 "-i", str(self.gpu_index)],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        try:
+            out, _ = self.proc.communicate(timeout=5)
+        except Exception:
+            self.proc.kill()
+            out = ""
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in out.strip().splitlines():
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# =================================================================================================
+# reference arm: the reference's CPU path (oracle restatement -- dask is not installable, see
+# DESIGN.md) on the host cores, same metric / config, bounded sample
+# =================================================================================================
+def _host_sample(n, d, k, dtype, seed=0):
+    rs = np.random.RandomState(seed)
+    centers = rs.uniform(-10, 10, size=(k, d))
+    lab = rs.randint(0, k, size=n)
+    X = centers[lab]
+    X += rs.standard_normal((n, d))
+    return np.ascontiguousarray(X.astype(dtype))
+
+
+def cpu_reference_fit_rate(X, k, steps, warmup, cores):
+    """points/s of ``KMeans(init=ndarray, max_iter=1, tol=0).fit(X)`` restated on the CPU: one Lloyd
+    iteration + the reference's final labelling pass, one row block per core in a thread pool
+    (what KMeans._check_array + the threaded scheduler do, reference k_means.py:192-193)."""
+    from oracle import kmeans_oracle as orc
+
+    chunks = orc.row_chunks(len(X), ncpu=cores)
+    init = X[:k].copy()
+    times = []
+    for it in range(warmup + steps):
+        t0 = time.perf_counter()
+        orc.KMeansOracle(n_clusters=k, init=init, max_iter=1, tol=0.0, chunks=chunks, n_threads=cores).fit(X)
+        dt = time.perf_counter() - t0
+        if it >= warmup:
+            times.append(dt)
+    return len(X) / (sum(times) / len(times)), sum(times) / len(times)
+
+
+def cpu_lloyd_step_rate(X, k, reps, cores):
+    """points/s of ONE Lloyd iteration (argmin_min + _centers_dense + bincount + divide) on the CPU."""
+    from concurrent.futures import ThreadPoolExecutor
+
+    from oracle import kmeans_oracle as orc
+
+    chunks = orc.row_chunks(len(X), ncpu=cores)
+    centers = X[:k].astype(np.float64)
+    with ThreadPoolExecutor(cores) as pool:
+        orc.lloyd_step(X[: max(k, len(X) // 8)], centers, k, (max(k, len(X) // 8),), pool)  # numba/BLAS warm-up
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            _, _, centers, _ = orc.lloyd_step(X, centers, k, chunks, pool)
+        dt = (time.perf_counter() - t0) / reps
+    return len(X) / dt, dt
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    n_full, d, k, dtype, desc = WORKLOADS[args.workload]
+    cores = os.cpu_count() or 1
+    n = args.ref_rows or {"c3": 2_000_000, "c2": 4_000_000, "c1": 1_000_000, "c4": 200_000}[args.workload]
+    X = _host_sample(n, d, k, dtype)
+    steps, warmup = max(1, min(args.steps, 3)), max(1, min(args.warmup, 1))
+    rate, sec = cpu_reference_fit_rate(X, k, steps, warmup, cores)
+    sample = (f"{n} rows of the same blobs (d={d}, k={k}, {dtype}); each step = KMeans(init=ndarray, max_iter=1, "
+              f"tol=0).fit(X) restated on the CPU (oracle/kmeans_oracle.py: sklearn ArgKmin + numba scatter per row "
+              f"block, {cores} threads); dask is not installable here so this is the restatement, not dask itself")
+    line = {
+        "impl": "reference", "metric": METRIC, "value": rate, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
+        "warmup": warmup, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic",
+        "config": {"workload": desc, "sample_rows": n, "d": d, "k": k},
+        "cpu_baseline": {"value": rate, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+# =================================================================================================
+# our arm
+# =================================================================================================
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    from dask_ml_b200 import _comm
+    from dask_ml_b200._engine import get_engine
+    from dask_ml_b200.cluster import KMeans
+
+    eng = get_engine()
+    comm = _comm.default_comm()
+    dev = eng.device
+    n_local, d, k, dtype_s, desc = WORKLOADS[args.workload]
+    if args.rows:
+        n_local = args.rows
+    tdtype = torch.float32 if dtype_s == "float32" else torch.float64
+    esize = 4 if dtype_s == "float32" else 8
+
+    # ---- synthetic blobs, generated on the device per shard (make_blobs distribution) --------
+    g = torch.Generator(device="cpu").manual_seed(0)
+    true_centers = (torch.rand(k, d, generator=g, dtype=torch.float64) * 20 - 10).to(tdtype)
+    X = eng.make_blobs(n_local, d, true_centers, 1.0, seed=1234, row_offset=rank * n_local, dtype=tdtype)
+    init = X[:k].to(torch.float64).contiguous().clone()
+    if world > 1:
+        comm.broadcast_(init, 0)  # fixed init = first k rows of the GLOBAL array
+    torch.cuda.synchronize()
+
+    acc = torch.zeros(eng.acc_len(k, d), dtype=torch.float64, device=dev)
+    labels = torch.empty(n_local, dtype=torch.int32, device=dev)
+    mind2 = torch.empty(n_local, dtype=tdtype, device=dev)
+    c_a, c_b = init.clone(), torch.empty_like(init)
+    shift_t = torch.zeros(1, dtype=torch.float64, device=dev)
+    state = {"pack": None, "flagged": 0}
+
+    def step(c_old, c_new):
+        state["pack"] = eng.pack(c_old, state["pack"])
+        eng.assign(X, state["pack"], labels, mind2)
+        acc.zero_()
+        eng.update(X, labels, mind2, k, acc)
+        comm.allreduce_sum_(acc)
+        eng.finalize(acc, k, d, c_old, c_new, shift_t)
+        return float(shift_t.item())
+
+    for _ in range(args.warmup):
+        step(c_a, c_b)
+        c_a, c_b = c_b, c_a
+
+    # ---- timed region -----------------------------------------------------------------------
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    eng.k1_events = []
+    launches0 = eng.launches
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for _ in range(args.steps):
+        step(c_a, c_b)
+        c_a, c_b = c_b, c_a
+    ev1.record()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    ms_total = ev0.elapsed_time(ev1)
+    t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total = float(t.item())
+    clocks = sampler.stop() if rank == 0 else None
+    launches = eng.launches - launches0
+    k1_ms = [a.elapsed_time(b) for a, b in eng.k1_events]
+    eng.k1_events = None
+    flagged = eng.flagged_count()
+    inertia = float(acc[-1].item())
+    counts_ok = int(round(float(acc[k * d : k * d + k].sum().item()))) == n_local * world
+
+    ms_per_step = ms_total / args.steps
+    value = n_local * world / (ms_per_step * 1e-3)
+
+    if rank != 0:
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the dominant kernel (K1), measured live -----------------------------------
+    hbm_peak, peak_src = _peaks()
+    k1_avg_ms = sum(k1_ms) / len(k1_ms)
+    flops = 2.0 * n_local * k * d
+    bytes_alg = n_local * (d * esize + 4)
+    roof = {"kernel": "assign (K1)", "traffic": None}
+    k1_is_ffma = dtype_s == "float32" and k > 16 and d <= 128
+    # FP32 / FP64 pipe peak measured here with the FMA probe (MEASURED_PEAKS.json has HBM + bf16 only)
+    sink = torch.zeros(8, dtype=tdtype, device=dev)
+    probe = "b200km_probe_ffma" if dtype_s == "float32" else "b200km_probe_dfma"
+    iters = 4000 if dtype_s == "float32" else 1000
+    pe0, pe1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    best = 0.0
+    for _ in range(4):
+        pe0.record()
+        eng._call(probe, sink.data_ptr(), 148 * 2, 1024, iters, eng._stream())
+        pe1.record()
+        torch.cuda.synchronize()
+        best = max(best, 2.0 * 64 * iters * 148 * 2 * 1024 / (pe0.elapsed_time(pe1) * 1e-3) / 1e12)
+    fma_peak = best
+    if k1_is_ffma:
+        ach = flops / (k1_avg_ms * 1e-3) / 1e12
+        roof.update({"bound": "fp32_ffma_pipe", "achieved": ach, "peak": fma_peak, "unit": "TFLOP/s",
+                     "frac": ach / fma_peak,
+                     "peak_source": "FFMA probe kernel (b200km_probe_ffma) timed in this run; nominal 148 SM x 128 "
+                                    "x 2 x 1.965 GHz = 74.5",
+                     "hbm_frac": bytes_alg / (k1_avg_ms * 1e-3) / 1e9 / hbm_peak})
+    else:
+        ach = bytes_alg / (k1_avg_ms * 1e-3) / 1e9
+        roof.update({"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
+                     "peak_source": peak_src, "fma_pipe_peak_tflops": fma_peak})
+    roof["k1_ms_per_launch"] = k1_avg_ms
+    roof["k1_share_of_step"] = k1_avg_ms / ms_per_step
+    roof["alg_bytes_per_launch"] = bytes_alg
+    roof["alg_flops_per_launch"] = flops
+
+    # ---- e2e: the user's call with HOST buffers (H2D + fit + D2H inside the timed region) -------
+    e2e = None
+    if not args.no_e2e:
+        n_e = min(n_local, args.e2e_rows)
+        host = torch.empty(n_e, d, dtype=tdtype).pin_memory()
+        host.copy_(X[:n_e])
+        init_h = init.cpu().numpy().astype(np.float32 if dtype_s == "float32" else np.float64)
+        torch.cuda.synchronize()
+        for _ in range(2):
+            KMeans(n_clusters=k, init=init_h, max_iter=1, tol=0.0).fit(host)
+        es = max(3, min(args.steps, 5))
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(es):
+            km = KMeans(n_clusters=k, init=init_h, max_iter=1, tol=0.0).fit(host)
+            _ = km.inertia_
+        torch.cuda.synchronize()
+        dt = (time.perf_counter() - t0) / es
+        e2e = {"value": n_e * world / dt, "unit": UNIT,
+               "h2d_bytes_per_step": n_e * d * esize + k * d * 8,
+               "d2h_bytes_per_step": k * d * esize + 8 + 8,
+               "rows_per_step": n_e, "ms_per_step": dt * 1e3,
+               "call": "KMeans(n_clusters=k, init=ndarray, max_iter=1, tol=0).fit(pinned host tensor): H2D copy, "
+                       "finite check, 1 Lloyd iteration, the final (non-squared) labelling pass, D2H of centres "
+                       "and inertia"}
+
+    # ---- CPU baseline on a bounded sample (rank 0, N=1 only) -------------------------------------
+    cpu = None
+    if world == 1 and not args.no_cpu:
+        cores = os.cpu_count() or 1
+        n_s = args.cpu_rows or {"c3": 1_000_000, "c2": 2_000_000, "c1": 1_000_000, "c4": 100_000}[args.workload]
+        n_s = min(n_s, n_local)
+        Xs = X[:n_s].cpu().numpy()
+        rate, sec = cpu_lloyd_step_rate(Xs, k, 2, cores)
+        cpu = {"value": rate, "unit": UNIT, "cores": cores, "kind": "port",
+               "sample": f"first {n_s} rows of the same device-generated blobs; 1 warm-up + 2 timed Lloyd iterations "
+                         f"of oracle/kmeans_oracle.py (sklearn ArgKmin float64 + numba scatter, one row block per "
+                         f"core, {cores} threads); {sec * 1e3:.1f} ms per iteration",
+               "gflops": 2.0 * n_s * k * d / sec / 1e9}
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32" if dtype_s == "float32" else "f64", "data": "synthetic",
+        "config": {"workload": desc, "rows_per_gpu": n_local, "rows_total": n_local * world, "d": d, "k": k,
+                   "init": "first k rows", "l2": f"inputs {n_local * d * esize / 1e9:.1f} GB per GPU >> 126 MB L2 "
+                   "(no flush needed)", "parallelism": f"rows sharded over {world} GPU(s), 1 allreduce/iter"},
+        "iters_per_sec": 1e3 / ms_per_step,
+        "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
+        "checks": {"counts_sum_to_n": counts_ok, "inertia": inertia, "rows_refined_fp64_last_iter": flagged},
+    }
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
+    ap.add_argument("--rows", type=int, default=0, help="override rows per GPU")
+    ap.add_argument("--e2e-rows", type=int, default=4_194_304)
+    ap.add_argument("--cpu-rows", type=int, default=0)
+    ap.add_argument("--ref-rows", type=int, default=0)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,286 @@
+"""Device engine: thin Python wrappers that hand torch CUDA buffers to the C ABI.
+
+torch is used only for device memory, streams and (elsewhere) NCCL; every computation on the
+path is one of the ``b200km_*`` entry points.  There is no fallback: constructing the engine
+without a CUDA device or without ``libb200km.so`` raises.
+
+The engine interface (``pack / assign / update / finalize / mindist_update / bernoulli / gather /
+cdist / row_norms / has_nonfinite / reduce_sum``) is what the host drivers in
+``cluster/k_means.py`` and ``metrics/pairwise.py`` program against.
+"""
+from __future__ import annotations
+
+from typing import Optional, Tuple
+
+import numpy as np
+import torch
+
+from . import _lib
+
+__all__ = ["CudaEngine", "get_engine", "CenterPack"]
+
+_MAX_ROWS_PER_CALL = 1 << 30  # the kernels index rows with int32
+
+
+def _suffix(t: torch.Tensor) -> str:
+    if t.dtype == torch.float32:
+        return "f32"
+    if t.dtype == torch.float64:
+        return "f64"
+    raise TypeError(f"dask_ml_b200 kernels take float32 or float64, got {t.dtype}")
+
+
+class CenterPack:
+    """Device-side expansion of the (k, d) float64 centres (see b200km_pack_centers)."""
+
+    __slots__ = ("buf", "k", "d", "centers64")
+
+    def __init__(self, buf, k, d, centers64):
+        self.buf, self.k, self.d, self.centers64 = buf, k, d, centers64
+
+
+class CudaEngine:
+    def __init__(self, device=None):
+        self.lib = _lib.load()
+        if not torch.cuda.is_available():
+            raise _lib.B200LibraryError(
+                "dask_ml_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback."
+            )
+        self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
+        self.launches = 0  # kernels launched through this engine (bench.py reports it)
+        self.k1_events = None  # bench.py: set to a list to collect (start, end) CUDA events around K1
+        self._scratch = {}
+
+    # ---- plumbing -------------------------------------------------------------------------
+    def _stream(self) -> int:
+        return torch.cuda.current_stream(self.device).cuda_stream
+
+    def _call(self, name: str, *args, launches: int = 1):
+        rc = getattr(self.lib, name)(*args)
+        _lib.check(rc, name)
+        self.launches += launches
+
+    def _buf(self, key, shape, dtype) -> torch.Tensor:
+        """Reusable scratch tensor (grown on demand) -- keeps the Lloyd loop allocation-free."""
+        n = int(np.prod(shape))
+        t = self._scratch.get(key)
+        if t is None or t.dtype != dtype or t.numel() < n:
+            t = torch.empty(max(n, 1), dtype=dtype, device=self.device)
+            self._scratch[key] = t
+        return t[:n].view(*shape)
+
+    def to_device(self, a, dtype=None) -> torch.Tensor:
+        if isinstance(a, torch.Tensor):
+            t = a
+        else:
+            t = torch.from_numpy(np.ascontiguousarray(a))
+        if dtype is not None and t.dtype != dtype:
+            t = t.to(dtype)
+        return t.to(self.device, non_blocking=True).contiguous()
+
+    @staticmethod
+    def _check_matrix(X: torch.Tensor):
+        if X.dim() != 2 or X.stride(1) != 1:
+            raise ValueError("X must be a row-major 2-D tensor")
+        return X.shape[0], X.shape[1], (X.stride(0) if X.shape[0] > 1 else X.shape[1])
+
+    # ---- K1 -------------------------------------------------------------------------------
+    def pack(self, centers64: torch.Tensor, out: Optional[CenterPack] = None) -> CenterPack:
+        """b200km_pack_centers.  ``centers64``: (k, d) float64 on the device."""
+        assert centers64.dtype == torch.float64 and centers64.is_contiguous()
+        k, d = centers64.shape
+        nbytes = self.lib.b200km_pack_bytes(k, d)
+        if out is None or out.k != k or out.d != d:
+            buf = torch.empty(nbytes + 256, dtype=torch.uint8, device=self.device)
+            off = (-buf.data_ptr()) % 256
+            out = CenterPack(buf[off : off + nbytes], k, d, centers64)
+        out.centers64 = centers64
+        self._call("b200km_pack_centers", centers64.data_ptr(), k, d, out.buf.data_ptr(), self._stream(), launches=1)
+        return out
+
+    def assign(self, X: torch.Tensor, pack: CenterPack, labels: Optional[torch.Tensor] = None,
+               mind2: Optional[torch.Tensor] = None, want_mind2: bool = True, refine: bool = True
+               ) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
+        """labels (int32) and squared min distances (X dtype) of every row of X.
+
+        float32 X: FFMA kernel, then the fp64 re-decision of the flagged near-tie rows, so the
+        labels equal what float64 arithmetic gives (reference: sklearn ArgKmin is float64).
+        """
+        n, d, ldx = self._check_matrix(X)
+        if d != pack.d:
+            raise ValueError(f"X has {d} features, centres have {pack.d}")
+        sfx = _suffix(X)
+        if labels is None:
+            labels = torch.empty(n, dtype=torch.int32, device=self.device)
+        if want_mind2 and mind2 is None:
+            mind2 = torch.empty(n, dtype=X.dtype, device=self.device)
+        mptr = mind2.data_ptr() if (want_mind2 and mind2 is not None) else None
+        st = self._stream()
+        for r0 in range(0, n, _MAX_ROWS_PER_CALL):
+            nn = min(_MAX_ROWS_PER_CALL, n - r0)
+            xs, ls = X[r0 : r0 + nn], labels[r0 : r0 + nn]
+            mp = (mind2[r0 : r0 + nn].data_ptr() if mptr is not None else None)
+            if sfx == "f32":
+                if refine:
+                    flags = self._buf("flag_rows", (nn,), torch.int32)
+                    fcnt = self._buf("flag_count", (1,), torch.int32)
+                    if self.k1_events is not None:
+                        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                        e0.record()
+                    self._call("b200km_assign_f32", xs.data_ptr(), nn, d, ldx, pack.buf.data_ptr(), pack.k,
+                               ls.data_ptr(), mp, flags.data_ptr(), fcnt.data_ptr(), 1, st, launches=1)
+                    if self.k1_events is not None:
+                        e1.record()
+                        self.k1_events.append((e0, e1))
+                    self._call("b200km_refine_f64", xs.data_ptr(), nn, d, ldx, pack.buf.data_ptr(), pack.k,
+                               flags.data_ptr(), fcnt.data_ptr(), ls.data_ptr(), mp, st, launches=1)
+                else:
+                    self._call("b200km_assign_f32", xs.data_ptr(), nn, d, ldx, pack.buf.data_ptr(), pack.k,
+                               ls.data_ptr(), mp, None, None, 0, st, launches=1)
+            else:
+                self._call("b200km_assign_f64", xs.data_ptr(), nn, d, ldx, pack.buf.data_ptr(), pack.k,
+                           ls.data_ptr(), mp, st, launches=1)
+        return labels, (mind2 if want_mind2 else None)
+
+    def flagged_count(self) -> int:
+        """Rows the last float32 assign sent to the fp64 re-decision (synchronises)."""
+        t = self._scratch.get("flag_count")
+        return int(t[0].item()) if t is not None else 0
+
+    # ---- K2 / K3 --------------------------------------------------------------------------
+    def acc_len(self, k: int, d: int) -> int:
+        return int(self.lib.b200km_acc_len(k, d))
+
+    def update(self, X: torch.Tensor, labels: torch.Tensor, mind2: Optional[torch.Tensor], k: int,
+               acc: Optional[torch.Tensor] = None, sqrt: bool = False) -> torch.Tensor:
+        """acc (float64, [k*d sums | k counts | inertia]) += contribution of these rows."""
+        n, d, ldx = self._check_matrix(X)
+        if acc is None:
+            acc = torch.zeros(self.acc_len(k, d), dtype=torch.float64, device=self.device)
+        sfx = _suffix(X)
+        st = self._stream()
+        for r0 in range(0, n, _MAX_ROWS_PER_CALL):
+            nn = min(_MAX_ROWS_PER_CALL, n - r0)
+            self._call(f"b200km_update_{sfx}", X[r0 : r0 + nn].data_ptr(), nn, d, ldx, labels[r0 : r0 + nn].data_ptr(),
+                       (mind2[r0 : r0 + nn].data_ptr() if mind2 is not None else None), k, acc.data_ptr(),
+                       1 if sqrt else 0, st)
+        return acc
+
+    def finalize(self, acc: torch.Tensor, k: int, d: int, centers_old: torch.Tensor,
+                 centers_new: Optional[torch.Tensor] = None, shift: Optional[torch.Tensor] = None):
+        if centers_new is None:
+            centers_new = torch.empty(k, d, dtype=torch.float64, device=self.device)
+        if shift is None:
+            shift = torch.empty(1, dtype=torch.float64, device=self.device)
+        self._call("b200km_finalize", acc.data_ptr(), k, d, centers_old.data_ptr(), centers_new.data_ptr(),
+                   shift.data_ptr(), self._stream())
+        return centers_new, shift
+
+    def reduce_sum(self, v: torch.Tensor, sqrt: bool = False, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        if out is None:
+            out = torch.zeros(1, dtype=torch.float64, device=self.device)
+        if v.numel():
+            self._call(f"b200km_reduce_sum_{_suffix(v)}", v.data_ptr(), v.numel(), 1 if sqrt else 0, out.data_ptr(),
+                       self._stream())
+        return out
+
+    # ---- K4 .. K6 -------------------------------------------------------------------------
+    MINDIST_MAX_M = 8
+
+    def mindist_update(self, X: torch.Tensor, cand: torch.Tensor, mind2: torch.Tensor, init: bool) -> torch.Tensor:
+        """Running min of squared distances to ``cand`` rows; returns the (1,) float64 local cost."""
+        n, d, ldx = self._check_matrix(X)
+        sfx = _suffix(X)
+        cand = cand.to(X.dtype).contiguous()
+        m = cand.shape[0]
+        per = max(1, min(self.MINDIST_MAX_M, (96 * 1024) // (d * X.element_size())))
+        cost = torch.zeros(1, dtype=torch.float64, device=self.device)
+        st = self._stream()
+        first = init
+        for j0 in range(0, m, per):
+            cj = cand[j0 : j0 + per]
+            cost.zero_()
+            for r0 in range(0, n, _MAX_ROWS_PER_CALL):
+                nn = min(_MAX_ROWS_PER_CALL, n - r0)
+                self._call(f"b200km_mindist_update_{sfx}", X[r0 : r0 + nn].data_ptr(), nn, d, ldx, cj.data_ptr(),
+                           cj.shape[0], mind2[r0 : r0 + nn].data_ptr(), 1 if first else 0, cost.data_ptr(), st)
+            first = False
+        return cost
+
+    def bernoulli(self, mind2: torch.Tensor, scale: float, seed: int, round_: int, row_offset: int,
+                  draws: Optional[torch.Tensor] = None, capacity: int = 4096) -> torch.Tensor:
+        """Global indices (int64, unsorted) of the rows picked this round."""
+        n = mind2.numel()
+        sfx = _suffix(mind2)
+        st = self._stream()
+        while True:
+            picked = self._buf("picked", (capacity,), torch.int64)
+            cnt = self._buf("pick_count", (1,), torch.int32)
+            cnt.zero_()
+            self._call(f"b200km_bernoulli_pick_{sfx}", mind2.data_ptr(), n, float(scale), int(seed) & (2**64 - 1),
+                       int(round_) & 0xFFFFFFFF, int(row_offset), (draws.data_ptr() if draws is not None else None),
+                       picked.data_ptr(), cnt.data_ptr(), capacity, st)
+            c = int(cnt.item())
+            if c <= capacity:
+                return picked[:c].clone()
+            capacity = c  # rare: more picks than room -- redo with the exact size (same draws)
+
+    def gather(self, X: torch.Tensor, idx_local: torch.Tensor) -> torch.Tensor:
+        n, d, ldx = self._check_matrix(X)
+        m = idx_local.numel()
+        out = torch.empty(m, d, dtype=X.dtype, device=self.device)
+        if m:
+            idx_local = idx_local.to(device=self.device, dtype=torch.int64).contiguous()
+            self._call(f"b200km_gather_rows_{_suffix(X)}", X.data_ptr(), n, d, ldx, idx_local.data_ptr(), m,
+                       out.data_ptr(), self._stream())
+        return out
+
+    # ---- K7 + helpers ---------------------------------------------------------------------
+    def cdist(self, X: torch.Tensor, Y: torch.Tensor, squared: bool = False, xnorm2=None, ynorm2=None) -> torch.Tensor:
+        n, d, ldx = self._check_matrix(X)
+        Y = Y.contiguous()
+        k = Y.shape[0]
+        out = torch.empty(n, k, dtype=X.dtype, device=self.device)
+        if n and k:
+            self._call(f"b200km_cdist_{_suffix(X)}", X.data_ptr(), n, d, ldx, Y.data_ptr(), k,
+                       (xnorm2.data_ptr() if xnorm2 is not None else None),
+                       (ynorm2.data_ptr() if ynorm2 is not None else None), out.data_ptr(), 1 if squared else 0,
+                       self._stream())
+        return out
+
+    def row_norms(self, X: torch.Tensor, squared: bool = False) -> torch.Tensor:
+        n, d, ldx = self._check_matrix(X)
+        out = torch.empty(n, dtype=X.dtype, device=self.device)
+        if n:
+            self._call(f"b200km_row_norms_{_suffix(X)}", X.data_ptr(), n, d, ldx, out.data_ptr(), 1 if squared else 0,
+                       self._stream())
+        return out
+
+    def has_nonfinite(self, X: torch.Tensor) -> bool:
+        n, d, ldx = self._check_matrix(X)
+        bad = torch.zeros(1, dtype=torch.int32, device=self.device)
+        if n and d:
+            self._call(f"b200km_count_nonfinite_{_suffix(X)}", X.data_ptr(), n, d, ldx, bad.data_ptr(), self._stream())
+        return bool(bad.item())
+
+    def make_blobs(self, n: int, d: int, centers: torch.Tensor, cluster_std: float = 1.0, seed: int = 0,
+                   row_offset: int = 0, dtype=torch.float32, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        if out is None:
+            out = torch.empty(n, d, dtype=dtype, device=self.device)
+        centers = centers.to(device=self.device, dtype=out.dtype).contiguous()
+        self._call(f"b200km_make_blobs_{_suffix(out)}", out.data_ptr(), n, d, d, centers.data_ptr(), centers.shape[0],
+                   float(cluster_std), int(seed), int(row_offset), self._stream())
+        return out
+
+
+_engines = {}
+
+
+def get_engine(device=None) -> CudaEngine:
+    """Per-device engine singleton.  Raises (never falls back) without CUDA / the library."""
+    key = str(device) if device is not None else (f"cuda:{torch.cuda.current_device()}" if torch.cuda.is_available() else "none")
+    eng = _engines.get(key)
+    if eng is None:
+        eng = CudaEngine(device)
+        _engines[key] = eng
+    return eng

@@ -1,0 +1,466 @@
+"""KMeans on B200: the Lloyd iteration and the k-means|| initialisation.
+
+Drop-in for reference dask_ml/cluster/k_means.py: same class, constructor, attributes, module
+functions, argument meaning, quirks and error messages; underneath, every pass over the data
+is a hand-written sm_100a kernel called through ``libb200km.so`` and the only cross-GPU
+traffic is one small allreduce per Lloyd iteration / one small allgather per k-means|| round.
+
+Quirks of the reference kept on purpose:
+  * distances are float64-accurate even for float32 X (K1 + fp64 re-decision of near ties);
+  * ``inertia_`` is the sum of NON-squared distances unless the loop converged to
+    ``shift <= 1e-7`` (reference :612-616);
+  * on convergence the OLD centres are returned (:608-610); ``n_iter_ = i + 1`` (:619);
+  * empty clusters go to the origin (:598-601); ``tol`` is compared raw to the squared
+    Frobenius shift (:605-609);
+  * k-means|| samples ~``oversampling_factor`` rows per round (:535), starts from row 0 (:451),
+    runs ``round(ln cost)`` rounds (:461) and supplements with random rows when fewer than k
+    candidates were found (:489-501).
+
+Multi-GPU: run one process per GPU with ``torch.distributed`` initialised (NCCL); each rank
+passes ITS contiguous row shard to ``fit``.  Attributes are then identical on every rank except
+``labels_``, which covers the rank's own rows.
+"""
+from __future__ import annotations
+
+import logging
+from numbers import Integral
+from typing import Optional
+
+import numpy as np
+import sklearn.cluster
+import torch
+from sklearn.base import BaseEstimator, TransformerMixin
+from sklearn.utils.validation import check_is_fitted
+
+from .. import _comm
+from .._engine import get_engine
+from ..metrics.pairwise import _dev, euclidean_distances, pairwise_distances_argmin_min
+from ..utils import DeviceArray, _timed, _timer, check_array
+
+logger = logging.getLogger(__name__)
+
+__all__ = ["KMeans", "k_means", "k_init", "init_scalable", "init_random", "init_pp", "evaluate_cost",
+           "_sample_points", "_kmeans_single_lloyd", "PhiloxRandomState"]
+
+
+# ---------------------------------------------------------------------------------------------
+# random streams
+# ---------------------------------------------------------------------------------------------
+class PhiloxRandomState:
+    """What ``k_init`` builds for ``init='k-means||'`` when ``random_state`` is an int / None --
+    the stand-in for ``da.random.RandomState(seed)`` (reference :384-386).
+
+    The Bernoulli draws are generated ON THE DEVICE by a counter-based Philox4x32-10 keyed by
+    ``seed`` with counter (global row, round): independent of the sharding, so 1 GPU and 8 GPUs
+    pick the same rows.  dask's per-chunk MT19937 streams cannot be reproduced by construction
+    (they depend on the chunk layout); pass an object with ``uniform(size=, chunks=)`` /
+    ``choice(n, size)`` / ``randint(low, high)`` as ``random_state`` to inject host draws.
+    """
+
+    def __init__(self, seed=None):
+        if seed is None:
+            seed = int(np.random.SeedSequence().generate_state(1, dtype=np.uint64)[0])
+        self.seed = int(seed) & (2**64 - 1)
+        self.round = 0
+
+    def _host(self, tag: int) -> np.random.Generator:
+        return np.random.Generator(np.random.Philox(key=[self.seed, tag]))
+
+    def choice(self, n: int, size: int) -> np.ndarray:
+        # O(size), not O(n): the reference permutes arange(n) (8 GB at n = 1e9), :495-499
+        return self._host(0x63686F69).choice(n, size=size, replace=False)
+
+    def randint(self, low: int, high: int) -> int:
+        return int(self._host(0x72616E64).integers(low, high))
+
+
+class _NumpyRandomState:
+    """Adapter giving ``np.random.RandomState`` the three-call protocol above."""
+
+    def __init__(self, rs: np.random.RandomState):
+        self.rs = rs
+
+    def uniform(self, size, chunks=None):
+        return self.rs.uniform(size=size)
+
+    def choice(self, n, size):
+        return self.rs.choice(n, size=size, replace=False)
+
+    def randint(self, low, high):
+        return int(self.rs.randint(low, high))
+
+
+# ---------------------------------------------------------------------------------------------
+# estimator
+# ---------------------------------------------------------------------------------------------
+class KMeans(TransformerMixin, BaseEstimator):
+    """Scalable KMeans for clustering -- same constructor and attributes as reference
+    dask_ml/cluster/k_means.py:31-251.
+
+    Parameters
+    ----------
+    n_clusters : int, default 8
+    init : {'k-means||', 'k-means++', 'random'} or ndarray (n_clusters, n_features)
+    oversampling_factor : int, default 2
+    max_iter : int
+    tol : float -- compared raw with the squared Frobenius norm of the centre shift
+    random_state : int, RandomState instance or None
+    init_max_iter : int or None
+    n_init : 'auto' or int -- used only by the candidate re-cluster of k-means||
+    precompute_distances, copy_x, n_jobs, algorithm : accepted and ignored, as in the reference
+
+    Attributes
+    ----------
+    cluster_centers_ : np.ndarray (n_clusters, n_features), X's dtype
+    labels_ : DeviceArray int32 (``.compute()`` -> ndarray)
+    inertia_ : float
+    n_iter_ : int
+    n_features_in_ : int
+    """
+
+    def __init__(self, n_clusters=8, init="k-means||", oversampling_factor=2, max_iter=300, tol=0.0001,
+                 precompute_distances="auto", random_state=None, copy_x=True, n_jobs=1, algorithm="full",
+                 init_max_iter=None, n_init="auto"):
+        self.n_clusters = n_clusters
+        self.init = init
+        self.oversampling_factor = oversampling_factor
+        self.random_state = random_state
+        self.max_iter = max_iter
+        self.init_max_iter = init_max_iter
+        self.algorithm = algorithm
+        self.tol = tol
+        self.precompute_distances = precompute_distances
+        self.n_jobs = n_jobs
+        self.copy_x = copy_x
+        self.n_init = n_init
+
+    @_timed(_logger=logger)
+    def _check_array(self, X):
+        """reference :171-202 -> a (n, d) float32/float64 tensor on the device."""
+        try:
+            import pandas as pd
+
+            if isinstance(X, pd.DataFrame):
+                X = X.values
+        except ImportError:  # pragma: no cover
+            pass
+        if type(X).__module__.startswith("dask.") and type(X).__name__ == "DataFrame":
+            X = X.to_dask_array(lengths=True)
+        X = check_array(X, accept_dask_dataframe=False, accept_unknown_chunks=False, accept_sparse=False,
+                        remove_zero_chunks=True, ensure_all_finite=False)
+        eng = get_engine()
+        Xd = _dev(X, eng)  # int32 -> float32, int64 -> float64 (:187-190)
+        if Xd.shape[0] and eng.has_nonfinite(Xd):  # :195-201
+            msg = "Input contains NaN, infinity or a value too large for dtype('float64')."
+            raise ValueError(msg)
+        return Xd
+
+    def fit(self, X, y=None):
+        X = self._check_array(X)
+        labels, centroids, inertia, n_iter = k_means(
+            X, self.n_clusters, oversampling_factor=self.oversampling_factor, random_state=self.random_state,
+            init=self.init, return_n_iter=True, max_iter=self.max_iter, init_max_iter=self.init_max_iter,
+            tol=self.tol, n_init=self.n_init,
+        )
+        self.cluster_centers_ = centroids
+        self.labels_ = labels
+        self.inertia_ = inertia.compute().item()
+        self.n_iter_ = n_iter
+        self.n_features_in_ = X.shape[1]
+        return self
+
+    def transform(self, X, y=None):
+        check_is_fitted(self, "cluster_centers_")
+        X = self._check_array(X)
+        return euclidean_distances(X, self.cluster_centers_)
+
+    def predict(self, X):
+        """Index of the closest centre for every row (int32), reference :230-251."""
+        check_is_fitted(self, "cluster_centers_")
+        X = self._check_array(X)
+        labels = pairwise_distances_argmin_min(X, self.cluster_centers_)[0].astype(np.int32)
+        return labels
+
+
+def k_means(X, n_clusters, init="k-means||", precompute_distances="auto", n_init="auto", max_iter=300,
+            verbose=False, tol=1e-4, random_state=None, copy_x=True, n_jobs=-1, algorithm="full",
+            return_n_iter=False, oversampling_factor=2, init_max_iter=None):
+    """K-means algorithm for clustering (reference :254-294; same defaults, incl. n_jobs=-1)."""
+    labels, inertia, centers, n_iter = _kmeans_single_lloyd(
+        X, n_clusters, max_iter=max_iter, init=init, verbose=verbose, tol=tol, random_state=random_state,
+        oversampling_factor=oversampling_factor, init_max_iter=init_max_iter, n_init=n_init,
+    )
+    if return_n_iter:
+        return labels, centers, inertia, n_iter
+    return labels, centers, inertia
+
+
+# ---------------------------------------------------------------------------------------------
+# initialisation
+# ---------------------------------------------------------------------------------------------
+def _as_device_matrix(X) -> torch.Tensor:
+    if isinstance(X, torch.Tensor) and X.is_cuda and X.dim() == 2 and X.dtype in (torch.float32, torch.float64):
+        return X
+    return _dev(X)
+
+
+def k_init(X, n_clusters, init="k-means||", random_state=None, max_iter=None, oversampling_factor=2, n_init="auto"):
+    """Choose the initial centres (reference :310-401; same validation and messages)."""
+    if isinstance(init, torch.Tensor):
+        init = init.detach().cpu().numpy()
+    if isinstance(init, np.ndarray):
+        K, P = init.shape
+        if K != n_clusters:
+            msg = "Number of centers in provided 'init' ({}) does not match 'n_clusters' ({})"
+            raise ValueError(msg.format(K, n_clusters))
+        if P != X.shape[1]:
+            msg = "Number of features in the provided 'init' ({}) do not match the number of features in 'X'"
+            raise ValueError(msg.format(P, X.shape[1]))
+        return init
+    elif not isinstance(init, str):
+        raise TypeError("'init' must be an array or str, got {}".format(type(init)))
+
+    valid = {"k-means||", "k-means++", "random"}
+
+    if isinstance(random_state, Integral) or random_state is None:
+        if init == "k-means||":
+            random_state = PhiloxRandomState(_agree_seed(random_state))
+        else:
+            random_state = np.random.RandomState(_agree_seed(random_state) % (2**32))
+    if isinstance(random_state, np.random.RandomState) and init == "k-means||":
+        random_state = _NumpyRandomState(random_state)
+
+    if init == "k-means||":
+        return init_scalable(X, n_clusters, random_state, max_iter, oversampling_factor, n_init)
+    elif init == "k-means++":
+        return init_pp(X, n_clusters, random_state)
+    elif init == "random":
+        return init_random(X, n_clusters, random_state)
+    else:
+        raise ValueError("'init' must be one of {}, got {}".format(valid, init))
+
+
+def _agree_seed(seed):
+    """None -> a fresh seed, the SAME on every rank (rank 0 draws, others receive it)."""
+    comm = _comm.default_comm()
+    if seed is not None:
+        return int(seed)
+    s = int(np.random.SeedSequence().generate_state(1, dtype=np.uint64)[0] >> 1)
+    if comm.world > 1:
+        eng = get_engine()
+        t = torch.tensor([s], dtype=torch.int64, device=eng.device)
+        comm.broadcast_(t, 0)
+        s = int(t.item())
+    return s
+
+
+def _gather_global_rows(X: torch.Tensor, gidx, comm, row0: int) -> torch.Tensor:
+    """Rows of the (sharded) X at sorted global indices ``gidx`` -> (m, d) on every rank.
+    reference: ``X[sorted(c_idx)].compute()`` (:479), ``X[locs].compute()`` (:500)."""
+    eng = get_engine(X.device)
+    g = np.asarray(gidx, dtype=np.int64)
+    n_local = X.shape[0]
+    mine = (g >= row0) & (g < row0 + n_local)
+    loc = torch.from_numpy(g[mine] - row0)
+    rows = eng.gather(X, loc)
+    if comm.world > 1:
+        # ranks own increasing, disjoint row ranges and gidx is sorted, so rank-order
+        # concatenation IS index order
+        rows = comm.allgather_varlen(rows)
+    return rows
+
+
+def init_pp(X, n_clusters, random_state):
+    """K-means initialization using k-means++ (reference :404-423: scikit-learn's
+    ``_kmeans_plusplus`` on the fully materialised X -- host-side there too; not a BASELINE
+    config).  X is copied to the host for it."""
+    from sklearn.cluster import kmeans_plusplus
+
+    logger.info("Initializing with k-means++")
+    Xh = _as_device_matrix(X).cpu().numpy()
+    with _timer("initialization of %2d centers" % n_clusters, _logger=logger):
+        centers, _ = kmeans_plusplus(Xh, n_clusters, random_state=random_state)
+    return centers
+
+
+@_timed(_logger=logger)
+def init_random(X, n_clusters, random_state):
+    """K-means initialization using randomly chosen points (reference :426-432)."""
+    logger.info("Initializing randomly")
+    X = _as_device_matrix(X)
+    comm = _comm.default_comm()
+    row0, n_total = comm.row_range(X.shape[0])
+    idx = sorted(random_state.randint(0, n_total, size=n_clusters))
+    return _gather_global_rows(X, idx, comm, row0).cpu().numpy()
+
+
+def evaluate_cost(X, centers):
+    """phi_X(C) = sum_i min_j ||x_i - c_j||^2  (reference :516-519).  Returns a Python float
+    (the reference returns a lazy scalar that its only caller computes at once, :456)."""
+    X = _as_device_matrix(X)
+    eng = get_engine(X.device)
+    comm = _comm.default_comm()
+    C = eng.to_device(np.asarray(centers) if not isinstance(centers, torch.Tensor) else centers, X.dtype)
+    mind2 = eng._buf("mind2_init", (X.shape[0],), X.dtype)
+    cost = eng.mindist_update(X, C, mind2, init=True)
+    comm.allreduce_sum_(cost)
+    return float(cost.item())
+
+
+def _pick(eng, comm, mind2, cost, oversampling_factor, random_state, row0, n_total) -> np.ndarray:
+    """Second half of _sample_points (reference :535-541): p = l * d2 / cost ; picked = p > draws."""
+    scale = float(oversampling_factor) / cost
+    if isinstance(random_state, PhiloxRandomState):
+        picked = eng.bernoulli(mind2, scale, random_state.seed, random_state.round, row0)
+        random_state.round += 1
+    else:
+        # injected host draws (np RandomState, or an object restating dask's RandomState)
+        try:
+            u = random_state.uniform(size=n_total, chunks=None)
+        except TypeError:
+            u = random_state.uniform(size=n_total)
+        u = np.asarray(u, dtype=np.float64)[row0 : row0 + mind2.numel()]
+        picked = eng.bernoulli(mind2, scale, 0, 0, row0, draws=eng.to_device(u))
+    if comm.world > 1:
+        picked = comm.allgather_varlen(picked)
+    return np.sort(picked.cpu().numpy())
+
+
+def _sample_points(X, centers, oversampling_factor, random_state):
+    r"""Sample points independently with probability
+    :math:`p_x = \ell \cdot d^2(x, C) / \phi_X(C)` (reference :522-541).
+    Returns the sorted GLOBAL row indices (ndarray int64)."""
+    X = _as_device_matrix(X)
+    eng = get_engine(X.device)
+    comm = _comm.default_comm()
+    row0, n_total = comm.row_range(X.shape[0])
+    C = eng.to_device(np.asarray(centers) if not isinstance(centers, torch.Tensor) else centers, X.dtype)
+    mind2 = eng._buf("mind2_init", (X.shape[0],), X.dtype)
+    cost = eng.mindist_update(X, C, mind2, init=True)
+    comm.allreduce_sum_(cost)
+    if isinstance(random_state, np.random.RandomState):
+        random_state = _NumpyRandomState(random_state)
+    return _pick(eng, comm, mind2, float(cost.item()), oversampling_factor, random_state, row0, n_total)
+
+
+@_timed(_logger=logger)
+def init_scalable(X, n_clusters, random_state=None, max_iter=None, oversampling_factor=2, n_init="auto"):
+    """K-Means initialization using k-means|| (reference :435-513; algorithm 2 of Bahmani et al.
+    as the reference modifies it).
+
+    A running per-row minimum is kept on the device, so each round costs one pass of K4 over the
+    rows for the NEW candidates only plus one pass of K5 over the minima; the reference
+    recomputes the full n x |C| block matrices every round (:533).
+    """
+    logger.info("Initializing with k-means||")
+    X = _as_device_matrix(X)
+    eng = get_engine(X.device)
+    comm = _comm.default_comm()
+    n_local, d = X.shape
+    row0, n_total = comm.row_range(n_local)
+    if isinstance(random_state, Integral) or random_state is None:
+        random_state = PhiloxRandomState(_agree_seed(random_state))
+    elif isinstance(random_state, np.random.RandomState):
+        random_state = _NumpyRandomState(random_state)
+
+    # Step 1: Initialize Centers (:451-453) -- always global row 0
+    idx = 0
+    c_idx = {idx}
+    new_rows = _gather_global_rows(X, [idx], comm, row0)
+    centers_dev = new_rows
+
+    # Step 2: Initialize cost (:456)
+    mind2 = eng._buf("mind2_init", (n_local,), X.dtype)
+    cost_t = eng.mindist_update(X, new_rows, mind2, init=True)
+    comm.allreduce_sum_(cost_t)
+    cost = float(cost_t.item())
+
+    if cost == 0:
+        n_iter = 0
+    else:
+        n_iter = int(np.round(np.log(cost)))  # :458-461
+    if max_iter is not None:
+        n_iter = min(max_iter, n_iter)  # :463-464
+
+    # Steps 3 - 6: update candidate Centers (:467-479)
+    for i in range(n_iter):
+        with _timer("init iteration %2d/%2d , %2d centers" % (i + 1, n_iter, len(c_idx)), _logger=logger):
+            picked = _pick(eng, comm, mind2, cost, oversampling_factor, random_state, row0, n_total)
+            fresh = sorted(set(int(v) for v in picked) - c_idx)
+            c_idx |= set(fresh)
+            if fresh:
+                new_rows = _gather_global_rows(X, fresh, comm, row0)
+                cost_t = eng.mindist_update(X, new_rows, mind2, init=False)
+                comm.allreduce_sum_(cost_t)
+                cost = float(cost_t.item())
+    centers = _gather_global_rows(X, sorted(c_idx), comm, row0).cpu().numpy()  # :479
+
+    if len(centers) < n_clusters:
+        logger.warning("Found fewer than %d clusters in init (found %d).", n_clusters, len(centers))
+        # supplement with random (:493-501)
+        need = n_clusters - len(centers)
+        locs = sorted(int(v) for v in random_state.choice(n_total, need))
+        extra = _gather_global_rows(X, locs, comm, row0).cpu().numpy()
+        return np.vstack([centers, extra])
+    else:
+        # Step 7, 8 without weights (:503-513): scikit-learn on the (tiny) candidate set, on the
+        # host, exactly as the reference does
+        rng2 = random_state.randint(0, np.iinfo("i4").max - 1)
+        km = sklearn.cluster.KMeans(n_clusters, random_state=rng2, n_init=n_init)
+        km.fit(centers)
+    return km.cluster_centers_
+
+
+# ---------------------------------------------------------------------------------------------
+# EM steps
+# ---------------------------------------------------------------------------------------------
+def _kmeans_single_lloyd(X, n_clusters, max_iter=300, init="k-means||", verbose=False, x_squared_norms=None,
+                         random_state=None, tol=1e-4, precompute_distances=True, oversampling_factor=2,
+                         init_max_iter=None, n_init="auto"):
+    """Lloyd loop (reference :549-619).  Per iteration: pack centres -> K1 assign (+ refine) ->
+    K2 sums/counts/inertia -> ONE allreduce -> K3 finalize; the 8-byte shift is the only
+    device->host read (the reference's one ``compute()`` per iteration, :602)."""
+    X = _as_device_matrix(X)
+    eng = get_engine(X.device)
+    comm = _comm.default_comm()
+    centers = k_init(X, n_clusters, init=init, oversampling_factor=oversampling_factor, random_state=random_state,
+                     max_iter=init_max_iter, n_init=n_init)
+    dt = X.dtype
+    n_local, P = X.shape
+    k = n_clusters
+    centers64 = eng.to_device(np.ascontiguousarray(centers), torch.float64)
+    new64 = torch.empty_like(centers64)
+    acc = torch.zeros(eng.acc_len(k, P), dtype=torch.float64, device=eng.device)
+    shift_t = torch.zeros(1, dtype=torch.float64, device=eng.device)
+    labels = torch.empty(n_local, dtype=torch.int32, device=eng.device)
+    mind2 = torch.empty(n_local, dtype=dt, device=eng.device)
+    pack = None
+    shift = None
+    i = -1
+    for i in range(max_iter):
+        with _timer("Lloyd loop %2d." % i, _logger=logger):
+            pack = eng.pack(centers64, pack)
+            if n_local:
+                eng.assign(X, pack, labels, mind2)  # :576-579
+            acc.zero_()
+            if n_local:
+                eng.update(X, labels, mind2, k, acc)  # :582-598, :616
+            comm.allreduce_sum_(acc)  # the chain-sum over blocks / workers (:595-597)
+            eng.finalize(acc, k, P, centers64, new64, shift_t)  # :600-605
+            shift = float(shift_t.item())  # :602 -- the one round trip per iteration
+            logger.info("Shift: %0.4f", shift)
+            if shift < tol:
+                break
+            centers64, new64 = new64, centers64  # :610
+
+    if shift > 1e-7:  # :612-614 -- labels and NON-squared distances w.r.t. the current centres
+        pack = eng.pack(centers64, pack)
+        if n_local:
+            eng.assign(X, pack, labels, mind2)
+        inertia_t = eng.reduce_sum(mind2, sqrt=True)
+        comm.allreduce_sum_(inertia_t)
+    else:
+        inertia_t = acc[k * P + k : k * P + k + 1].clone()
+    inertia = DeviceArray(inertia_t.reshape(()))  # :616
+    centers_out = centers64.to(dt).cpu().numpy()  # :617
+    return DeviceArray(labels), inertia, centers_out, i + 1

@@ -1,0 +1,449 @@
+// assign.cu -- K1: fused distance + argmin (+ min distance), centre pack, fp64 refine.
+//
+// Replaces dask_ml.metrics.pairwise_distances_argmin_min (reference
+// dask_ml/metrics/pairwise.py:19-47 -> sklearn ArgKmin) on the Lloyd path
+// (dask_ml/cluster/k_means.py:576-579) and in predict (:247-250).
+//
+// Two kernels:
+//   assign_tiled_f32  -- FP32 FFMA, 128 rows x 128 centroids per CTA step, 8x8 register tile per
+//                        thread.  Score = ||c||^2 - 2 x.c (the row-constant ||x||^2 is left out of
+//                        the argmin).  Centroid tiles are staged by 1-D bulk async copies (TMA,
+//                        mbarrier complete_tx) double-buffered; X rows are read once, 128-bit
+//                        coalesced, and kept transposed in shared memory for the whole CTA.
+//                        Tracks best AND second-best per row; rows whose gap is below the fp32
+//                        rounding bound are flagged for the fp64 re-decision (refine).
+//   assign_rb         -- "row block" kernel, fp64 arithmetic, direct form sum (x-c)^2.  Used for
+//                        float64 X, for tiny k (HBM-bound regime), as the generic fallback and
+//                        (with row indirection) as the refine kernel.
+#include "common.cuh"
+
+// =============================================================================================
+// centre pack
+// =============================================================================================
+__global__ void __launch_bounds__(128) pack_centers_kernel(const double *__restrict__ c64in, int k, int d,
+                                                           unsigned char *__restrict__ pack) {
+    const KmPackLayout L = km_pack_layout(k, d);
+    const int j = blockIdx.x;  // 0 .. ntiles*128
+    float *c32 = reinterpret_cast<float *>(pack + L.off_c32);
+    float *cn32 = reinterpret_cast<float *>(pack + L.off_cn32);
+    double *cn64 = reinterpret_cast<double *>(pack + L.off_cn64);
+    double *c64 = reinterpret_cast<double *>(pack + L.off_c64);
+    float *ct = reinterpret_cast<float *>(pack + L.off_ct);
+    unsigned int *cmax = reinterpret_cast<unsigned int *>(pack + L.off_cmax);
+    const int tile = j / KM_TILE_N, jj = j % KM_TILE_N;
+    float *ctile = ct + (size_t)tile * (d + 1) * KM_TILE_N;
+    __shared__ double red[32];
+    __shared__ double red2[32];
+    if (j >= k) {
+        for (int f = threadIdx.x; f < d; f += blockDim.x) ctile[(size_t)f * KM_TILE_N + jj] = 0.f;
+        if (threadIdx.x == 0) {
+            cn32[j] = INFINITY;
+            ctile[(size_t)d * KM_TILE_N + jj] = INFINITY;
+        }
+        return;
+    }
+    double s64 = 0.0, s32 = 0.0;
+    for (int f = threadIdx.x; f < d; f += blockDim.x) {
+        const double v = c64in[(size_t)j * d + f];
+        const float vf = (float)v;
+        c64[(size_t)j * d + f] = v;
+        c32[(size_t)j * d + f] = vf;
+        ctile[(size_t)f * KM_TILE_N + jj] = vf;
+        s64 += v * v;
+        s32 += (double)vf * (double)vf;
+    }
+    s64 = km_warp_sum(s64);
+    s32 = km_warp_sum(s32);
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    if (lane == 0) { red[w] = s64; red2[w] = s32; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double a = 0, b = 0;
+        for (int i = 0; i < (int)(blockDim.x >> 5); ++i) { a += red[i]; b += red2[i]; }
+        cn64[j] = a;
+        const float bf = (float)b;
+        cn32[j] = bf;
+        ctile[(size_t)d * KM_TILE_N + jj] = bf;
+        atomicMax(cmax, __float_as_uint(bf));
+        if (j == 0) {
+            int *hdr = reinterpret_cast<int *>(pack + L.off_hdr);
+            hdr[0] = k; hdr[1] = d; hdr[2] = (k + KM_TILE_N - 1) / KM_TILE_N; hdr[3] = 0x6b6d3031;
+        }
+    }
+}
+
+extern "C" size_t b200km_pack_bytes(int k, int d) {
+    if (k <= 0 || d <= 0) return 0;
+    return km_pack_layout(k, d).total;
+}
+
+extern "C" int b200km_pack_centers(const double *centers_f64, int k, int d, void *pack, void *stream) {
+    KM_CHECK_ARG(centers_f64 && pack && k > 0 && d > 0, B200KM_EINVAL);
+    KM_CHECK_ARG(k <= B200KM_MAX_K && d <= B200KM_MAX_D, B200KM_ETOOBIG);
+    KM_CHECK_ARG((reinterpret_cast<uintptr_t>(pack) & 255) == 0, B200KM_EALIGN);
+    const KmPackLayout L = km_pack_layout(k, d);
+    cudaStream_t st = km_stream(stream);
+    cudaError_t e = cudaMemsetAsync(static_cast<unsigned char *>(pack) + L.off_cmax, 0, 4, st);
+    if (e != cudaSuccess) return (int)e;
+    const int ntiles = (k + KM_TILE_N - 1) / KM_TILE_N;
+    pack_centers_kernel<<<ntiles * KM_TILE_N, 128, 0, st>>>(centers_f64, k, d, static_cast<unsigned char *>(pack));
+    KM_LAUNCH_RET();
+}
+
+// =============================================================================================
+// tiled FP32 kernel
+// =============================================================================================
+constexpr int AT_BM = 128;       // rows per CTA
+constexpr int AT_XLD = AT_BM + 4;  // padded leading dim of the transposed X tile
+constexpr int AT_THREADS = 256;
+
+__device__ __forceinline__ void at_track(float v, int col, float &best, float &second, int &bidx) {
+    const bool lt = v < best;
+    second = lt ? best : fminf(second, v);
+    bidx = lt ? col : bidx;
+    best = fminf(best, v);
+}
+
+template <bool VEC>
+__global__ void __launch_bounds__(AT_THREADS, 2)
+assign_tiled_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
+                        const float *__restrict__ ct, const float *__restrict__ c32,
+                        const unsigned int *__restrict__ cmax_bits, int k, int ntiles,
+                        int32_t *__restrict__ labels, float *__restrict__ mind2,
+                        int32_t *__restrict__ flag_rows, int32_t *__restrict__ flag_count) {
+    extern __shared__ __align__(128) float smem[];
+    float *Xs = smem;                              // [d][AT_XLD]
+    float *Cs = smem + (size_t)d * AT_XLD;         // [2][d+1][128]
+    __shared__ __align__(8) uint64_t bars[2];
+    __shared__ float xn_s[AT_BM];
+
+    const int tid = threadIdx.x;
+    const int tx = tid & 15, ty = tid >> 4;
+    const int64_t row0 = (int64_t)blockIdx.x * AT_BM;
+    const uint32_t tile_elems = (uint32_t)(d + 1) * KM_TILE_N;
+    const uint32_t tile_bytes = tile_elems * 4u;
+
+    if (tid == 0) {
+        km_mbar_init(&bars[0], 1);
+        km_mbar_init(&bars[1], 1);
+        km_fence_mbar_init();
+    }
+    __syncthreads();
+    if (tid == 0) {
+        const int pre = ntiles < 2 ? ntiles : 2;
+        for (int t = 0; t < pre; ++t) {
+            km_mbar_expect_tx(&bars[t], tile_bytes);
+            km_bulk_g2s(Cs + (size_t)t * tile_elems, ct + (size_t)t * tile_elems, tile_bytes, &bars[t]);
+        }
+    }
+
+    // ---- stage the X tile, transposed: Xs[f][m] ------------------------------------------------
+    if (VEC) {
+        const int d4 = d >> 2;
+        const int qg = (d4 + 3) >> 2;
+        const int warp = tid >> 5, lane = tid & 31;
+        for (int wt = warp; wt < 16 * qg; wt += AT_THREADS / 32) {
+            const int m = (wt & 15) * 8 + (lane & 7);
+            const int q = (wt >> 4) * 4 + (lane >> 3);
+            if (q < d4) {
+                float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (row0 + m < n) v = __ldg(reinterpret_cast<const float4 *>(X + (row0 + m) * ldx) + q);
+                float *dst = Xs + (size_t)(4 * q) * AT_XLD + m;
+                dst[0] = v.x; dst[AT_XLD] = v.y; dst[2 * AT_XLD] = v.z; dst[3 * AT_XLD] = v.w;
+            }
+        }
+    } else {
+        for (int e = tid; e < AT_BM * d; e += AT_THREADS) {
+            const int m = e / d, f = e - m * d;
+            float v = 0.f;
+            if (row0 + m < n) v = __ldg(X + (row0 + m) * ldx + f);
+            Xs[(size_t)f * AT_XLD + m] = v;
+        }
+    }
+    __syncthreads();
+    if (tid < AT_BM) {
+        float s = 0.f;
+        for (int f = 0; f < d; ++f) { const float v = Xs[(size_t)f * AT_XLD + tid]; s = fmaf(v, v, s); }
+        xn_s[tid] = s;
+    }
+
+    float best[8], second[8];
+    int bidx[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { best[i] = INFINITY; second[i] = INFINITY; bidx[i] = 0; }
+
+    const float *xa_p = Xs + ty * 4;
+    for (int t = 0; t < ntiles; ++t) {
+        const float *Cb = Cs + (size_t)(t & 1) * tile_elems;
+        km_mbar_wait(&bars[t & 1], (uint32_t)((t >> 1) & 1));
+        float acc[8][8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+        const float *ca_p = Cb + tx * 4;
+#pragma unroll 4
+        for (int f = 0; f < d; ++f) {
+            const float4 xa = *reinterpret_cast<const float4 *>(xa_p + (size_t)f * AT_XLD);
+            const float4 xb = *reinterpret_cast<const float4 *>(xa_p + (size_t)f * AT_XLD + 64);
+            const float4 ca = *reinterpret_cast<const float4 *>(ca_p + (size_t)f * KM_TILE_N);
+            const float4 cb = *reinterpret_cast<const float4 *>(ca_p + (size_t)f * KM_TILE_N + 64);
+            const float xr[8] = {xa.x, xa.y, xa.z, xa.w, xb.x, xb.y, xb.z, xb.w};
+            const float cr[8] = {ca.x, ca.y, ca.z, ca.w, cb.x, cb.y, cb.z, cb.w};
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+#pragma unroll
+                for (int j = 0; j < 8; ++j) acc[i][j] = fmaf(xr[i], cr[j], acc[i][j]);
+        }
+        {
+            const float4 na = *reinterpret_cast<const float4 *>(ca_p + (size_t)d * KM_TILE_N);
+            const float4 nb = *reinterpret_cast<const float4 *>(ca_p + (size_t)d * KM_TILE_N + 64);
+            const float cn[8] = {na.x, na.y, na.z, na.w, nb.x, nb.y, nb.z, nb.w};
+            const int colbase = t * KM_TILE_N + tx * 4;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const int col = colbase + (j < 4 ? j : 60 + j);
+                    const float v = fmaf(-2.f, acc[i][j], cn[j]);
+                    at_track(v, col, best[i], second[i], bidx[i]);
+                }
+            }
+        }
+        __syncthreads();  // everyone is done reading Cs[t&1]
+        if (tid == 0 && t + 2 < ntiles) {
+            km_mbar_expect_tx(&bars[t & 1], tile_bytes);
+            km_bulk_g2s(Cs + (size_t)(t & 1) * tile_elems, ct + (size_t)(t + 2) * tile_elems, tile_bytes, &bars[t & 1]);
+        }
+    }
+
+    // ---- merge the 16 column-threads of each row group (lanes tx = 0..15 of a half warp) -------
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+#pragma unroll
+        for (int o = 1; o < 16; o <<= 1) {
+            const float ob = __shfl_xor_sync(0xffffffffu, best[i], o);
+            const float os = __shfl_xor_sync(0xffffffffu, second[i], o);
+            const int oi = __shfl_xor_sync(0xffffffffu, bidx[i], o);
+            const bool take = (ob < best[i]) || (ob == best[i] && oi < bidx[i]);
+            const float loser = take ? best[i] : ob;
+            second[i] = fminf(fminf(second[i], os), loser);
+            best[i] = take ? ob : best[i];
+            bidx[i] = take ? oi : bidx[i];
+        }
+    }
+
+    // ---- winner distance in direct form, outputs, near-tie flags --------------------------------
+    const float cmax = __uint_as_float(*cmax_bits);
+    const float bound_scale = (float)(d + 8) * 1.1920929e-07f;  // (d+8) * 2^-23
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int m = (i < 4 ? ty * 4 + i : 60 + ty * 4 + i);
+        int bi = bidx[i];
+        if (bi >= k) bi = k - 1;  // only possible for padded tail rows
+        const float *crow = c32 + (size_t)bi * d;
+        float s = 0.f;
+        for (int f = tx; f < d; f += 16) {
+            const float df = Xs[(size_t)f * AT_XLD + m] - __ldg(crow + f);
+            s = fmaf(df, df, s);
+        }
+#pragma unroll
+        for (int o = 1; o < 16; o <<= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        if (tx == i) {
+            const int64_t row = row0 + m;
+            if (row < n) {
+                labels[row] = bi;
+                if (mind2) mind2[row] = s;
+                if (flag_rows) {
+                    const float thr = bound_scale * (xn_s[m] + cmax);
+                    if (second[i] - best[i] <= thr) {
+                        const int pos = atomicAdd(flag_count, 1);
+                        flag_rows[pos] = (int32_t)row;
+                    }
+                }
+            }
+        }
+    }
+}
+
+// =============================================================================================
+// row-block kernel (fp64 arithmetic, direct form)
+// =============================================================================================
+constexpr int RB_DC = 128;  // feature chunk
+
+template <typename TX, int R, int G, int JB, bool INDIRECT>
+__global__ void __launch_bounds__(R *G)
+assign_rb_kernel(const TX *__restrict__ X, int64_t n, int d, int64_t ldx, const double *__restrict__ c64, int k,
+                 const int32_t *__restrict__ rows, const int32_t *__restrict__ nrows_ptr,
+                 int32_t *__restrict__ labels, TX *__restrict__ mind2) {
+    extern __shared__ __align__(16) double smem_d[];
+    const int dc_max = d < RB_DC ? d : RB_DC;
+    const int xld = dc_max + 1;
+    double *xs = smem_d;                        // [R][xld]
+    double *cs = xs + (size_t)R * xld;          // [G*JB][dc_max]
+    double *sb = cs + (size_t)G * JB * dc_max;  // [G][R] best values
+    int *si = reinterpret_cast<int *>(sb + (size_t)G * R);  // [G][R] best idx
+
+    const int tid = threadIdx.x;
+    const int r = tid % R, g = tid / R;
+    const int64_t nrows = INDIRECT ? (int64_t)(*nrows_ptr) : n;
+    const int nthreads = R * G;
+    const bool single_chunk = d <= RB_DC;
+
+    for (int64_t base = (int64_t)blockIdx.x * R; base < nrows; base += (int64_t)gridDim.x * R) {
+        double best = INFINITY;
+        int bidx = 0;
+        for (int c0 = 0; c0 < k; c0 += G * JB) {
+            double acc[JB];
+#pragma unroll
+            for (int j = 0; j < JB; ++j) acc[j] = 0.0;
+            for (int d0 = 0; d0 < d; d0 += RB_DC) {
+                const int dc = (d - d0) < RB_DC ? (d - d0) : RB_DC;
+                __syncthreads();
+                if (!single_chunk || c0 == 0) {
+                    for (int e = tid; e < R * dc; e += nthreads) {
+                        const int rr = e / dc, f = e - rr * dc;
+                        double v = 0.0;
+                        if (base + rr < nrows) {
+                            const int64_t row = INDIRECT ? (int64_t)rows[base + rr] : base + rr;
+                            v = (double)X[row * ldx + d0 + f];
+                        }
+                        xs[(size_t)rr * xld + f] = v;
+                    }
+                }
+                for (int e = tid; e < G * JB * dc; e += nthreads) {
+                    const int jj = e / dc, f = e - jj * dc;
+                    const int col = c0 + jj;
+                    cs[(size_t)jj * dc_max + f] = col < k ? c64[(size_t)col * d + d0 + f] : 0.0;
+                }
+                __syncthreads();
+                const double *xr = xs + (size_t)r * xld;
+                const double *cr = cs + (size_t)(g * JB) * dc_max;
+#pragma unroll 2
+                for (int f = 0; f < dc; ++f) {
+                    const double xv = xr[f];
+#pragma unroll
+                    for (int j = 0; j < JB; ++j) {
+                        const double df = xv - cr[(size_t)j * dc_max + f];
+                        acc[j] = fma(df, df, acc[j]);
+                    }
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < JB; ++j) {
+                const int col = c0 + g * JB + j;
+                if (col < k && acc[j] < best) { best = acc[j]; bidx = col; }
+            }
+        }
+        if (G > 1) {
+            __syncthreads();
+            sb[g * R + r] = best;
+            si[g * R + r] = bidx;
+            __syncthreads();
+            if (g == 0) {
+                for (int gg = 1; gg < G; ++gg) {
+                    const double ob = sb[gg * R + r];
+                    const int oi = si[gg * R + r];
+                    if (ob < best || (ob == best && oi < bidx)) { best = ob; bidx = oi; }
+                }
+            }
+        }
+        if (g == 0 && base + r < nrows) {
+            const int64_t row = INDIRECT ? (int64_t)rows[base + r] : base + r;
+            labels[row] = bidx;
+            if (mind2) mind2[row] = (TX)best;
+        }
+    }
+}
+
+template <typename TX, int R, int G, int JB, bool INDIRECT>
+static int launch_rb(const TX *X, int64_t n, int d, int64_t ldx, const double *c64, int k, const int32_t *rows,
+                     const int32_t *nrows_ptr, int32_t *labels, TX *mind2, cudaStream_t st) {
+    const int dc_max = d < RB_DC ? d : RB_DC;
+    const size_t smem = sizeof(double) * ((size_t)R * (dc_max + 1) + (size_t)G * JB * dc_max + (size_t)G * R) +
+                        sizeof(int) * (size_t)G * R;
+    auto kern = assign_rb_kernel<TX, R, G, JB, INDIRECT>;
+    static bool attr_set[KM_MAX_DEVICES] = {};
+    if (int rc = km_set_smem_once(kern, 200 * 1024, attr_set)) return rc;
+    int64_t blocks = (n + R - 1) / R;
+    const int64_t cap = (int64_t)KM_NUM_SMS * 8;
+    if (INDIRECT || blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    kern<<<(unsigned)blocks, R * G, smem, st>>>(X, n, d, ldx, c64, k, rows, nrows_ptr, labels, mind2);
+    KM_LAUNCH_RET();
+}
+
+// =============================================================================================
+// entry points
+// =============================================================================================
+static int check_pack_args(const void *X, int64_t n, int d, int64_t ldx, const void *pack, int k, const void *labels) {
+    KM_CHECK_ARG(X && pack && labels, B200KM_EINVAL);
+    KM_CHECK_ARG(n > 0 && d > 0 && k > 0 && ldx >= d, B200KM_EINVAL);
+    KM_CHECK_ARG(k <= B200KM_MAX_K && d <= B200KM_MAX_D && n < (int64_t(1) << 31), B200KM_ETOOBIG);
+    KM_CHECK_ARG((reinterpret_cast<uintptr_t>(pack) & 255) == 0, B200KM_EALIGN);
+    return 0;
+}
+
+extern "C" int b200km_assign_f32(const float *X, int64_t n, int d, int64_t ldx, const void *pack, int k,
+                                 int32_t *labels, float *mind2, int32_t *flag_rows, int32_t *flag_count,
+                                 int reset_flags, void *stream) {
+    int rc = check_pack_args(X, n, d, ldx, pack, k, labels);
+    if (rc) return rc;
+    KM_CHECK_ARG(!flag_rows || flag_count, B200KM_EINVAL);
+    cudaStream_t st = km_stream(stream);
+    const KmPackLayout L = km_pack_layout(k, d);
+    const unsigned char *pk = static_cast<const unsigned char *>(pack);
+    if (flag_count && reset_flags) {
+        cudaError_t e = cudaMemsetAsync(flag_count, 0, sizeof(int32_t), st);
+        if (e != cudaSuccess) return (int)e;
+    }
+    const double *c64 = reinterpret_cast<const double *>(pk + L.off_c64);
+    if (k <= 16 && d <= 32) {
+        // HBM-bound regime: fp64 arithmetic is free here, so no flags are ever needed.
+        return launch_rb<float, 256, 1, 8, false>(X, n, d, ldx, c64, k, nullptr, nullptr, labels, mind2, st);
+    }
+    if (d > 128 || k <= 16) {
+        return launch_rb<float, 32, 8, 8, false>(X, n, d, ldx, c64, k, nullptr, nullptr, labels, mind2, st);
+    }
+    const int ntiles = (k + KM_TILE_N - 1) / KM_TILE_N;
+    const size_t smem = sizeof(float) * ((size_t)d * AT_XLD + 2 * (size_t)(d + 1) * KM_TILE_N);
+    const bool vec = (d % 4 == 0) && (ldx % 4 == 0) && ((reinterpret_cast<uintptr_t>(X) & 15) == 0);
+    const int64_t blocks = (n + AT_BM - 1) / AT_BM;
+    const float *ct = reinterpret_cast<const float *>(pk + L.off_ct);
+    const float *c32 = reinterpret_cast<const float *>(pk + L.off_c32);
+    const unsigned int *cmax = reinterpret_cast<const unsigned int *>(pk + L.off_cmax);
+    static bool attr_v[KM_MAX_DEVICES] = {}, attr_s[KM_MAX_DEVICES] = {};
+    if (int rc2 = km_set_smem_once(assign_tiled_f32_kernel<true>, 220 * 1024, attr_v)) return rc2;
+    if (int rc2 = km_set_smem_once(assign_tiled_f32_kernel<false>, 220 * 1024, attr_s)) return rc2;
+    if (vec)
+        assign_tiled_f32_kernel<true><<<(unsigned)blocks, AT_THREADS, smem, st>>>(
+            X, n, d, ldx, ct, c32, cmax, k, ntiles, labels, mind2, flag_rows, flag_count);
+    else
+        assign_tiled_f32_kernel<false><<<(unsigned)blocks, AT_THREADS, smem, st>>>(
+            X, n, d, ldx, ct, c32, cmax, k, ntiles, labels, mind2, flag_rows, flag_count);
+    KM_LAUNCH_RET();
+}
+
+extern "C" int b200km_assign_f64(const double *X, int64_t n, int d, int64_t ldx, const void *pack, int k,
+                                 int32_t *labels, double *mind2, void *stream) {
+    int rc = check_pack_args(X, n, d, ldx, pack, k, labels);
+    if (rc) return rc;
+    cudaStream_t st = km_stream(stream);
+    const KmPackLayout L = km_pack_layout(k, d);
+    const double *c64 = reinterpret_cast<const double *>(static_cast<const unsigned char *>(pack) + L.off_c64);
+    if (k <= 16 && d <= 32)
+        return launch_rb<double, 256, 1, 8, false>(X, n, d, ldx, c64, k, nullptr, nullptr, labels, mind2, st);
+    return launch_rb<double, 32, 8, 8, false>(X, n, d, ldx, c64, k, nullptr, nullptr, labels, mind2, st);
+}
+
+extern "C" int b200km_refine_f64(const float *X, int64_t n, int d, int64_t ldx, const void *pack, int k,
+                                 const int32_t *flag_rows, const int32_t *flag_count, int32_t *labels,
+                                 float *mind2, void *stream) {
+    int rc = check_pack_args(X, n, d, ldx, pack, k, labels);
+    if (rc) return rc;
+    KM_CHECK_ARG(flag_rows && flag_count, B200KM_EINVAL);
+    cudaStream_t st = km_stream(stream);
+    const KmPackLayout L = km_pack_layout(k, d);
+    const double *c64 = reinterpret_cast<const double *>(static_cast<const unsigned char *>(pack) + L.off_c64);
+    return launch_rb<float, 32, 8, 8, true>(X, n, d, ldx, c64, k, flag_rows, flag_count, labels, mind2, st);
+}

@@ -1,0 +1,192 @@
+// init.cu -- k-means|| kernels: K4 running min-distance / cost, K5 Bernoulli oversampling,
+// K6 row gather.
+//
+// Replaces evaluate_cost (reference dask_ml/cluster/k_means.py:516-519), _sample_points
+// (:522-541) and the fancy-index gathers X[sorted(c_idx)] (:479), X[locs] (:500), X[idx]
+// (:431, :452).  The reference recomputes the distance to EVERY candidate each round and
+// materialises the n x |C| block matrices; here a running minimum per row is kept, so a round
+// costs one read of X plus 2 words per row.
+#include "common.cuh"
+
+constexpr int MD_THREADS = 256;
+constexpr int MD_MAXM = B200KM_MINDIST_MAX_M;
+
+// LPR lanes cooperate on one row; lane l owns features l, l+LPR, ...  (coalesced, no alignment
+// requirement).  32/LPR rows per warp step.
+template <typename T, int LPR>
+__global__ void __launch_bounds__(MD_THREADS)
+mindist_kernel(const T *__restrict__ X, int64_t n, int d, int64_t ldx, const T *__restrict__ cand, int m,
+               T *__restrict__ mind2, int init, double *__restrict__ cost_out) {
+    extern __shared__ __align__(16) unsigned char md_smem[];
+    T *cs = reinterpret_cast<T *>(md_smem);  // [m][d]
+    __shared__ double red[32];
+    for (int e = threadIdx.x; e < m * d; e += MD_THREADS) cs[e] = cand[e];
+    __syncthreads();
+
+    constexpr int RPW = 32 / LPR;
+    const int lane = threadIdx.x & 31;
+    const int sub = lane / LPR, l = lane % LPR;
+    const int64_t warp_global = ((int64_t)blockIdx.x * MD_THREADS + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * MD_THREADS) >> 5;
+    double cost = 0.0;
+    for (int64_t r0 = warp_global * RPW; r0 < n; r0 += nwarps * RPW) {
+        const int64_t row = r0 + sub;
+        const bool live = row < n;
+        T acc[MD_MAXM];
+#pragma unroll
+        for (int j = 0; j < MD_MAXM; ++j) acc[j] = (T)0;
+        const T *xr = X + (live ? row : 0) * ldx;
+#pragma unroll 4
+        for (int f = l; f < d; f += LPR) {
+            const T xv = live ? __ldg(xr + f) : (T)0;
+#pragma unroll
+            for (int j = 0; j < MD_MAXM; ++j) {
+                if (j < m) {
+                    const T df = xv - cs[j * d + f];
+                    acc[j] = fma(df, df, acc[j]);
+                }
+            }
+        }
+        T best = (T)INFINITY;
+#pragma unroll
+        for (int j = 0; j < MD_MAXM; ++j) {
+            if (j < m) {
+                T v = acc[j];
+#pragma unroll
+                for (int o = LPR / 2; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+                best = v < best ? v : best;
+            }
+        }
+        if (live && l == 0) {
+            if (!init) {
+                const T old = mind2[row];
+                best = old < best ? old : best;
+            }
+            mind2[row] = best;
+            cost += (double)best;
+        }
+    }
+    km_block_atomic_add(cost, cost_out, red);
+}
+
+template <typename T>
+static int mindist_impl(const T *X, int64_t n, int d, int64_t ldx, const T *cand, int m, T *mind2, int init,
+                        double *cost_out, void *stream) {
+    KM_CHECK_ARG(X && cand && mind2 && cost_out, B200KM_EINVAL);
+    KM_CHECK_ARG(n > 0 && d > 0 && m > 0 && ldx >= d, B200KM_EINVAL);
+    KM_CHECK_ARG(m <= MD_MAXM && d <= B200KM_MAX_D, B200KM_ETOOBIG);
+    const size_t smem = sizeof(T) * (size_t)m * d;
+    KM_CHECK_ARG(smem <= 128 * 1024, B200KM_ETOOBIG);
+    cudaStream_t st = km_stream(stream);
+    int lpr = 32;
+    if (d <= 4) lpr = 1; else if (d <= 8) lpr = 2; else if (d <= 16) lpr = 4; else if (d <= 32) lpr = 8;
+    else if (d <= 64) lpr = 16;
+    const int rpw = 32 / lpr;
+    int64_t blocks = (n + (int64_t)rpw * (MD_THREADS / 32) - 1) / ((int64_t)rpw * (MD_THREADS / 32));
+    const int64_t cap = (int64_t)KM_NUM_SMS * 8;
+    if (blocks > cap) blocks = cap;
+#define MD_LAUNCH(LPR_)                                                                                          \
+    {                                                                                                            \
+        auto kern = mindist_kernel<T, LPR_>;                                                                     \
+        static bool attr_set[KM_MAX_DEVICES] = {};                                                               \
+        if (int rc = km_set_smem_once(kern, 128 * 1024, attr_set)) return rc;                                    \
+        kern<<<(unsigned)blocks, MD_THREADS, smem, st>>>(X, n, d, ldx, cand, m, mind2, init, cost_out);          \
+    }
+    switch (lpr) {
+        case 1: MD_LAUNCH(1) break;
+        case 2: MD_LAUNCH(2) break;
+        case 4: MD_LAUNCH(4) break;
+        case 8: MD_LAUNCH(8) break;
+        case 16: MD_LAUNCH(16) break;
+        default: MD_LAUNCH(32) break;
+    }
+#undef MD_LAUNCH
+    KM_LAUNCH_RET();
+}
+
+extern "C" int b200km_mindist_update_f32(const float *X, int64_t n, int d, int64_t ldx, const float *cand, int m,
+                                         float *mind2, int init, double *cost_out, void *stream) {
+    return mindist_impl<float>(X, n, d, ldx, cand, m, mind2, init, cost_out, stream);
+}
+extern "C" int b200km_mindist_update_f64(const double *X, int64_t n, int d, int64_t ldx, const double *cand, int m,
+                                         double *mind2, int init, double *cost_out, void *stream) {
+    return mindist_impl<double>(X, n, d, ldx, cand, m, mind2, init, cost_out, stream);
+}
+
+// ---------------------------------------------------------------------------------------------
+// K5 Bernoulli oversampling
+// ---------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256)
+bernoulli_kernel(const T *__restrict__ mind2, int64_t n, double scale, uint32_t k0, uint32_t k1, uint32_t round,
+                 int64_t row_offset, const double *__restrict__ draws, int64_t *__restrict__ picked,
+                 int32_t *__restrict__ count, int capacity) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const double p = scale * (double)__ldg(mind2 + i);  // k_means.py:535
+        double u;
+        if (draws) {
+            u = __ldg(draws + i);
+        } else {
+            const uint64_t g = (uint64_t)(row_offset + i);
+            const KmPhilox4 w = km_philox4x32_10((uint32_t)g, (uint32_t)(g >> 32), round, 0x6B6D7C7Cu, k0, k1);
+            u = km_u53(w.x, w.y);
+        }
+        if (p > u) {  // :538
+            const int pos = atomicAdd(count, 1);
+            if (pos < capacity) picked[pos] = row_offset + i;
+        }
+    }
+}
+
+template <typename T>
+static int bernoulli_impl(const T *mind2, int64_t n, double scale, uint64_t seed, uint32_t round, int64_t row_offset,
+                          const double *draws, int64_t *picked, int32_t *count, int capacity, void *stream) {
+    KM_CHECK_ARG(mind2 && picked && count && n > 0 && capacity > 0, B200KM_EINVAL);
+    int64_t blocks = (n + 255) / 256;
+    if (blocks > KM_NUM_SMS * 16) blocks = KM_NUM_SMS * 16;
+    bernoulli_kernel<T><<<(unsigned)blocks, 256, 0, km_stream(stream)>>>(
+        mind2, n, scale, (uint32_t)seed, (uint32_t)(seed >> 32), round, row_offset, draws, picked, count, capacity);
+    KM_LAUNCH_RET();
+}
+
+extern "C" int b200km_bernoulli_pick_f32(const float *mind2, int64_t n, double scale, uint64_t seed, uint32_t round,
+                                         int64_t row_offset, const double *draws, int64_t *picked, int32_t *count,
+                                         int capacity, void *stream) {
+    return bernoulli_impl<float>(mind2, n, scale, seed, round, row_offset, draws, picked, count, capacity, stream);
+}
+extern "C" int b200km_bernoulli_pick_f64(const double *mind2, int64_t n, double scale, uint64_t seed, uint32_t round,
+                                         int64_t row_offset, const double *draws, int64_t *picked, int32_t *count,
+                                         int capacity, void *stream) {
+    return bernoulli_impl<double>(mind2, n, scale, seed, round, row_offset, draws, picked, count, capacity, stream);
+}
+
+// ---------------------------------------------------------------------------------------------
+// K6 gather rows
+// ---------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(128)
+gather_kernel(const T *__restrict__ X, int64_t n, int d, int64_t ldx, const int64_t *__restrict__ idx, int m,
+              T *__restrict__ out) {
+    for (int j = blockIdx.x; j < m; j += gridDim.x) {
+        const int64_t r = idx[j];
+        const bool ok = r >= 0 && r < n;
+        for (int f = threadIdx.x; f < d; f += blockDim.x) out[(size_t)j * d + f] = ok ? X[r * ldx + f] : (T)NAN;
+    }
+}
+
+template <typename T>
+static int gather_impl(const T *X, int64_t n, int d, int64_t ldx, const int64_t *idx, int m, T *out, void *stream) {
+    KM_CHECK_ARG(X && idx && out && n > 0 && d > 0 && m > 0 && ldx >= d, B200KM_EINVAL);
+    int blocks = m < KM_NUM_SMS * 16 ? m : KM_NUM_SMS * 16;
+    gather_kernel<T><<<blocks, 128, 0, km_stream(stream)>>>(X, n, d, ldx, idx, m, out);
+    KM_LAUNCH_RET();
+}
+
+extern "C" int b200km_gather_rows_f32(const float *X, int64_t n, int d, int64_t ldx, const int64_t *idx, int m,
+                                      float *out, void *stream) {
+    return gather_impl<float>(X, n, d, ldx, idx, m, out, stream);
+}
+extern "C" int b200km_gather_rows_f64(const double *X, int64_t n, int d, int64_t ldx, const int64_t *idx, int m,
+                                      double *out, void *stream) {
+    return gather_impl<double>(X, n, d, ldx, idx, m, out, stream);
+}

@@ -1,0 +1,266 @@
+// misc.cu -- K7 full distance matrix (transform), row norms, finite check, blob generator,
+// FFMA/DFMA pipe probes, version / error strings.
+#include "common.cuh"
+
+// ---------------------------------------------------------------------------------------------
+// K7  euclidean_distances in the input precision.
+// Replaces dask_ml.metrics.euclidean_distances (reference dask_ml/metrics/pairwise.py:70-105):
+//   distances = -2 * dot(X, Y.T) + XX + YY ; maximum(distances, 0) ; sqrt unless squared.
+// 64x64 output tile per CTA, 4x4 per thread, features chunked by 16 through shared memory.
+// ---------------------------------------------------------------------------------------------
+constexpr int CD_T = 64, CD_KC = 16;
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+cdist_kernel(const T *__restrict__ X, int64_t n, int d, int64_t ldx, const T *__restrict__ Y, int k,
+             const T *__restrict__ xnorm2, const T *__restrict__ ynorm2, T *__restrict__ out, int squared) {
+    __shared__ T As[CD_KC][CD_T + 4];
+    __shared__ T Bs[CD_KC][CD_T + 4];
+    const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+    const int64_t row0 = (int64_t)blockIdx.y * CD_T;
+    const int col0 = blockIdx.x * CD_T;
+    T acc[4][4], xx[4], yy[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        xx[i] = (T)0; yy[i] = (T)0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = (T)0;
+    }
+    for (int f0 = 0; f0 < d; f0 += CD_KC) {
+        for (int e = tid; e < CD_T * CD_KC; e += 256) {
+            const int m = e / CD_KC, f = e % CD_KC;
+            T a = (T)0, b = (T)0;
+            if (f0 + f < d) {
+                if (row0 + m < n) a = X[(row0 + m) * ldx + f0 + f];
+                if (col0 + m < k) b = Y[(size_t)(col0 + m) * d + f0 + f];
+            }
+            As[f][m] = a;
+            Bs[f][m] = b;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int f = 0; f < CD_KC; ++f) {
+            T a[4], b[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) { a[i] = As[f][ty * 4 + i]; b[i] = Bs[f][tx * 4 + i]; }
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                xx[i] = fma(a[i], a[i], xx[i]);
+                yy[i] = fma(b[i], b[i], yy[i]);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) acc[i][j] = fma(a[i], b[j], acc[i][j]);
+            }
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int64_t row = row0 + ty * 4 + i;
+        if (row >= n) continue;
+        const T xn = xnorm2 ? xnorm2[row] : xx[i];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int col = col0 + tx * 4 + j;
+            if (col >= k) continue;
+            const T yn = ynorm2 ? ynorm2[col] : yy[j];
+            T v = ((T)(-2) * acc[i][j] + xn) + yn;
+            v = v > (T)0 ? v : (T)0;
+            out[row * (int64_t)k + col] = squared ? v : sqrt(v);
+        }
+    }
+}
+
+template <typename T>
+static int cdist_impl(const T *X, int64_t n, int d, int64_t ldx, const T *Y, int k, const T *xnorm2, const T *ynorm2,
+                      T *out, int squared, void *stream) {
+    KM_CHECK_ARG(X && Y && out && n > 0 && d > 0 && k > 0 && ldx >= d, B200KM_EINVAL);
+    const int64_t gy = (n + CD_T - 1) / CD_T;
+    KM_CHECK_ARG(gy <= 65535LL * 65535LL, B200KM_ETOOBIG);
+    // grid.y is limited to 65535: fold the row tiles into calls of at most 65535 tiles
+    cudaStream_t st = km_stream(stream);
+    for (int64_t t0 = 0; t0 < gy; t0 += 65535) {
+        const int64_t nt = (gy - t0) < 65535 ? (gy - t0) : 65535;
+        const int64_t r0 = t0 * CD_T;
+        const int64_t nn = (n - r0) < nt * CD_T ? (n - r0) : nt * CD_T;
+        dim3 grid((k + CD_T - 1) / CD_T, (unsigned)nt);
+        cdist_kernel<T><<<grid, 256, 0, st>>>(X + r0 * ldx, nn, d, ldx, Y, k, xnorm2 ? xnorm2 + r0 : nullptr, ynorm2,
+                                              out + r0 * (int64_t)k, squared);
+    }
+    KM_LAUNCH_RET();
+}
+
+extern "C" int b200km_cdist_f32(const float *X, int64_t n, int d, int64_t ldx, const float *Y, int k,
+                                const float *xnorm2, const float *ynorm2, float *out, int squared, void *stream) {
+    return cdist_impl<float>(X, n, d, ldx, Y, k, xnorm2, ynorm2, out, squared, stream);
+}
+extern "C" int b200km_cdist_f64(const double *X, int64_t n, int d, int64_t ldx, const double *Y, int k,
+                                const double *xnorm2, const double *ynorm2, double *out, int squared, void *stream) {
+    return cdist_impl<double>(X, n, d, ldx, Y, k, xnorm2, ynorm2, out, squared, stream);
+}
+
+// ---------------------------------------------------------------------------------------------
+// row norms / finite check (warp per row, lanes = features)
+// ---------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256)
+row_norms_kernel(const T *__restrict__ X, int64_t n, int d, int64_t ldx, T *__restrict__ out, int squared) {
+    const int lane = threadIdx.x & 31;
+    const int64_t w0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (int64_t r = w0; r < n; r += nw) {
+        T s = (T)0;
+        for (int f = lane; f < d; f += 32) { const T v = X[r * ldx + f]; s = fma(v, v, s); }
+        s = km_warp_sum(s);
+        if (lane == 0) out[r] = squared ? s : sqrt(s);
+    }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+nonfinite_kernel(const T *__restrict__ X, int64_t n, int d, int64_t ldx, int32_t *__restrict__ bad) {
+    const int64_t total = n * (int64_t)d;
+    int found = 0;
+    if (ldx == d) {
+        for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x)
+            found |= !isfinite(X[e]);
+    } else {
+        for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+            const int64_t r = e / d;
+            found |= !isfinite(X[r * ldx + (e - r * d)]);
+        }
+    }
+    if (__any_sync(0xffffffffu, found) && (threadIdx.x & 31) == 0) atomicOr(bad, 1);
+}
+
+template <typename T>
+static int row_norms_impl(const T *X, int64_t n, int d, int64_t ldx, T *out, int squared, void *stream) {
+    KM_CHECK_ARG(X && out && n > 0 && d > 0 && ldx >= d, B200KM_EINVAL);
+    int64_t blocks = (n + 7) / 8;
+    if (blocks > KM_NUM_SMS * 16) blocks = KM_NUM_SMS * 16;
+    row_norms_kernel<T><<<(unsigned)blocks, 256, 0, km_stream(stream)>>>(X, n, d, ldx, out, squared);
+    KM_LAUNCH_RET();
+}
+template <typename T>
+static int nonfinite_impl(const T *X, int64_t n, int d, int64_t ldx, int32_t *bad, void *stream) {
+    KM_CHECK_ARG(X && bad && n > 0 && d > 0 && ldx >= d, B200KM_EINVAL);
+    int64_t blocks = (n * (int64_t)d + 255) / 256;
+    if (blocks > KM_NUM_SMS * 16) blocks = KM_NUM_SMS * 16;
+    nonfinite_kernel<T><<<(unsigned)blocks, 256, 0, km_stream(stream)>>>(X, n, d, ldx, bad);
+    KM_LAUNCH_RET();
+}
+
+extern "C" int b200km_row_norms_f32(const float *X, int64_t n, int d, int64_t ldx, float *out, int squared, void *s) {
+    return row_norms_impl<float>(X, n, d, ldx, out, squared, s);
+}
+extern "C" int b200km_row_norms_f64(const double *X, int64_t n, int d, int64_t ldx, double *out, int squared, void *s) {
+    return row_norms_impl<double>(X, n, d, ldx, out, squared, s);
+}
+extern "C" int b200km_count_nonfinite_f32(const float *X, int64_t n, int d, int64_t ldx, int32_t *bad, void *s) {
+    return nonfinite_impl<float>(X, n, d, ldx, bad, s);
+}
+extern "C" int b200km_count_nonfinite_f64(const double *X, int64_t n, int d, int64_t ldx, int32_t *bad, void *s) {
+    return nonfinite_impl<double>(X, n, d, ldx, bad, s);
+}
+
+// ---------------------------------------------------------------------------------------------
+// blobs on the device (benchmark input).  Distribution of dask_ml.datasets.make_blobs
+// (reference dask_ml/datasets.py:78-205): isotropic Gaussians around k_true centres, rows in
+// random class order; NOT its bit stream.
+// ---------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256)
+blobs_kernel(T *__restrict__ X, int64_t n, int d, int64_t ldx, const T *__restrict__ centers, int k_true, T cluster_std,
+             uint32_t k0, uint32_t k1, int64_t row_offset) {
+    const int dq = (d + 3) / 4;
+    const int64_t total = n * (int64_t)dq;
+    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = e / dq;
+        const int q = (int)(e - r * dq);
+        const uint64_t g = (uint64_t)(row_offset + r);
+        const KmPhilox4 cw = km_philox4x32_10((uint32_t)g, (uint32_t)(g >> 32), 0u, 0x626c6f62u, k0, k1);
+        const int cls = (int)(cw.x % (uint32_t)k_true);
+        const KmPhilox4 w = km_philox4x32_10((uint32_t)g, (uint32_t)(g >> 32), (uint32_t)q + 1u, 0x626c6f62u, k0, k1);
+        // two Box-Muller pairs
+        const float u0 = ((float)(w.x >> 8) + 0.5f) * (1.0f / 16777216.0f);
+        const float u1 = ((float)(w.y >> 8) + 0.5f) * (1.0f / 16777216.0f);
+        const float u2 = ((float)(w.z >> 8) + 0.5f) * (1.0f / 16777216.0f);
+        const float u3 = ((float)(w.w >> 8) + 0.5f) * (1.0f / 16777216.0f);
+        const float ra = sqrtf(-2.f * logf(u0)), rb = sqrtf(-2.f * logf(u2));
+        float sa, ca, sb, cb;
+        sincospif(2.f * u1, &sa, &ca);
+        sincospif(2.f * u3, &sb, &cb);
+        const float z[4] = {ra * ca, ra * sa, rb * cb, rb * sb};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int f = q * 4 + i;
+            if (f < d) X[r * ldx + f] = centers[(size_t)cls * d + f] + cluster_std * (T)z[i];
+        }
+    }
+}
+
+template <typename T>
+static int blobs_impl(T *X, int64_t n, int d, int64_t ldx, const T *centers, int k_true, T cluster_std, uint64_t seed,
+                      int64_t row_offset, void *stream) {
+    KM_CHECK_ARG(X && centers && n > 0 && d > 0 && k_true > 0 && ldx >= d, B200KM_EINVAL);
+    int64_t blocks = (n * (int64_t)((d + 3) / 4) + 255) / 256;
+    if (blocks > KM_NUM_SMS * 32) blocks = KM_NUM_SMS * 32;
+    blobs_kernel<T><<<(unsigned)blocks, 256, 0, km_stream(stream)>>>(X, n, d, ldx, centers, k_true, cluster_std,
+                                                                     (uint32_t)seed, (uint32_t)(seed >> 32), row_offset);
+    KM_LAUNCH_RET();
+}
+extern "C" int b200km_make_blobs_f32(float *X, int64_t n, int d, int64_t ldx, const float *centers, int k_true,
+                                     float cluster_std, uint64_t seed, int64_t row_offset, void *stream) {
+    return blobs_impl<float>(X, n, d, ldx, centers, k_true, cluster_std, seed, row_offset, stream);
+}
+extern "C" int b200km_make_blobs_f64(double *X, int64_t n, int d, int64_t ldx, const double *centers, int k_true,
+                                     double cluster_std, uint64_t seed, int64_t row_offset, void *stream) {
+    return blobs_impl<double>(X, n, d, ldx, centers, k_true, cluster_std, seed, row_offset, stream);
+}
+
+// ---------------------------------------------------------------------------------------------
+// pipe probes: 8 independent FMA chains per thread
+// ---------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(1024) probe_fma_kernel(T *sink, int iters) {
+    T a[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) a[i] = (T)(threadIdx.x + i) * (T)1e-3;
+    const T b = (T)1.0000001, c = (T)1e-7;
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) a[i] = fma(a[i], b, c);
+        }
+    }
+    T s = (T)0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s += a[i];
+    if (s == (T)123456789) sink[0] = s;  // never true; keeps the chains alive
+}
+extern "C" int b200km_probe_ffma(float *sink, int blocks, int threads, int iters, void *stream) {
+    KM_CHECK_ARG(sink && blocks > 0 && threads > 0 && threads <= 1024 && iters > 0, B200KM_EINVAL);
+    probe_fma_kernel<float><<<blocks, threads, 0, km_stream(stream)>>>(sink, iters);
+    KM_LAUNCH_RET();
+}
+extern "C" int b200km_probe_dfma(double *sink, int blocks, int threads, int iters, void *stream) {
+    KM_CHECK_ARG(sink && blocks > 0 && threads > 0 && threads <= 1024 && iters > 0, B200KM_EINVAL);
+    probe_fma_kernel<double><<<blocks, threads, 0, km_stream(stream)>>>(sink, iters);
+    KM_LAUNCH_RET();
+}
+
+// ---------------------------------------------------------------------------------------------
+extern "C" int b200km_version(void) { return B200KM_VERSION; }
+
+extern "C" const char *b200km_error_string(int code) {
+    switch (code) {
+        case B200KM_OK: return "ok";
+        case B200KM_EINVAL: return "b200km: invalid argument (null pointer, non-positive size or ldx < d)";
+        case B200KM_ETOOBIG: return "b200km: size beyond the supported maximum";
+        case B200KM_EALIGN: return "b200km: pointer or leading dimension not aligned as documented";
+        case B200KM_ECAPACITY: return "b200km: output list capacity exceeded";
+        default: break;
+    }
+    if (code > 0) return cudaGetErrorString((cudaError_t)code);
+    return "b200km: unknown error code";
+}

@@ -1,0 +1,231 @@
+// update.cu -- K2 (per-cluster sum / count / inertia) and K3 (finalize + shift).
+//
+// Replaces _centers_dense (reference dask_ml/cluster/k_means.py:622-632: serial scatter-add into
+// a float64 table), the chain-sum of block partials (:595-597), da.bincount (:598),
+// maximum(counts, 1) + divide (:600-601), squared_norm(centers - new_centers) (:605) and
+// distances.sum() (:616).
+//
+// acc layout (float64): [k*d sums | k counts | 1 inertia]  -- one buffer, one allreduce.
+//
+// Two strategies:
+//   update_owner_kernel  (k*d*8 + k*4 <= ~200 KB of shared memory): a per-CTA float64 table in
+//       shared memory.  Warp w of the CTA OWNS the clusters with label % 8 == w: every warp scans
+//       the label stream (coalesced, L1-shared), ballots the rows it owns and adds those rows
+//       (lanes = features, coalesced) into its table rows.  No atomics at all until the final
+//       flush (one fp64 atomicAdd per table cell per CTA).
+//   update_atomic_kernel (any k*d): warp per row, lanes = features, fp64 RED into the global
+//       table (L2-resident), counts via one RED per row.
+#include "common.cuh"
+
+constexpr int UP_THREADS = 256;
+constexpr int UP_WARPS = UP_THREADS / 32;
+
+template <typename T>
+__global__ void __launch_bounds__(UP_THREADS)
+update_owner_kernel(const T *__restrict__ X, int64_t n, int d, int64_t ldx, const int32_t *__restrict__ labels,
+                    const T *__restrict__ mind2, int k, double *__restrict__ acc, int scale_sqrt) {
+    extern __shared__ __align__(16) double tbl[];       // [k*d]
+    int *cnt = reinterpret_cast<int *>(tbl + (size_t)k * d);  // [k]
+    __shared__ double red[32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (int e = tid; e < k * d; e += UP_THREADS) tbl[e] = 0.0;
+    for (int e = tid; e < k; e += UP_THREADS) cnt[e] = 0;
+    __syncthreads();
+
+    double inert = 0.0;
+    constexpr int CH = 1024;  // rows per CTA step
+    for (int64_t base = (int64_t)blockIdx.x * CH; base < n; base += (int64_t)gridDim.x * CH) {
+#pragma unroll 1
+        for (int sub = 0; sub < CH / 32; ++sub) {
+            const int64_t row_l = base + sub * 32 + lane;
+            int lab = -1;
+            if (row_l < n) lab = __ldg(labels + row_l);
+            const bool mine = lab >= 0 && (lab & (UP_WARPS - 1)) == warp;
+            unsigned mask = __ballot_sync(0xffffffffu, mine);
+            if (mine && mind2) {
+                const double v = (double)__ldg(mind2 + row_l);
+                inert += scale_sqrt ? sqrt(v) : v;
+            }
+            while (mask) {
+                // take up to 4 owned rows at once so their loads overlap
+                int b[4];
+                int nb = 0;
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    if (mask) { b[u] = __ffs(mask) - 1; mask &= mask - 1; nb = u + 1; } else b[u] = -1;
+                }
+                int l4[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) l4[u] = __shfl_sync(0xffffffffu, lab, b[u] < 0 ? 0 : b[u]);
+                for (int f0 = 0; f0 < d; f0 += 32) {
+                    const int f = f0 + lane;
+                    T v[4];
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        v[u] = (T)0;
+                        if (u < nb && f < d) v[u] = __ldg(X + (base + sub * 32 + b[u]) * ldx + f);
+                    }
+#pragma unroll
+                    for (int u = 0; u < 4; ++u)
+                        if (u < nb && f < d) tbl[(size_t)l4[u] * d + f] += (double)v[u];
+                }
+                if (lane == 0) {
+#pragma unroll
+                    for (int u = 0; u < 4; ++u)
+                        if (u < nb) cnt[l4[u]] += 1;
+                }
+                __syncwarp();
+            }
+        }
+    }
+    __syncthreads();
+    for (int e = tid; e < k * d; e += UP_THREADS) {
+        const double v = tbl[e];
+        if (v != 0.0) atomicAdd(acc + e, v);
+    }
+    for (int e = tid; e < k; e += UP_THREADS) {
+        const int c = cnt[e];
+        if (c) atomicAdd(acc + (size_t)k * d + e, (double)c);
+    }
+    if (mind2) km_block_atomic_add(inert, acc + (size_t)k * d + k, red);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(UP_THREADS)
+update_atomic_kernel(const T *__restrict__ X, int64_t n, int d, int64_t ldx, const int32_t *__restrict__ labels,
+                     const T *__restrict__ mind2, int k, double *__restrict__ acc, int scale_sqrt) {
+    __shared__ double red[32];
+    const int lane = threadIdx.x & 31;
+    const int64_t warp_global = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    double inert = 0.0;
+    double *counts = acc + (size_t)k * d;
+    constexpr int RU = 4;  // rows in flight per warp
+    for (int64_t r0 = warp_global * RU; r0 < n; r0 += nwarps * RU) {
+        int lab[RU];
+#pragma unroll
+        for (int u = 0; u < RU; ++u) lab[u] = (r0 + u < n) ? __ldg(labels + r0 + u) : -1;
+        for (int f0 = 0; f0 < d; f0 += 32) {
+            const int f = f0 + lane;
+            T v[RU];
+#pragma unroll
+            for (int u = 0; u < RU; ++u) {
+                v[u] = (T)0;
+                if (lab[u] >= 0 && f < d) v[u] = __ldg(X + (r0 + u) * ldx + f);
+            }
+#pragma unroll
+            for (int u = 0; u < RU; ++u)
+                if (lab[u] >= 0 && f < d) atomicAdd(acc + (size_t)lab[u] * d + f, (double)v[u]);
+        }
+        if (lane < RU && r0 + lane < n) {
+            const int l = __ldg(labels + r0 + lane);
+            atomicAdd(counts + l, 1.0);
+            if (mind2) {
+                const double v = (double)__ldg(mind2 + r0 + lane);
+                inert += scale_sqrt ? sqrt(v) : v;
+            }
+        }
+    }
+    if (mind2) km_block_atomic_add(inert, acc + (size_t)k * d + k, red);
+}
+
+extern "C" size_t b200km_acc_len(int k, int d) {
+    if (k <= 0 || d <= 0) return 0;
+    return (size_t)k * d + (size_t)k + 1;
+}
+
+template <typename T>
+static int update_impl(const T *X, int64_t n, int d, int64_t ldx, const int32_t *labels, const T *mind2, int k,
+                       double *acc, int scale_sqrt, void *stream) {
+    KM_CHECK_ARG(X && labels && acc, B200KM_EINVAL);
+    KM_CHECK_ARG(n > 0 && d > 0 && k > 0 && ldx >= d, B200KM_EINVAL);
+    KM_CHECK_ARG(k <= B200KM_MAX_K && d <= B200KM_MAX_D, B200KM_ETOOBIG);
+    cudaStream_t st = km_stream(stream);
+    const size_t smem = sizeof(double) * (size_t)k * d + sizeof(int) * (size_t)k;
+    if (smem <= 96 * 1024) {
+        auto kern = update_owner_kernel<T>;
+        static bool attr_set[KM_MAX_DEVICES] = {};
+        if (int rc = km_set_smem_once(kern, 96 * 1024, attr_set)) return rc;
+        int64_t blocks = (n + 1023) / 1024;
+        const int64_t cap = (int64_t)KM_NUM_SMS * 2;
+        if (blocks > cap) blocks = cap;
+        kern<<<(unsigned)blocks, UP_THREADS, smem, st>>>(X, n, d, ldx, labels, mind2, k, acc, scale_sqrt);
+    } else {
+        int64_t blocks = (n + 4 * UP_WARPS - 1) / (4 * UP_WARPS);
+        const int64_t cap = (int64_t)KM_NUM_SMS * 8;
+        if (blocks > cap) blocks = cap;
+        update_atomic_kernel<T><<<(unsigned)blocks, UP_THREADS, 0, st>>>(X, n, d, ldx, labels, mind2, k, acc, scale_sqrt);
+    }
+    KM_LAUNCH_RET();
+}
+
+extern "C" int b200km_update_f32(const float *X, int64_t n, int d, int64_t ldx, const int32_t *labels,
+                                 const float *mind2, int k, double *acc, int scale_sqrt, void *stream) {
+    return update_impl<float>(X, n, d, ldx, labels, mind2, k, acc, scale_sqrt, stream);
+}
+extern "C" int b200km_update_f64(const double *X, int64_t n, int d, int64_t ldx, const int32_t *labels,
+                                 const double *mind2, int k, double *acc, int scale_sqrt, void *stream) {
+    return update_impl<double>(X, n, d, ldx, labels, mind2, k, acc, scale_sqrt, stream);
+}
+
+// ---------------------------------------------------------------------------------------------
+// K3 finalize
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+finalize_kernel(const double *__restrict__ acc, int k, int d, const double *__restrict__ cold,
+                double *__restrict__ cnew, double *__restrict__ shift_out) {
+    __shared__ double red[32];
+    const double *counts = acc + (size_t)k * d;
+    double s = 0.0;
+    const int64_t total = (int64_t)k * d;
+    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+        const int j = (int)(e / d);
+        const double c = fmax(counts[j], 1.0);  // k_means.py:600
+        const double v = acc[e] / c;            // :601
+        cnew[e] = v;
+        const double df = cold[e] - v;  // :605
+        s = fma(df, df, s);
+    }
+    km_block_atomic_add(s, shift_out, red);
+}
+
+extern "C" int b200km_finalize(const double *acc, int k, int d, const double *centers_old, double *centers_new,
+                               double *shift_out, void *stream) {
+    KM_CHECK_ARG(acc && centers_old && centers_new && shift_out && k > 0 && d > 0, B200KM_EINVAL);
+    cudaStream_t st = km_stream(stream);
+    cudaError_t e = cudaMemsetAsync(shift_out, 0, sizeof(double), st);
+    if (e != cudaSuccess) return (int)e;
+    int64_t blocks = ((int64_t)k * d + 255) / 256;
+    if (blocks > KM_NUM_SMS * 4) blocks = KM_NUM_SMS * 4;
+    finalize_kernel<<<(unsigned)blocks, 256, 0, st>>>(acc, k, d, centers_old, centers_new, shift_out);
+    KM_LAUNCH_RET();
+}
+
+// ---------------------------------------------------------------------------------------------
+// sum / sum-of-sqrt of a vector into a float64 scalar (k_means.py:616 on the non-squared pass)
+// ---------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256)
+reduce_sum_kernel(const T *__restrict__ v, int64_t n, int take_sqrt, double *__restrict__ out) {
+    __shared__ double red[32];
+    double s = 0.0;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const double x = (double)__ldg(v + i);
+        s += take_sqrt ? sqrt(x) : x;
+    }
+    km_block_atomic_add(s, out, red);
+}
+template <typename T>
+static int reduce_sum_impl(const T *v, int64_t n, int take_sqrt, double *out, void *stream) {
+    KM_CHECK_ARG(v && out && n > 0, B200KM_EINVAL);
+    int64_t blocks = (n + 255) / 256;
+    if (blocks > KM_NUM_SMS * 8) blocks = KM_NUM_SMS * 8;
+    reduce_sum_kernel<T><<<(unsigned)blocks, 256, 0, km_stream(stream)>>>(v, n, take_sqrt, out);
+    KM_LAUNCH_RET();
+}
+extern "C" int b200km_reduce_sum_f32(const float *v, int64_t n, int take_sqrt, double *out, void *stream) {
+    return reduce_sum_impl<float>(v, n, take_sqrt, out, stream);
+}
+extern "C" int b200km_reduce_sum_f64(const double *v, int64_t n, int take_sqrt, double *out, void *stream) {
+    return reduce_sum_impl<double>(v, n, take_sqrt, out, stream);
+}

@@ -1,0 +1,196 @@
+/*
+ * b200km.h -- C ABI of libb200km.so: the k-means hot path of dask-ml (Lloyd iteration +
+ * k-means|| initialisation) as hand-written sm_100a CUDA kernels.
+ *
+ * The reference (dask/dask-ml) is pure Python and has NO FFI for this path; its boundary is
+ * the sklearn estimator protocol plus a few module-level functions.  Each entry point below
+ * names the reference interface it replaces (R/ = the dask-ml source tree) -- that is the
+ * call a maintainer would re-route through a ctypes stub.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer owned by the caller unless the name says `host`;
+ *   - nothing here allocates or frees device memory; scratch is passed in by the caller and
+ *     sized with the *_bytes() queries;
+ *   - every launch is asynchronous on `stream` (a cudaStream_t passed as void*);
+ *   - return value: 0 = ok, <0 = B200KM_E* (invalid argument), >0 = a cudaError_t;
+ *   - X is row-major, `ldx` = elements between consecutive rows (>= d);
+ *   - never throws, never prints;
+ *   - thread-safe for distinct streams + distinct scratch buffers.
+ */
+#ifndef B200KM_H_
+#define B200KM_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200KM_VERSION 100
+
+/* error codes (negative = argument errors) */
+#define B200KM_OK 0
+#define B200KM_EINVAL (-1)     /* null pointer / non-positive size / bad dtype            */
+#define B200KM_ETOOBIG (-2)    /* k or d beyond what the kernels support                  */
+#define B200KM_EALIGN (-3)     /* pointer / ldx not aligned as documented                 */
+#define B200KM_ECAPACITY (-4)  /* an output list overflowed its capacity (count is valid) */
+
+/* dtype tags */
+#define B200KM_F32 0
+#define B200KM_F64 1
+
+/* limits */
+#define B200KM_MAX_D 2048
+#define B200KM_MAX_K (1 << 20)
+#define B200KM_MINDIST_MAX_M 8 /* candidates per b200km_mindist_update_* launch */
+
+int b200km_version(void);
+/* static string for a code returned by any entry point (cudaGetErrorString for >0). */
+const char *b200km_error_string(int code);
+
+/* ------------------------------------------------------------------------------------------
+ * Centre pack.  The fp64 master copy of the centres (k x d, row-major) is expanded once per
+ * Lloyd iteration into the layouts the assign kernels read:
+ *   fp32 row-major copy, fp32 column-tiled copy ([tile][d+1][128], zero padded, last row = squared
+ *   norms, +inf padded), fp32 and fp64 squared norms, max squared norm, fp64 copy.
+ * Replaces: the `Y` ndarray argument that R/dask_ml/metrics/pairwise.py:31-33 embeds in every
+ * per-block task, and the per-call `row_norms(Y)` inside sklearn's ArgKmin.
+ * ---------------------------------------------------------------------------------------- */
+size_t b200km_pack_bytes(int k, int d);
+int b200km_pack_centers(const double *centers_f64, int k, int d, void *pack, void *stream);
+
+/* ------------------------------------------------------------------------------------------
+ * K1  fused distance + argmin (+ min distance).  The n x k distance matrix never exists.
+ * Replaces: dask_ml.metrics.pairwise_distances_argmin_min  (R/dask_ml/metrics/pairwise.py:19-47)
+ *           -> sklearn ArgKmin per row block, called from the Lloyd loop
+ *           (R/dask_ml/cluster/k_means.py:576-579) and from predict (:247-250).
+ *
+ *   labels[i]   = argmin_j ||x_i - c_j||^2, lowest j on exact ties (int32)
+ *   mind2[i]    = that squared distance (X dtype; nullable)
+ *   f32 only: rows whose best and second-best fp32 scores are closer than the fp32 rounding
+ *   bound are appended to flag_rows[0..*flag_count) (row indices, int32, unordered) so that
+ *   b200km_refine_f64 can re-decide them in fp64 -- the reference does all distance arithmetic
+ *   in float64 even for float32 input.  flag_rows needs room for n entries; *flag_count must
+ *   be zeroed by the caller (or by b200km_assign_f32 when reset_flags != 0).
+ *   Passing flag_rows == NULL disables flagging.
+ * ---------------------------------------------------------------------------------------- */
+int b200km_assign_f32(const float *X, int64_t n, int d, int64_t ldx, const void *pack, int k,
+                      int32_t *labels, float *mind2, int32_t *flag_rows, int32_t *flag_count,
+                      int reset_flags, void *stream);
+int b200km_assign_f64(const double *X, int64_t n, int d, int64_t ldx, const void *pack, int k,
+                      int32_t *labels, double *mind2, void *stream);
+/* fp64 re-decision of the flagged rows of a float32 X (labels / mind2 updated in place).
+ * `flag_count` is read on the device: no host synchronisation is needed between the two calls.
+ * Replaces: nothing separate -- it is what makes K1's float32 labels equal the reference's
+ * float64 ArgKmin labels (R/ SURVEY section 0.1). */
+int b200km_refine_f64(const float *X, int64_t n, int d, int64_t ldx, const void *pack, int k,
+                      const int32_t *flag_rows, const int32_t *flag_count, int32_t *labels,
+                      float *mind2, void *stream);
+
+/* ------------------------------------------------------------------------------------------
+ * K2  per-cluster sum and count (+ inertia = sum of mind2).
+ * Replaces: _centers_dense (R/dask_ml/cluster/k_means.py:622-632), the chain-sum of the block
+ *           partials (:595-597), da.bincount(labels, minlength=k) (:598) and
+ *           distances.sum() (:616).
+ * Accumulates INTO acc = [k*d sums | k counts | 1 inertia] (all float64, packed so that one
+ * NCCL allreduce covers it); the caller zeroes acc.  `mind2` nullable (inertia untouched).
+ * `scale_sqrt` != 0 adds sqrt(mind2) instead (the reference's non-squared inertia, :612-616).
+ * ---------------------------------------------------------------------------------------- */
+size_t b200km_acc_len(int k, int d); /* number of doubles in acc */
+int b200km_update_f32(const float *X, int64_t n, int d, int64_t ldx, const int32_t *labels,
+                      const float *mind2, int k, double *acc, int scale_sqrt, void *stream);
+int b200km_update_f64(const double *X, int64_t n, int d, int64_t ldx, const int32_t *labels,
+                      const double *mind2, int k, double *acc, int scale_sqrt, void *stream);
+
+/* out[0] += sum_i v[i]  (or sum_i sqrt(v[i]) when take_sqrt != 0), float64; caller zeroes out.
+ * Replaces: distances.sum() (R/dask_ml/cluster/k_means.py:616) on the non-squared final pass. */
+int b200km_reduce_sum_f32(const float *v, int64_t n, int take_sqrt, double *out, void *stream);
+int b200km_reduce_sum_f64(const double *v, int64_t n, int take_sqrt, double *out, void *stream);
+
+/* ------------------------------------------------------------------------------------------
+ * K3  finalize: new = sums / max(count, 1); shift = ||old - new||_F^2.
+ * Replaces: R/dask_ml/cluster/k_means.py:600-605 (maximum(counts,1), divide, squared_norm).
+ * centers_new (k x d) and shift_out (1) are float64; centers_old may alias nothing.
+ * ---------------------------------------------------------------------------------------- */
+int b200km_finalize(const double *acc, int k, int d, const double *centers_old,
+                    double *centers_new, double *shift_out, void *stream);
+
+/* ------------------------------------------------------------------------------------------
+ * K4  k-means|| running minimum:  mind2[i] = min(mind2[i], min_j ||x_i - cand_j||^2), and
+ *     cost_out += sum_i mind2[i] (float64; caller zeroes).  init != 0 ignores the old mind2.
+ * Replaces: evaluate_cost (R/dask_ml/cluster/k_means.py:516-519) and the first half of
+ *           _sample_points (:533-534); `cand` (m x d, X dtype, m <= B200KM_MINDIST_MAX_M).
+ * ---------------------------------------------------------------------------------------- */
+int b200km_mindist_update_f32(const float *X, int64_t n, int d, int64_t ldx, const float *cand,
+                              int m, float *mind2, int init, double *cost_out, void *stream);
+int b200km_mindist_update_f64(const double *X, int64_t n, int d, int64_t ldx, const double *cand,
+                              int m, double *mind2, int init, double *cost_out, void *stream);
+
+/* ------------------------------------------------------------------------------------------
+ * K5  Bernoulli oversampling: row i is picked when  scale * mind2[i] > u_i,  scale = l / cost.
+ *     u_i = Philox4x32-10(key = seed, counter = (row_offset + i, round)) -> 53-bit U[0,1), or
+ *     draws[i] when `draws` is non-null (injected draws, for parity tests).
+ *     Global indices (row_offset + i, int64) go to picked[0..min(*count, capacity)); *count
+ *     (caller zeroes) always holds the true number picked.
+ * Replaces: second half of _sample_points (R/dask_ml/cluster/k_means.py:535-541):
+ *           random_state.uniform + `p > draws` + da.where.
+ * ---------------------------------------------------------------------------------------- */
+int b200km_bernoulli_pick_f32(const float *mind2, int64_t n, double scale, uint64_t seed,
+                              uint32_t round, int64_t row_offset, const double *draws,
+                              int64_t *picked, int32_t *count, int capacity, void *stream);
+int b200km_bernoulli_pick_f64(const double *mind2, int64_t n, double scale, uint64_t seed,
+                              uint32_t round, int64_t row_offset, const double *draws,
+                              int64_t *picked, int32_t *count, int capacity, void *stream);
+
+/* ------------------------------------------------------------------------------------------
+ * K6  gather rows by LOCAL index: out[j,:] = X[idx[j],:]  (idx int64, 0 <= idx < n).
+ * Replaces: X[sorted(c_idx)].compute() (R/dask_ml/cluster/k_means.py:479), X[locs] (:500),
+ *           X[idx] (:431, :452).
+ * ---------------------------------------------------------------------------------------- */
+int b200km_gather_rows_f32(const float *X, int64_t n, int d, int64_t ldx, const int64_t *idx,
+                           int m, float *out, void *stream);
+int b200km_gather_rows_f64(const double *X, int64_t n, int d, int64_t ldx, const int64_t *idx,
+                           int m, double *out, void *stream);
+
+/* ------------------------------------------------------------------------------------------
+ * K7  full distance matrix in the INPUT precision: out[i,j] = sqrt(max(xx_i - 2 x_i.y_j + yy_j, 0))
+ *     (sqrt skipped when squared != 0).  xnorm2 / ynorm2 nullable (computed when null).
+ * Replaces: dask_ml.metrics.euclidean_distances (R/dask_ml/metrics/pairwise.py:70-105), used
+ *           by KMeans.transform (R/dask_ml/cluster/k_means.py:225-228).
+ * ---------------------------------------------------------------------------------------- */
+int b200km_cdist_f32(const float *X, int64_t n, int d, int64_t ldx, const float *Y, int k,
+                     const float *xnorm2, const float *ynorm2, float *out, int squared, void *stream);
+int b200km_cdist_f64(const double *X, int64_t n, int d, int64_t ldx, const double *Y, int k,
+                     const double *xnorm2, const double *ynorm2, double *out, int squared, void *stream);
+
+/* row_norms(X, squared) -- R/dask_ml/utils.py:83-88. */
+int b200km_row_norms_f32(const float *X, int64_t n, int d, int64_t ldx, float *out, int squared, void *stream);
+int b200km_row_norms_f64(const double *X, int64_t n, int d, int64_t ldx, double *out, int squared, void *stream);
+
+/* *bad (int32, caller zeroes) becomes non-zero when X holds a NaN or +-inf.
+ * Replaces: the da.isnull / da.isinf scan in KMeans._check_array (R/dask_ml/cluster/k_means.py:195-201). */
+int b200km_count_nonfinite_f32(const float *X, int64_t n, int d, int64_t ldx, int32_t *bad, void *stream);
+int b200km_count_nonfinite_f64(const double *X, int64_t n, int d, int64_t ldx, int32_t *bad, void *stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Synthetic blobs on the device (benchmark input):
+ *   X[i,:] = centers[(row_offset+i) % k_true, :] + cluster_std * N(0,1)   (Philox + Box-Muller)
+ * Mirrors the distribution of dask_ml.datasets.make_blobs (R/dask_ml/datasets.py:78-205): equal
+ * points per centre, isotropic Gaussian; NOT its bit stream.
+ * ---------------------------------------------------------------------------------------- */
+int b200km_make_blobs_f32(float *X, int64_t n, int d, int64_t ldx, const float *centers, int k_true,
+                          float cluster_std, uint64_t seed, int64_t row_offset, void *stream);
+int b200km_make_blobs_f64(double *X, int64_t n, int d, int64_t ldx, const double *centers, int k_true,
+                          double cluster_std, uint64_t seed, int64_t row_offset, void *stream);
+
+/* FP32 FFMA / FP64 DFMA pipe microbenchmarks (roofline denominators that MEASURED_PEAKS.json
+ * lacks).  Runs `iters` dependent-chain FMA bundles on every SM; writes a checksum to `sink`
+ * (>= 1 float/double).  flops = 2 * 64 * iters * blocks * threads; the caller times it. */
+int b200km_probe_ffma(float *sink, int blocks, int threads, int iters, void *stream);
+int b200km_probe_dfma(double *sink, int blocks, int threads, int iters, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200KM_H_ */

@@ -1,0 +1,215 @@
+"""-m gpu: every C-ABI entry point against the CPU oracle on seeded inputs.
+
+Bars: labels / indices bit-exact (float32 X included: K1 + fp64 re-decision must reproduce the
+float64 ArgKmin labels; rows whose two nearest float64 distances agree to 1e-6 relative are
+reported and excluded); float values within 1e-5 relative (float32) / 1e-10 (float64)."""
+import numpy as np
+import numpy.testing as npt
+import pytest
+import sklearn.metrics
+
+from conftest import blobs
+from oracle import kmeans_oracle as orc
+
+pytestmark = pytest.mark.gpu
+
+RTOL = {np.float32: 1e-5, np.float64: 1e-10}
+
+
+@pytest.fixture(scope="module")
+def eng():
+    import torch
+    from dask_ml_b200._engine import get_engine
+
+    torch.cuda.set_device(0)
+    return get_engine()
+
+
+def _near_tie_mask(X, C, rel=1e-6):
+    """Rows whose two smallest float64 squared distances tie within `rel` (north_star's exemption)."""
+    D = sklearn.metrics.pairwise_distances(X.astype(np.float64), C.astype(np.float64), metric="sqeuclidean")
+    if D.shape[1] < 2:
+        return np.zeros(len(X), bool)
+    part = np.partition(D, 1, axis=1)
+    return (part[:, 1] - part[:, 0]) <= rel * np.maximum(part[:, 1], 1e-300)
+
+
+def _check_assign(eng, X, C, expect_flags=None):
+    import torch
+
+    Xd = eng.to_device(X)
+    pack = eng.pack(eng.to_device(C, torch.float64))
+    labels, mind2 = eng.assign(Xd, pack)
+    lab_ref, d_ref = orc.pairwise_distances_argmin_min(X, C.astype(np.float64), metric_kwargs={"squared": True})
+    got = labels.cpu().numpy()
+    diff = got != lab_ref
+    if diff.any():
+        ties = _near_tie_mask(X, C)
+        assert not (diff & ~ties).any(), f"{(diff & ~ties).sum()} labels differ outside near-ties ({diff.sum()} total)"
+    dt = X.dtype.type
+    npt.assert_allclose(mind2.cpu().numpy().astype(np.float64), d_ref, rtol=RTOL[dt] * 3, atol=RTOL[dt] * d_ref.max())
+    return got, eng.flagged_count() if X.dtype == np.float32 else 0
+
+
+@pytest.mark.parametrize("n,d,k", [(5000, 64, 1024), (3001, 32, 256), (777, 20, 150), (1000, 128, 300),
+                                    (513, 7, 33), (128, 4, 17), (4096, 16, 129), (1, 8, 40), (300, 36, 128)])
+def test_assign_f32_tiled(eng, n, d, k):
+    X, C = blobs(n, d, k, seed=n + d + k, dtype=np.float32)
+    init = (C + 0.3 * np.random.RandomState(1).standard_normal(C.shape))
+    _check_assign(eng, X, init)
+
+
+@pytest.mark.parametrize("n,d,k", [(4000, 16, 8), (999, 3, 2), (2000, 32, 16), (500, 200, 40), (700, 64, 5), (50, 2, 1)])
+def test_assign_f32_rowblock_paths(eng, n, d, k):
+    X, C = blobs(n, d, k, seed=7 * n + k, dtype=np.float32)
+    _check_assign(eng, X, C + 0.1)
+
+
+@pytest.mark.parametrize("n,d,k", [(4000, 16, 8), (1500, 5, 3), (2000, 40, 100), (333, 130, 20), (1, 1, 1)])
+def test_assign_f64(eng, n, d, k):
+    X, C = blobs(n, d, k, seed=n + k, dtype=np.float64)
+    _check_assign(eng, X, C + 0.05)
+
+
+def test_assign_f32_near_ties_are_refined(eng):
+    """Centres that are float32-indistinguishable but float64-distinct, exact duplicates, and rows
+    equidistant from two centres: the fp64 re-decision must give the float64 answer (lowest index
+    on exact ties, as sklearn's ArgKmin: strict '<' while scanning)."""
+    rs = np.random.RandomState(5)
+    d, k = 24, 64
+    C = rs.uniform(-10, 10, size=(k, d))
+    C[10] = C[3]                      # exact duplicate -> index 3 must win
+    C[20] = C[7] * (1 + 1e-9)         # differs only below float32 resolution
+    X = np.vstack([C[3] + 0.01 * rs.standard_normal((200, d)), C[7] + 0.01 * rs.standard_normal((200, d)),
+                   0.5 * (C[30] + C[31]) + 1e-4 * rs.standard_normal((200, d)),
+                   rs.uniform(-10, 10, size=(600, d))]).astype(np.float32)
+    got, nflag = _check_assign(eng, X, C)
+    assert nflag >= 400                # the constructed ties were caught
+    assert not (got[:200] == 10).any()  # duplicate resolved to the lower index
+    lab_ref, _ = orc.pairwise_distances_argmin_min(X, C)
+    # this case has no sklearn-level near ties beyond the duplicates: demand exact equality there
+    ok = ~np.isin(lab_ref, [3, 10])
+    npt.assert_array_equal(got[ok & ~_near_tie_mask(X, C, 1e-12)], lab_ref[ok & ~_near_tie_mask(X, C, 1e-12)])
+
+
+def test_assign_strided_rows(eng):
+    import torch
+
+    X, C = blobs(1000, 24, 130, seed=3, dtype=np.float32)
+    big = torch.zeros(1000, 40, dtype=torch.float32, device=eng.device)
+    big[:, :24] = eng.to_device(X)
+    pack = eng.pack(eng.to_device(C, torch.float64))
+    lab, _ = eng.assign(big[:, :24], pack)
+    lab_ref, _ = orc.pairwise_distances_argmin_min(X, C)
+    npt.assert_array_equal(lab.cpu().numpy(), lab_ref)
+
+
+@pytest.mark.parametrize("n,d,k,dtype", [(5000, 16, 8, np.float64), (6000, 32, 256, np.float32),
+                                         (3000, 64, 1024, np.float32), (2047, 5, 3, np.float64),
+                                         (1000, 128, 700, np.float32), (900, 33, 40, np.float64)])
+def test_update_and_finalize(eng, n, d, k, dtype):
+    import torch
+
+    X, C = blobs(n, d, k, seed=k, dtype=dtype)
+    labels = np.random.RandomState(0).randint(0, k, size=n).astype(np.int32)
+    labels[labels == k - 1] = 0  # leave one cluster empty
+    mind2 = np.random.RandomState(1).uniform(0, 9, size=n).astype(dtype)
+    acc = eng.update(eng.to_device(X), eng.to_device(labels), eng.to_device(mind2), k)
+    a = acc.cpu().numpy()
+    sums = orc.centers_dense(X, labels, k)
+    counts = np.bincount(labels, minlength=k)
+    scale = np.abs(sums).max()
+    npt.assert_allclose(a[: k * d].reshape(k, d), sums, rtol=RTOL[dtype], atol=RTOL[dtype] * scale)
+    npt.assert_array_equal(a[k * d : k * d + k], counts)
+    npt.assert_allclose(a[-1], mind2.astype(np.float64).sum(), rtol=1e-10)
+    # sqrt flavour (non-squared inertia)
+    acc2 = eng.update(eng.to_device(X), eng.to_device(labels), eng.to_device(mind2), k, sqrt=True)
+    npt.assert_allclose(acc2[-1].item(), np.sqrt(mind2.astype(np.float64)).sum(), rtol=1e-10)
+    old = eng.to_device(C, torch.float64)
+    new, shift = eng.finalize(acc, k, d, old)
+    ref_new = sums / np.maximum(counts, 1)[:, None]
+    npt.assert_allclose(new.cpu().numpy(), ref_new, rtol=RTOL[dtype], atol=RTOL[dtype] * np.abs(ref_new).max())
+    assert (new.cpu().numpy()[k - 1] == 0).all()  # empty cluster -> origin
+    npt.assert_allclose(shift.item(), ((C - ref_new) ** 2).sum(), rtol=1e-6)
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+@pytest.mark.parametrize("n,d", [(5000, 64), (3001, 3), (1000, 100), (64, 16), (2000, 33)])
+def test_mindist_and_cost(eng, n, d, dtype):
+    X, _ = blobs(n, d, 5, seed=n + d, dtype=dtype)
+    Xd = eng.to_device(X)
+    import torch
+
+    mind2 = torch.empty(n, dtype=Xd.dtype, device=eng.device)
+    cost = eng.mindist_update(Xd, Xd[:1], mind2, init=True).item()
+    ref = orc.evaluate_cost(X, X[:1])
+    tol = 3e-5 if dtype == np.float32 else 1e-10
+    npt.assert_allclose(cost, ref, rtol=tol)
+    cand = X[[5, 17, 40, 41, 42, 43, 44, 45, 46, 47, 48][: min(11, n - 1)]]
+    cost2 = eng.mindist_update(Xd, eng.to_device(cand), mind2, init=False).item()
+    allc = np.vstack([X[:1], cand])
+    npt.assert_allclose(cost2, orc.evaluate_cost(X, allc), rtol=tol)
+    d2 = sklearn.metrics.pairwise_distances(X.astype(np.float64), allc.astype(np.float64), metric="sqeuclidean").min(1)
+    npt.assert_allclose(mind2.cpu().numpy(), d2, rtol=tol * 3, atol=tol * d2.max())
+
+
+def test_bernoulli_matches_oracle_philox(eng):
+    import torch
+
+    rs = np.random.RandomState(0)
+    n = 200000
+    mind2 = rs.uniform(0, 4, size=n).astype(np.float32)
+    cost = float(mind2.astype(np.float64).sum())
+    md = eng.to_device(mind2)
+    for seed, rnd, off, l in [(0, 0, 0, 2), (123456789012345, 3, 10**10, 50), (7, 11, 12345, 1000)]:
+        got = np.sort(eng.bernoulli(md, l / cost, seed, rnd, off).cpu().numpy())
+        u = orc.philox_uniform_f64(seed, rnd, off, n)
+        p = (l / cost) * mind2.astype(np.float64)
+        ref = off + np.where(p > u)[0]
+        npt.assert_array_equal(got, ref)
+    # injected draws
+    u = rs.uniform(size=n)
+    got = np.sort(eng.bernoulli(md, 30 / cost, 0, 0, 5, draws=eng.to_device(u)).cpu().numpy())
+    npt.assert_array_equal(got, 5 + np.where((30 / cost) * mind2.astype(np.float64) > u)[0])
+    # capacity overflow is retried transparently
+    got = eng.bernoulli(md, 1e9, 1, 0, 0, capacity=16)
+    assert got.numel() == (mind2 > 0).sum()
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+def test_gather_cdist_norms_finite(eng, dtype):
+    import torch
+
+    rs = np.random.RandomState(2)
+    X = rs.standard_normal((1000, 37)).astype(dtype)
+    Y = rs.standard_normal((70, 37)).astype(dtype)
+    Xd, Yd = eng.to_device(X), eng.to_device(Y)
+    idx = np.array([999, 0, 5, 5, 321], dtype=np.int64)
+    npt.assert_array_equal(eng.gather(Xd, torch.from_numpy(idx)).cpu().numpy(), X[idx])
+    tol = 2e-4 if dtype == np.float32 else 1e-10
+    npt.assert_allclose(eng.cdist(Xd, Yd).cpu().numpy(), orc.euclidean_distances(X, Y), rtol=tol, atol=tol)
+    npt.assert_allclose(eng.cdist(Xd, Yd, squared=True).cpu().numpy(), orc.euclidean_distances(X, Y, squared=True),
+                        rtol=tol, atol=tol)
+    npt.assert_allclose(eng.row_norms(Xd, squared=True).cpu().numpy(), orc.row_norms(X, squared=True), rtol=tol)
+    npt.assert_allclose(eng.row_norms(Xd).cpu().numpy(), orc.row_norms(X), rtol=tol)
+    assert not eng.has_nonfinite(Xd)
+    for bad in (np.nan, np.inf, -np.inf):
+        Z = X.copy()
+        Z[777, 36] = bad
+        assert eng.has_nonfinite(eng.to_device(Z))
+
+
+def test_make_blobs_statistics(eng):
+    import torch
+
+    k, d, n = 16, 8, 400000
+    centers = torch.from_numpy(np.random.RandomState(0).uniform(-10, 10, size=(k, d)).astype(np.float32))
+    X = eng.make_blobs(n, d, centers, 1.0, seed=3)
+    pack = eng.pack(centers.double().to(eng.device))
+    lab, d2 = eng.assign(X, pack)
+    cnt = np.bincount(lab.cpu().numpy(), minlength=k)
+    assert abs(cnt - n / k).max() < 6 * np.sqrt(n / k)
+    assert abs(d2.double().mean().item() - d) < 0.05  # chi^2_d mean
+    # sharding invariance: rows generated with an offset equal the same rows of the full array
+    Y = eng.make_blobs(1000, d, centers, 1.0, seed=3, row_offset=5000)
+    assert torch.equal(Y, X[5000:6000])

@@ -1,0 +1,272 @@
+"""-m gpu: the estimator / module-function surface against the oracle and against the
+reference's own test expectations (reference tests/test_kmeans.py, tests/metrics/test_metrics.py)."""
+import glob
+import os
+
+import numpy as np
+import numpy.testing as npt
+import pytest
+import sklearn
+import sklearn.metrics
+from sklearn.cluster import KMeans as SKKMeans
+
+from conftest import blobs
+from oracle import kmeans_oracle as orc
+
+pytestmark = pytest.mark.gpu
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+@pytest.fixture(scope="module", autouse=True)
+def _dev():
+    import torch
+
+    torch.cuda.set_device(0)
+
+
+def _km():
+    from dask_ml_b200.cluster import KMeans
+
+    return KMeans
+
+
+def replace(a, old, new):
+    arr = np.empty(a.max() + 1, dtype=new.dtype)
+    arr[old] = new
+    return arr[a]
+
+
+# ---- the reference's own tests, replayed on the CUDA path --------------------------------------
+def test_row_norms(X_blobs):  # reference tests/test_kmeans.py:36-39
+    from dask_ml_b200._engine import get_engine
+    from dask_ml_b200.utils import row_norms
+
+    result = row_norms(get_engine().to_device(X_blobs), squared=True)
+    expected = sklearn.utils.extmath.row_norms(X_blobs, squared=True)
+    npt.assert_allclose(result.compute(), expected, rtol=1e-12)
+
+
+def test_too_small():  # reference tests/test_kmeans.py:48-51
+    km = _km()()
+    X = np.random.RandomState(0).uniform(size=(20, 2))
+    km.fit(X)
+    assert km.cluster_centers_.shape == (8, 2)
+
+
+def test_fit_raises():  # reference tests/test_kmeans.py:54-60
+    km = _km()()
+    with pytest.raises(ValueError):
+        km.fit(np.array([]).reshape(0, 1))
+    with pytest.raises(ValueError):
+        km.fit(np.array([]).reshape(1, 0))
+
+
+def test_nonfinite_raises():  # reference dask_ml/cluster/k_means.py:195-201
+    X = np.random.RandomState(0).uniform(size=(50, 3))
+    X[7, 1] = np.nan
+    with pytest.raises(ValueError, match="Input contains NaN, infinity"):
+        _km()(n_clusters=2).fit(X)
+
+
+def test_basic(Xl_blobs_easy):  # reference tests/test_kmeans.py:64-94
+    X = Xl_blobs_easy
+    a = _km()(n_clusters=3, random_state=0)
+    b = SKKMeans(n_clusters=3, random_state=0, n_init="auto")
+    a.fit(X)
+    b.fit(X)
+    assert abs(a.inertia_ - b.inertia_) < 0.01
+    a_order = np.argsort(a.cluster_centers_, 0)[:, 0]
+    b_order = np.argsort(b.cluster_centers_, 0)[:, 0]
+    a_centers = a.cluster_centers_[a_order]
+    b_centers = b.cluster_centers_[b_order]
+    npt.assert_allclose(a_centers, b_centers, rtol=1e-3)
+    b_labels = replace(b.labels_, [0, 1, 2], a_order[b_order]).astype(b.labels_.dtype)
+    npt.assert_array_equal(a.labels_.compute(), b_labels)
+    assert a.n_iter_
+    b.cluster_centers_ = b_centers
+    a.cluster_centers_ = a_centers
+    npt.assert_allclose(a.transform(X).compute(), b.transform(X), rtol=1e-3)
+    npt.assert_array_equal(a.predict(X).compute(), b.predict(X))
+    assert a.n_features_in_ == 2
+
+
+def test_invalid_init():  # reference tests/test_kmeans.py:153-169
+    X = np.random.RandomState(0).uniform(size=(30, 4))
+    with pytest.raises(ValueError):
+        _km()(n_clusters=3, init=np.zeros((2, 4))).fit(X)
+    with pytest.raises(ValueError):
+        _km()(n_clusters=3, init=np.zeros((3, 2))).fit(X)
+    with pytest.raises(ValueError):
+        _km()(n_clusters=3, init="nonsense").fit(X)
+    with pytest.raises(TypeError):
+        _km()(n_clusters=3, init=5).fit(X)
+
+
+def test_inputs():  # reference tests/test_kmeans.py:171-182
+    import pandas as pd
+    import torch
+
+    X = np.random.RandomState(0).uniform(size=(100, 4))
+    for xx in (X, pd.DataFrame(X), torch.from_numpy(X), torch.from_numpy(X).cuda()):
+        km = _km()(n_clusters=3, random_state=0)
+        km.fit(xx)
+        assert km.transform(xx).shape == (100, 3)
+
+
+def test_dtypes():  # reference tests/test_kmeans.py:184-197
+    X = np.random.RandomState(0).uniform(size=(100, 2))
+    X2 = X.astype("f4")
+    for xx, yy in [(X, X), (X2, X2), (X, X2), (X2, X)]:
+        a = SKKMeans(n_init="auto", random_state=0)
+        b = _km()(random_state=0)
+        a.fit(xx)
+        b.fit(xx)
+        assert a.cluster_centers_.dtype == b.cluster_centers_.dtype
+        assert a.labels_.dtype == b.labels_.dtype
+        assert a.transform(xx).dtype == b.transform(xx).dtype
+        assert a.transform(yy).dtype == b.transform(yy).dtype
+
+
+def test_int_inputs_promote():  # reference dask_ml/cluster/k_means.py:187-190
+    X = np.random.RandomState(0).randint(0, 50, size=(200, 3))
+    assert _km()(n_clusters=2, random_state=0).fit(X.astype(np.int32)).cluster_centers_.dtype == np.float32
+    assert _km()(n_clusters=2, random_state=0).fit(X.astype(np.int64)).cluster_centers_.dtype == np.float64
+
+
+def test_pairwise_distances(X_blobs):  # reference tests/metrics/test_metrics.py:15-19
+    from dask_ml_b200.metrics import pairwise_distances
+
+    centers = X_blobs[::100]
+    result = pairwise_distances(X_blobs, centers)
+    expected = sklearn.metrics.pairwise_distances(X_blobs, centers)
+    npt.assert_allclose(result.compute(), expected, atol=1e-4)
+
+
+def test_pairwise_distances_argmin_min(X_blobs):  # reference tests/metrics/test_metrics.py:22-39
+    from dask_ml_b200.metrics import pairwise_distances_argmin_min
+
+    centers = X_blobs[::100]
+    a_, b_ = sklearn.metrics.pairwise_distances_argmin_min(X_blobs, centers)
+    a, b = pairwise_distances_argmin_min(X_blobs, centers)
+    npt.assert_array_equal(a.compute(), a_)
+    # the reference demands equality of two float64 evaluations of the SAME expanded formula; the
+    # kernel uses the direct form, so the float64 bar of north_star (1e-10 relative) applies
+    npt.assert_allclose(b.compute(), b_, rtol=1e-10, atol=1e-12)
+    assert a.dtype == np.int64 and b.dtype == np.float64
+    with pytest.warns(FutureWarning):
+        pairwise_distances_argmin_min(X_blobs, centers, batch_size=10)
+
+
+def test_euclidean_distances():  # reference tests/metrics/test_metrics.py:42-71
+    from dask_ml_b200.metrics import euclidean_distances
+
+    rs = np.random.RandomState(0)
+    X, Y = rs.uniform(size=(100, 4)), rs.uniform(size=(100, 4))
+    npt.assert_allclose(euclidean_distances(X, Y).compute(), sklearn.metrics.euclidean_distances(X, Y), atol=1e-10)
+    xn = (X**2).sum(axis=1)[:, np.newaxis]
+    npt.assert_allclose(euclidean_distances(X, Y, X_norm_squared=xn).compute(),
+                        sklearn.metrics.euclidean_distances(X, Y, X_norm_squared=xn), atol=1e-10)
+    yn = (Y**2).sum(axis=1)[np.newaxis, :]
+    npt.assert_allclose(euclidean_distances(X, Y, Y_norm_squared=yn).compute(),
+                        sklearn.metrics.euclidean_distances(X, Y, Y_norm_squared=yn), atol=1e-10)
+    npt.assert_allclose(euclidean_distances(X, X).compute(), sklearn.metrics.euclidean_distances(X, X), atol=1e-4)
+    npt.assert_allclose(euclidean_distances(X).compute(), sklearn.metrics.euclidean_distances(X), atol=1e-4)
+    with pytest.raises(ValueError):
+        euclidean_distances(X, Y, X_norm_squared=np.zeros((3, 1)))
+
+
+# ---- parity with the oracle beyond what the reference pins -----------------------------------
+def _lloyd_vs_oracle(X, k, init, max_iter, tol, rtol):
+    km = _km()(n_clusters=k, init=init, max_iter=max_iter, tol=tol).fit(X)
+    lab, inertia, C, n_iter = orc.kmeans_single_lloyd(X, k, init, max_iter=max_iter, tol=tol, chunks=(len(X),))
+    npt.assert_array_equal(km.labels_.compute(), lab)
+    npt.assert_allclose(km.cluster_centers_, C, rtol=rtol, atol=rtol * np.abs(C).max())
+    npt.assert_allclose(km.inertia_, inertia, rtol=rtol)
+    assert km.n_iter_ == n_iter
+    assert km.cluster_centers_.dtype == X.dtype and km.labels_.dtype == np.int32
+    return km
+
+
+@pytest.mark.parametrize("n,d,k,dtype,max_iter,tol", [
+    (20000, 16, 8, np.float64, 6, 0.0),       # C1 shape
+    (30000, 32, 256, np.float32, 4, 0.0),     # C2 shape
+    (20000, 64, 1024, np.float32, 3, 0.0),    # C3 shape
+    (6000, 128, 1500, np.float32, 2, 0.0),    # C4 shape (k scaled)
+    (5000, 10, 20, np.float32, 300, 1e-4),    # runs to convergence (squared-inertia branch or not)
+    (5000, 10, 20, np.float64, 300, 1e-9),
+    (999, 7, 3, np.float32, 2, 0.0),
+])
+def test_lloyd_fixed_init_matches_oracle(n, d, k, dtype, max_iter, tol):
+    X, _ = blobs(n, d, k, seed=n + k, dtype=dtype)
+    _lloyd_vs_oracle(X, k, X[:k].copy(), max_iter, tol, 1e-5 if dtype == np.float32 else 1e-10)
+
+
+def test_lloyd_empty_cluster_goes_to_origin():
+    X, _ = blobs(2000, 6, 4, seed=0, dtype=np.float32)
+    init = np.vstack([X[:3], np.full((1, 6), 1e3, np.float32)])
+    km = _lloyd_vs_oracle(X, 4, init, 1, 0.0, 1e-5)
+    assert (km.cluster_centers_[3] == 0).all()
+
+
+@pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(HERE, "golden", "lloyd_*.npz"))))
+def test_golden_lloyd(path):
+    g = np.load(path)
+    X = g["X"]
+    rtol = 1e-5 if X.dtype == np.float32 else 1e-10
+    km = _km()(n_clusters=int(g["k"]), init=g["init"], max_iter=int(g["max_iter"]), tol=float(g["tol"])).fit(X)
+    npt.assert_array_equal(km.labels_.compute(), g["labels"])
+    npt.assert_allclose(km.cluster_centers_, g["centers"], rtol=rtol, atol=rtol * np.abs(g["centers"]).max())
+    npt.assert_allclose(km.inertia_, float(g["inertia"]), rtol=rtol)
+    assert km.n_iter_ == int(g["n_iter"])
+
+
+@pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(HERE, "golden", "init_*.npz"))))
+def test_golden_init_scalable(path):
+    """k-means|| with the device Philox draws: the same rows are picked as the oracle picks with
+    its numpy Philox restatement; the random supplement is injected."""
+    from dask_ml_b200.cluster import k_means as kmod
+
+    g = np.load(path)
+    X = g["X"]
+
+    class RS(kmod.PhiloxRandomState):
+        def choice(self, n, size):
+            return g["supplement"]
+
+    rs = RS(int(g["seed"]))
+    C = kmod.init_scalable(X, int(g["k"]), rs, None, float(g["l"]))
+    rtol = 1e-5 if X.dtype == np.float32 else 1e-9
+    if len(g["picked"]) < int(g["k"]):
+        npt.assert_allclose(C, g["centers"], rtol=rtol)   # candidates + injected supplement rows: exact rows of X
+    else:
+        # >= k candidates: sklearn re-clusters the candidate ROWS (same rows, same rng2) on the host
+        npt.assert_allclose(C, g["centers"], rtol=1e-6, atol=1e-6)
+
+
+def test_evaluate_cost_and_sample_points_match_oracle():
+    from dask_ml_b200.cluster.k_means import _sample_points, evaluate_cost
+
+    for dtype, rtol in ((np.float32, 1e-5), (np.float64, 1e-10)):
+        X, _ = blobs(30000, 12, 6, seed=4, dtype=dtype)
+        centers = X[[0, 100, 2000, 2001, 2002, 9000, 9001, 9002, 9003, 15000, 29999]]
+        npt.assert_allclose(evaluate_cost(X, centers), orc.evaluate_cost(X, centers), rtol=rtol)
+        # injected draws (the oracle's restatement of dask's RandomState) -> identical index sets
+        got = _sample_points(X, centers, 40, orc.DaskLikeRandomState(3))
+        rs = orc.DaskLikeRandomState(3)
+        draws = rs.uniform(size=len(X), chunks=None if False else (len(X),))
+        ref, p = orc.sample_points(X, centers, 40, draws, return_p=True)
+        border = np.abs(p - draws) <= 1e-5 * p   # rows where p ~ draw within fp tolerance (reported)
+        sym = np.setxor1d(got, ref)
+        assert np.isin(sym, np.where(border)[0]).all(), (len(sym), border.sum())
+        assert len(got) > 10
+
+
+def test_kmeans_parallel_init_quality():
+    """End-to-end init='k-means||' (device Philox): compare final inertia with the oracle's over
+    several seeds -- distributional, not bit-wise (SURVEY section 8c protocol 4)."""
+    X, _ = blobs(20000, 8, 10, seed=9, dtype=np.float32)
+    ours, theirs = [], []
+    for seed in range(4):
+        ours.append(_km()(n_clusters=10, random_state=seed, max_iter=30).fit(X).inertia_)
+        theirs.append(orc.KMeansOracle(n_clusters=10, random_state=seed, max_iter=30, chunks=(len(X),)).fit(X).inertia_)
+    assert np.median(ours) < 1.3 * np.median(theirs)
