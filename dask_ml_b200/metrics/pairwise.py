@@ -79,7 +79,9 @@ def pairwise_distances(X, Y, metric="euclidean", n_jobs: Optional[int] = None, *
         raise ValueError(f"metric={metric!r}: only 'euclidean' is on the k-means path")
     eng = get_engine()
     Xd = _dev(X, eng)
-    Yd = _dev(Y, eng, Xd.dtype)
+    Yd = _dev(Y, eng)
+    if Yd.dtype != Xd.dtype:
+        Xd, Yd = Xd.to(torch.float64), Yd.to(torch.float64)
     squared = metric == "sqeuclidean" or bool(kwargs.get("squared", False))
     return DeviceArray(eng.cdist(Xd, Yd, squared=squared))
 
@@ -90,7 +92,9 @@ def euclidean_distances(X, Y=None, Y_norm_squared=None, squared: bool = False, X
     eng = get_engine()
     Xd = _dev(X, eng)
     same = Y is None or Y is X
-    Yd = Xd if same else _dev(Y, eng, Xd.dtype)
+    Yd = Xd if same else _dev(Y, eng)
+    if Yd.dtype != Xd.dtype:  # numpy promotion of -2 * dot(X, Y.T) + XX + YY (:101)
+        Xd, Yd = Xd.to(torch.float64), Yd.to(torch.float64)
     xn = yn = None
     if X_norm_squared is not None:
         XX = np.asarray(X_norm_squared.compute() if hasattr(X_norm_squared, "compute") else X_norm_squared)
