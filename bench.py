@@ -116,17 +116,22 @@ def cpu_reference_fit_rate(X, k, steps, warmup, cores):
     """points/s of ``KMeans(init=ndarray, max_iter=1, tol=0).fit(X)`` restated on the CPU: one Lloyd
     iteration + the reference's final labelling pass, one row block per core in a thread pool
     (what KMeans._check_array + the threaded scheduler do, reference k_means.py:192-193)."""
+    from threadpoolctl import threadpool_limits
+
     from oracle import kmeans_oracle as orc
 
     chunks = orc.row_chunks(len(X), ncpu=cores)
     init = X[:k].copy()
     times = []
-    for it in range(warmup + steps):
-        t0 = time.perf_counter()
-        orc.KMeansOracle(n_clusters=k, init=init, max_iter=1, tol=0.0, chunks=chunks, n_threads=cores).fit(X)
-        dt = time.perf_counter() - t0
-        if it >= warmup:
-            times.append(dt)
+    # one single-threaded sklearn/BLAS call per row block, `cores` blocks in flight (dask's threaded
+    # scheduler); without the limit sklearn's OpenMP x the pool oversubscribes and OpenBLAS aborts
+    with threadpool_limits(limits=1):
+        for it in range(warmup + steps):
+            t0 = time.perf_counter()
+            orc.KMeansOracle(n_clusters=k, init=init, max_iter=1, tol=0.0, chunks=chunks, n_threads=cores).fit(X)
+            dt = time.perf_counter() - t0
+            if it >= warmup:
+                times.append(dt)
     return len(X) / (sum(times) / len(times)), sum(times) / len(times)
 
 
@@ -134,11 +139,13 @@ def cpu_lloyd_step_rate(X, k, reps, cores):
     """points/s of ONE Lloyd iteration (argmin_min + _centers_dense + bincount + divide) on the CPU."""
     from concurrent.futures import ThreadPoolExecutor
 
+    from threadpoolctl import threadpool_limits
+
     from oracle import kmeans_oracle as orc
 
     chunks = orc.row_chunks(len(X), ncpu=cores)
     centers = X[:k].astype(np.float64)
-    with ThreadPoolExecutor(cores) as pool:
+    with threadpool_limits(limits=1), ThreadPoolExecutor(cores) as pool:
         orc.lloyd_step(X[: max(k, len(X) // 8)], centers, k, (max(k, len(X) // 8),), pool)  # numba/BLAS warm-up
         t0 = time.perf_counter()
         for _ in range(reps):

@@ -316,7 +316,7 @@ def _pick(eng, comm, mind2, cost, oversampling_factor, random_state, row0, n_tot
     else:
         # injected host draws (np RandomState, or an object restating dask's RandomState)
         try:
-            u = random_state.uniform(size=n_total, chunks=None)
+            u = random_state.uniform(size=n_total, chunks=(n_total,))  # dask-style signature
         except TypeError:
             u = random_state.uniform(size=n_total)
         u = np.asarray(u, dtype=np.float64)[row0 : row0 + mind2.numel()]

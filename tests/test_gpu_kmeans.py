@@ -151,7 +151,8 @@ def test_pairwise_distances_argmin_min(X_blobs):  # reference tests/metrics/test
     npt.assert_array_equal(a.compute(), a_)
     # the reference demands equality of two float64 evaluations of the SAME expanded formula; the
     # kernel uses the direct form, so the float64 bar of north_star (1e-10 relative) applies
-    npt.assert_allclose(b.compute(), b_, rtol=1e-10, atol=1e-12)
+    # (atol: the centres are rows of X; sklearn's expanded formula returns sqrt(~1e-16) there, not 0)
+    npt.assert_allclose(b.compute(), b_, rtol=1e-10, atol=1e-7)
     assert a.dtype == np.int64 and b.dtype == np.float64
     with pytest.warns(FutureWarning):
         pairwise_distances_argmin_min(X_blobs, centers, batch_size=10)
