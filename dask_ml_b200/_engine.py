@@ -138,8 +138,14 @@ class CudaEngine:
                     self._call("b200km_assign_f32", xs.data_ptr(), nn, d, ldx, pack.buf.data_ptr(), pack.k,
                                ls.data_ptr(), mp, None, None, 0, st, launches=1)
             else:
+                if self.k1_events is not None:
+                    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    e0.record()
                 self._call("b200km_assign_f64", xs.data_ptr(), nn, d, ldx, pack.buf.data_ptr(), pack.k,
                            ls.data_ptr(), mp, st, launches=1)
+                if self.k1_events is not None:
+                    e1.record()
+                    self.k1_events.append((e0, e1))
         return labels, (mind2 if want_mind2 else None)
 
     def flagged_count(self) -> int:
