@@ -28,6 +28,8 @@ _P = c_void_p  # device pointers and the stream are passed as plain addresses
 # name -> (restype, argtypes).  Kept in the order of include/b200km.h; tests/test_abi.py checks
 # that this table, the header and the exported symbols agree.
 PROTOTYPES = {
+    "b200km_set_option": (c_int, [c_int, c_int]),
+    "b200km_get_option": (c_int, [c_int]),
     "b200km_version": (c_int, []),
     "b200km_error_string": (c_char_p, [c_int]),
     "b200km_pack_bytes": (c_size_t, [c_int, c_int]),

@@ -17,6 +17,10 @@
 //                        (with row indirection) as the refine kernel.
 #include "common.cuh"
 
+int km_launch_pack_tc(int k, int d, void *pack, cudaStream_t st);  // assign_tc.cu
+int km_launch_assign_tc(const float *X, int64_t n, int d, int64_t ldx, const void *pack, int k, int32_t *labels,
+                        float *mind2, int32_t *flag_rows, int32_t *flag_count, cudaStream_t st);
+
 // =============================================================================================
 // centre pack
 // =============================================================================================
@@ -87,7 +91,9 @@ extern "C" int b200km_pack_centers(const double *centers_f64, int k, int d, void
     if (e != cudaSuccess) return (int)e;
     const int ntiles = (k + KM_TILE_N - 1) / KM_TILE_N;
     pack_centers_kernel<<<ntiles * KM_TILE_N, 128, 0, st>>>(centers_f64, k, d, static_cast<unsigned char *>(pack));
-    KM_LAUNCH_RET();
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return (int)e;
+    return km_launch_pack_tc(k, d, pack, st);
 }
 
 // =============================================================================================
@@ -376,6 +382,27 @@ static int launch_rb(const TX *X, int64_t n, int d, int64_t ldx, const double *c
 // =============================================================================================
 // entry points
 // =============================================================================================
+
+static int g_k1_variant = 0;  // B200KM_OPT_K1_VARIANT: 0 auto, 1 FFMA, 2 tcgen05 3xTF32
+
+extern "C" int b200km_set_option(int key, int value) {
+    if (key == B200KM_OPT_K1_VARIANT && value >= 0 && value <= 2) {
+        g_k1_variant = value;
+        return 0;
+    }
+    return B200KM_EINVAL;
+}
+extern "C" int b200km_get_option(int key) {
+    if (key == B200KM_OPT_K1_VARIANT) return g_k1_variant;
+    return B200KM_EINVAL;
+}
+
+static bool use_tc_path(int d, int k) {
+    if (d > KM_TC_MAX_D) return false;
+    if (g_k1_variant == 1) return false;
+    if (g_k1_variant == 2) return true;
+    return false;  // auto: FFMA until the tensor-core path is validated on every shape class
+}
 static int check_pack_args(const void *X, int64_t n, int d, int64_t ldx, const void *pack, int k, const void *labels) {
     KM_CHECK_ARG(X && pack && labels, B200KM_EINVAL);
     KM_CHECK_ARG(n > 0 && d > 0 && k > 0 && ldx >= d, B200KM_EINVAL);
@@ -405,6 +432,7 @@ extern "C" int b200km_assign_f32(const float *X, int64_t n, int d, int64_t ldx, 
     if (d > 128 || k <= 16) {
         return launch_rb<float, 32, 8, 8, false>(X, n, d, ldx, c64, k, nullptr, nullptr, labels, mind2, st);
     }
+    if (use_tc_path(d, k)) return km_launch_assign_tc(X, n, d, ldx, pack, k, labels, mind2, flag_rows, flag_count, st);
     const int ntiles = (k + KM_TILE_N - 1) / KM_TILE_N;
     const size_t smem = sizeof(float) * ((size_t)d * AT_XLD + 2 * (size_t)(d + 1) * KM_TILE_N);
     const bool vec = (d % 4 == 0) && (ldx % 4 == 0) && ((reinterpret_cast<uintptr_t>(X) & 15) == 0);

@@ -46,6 +46,16 @@ static inline int km_set_smem_once(Kern kern, int bytes, bool *flags) {
 // ---------------------------------------------------------------------------------------------
 constexpr int KM_TILE_N = 128;  // centroid tile width of the tiled assign kernel
 
+// tcgen05 (3xTF32) image: per 64-centroid column tile, chunk-major no-swizzle K-major operand
+//   hi part: (kpad/4 + 2) chunks x 64 rows x 16 B   (last two chunks = augmented K-step carrying ||c||^2)
+//   lo part:  kpad/4      chunks x 64 rows x 16 B
+constexpr int KM_TC_BN = 64;
+constexpr int KM_TC_MAX_D = 64;
+__host__ __device__ inline int km_tc_kpad(int d) { return (d + 7) & ~7; }
+__host__ __device__ inline size_t km_tc_hi_bytes(int d) { return (size_t)KM_TC_BN * 16 * (km_tc_kpad(d) / 4 + 2); }
+__host__ __device__ inline size_t km_tc_lo_bytes(int d) { return (size_t)KM_TC_BN * 16 * (km_tc_kpad(d) / 4); }
+__host__ __device__ inline size_t km_tc_tile_bytes(int d) { return km_tc_hi_bytes(d) + km_tc_lo_bytes(d); }
+
 struct KmPackLayout {
     size_t off_hdr;   // int32[4]: k, d, ntiles, magic
     size_t off_cmax;  // uint32: bits of max_j ||c_j||^2 (fp32, non-negative)
@@ -54,6 +64,7 @@ struct KmPackLayout {
     size_t off_cn64;  // double[k]         ||c64_j||^2
     size_t off_c64;   // double[k*d]       copy of the fp64 master
     size_t off_ct;    // float[ntiles][d+1][128] column-tiled fp32 centres (zero padded); row d = norms
+    size_t off_tc;    // tcgen05 image: ceil(k/64) tiles of km_tc_tile_bytes(d) (absent when d > KM_TC_MAX_D)
     size_t total;
 };
 
@@ -70,6 +81,8 @@ __host__ __device__ inline KmPackLayout km_pack_layout(int k, int d) {
     L.off_cn64 = o; o = km_align256(o + sizeof(double) * (size_t)k);
     L.off_c64 = o;  o = km_align256(o + sizeof(double) * (size_t)k * d);
     L.off_ct = o;   o = km_align256(o + sizeof(float) * ntiles * (size_t)(d + 1) * KM_TILE_N);
+    L.off_tc = o;
+    if (d <= KM_TC_MAX_D) o = km_align256(o + (size_t)((k + KM_TC_BN - 1) / KM_TC_BN) * km_tc_tile_bytes(d));
     L.total = o;
     return L;
 }

@@ -45,6 +45,11 @@ extern "C" {
 #define B200KM_MAX_K (1 << 20)
 #define B200KM_MINDIST_MAX_M 8 /* candidates per b200km_mindist_update_* launch */
 
+/* options (process-wide; meant for benchmarks and tests) */
+#define B200KM_OPT_K1_VARIANT 1 /* 0 = auto, 1 = FP32 FFMA kernel, 2 = tcgen05 3xTF32 kernel (d <= 64) */
+int b200km_set_option(int key, int value);
+int b200km_get_option(int key);
+
 int b200km_version(void);
 /* static string for a code returned by any entry point (cudaGetErrorString for >0). */
 const char *b200km_error_string(int code);

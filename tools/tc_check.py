@@ -1,0 +1,43 @@
+"""Debug harness: tcgen05 K1 variant vs the FFMA variant and the float64 numpy answer."""
+import sys, os, time
+import numpy as np, torch
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from dask_ml_b200._engine import get_engine
+
+eng = get_engine()
+lib = eng.lib
+def run(n, d, k, seed=0):
+    rs = np.random.RandomState(seed)
+    C = rs.uniform(-10, 10, size=(k, d))
+    X = (C[rs.randint(0, k, n)] + rs.standard_normal((n, d))).astype(np.float32)
+    Cq = C + 0.3 * rs.standard_normal(C.shape)
+    Xd = eng.to_device(X); pack = eng.pack(eng.to_device(Cq, torch.float64))
+    D = ((X.astype(np.float64)[:, None, :] - Cq[None]) ** 2).sum(-1) if n * k <= 4e7 else None
+    out = {}
+    for var in (1, 2):
+        lib.b200km_set_option(1, var)
+        lab, m2 = eng.assign(Xd, pack, refine=False)
+        torch.cuda.synchronize()
+        out[var] = (lab.cpu().numpy().copy(), m2.cpu().numpy().copy())
+    lib.b200km_set_option(1, 0)
+    l1, l2 = out[1][0], out[2][0]
+    msg = f"n={n} d={d} k={k}: ffma-vs-tc label mismatches {int((l1 != l2).sum())}"
+    if D is not None:
+        ref = D.argmin(1)
+        msg += f"; ffma-vs-f64 {(l1 != ref).sum()}, tc-vs-f64 {(l2 != ref).sum()}; mind2 maxrel {np.abs(out[2][1]-D.min(1)).max()/D.min(1).max():.2e}"
+    print(msg, flush=True)
+
+for shape in [(256, 64, 64), (256, 64, 128), (1000, 64, 1024), (5000, 32, 256), (777, 20, 150), (513, 8, 33), (100000, 64, 1024), (3000, 48, 500)]:
+    run(*shape)
+# timing
+n, d, k = 8_000_000, 64, 1024
+X = torch.randn(n, d, device=eng.device); C = torch.randn(k, d, dtype=torch.float64, device=eng.device) * 3
+pack = eng.pack(C)
+for var in (1, 2):
+    lib.b200km_set_option(1, var)
+    lab, m2 = eng.assign(X, pack, refine=False)
+    torch.cuda.synchronize(); t0 = time.perf_counter()
+    for _ in range(3): eng.assign(X, pack, lab, m2, refine=False)
+    torch.cuda.synchronize(); dt = (time.perf_counter() - t0) / 3
+    print(f"variant {var}: {dt*1e3:.2f} ms  {n/dt/1e6:.1f} Mpts/s  {2*n*k*d/dt/1e12:.1f} TFLOP/s-equivalent", flush=True)
+lib.b200km_set_option(1, 0)
