@@ -9,21 +9,25 @@
 //      + Xaug.Baug^T                         (one extra K-step that adds ||c||^2 exactly)
 // so the epilogue only has to track (best, second, argmin) per row -- no per-element norm add.
 //
-// CTA = 192 threads, persistent, one per SM, 256 rows (two M=128 row tiles) per step:
-//   warp 0      : producer -- one 1-D bulk async copy (TMA, mbarrier complete_tx) per 64-centroid stage
-//   warp 1      : TMEM allocator + single-thread tcgen05.mma issuer (M=128, N=64, K=8, kind::tf32)
+// CTA = 192 threads, persistent, one per SM, 128 rows (one M=128 row tile) per step:
+//   warp 0      : producer -- one 1-D bulk async copy (TMA, mbarrier complete_tx) per K-step block of a
+//                 256-centroid column tile (16 KB: hi + lo parts of 8 features)
+//   warp 1      : TMEM allocator + tcgen05.mma issue (M=128, N=256, K=8, kind::tf32, one elected lane)
 //   warps 2..5  : X staging (LDG.128 -> cvt.rna.tf32 split -> STS in the UMMA canonical no-swizzle
-//                 K-major layout) and the epilogue (tcgen05.ld 32x32b.x32 -> argmin tracking)
-// Pipelines: B ring (2 smem stages), accumulator ring (4 TMEM stages of 2x64 columns).
-// Both row tiles share every B stage, which halves the L2 -> SMEM centroid traffic per row.
+//                 K-major layout, double-buffered so the next step is staged under the current one) and
+//                 the epilogue (tcgen05.ld 32x32b.x32, double-buffered against the argmin tracking)
+// N = 256 per MMA keeps the tensor core's shared-memory operand fetch (A 4 KB + B 8 KB per K-step) below
+// its 128-cycle math time; with N = 64 the fetch dominated and the pipe ran at 36 % (profiles/).
+// Pipelines: B ring (5 smem stages), accumulator ring (2 TMEM stages of 256 columns), 2 X buffers.
 #include "common.cuh"
 
 namespace {
 
 constexpr int TC_THREADS = 192;
-constexpr int TC_ROWS = 256;     // rows per CTA step (2 row tiles of 128)
-constexpr int TC_BSTAGES = 2;
-constexpr int TC_ASTAGES = 4;    // accumulator stages: 4 x (2 x 64) = 512 TMEM columns
+constexpr int TC_ROWS = 128;     // rows per CTA step
+constexpr int TC_BSTAGES = 5;    // ring of K-step blocks
+constexpr int TC_STAGE_BYTES = KM_TC_KS_BYTES;
+constexpr int TC_ASTAGES = 2;    // accumulator stages: 2 x 256 = 512 TMEM columns
 constexpr uint32_t TC_SPIN_LIMIT = 1u << 27;
 
 __device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
@@ -48,21 +52,29 @@ __device__ __forceinline__ void mbar_wait_bounded(uint64_t *bar, uint32_t parity
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 
-__device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
-    // no-swizzle ("interleave") K-major canonical layout: 8-row x 16-byte core matrices;
-    // LBO = byte distance between the two 16-byte K chunks of one MMA, SBO = between 8-row groups.
-    const uint32_t lo = ((saddr & 0x3FFFFu) >> 4) | (((lbo_bytes >> 4) & 0x3FFFu) << 16);
-    const uint32_t hi = ((sbo_bytes >> 4) & 0x3FFFu) | (1u << 14);  // version = 1 (Blackwell)
-    return ((uint64_t)hi << 32) | lo;
-}
-__device__ __forceinline__ void mma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
-                                         uint32_t accumulate) {
+// Shared-memory matrix descriptors: no-swizzle ("interleave") K-major canonical layout, 8-row x 16-byte
+// core matrices; LBO = byte distance between the two 16-byte K chunks of one MMA (bits 16-29, >>4),
+// SBO = byte distance between 8-row groups (bits 32-45, >>4), version 1 at bits 46-47.
+// descriptors are passed as their low words; the high word (SBO = 128 B, version 1) is shared
+__device__ __forceinline__ void mma_tf32(uint32_t tmem_d, uint32_t adesc_lo, uint32_t bdesc_lo, uint32_t desc_hi,
+                                         uint32_t idesc, uint32_t accumulate) {
     asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, {%5, %6, %7, %8}, p;\n\t}"
-        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate), "r"(0u), "r"(0u), "r"(0u), "r"(0u)
+        "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\t"
+        "setp.ne.b32 p, %5, 0;\n\t"
+        "mov.b64 da, {%1, %3};\n\t"
+        "mov.b64 db, {%2, %3};\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], da, db, %4, {%6, %6, %6, %6}, p;\n\t}"
+        ::"r"(tmem_d), "r"(adesc_lo), "r"(bdesc_lo), "r"(desc_hi), "r"(idesc), "r"(accumulate), "r"(0u)
         : "memory");
+}
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile(
+        "{\n\t.reg .b32 rx;\n\t.reg .pred px;\n\t"
+        "elect.sync rx|px, 0xFFFFFFFF;\n\t"
+        "selp.u32 %0, 1, 0, px;\n\t}"
+        : "=r"(pred));
+    return pred != 0;
 }
 __device__ __forceinline__ void mma_commit(uint64_t *bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(km_smem_u32(bar))
@@ -81,6 +93,7 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
         : "memory");
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 
 __device__ __forceinline__ float tf32_rna(float x) {
     uint32_t u;
@@ -88,11 +101,16 @@ __device__ __forceinline__ float tf32_rna(float x) {
     return __uint_as_float(u);
 }
 
-__device__ __forceinline__ void track(float v, int col, float &best, float &second, int &bidx) {
-    const bool lt = v < best;
-    second = lt ? best : fminf(second, v);
-    bidx = lt ? col : bidx;
-    best = fminf(best, v);
+// 5 ALU ops per score: FSETP + 3 FMNMX + SEL(imm).  `jloc` is the index inside the current chunk.
+__device__ __forceinline__ void track(float v, int j, float &best, float &second, int &jloc) {
+    asm("{\n\t.reg .pred p;\n\t.reg .f32 t;\n\t"
+        "setp.lt.f32 p, %3, %0;\n\t"
+        "max.f32 t, %0, %3;\n\t"
+        "min.f32 %1, %1, t;\n\t"
+        "min.f32 %0, %0, %3;\n\t"
+        "selp.b32 %2, %4, %2, p;\n\t}"
+        : "+f"(best), "+f"(second), "+r"(jloc)
+        : "f"(v), "r"(j));
 }
 
 struct TcBars {
@@ -100,8 +118,8 @@ struct TcBars {
     uint64_t b_empty[TC_BSTAGES];
     uint64_t a_full[TC_ASTAGES];
     uint64_t a_empty[TC_ASTAGES];
-    uint64_t x_ready;
-    uint64_t x_free;
+    uint64_t x_ready[2];
+    uint64_t x_free[2];
     uint32_t tmem_base;
     uint32_t pad;
 };
@@ -119,19 +137,19 @@ __global__ void __launch_bounds__(64) pack_tc_kernel(int k, int d, unsigned char
     const int tile = j / KM_TC_BN, jj = j % KM_TC_BN;
     const int kpad = km_tc_kpad(d);
     unsigned char *img = pack + L.off_tc + (size_t)tile * km_tc_tile_bytes(d);
-    float *hi = reinterpret_cast<float *>(img);
-    float *lo = reinterpret_cast<float *>(img + km_tc_hi_bytes(d));
     for (int f = threadIdx.x; f < kpad; f += blockDim.x) {
         float v = 0.f;
         if (j < k && f < d) v = -2.f * c32[(size_t)j * d + f];
         const float h = tf32_rna(v);
         const float l = tf32_rna(v - h);
-        const size_t o = ((size_t)(f >> 2) * KM_TC_BN + jj) * 4 + (f & 3);
-        hi[o] = h;
-        lo[o] = l;
+        const int ks = f >> 3, fc = f & 7;
+        unsigned char *blk = img + KM_TC_AUG_BYTES + (size_t)ks * KM_TC_KS_BYTES;
+        const size_t o = ((size_t)(fc >> 2) * KM_TC_BN + jj) * 4 + (fc & 3);
+        reinterpret_cast<float *>(blk)[o] = h;
+        reinterpret_cast<float *>(blk + KM_TC_KS_BYTES / 2)[o] = l;
     }
     if (threadIdx.x < 8) {
-        // augmented K-step: chunk kpad/4 = [cn_h, cn_m, cn_l, 0], chunk kpad/4+1 = 0
+        // augmented K-step: chunk 0 = [cn_h, cn_m, cn_l, 0], chunk 1 = 0
         float v = 0.f;
         if (threadIdx.x < 3) {
             if (j < k) {
@@ -144,8 +162,8 @@ __global__ void __launch_bounds__(64) pack_tc_kernel(int k, int d, unsigned char
                 v = threadIdx.x == 0 ? 1e30f : 0.f;  // padded columns never win
             }
         }
-        const int f = kpad + threadIdx.x;
-        hi[((size_t)(f >> 2) * KM_TC_BN + jj) * 4 + (f & 3)] = v;
+        const int f = threadIdx.x;
+        reinterpret_cast<float *>(img)[((size_t)(f >> 2) * KM_TC_BN + jj) * 4 + (f & 3)] = v;
     }
 }
 
@@ -169,15 +187,14 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
     extern __shared__ __align__(1024) unsigned char tc_smem[];
     const int kpad = km_tc_kpad(d);
     const int nch = kpad / 4;                 // 16-byte K chunks of the real features
-    const uint32_t xhi_bytes = (uint32_t)(nch + 2) * 128 * 16;  // per row tile
+    const int nks = kpad / 8;                 // K-steps
+    const uint32_t xhi_bytes = (uint32_t)(nch + 2) * 128 * 16;
     const uint32_t xlo_bytes = (uint32_t)nch * 128 * 16;
-    const uint32_t bhi_bytes = (uint32_t)km_tc_hi_bytes(d);
-    const uint32_t blo_bytes = (uint32_t)km_tc_lo_bytes(d);
-    const uint32_t stage_bytes = bhi_bytes + blo_bytes;
-    unsigned char *xhi = tc_smem;                          // [2][nch+2][128][16B]
-    unsigned char *xlo = xhi + 2 * xhi_bytes;              // [2][nch][128][16B]
-    unsigned char *bst = xlo + 2 * xlo_bytes;              // [TC_BSTAGES][stage_bytes]
-    TcBars *bars = reinterpret_cast<TcBars *>(bst + TC_BSTAGES * stage_bytes);
+    const uint32_t xbuf_bytes = xhi_bytes + xlo_bytes;     // one X buffer: hi part then lo part
+    const uint32_t tile_bytes = (uint32_t)km_tc_tile_bytes(d);
+    unsigned char *xb = tc_smem;                           // [2][xbuf_bytes]
+    unsigned char *bst = xb + 2 * xbuf_bytes;              // [TC_BSTAGES][TC_STAGE_BYTES]
+    TcBars *bars = reinterpret_cast<TcBars *>(bst + TC_BSTAGES * TC_STAGE_BYTES);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int ntc = (k + KM_TC_BN - 1) / KM_TC_BN;
@@ -186,8 +203,7 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
     if (tid == 0) {
         for (int i = 0; i < TC_BSTAGES; ++i) { km_mbar_init(&bars->b_full[i], 1); km_mbar_init(&bars->b_empty[i], 1); }
         for (int i = 0; i < TC_ASTAGES; ++i) { km_mbar_init(&bars->a_full[i], 1); km_mbar_init(&bars->a_empty[i], 128); }
-        km_mbar_init(&bars->x_ready, 128);
-        km_mbar_init(&bars->x_free, 1);
+        for (int i = 0; i < 2; ++i) { km_mbar_init(&bars->x_ready[i], 128); km_mbar_init(&bars->x_free[i], 1); }
         km_fence_mbar_init();
     }
     if (warp == 1) {
@@ -197,12 +213,13 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
                      : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
-    // constant augmented chunks of Xhi: chunk nch = [1,1,1,0], chunk nch+1 = 0 (both row tiles)
+    // constant augmented chunks of Xhi: chunk nch = [1,1,1,0], chunk nch+1 = 0 (both X buffers)
     for (int e = tid; e < 2 * 2 * 128; e += TC_THREADS) {
-        const int rt = e / 256, c = (e / 128) & 1, r = e & 127;
+        const int bf = e / 256, c = (e / 128) & 1, r = e & 127;
         float4 v = c == 0 ? make_float4(1.f, 1.f, 1.f, 0.f) : make_float4(0.f, 0.f, 0.f, 0.f);
-        *reinterpret_cast<float4 *>(xhi + (size_t)rt * xhi_bytes + ((size_t)(nch + c) * 128 + r) * 16) = v;
+        *reinterpret_cast<float4 *>(xb + (size_t)bf * xbuf_bytes + ((size_t)(nch + c) * 128 + r) * 16) = v;
     }
+    km_fence_proxy_async();
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -213,97 +230,107 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
         if (lane == 0) {
             uint32_t it = 0;
             for (int64_t step = blockIdx.x; step < nsteps; step += gridDim.x) {
-                for (int t = 0; t < ntc; ++t, ++it) {
-                    const int s = it % TC_BSTAGES;
-                    const uint32_t ph = (it / TC_BSTAGES) & 1;
-                    mbar_wait_bounded(&bars->b_empty[s], ph ^ 1);
-                    km_mbar_expect_tx(&bars->b_full[s], stage_bytes);
-                    km_bulk_g2s(bst + (size_t)s * stage_bytes, tc_img + (size_t)t * stage_bytes, stage_bytes,
-                                &bars->b_full[s]);
+                for (int t = 0; t < ntc; ++t) {
+                    const unsigned char *src = tc_img + (size_t)t * tile_bytes;
+                    for (int b = 0; b <= nks; ++b, ++it) {
+                        const int s = it % TC_BSTAGES;
+                        const uint32_t ph = (it / TC_BSTAGES) & 1;
+                        const uint32_t bytes = b == 0 ? (uint32_t)KM_TC_AUG_BYTES : (uint32_t)KM_TC_KS_BYTES;
+                        mbar_wait_bounded(&bars->b_empty[s], ph ^ 1);
+                        km_mbar_expect_tx(&bars->b_full[s], bytes);
+                        km_bulk_g2s(bst + (size_t)s * TC_STAGE_BYTES, src, bytes, &bars->b_full[s]);
+                        src += bytes;
+                    }
                 }
             }
         }
     } else if (warp == 1) {
-        // ================= MMA issuer =================
-        if (lane == 0) {
-            // instruction descriptor: D=F32, A=B=TF32, both K-major, N=64, M=128
-            const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(KM_TC_BN >> 3) << 17) |
-                                   ((uint32_t)(128 >> 4) << 24);
-            const uint32_t xhi_a = km_smem_u32(xhi), xlo_a = km_smem_u32(xlo), bst_a = km_smem_u32(bst);
-            uint32_t it = 0, xphase = 0;
-            for (int64_t step = blockIdx.x; step < nsteps; step += gridDim.x, xphase ^= 1) {
-                mbar_wait_bounded(&bars->x_ready, xphase);
-                tc_fence_after();
-                for (int t = 0; t < ntc; ++t, ++it) {
+        // ================= MMA issuer (warp-uniform control flow, one elected lane issues) =======
+        // instruction descriptor: D=F32, A=B=TF32, both K-major, N=256, M=128
+        const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(KM_TC_BN >> 3) << 17) |
+                               ((uint32_t)(128 >> 4) << 24);
+        const uint32_t desc_hi = (128u >> 4) | (1u << 14);           // SBO = 128 B, version = 1
+        const uint32_t a_lbo = (2048u >> 4) << 16;                   // A: 128 rows x 16 B per K chunk
+        const uint32_t b_lbo = ((uint32_t)(KM_TC_BN * 16) >> 4) << 16;  // B: 256 rows x 16 B per K chunk
+        const uint32_t xb_a = km_smem_u32(xb), bst_a = km_smem_u32(bst);
+        const bool leader = elect_one();
+        uint32_t it = 0, ita = 0, li = 0;
+        for (int64_t step = blockIdx.x; step < nsteps; step += gridDim.x, ++li) {
+            const uint32_t xbuf = li & 1;
+            mbar_wait_bounded(&bars->x_ready[xbuf], (li >> 1) & 1);
+            tc_fence_after();
+            const uint32_t ah = (((xb_a + xbuf * xbuf_bytes) & 0x3FFFFu) >> 4) | a_lbo;
+            const uint32_t al = ah + (xhi_bytes >> 4);
+            for (int t = 0; t < ntc; ++t, ++ita) {
+                const int a = ita % TC_ASTAGES;
+                const uint32_t aph = (ita / TC_ASTAGES) & 1;
+                mbar_wait_bounded(&bars->a_empty[a], aph ^ 1);
+                const uint32_t dcol = tmem_base + (uint32_t)(a * KM_TC_BN);
+                for (int b = 0; b <= nks; ++b, ++it) {
                     const int s = it % TC_BSTAGES;
                     const uint32_t bph = (it / TC_BSTAGES) & 1;
-                    const int a = it % TC_ASTAGES;
-                    const uint32_t aph = (it / TC_ASTAGES) & 1;
-                    mbar_wait_bounded(&bars->a_empty[a], aph ^ 1);
                     mbar_wait_bounded(&bars->b_full[s], bph);
                     tc_fence_after();
-                    const uint32_t bhi_a = bst_a + s * stage_bytes, blo_a = bhi_a + bhi_bytes;
-#pragma unroll 1
-                    for (int rt = 0; rt < 2; ++rt) {
-                        const uint32_t dcol = tmem_base + (uint32_t)(a * 128 + rt * 64);
-                        const uint32_t ah = xhi_a + rt * xhi_bytes, al = xlo_a + rt * xlo_bytes;
-                        // augmented step first (overwrites the accumulator): + ||c||^2
-                        mma_tf32(dcol, make_smem_desc(ah + (uint32_t)nch * 2048u, 2048u, 128u),
-                                 make_smem_desc(bhi_a + (uint32_t)nch * 1024u, 1024u, 128u), idesc, 0u);
-                        for (int ks = 0; ks < nch / 2; ++ks) {
-                            const uint64_t da_h = make_smem_desc(ah + (uint32_t)ks * 4096u, 2048u, 128u);
-                            const uint64_t da_l = make_smem_desc(al + (uint32_t)ks * 4096u, 2048u, 128u);
-                            const uint64_t db_h = make_smem_desc(bhi_a + (uint32_t)ks * 2048u, 1024u, 128u);
-                            const uint64_t db_l = make_smem_desc(blo_a + (uint32_t)ks * 2048u, 1024u, 128u);
-                            mma_tf32(dcol, da_l, db_h, idesc, 1u);
-                            mma_tf32(dcol, da_h, db_l, idesc, 1u);
-                            mma_tf32(dcol, da_h, db_h, idesc, 1u);
+                    const uint32_t bh = (((bst_a + s * TC_STAGE_BYTES) & 0x3FFFFu) >> 4) | b_lbo;
+                    if (leader) {
+                        if (b == 0) {
+                            // augmented step first (overwrites the accumulator): + ||c||^2
+                            mma_tf32(dcol, ah + (uint32_t)nch * 128u, bh, desc_hi, idesc, 0u);
+                        } else {
+                            const uint32_t ao = (uint32_t)(b - 1) * 256u;
+                            const uint32_t bl = bh + ((uint32_t)(KM_TC_KS_BYTES / 2) >> 4);
+                            mma_tf32(dcol, al + ao, bh, desc_hi, idesc, 1u);
+                            mma_tf32(dcol, ah + ao, bl, desc_hi, idesc, 1u);
+                            mma_tf32(dcol, ah + ao, bh, desc_hi, idesc, 1u);
                         }
+                        mma_commit(&bars->b_empty[s]);  // smem stage reusable once these MMAs retire
+                        if (b == nks) mma_commit(&bars->a_full[a]);  // accumulator ready for the epilogue
                     }
-                    mma_commit(&bars->b_empty[s]);  // smem stage reusable once these MMAs retire
-                    mma_commit(&bars->a_full[a]);   // accumulator stage ready for the epilogue
+                    __syncwarp();
                 }
-                mma_commit(&bars->x_free);  // X tile no longer read by the tensor core
             }
+            if (leader) mma_commit(&bars->x_free[xbuf]);  // X buffer no longer read by the tensor core
+            __syncwarp();
         }
     } else {
         // ================= X staging + epilogue (warps 2..5, 128 threads) =================
         const int q4 = warp & 3;                 // TMEM lane quarter this warp may access
-        const int rl = q4 * 32 + lane;           // row within a row tile == TMEM lane (also staged by this thread)
+        const int rl = q4 * 32 + lane;           // row within the tile == TMEM lane (also staged by this thread)
         const float cmax = __uint_as_float(*cmax_bits);
         const float bound_scale = 2.0f * (float)(d + 8) * 1.1920929e-07f;
-        uint32_t it = 0, fphase = 0;
-        bool first = true;
-        for (int64_t step = blockIdx.x; step < nsteps; step += gridDim.x) {
-            const int64_t row0 = step * TC_ROWS;
-            if (!first) {
-                mbar_wait_bounded(&bars->x_free, fphase);
-                fphase ^= 1;
-            }
-            first = false;
-            // ---- stage both row tiles: this thread owns rows rl and 128+rl of this step ---------------
-            float xn[2];
+        constexpr int NCH_MAX = KM_TC_MAX_D / 4;
+        float xn_buf[2] = {0.f, 0.f};
+
+        // stage the rows of `step` into X buffer `bf`; `use` = how many times that buffer was staged before
+        auto stage = [&](int64_t step, uint32_t bf, uint32_t use) {
+            const int64_t row = step * TC_ROWS + rl;
+            const bool live = row < n;
+            const float *xr = X + (live ? row : 0) * ldx;
+            float4 xv[NCH_MAX];
 #pragma unroll
-            for (int rt = 0; rt < 2; ++rt) {
-                const int64_t row = row0 + rt * 128 + rl;
-                const bool live = row < n;
-                const float *xr = X + (live ? row : 0) * ldx;
-                unsigned char *ph = xhi + (size_t)rt * xhi_bytes + (size_t)rl * 16;
-                unsigned char *pl = xlo + (size_t)rt * xlo_bytes + (size_t)rl * 16;
-                float s = 0.f;
-                for (int c = 0; c < nch; ++c) {
-                    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-                    if (live) {
-                        if (VEC) {
-                            v = __ldg(reinterpret_cast<const float4 *>(xr) + c);
-                        } else {
-                            const int f = c * 4;
-                            v.x = f + 0 < d ? __ldg(xr + f + 0) : 0.f;
-                            v.y = f + 1 < d ? __ldg(xr + f + 1) : 0.f;
-                            v.z = f + 2 < d ? __ldg(xr + f + 2) : 0.f;
-                            v.w = f + 3 < d ? __ldg(xr + f + 3) : 0.f;
-                        }
+            for (int c = 0; c < NCH_MAX; ++c) {
+                float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (c < nch && live) {
+                    if (VEC) {
+                        if (c * 4 < d) v = __ldg(reinterpret_cast<const float4 *>(xr) + c);
+                    } else {
+                        const int f = c * 4;
+                        v.x = f + 0 < d ? __ldg(xr + f + 0) : 0.f;
+                        v.y = f + 1 < d ? __ldg(xr + f + 1) : 0.f;
+                        v.z = f + 2 < d ? __ldg(xr + f + 2) : 0.f;
+                        v.w = f + 3 < d ? __ldg(xr + f + 3) : 0.f;
                     }
+                }
+                xv[c] = v;
+            }
+            if (use > 0) mbar_wait_bounded(&bars->x_free[bf], (use - 1) & 1);  // tensor core done with it
+            unsigned char *ph = xb + (size_t)bf * xbuf_bytes + (size_t)rl * 16;
+            unsigned char *pl = ph + xhi_bytes;
+            float s = 0.f;
+#pragma unroll
+            for (int c = 0; c < NCH_MAX; ++c) {
+                if (c < nch) {
+                    const float4 v = xv[c];
                     s = fmaf(v.x, v.x, s); s = fmaf(v.y, v.y, s); s = fmaf(v.z, v.z, s); s = fmaf(v.w, v.w, s);
                     float4 h, l;
                     h.x = tf32_rna(v.x); h.y = tf32_rna(v.y); h.z = tf32_rna(v.z); h.w = tf32_rna(v.w);
@@ -312,66 +339,90 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
                     *reinterpret_cast<float4 *>(ph + (size_t)c * 2048) = h;
                     *reinterpret_cast<float4 *>(pl + (size_t)c * 2048) = l;
                 }
-                xn[rt] = s;
             }
+            xn_buf[bf] = s;
             km_fence_proxy_async();   // generic-proxy smem writes -> visible to the tensor core (async proxy)
-            mbar_arrive(&bars->x_ready);
+            mbar_arrive(&bars->x_ready[bf]);
+        };
 
-            // ---- epilogue over the column tiles ----------------------------------------------------
-            float best[2] = {INFINITY, INFINITY}, second[2] = {INFINITY, INFINITY};
-            int bidx[2] = {0, 0};
+        uint32_t it = 0, li = 0;
+        if ((int64_t)blockIdx.x < nsteps) stage(blockIdx.x, 0, 0);
+        for (int64_t step = blockIdx.x; step < nsteps; step += gridDim.x, ++li) {
+            const int64_t row0 = step * TC_ROWS;
+            const uint32_t xbuf = li & 1;
+            float best = INFINITY, second = INFINITY;
+            int bidx = 0;
             for (int t = 0; t < ntc; ++t, ++it) {
                 const int a = it % TC_ASTAGES;
                 const uint32_t aph = (it / TC_ASTAGES) & 1;
                 mbar_wait_bounded(&bars->a_full[a], aph);
                 tc_fence_after();
-                const uint32_t tbase = tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(a * 128);
+                const uint32_t tbase = tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(a * KM_TC_BN);
+                uint32_t ra[32], rb[32];
+                tmem_ld32(tbase, ra);
+                tmem_ld_wait();
 #pragma unroll
-                for (int rt = 0; rt < 2; ++rt) {
+                for (int c = 0; c < KM_TC_BN / 32; ++c) {   // 32 columns per chunk
+                    uint32_t (&cur)[32] = (c & 1) ? rb : ra;
+                    uint32_t (&nxt)[32] = (c & 1) ? ra : rb;
+                    if (c + 1 < KM_TC_BN / 32) tmem_ld32(tbase + (uint32_t)((c + 1) * 32), nxt);  // flies under this chunk
+                    const float before = best;
+                    int jloc = 0;
 #pragma unroll
-                    for (int h = 0; h < 2; ++h) {
-                        uint32_t r[32];
-                        tmem_ld32(tbase + (uint32_t)(rt * 64 + h * 32), r);
-                        tmem_ld_wait();
-                        const int colbase = t * KM_TC_BN + h * 32;
-#pragma unroll
-                        for (int j = 0; j < 32; ++j)
-                            track(__uint_as_float(r[j]), colbase + j, best[rt], second[rt], bidx[rt]);
-                    }
+                    for (int j = 0; j < 32; ++j) track(__uint_as_float(cur[j]), j, best, second, jloc);
+                    bidx = best < before ? t * KM_TC_BN + c * 32 + jloc : bidx;
+                    if (c + 1 < KM_TC_BN / 32) tmem_ld_wait();
                 }
                 tc_fence_before();
                 mbar_arrive(&bars->a_empty[a]);
+                // after the first tile: stage the NEXT step's rows into the other X buffer, so the
+                // tensor core never waits for X at a step boundary
+                if (t == 0 && step + gridDim.x < nsteps) stage(step + gridDim.x, xbuf ^ 1, (li + 1) >> 1);
             }
 
             // ---- winner distance (direct form, fp32), outputs, near-tie flags ---------------------
-#pragma unroll
-            for (int rt = 0; rt < 2; ++rt) {
-                const int64_t row = row0 + rt * 128 + rl;
-                if (row >= n) continue;
-                int bi = bidx[rt];
-                if (bi >= k) bi = k - 1;
-                const unsigned char *ph = xhi + (size_t)rt * xhi_bytes + (size_t)rl * 16;
-                const unsigned char *pl = xlo + (size_t)rt * xlo_bytes + (size_t)rl * 16;
+            const int64_t row = row0 + rl;
+            if (row < n) {
+                const int bi = bidx >= k ? k - 1 : bidx;
                 const float *crow = c32 + (size_t)bi * d;
-                float s = 0.f;
-                for (int c = 0; c < nch; ++c) {
-                    const float4 h = *reinterpret_cast<const float4 *>(ph + (size_t)c * 2048);
-                    const float4 l = *reinterpret_cast<const float4 *>(pl + (size_t)c * 2048);
-                    const float xv[4] = {h.x + l.x, h.y + l.y, h.z + l.z, h.w + l.w};
+                float4 cv[NCH_MAX];
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        const int f = c * 4 + i;
-                        if (f < d) {
-                            const float df = xv[i] - __ldg(crow + f);
-                            s = fmaf(df, df, s);
+                for (int c = 0; c < NCH_MAX; ++c) {
+                    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (c < nch) {
+                        if (VEC) {
+                            if (c * 4 < d) v = __ldg(reinterpret_cast<const float4 *>(crow) + c);
+                        } else {
+                            const int f = c * 4;
+                            v.x = f + 0 < d ? __ldg(crow + f + 0) : 0.f;
+                            v.y = f + 1 < d ? __ldg(crow + f + 1) : 0.f;
+                            v.z = f + 2 < d ? __ldg(crow + f + 2) : 0.f;
+                            v.w = f + 3 < d ? __ldg(crow + f + 3) : 0.f;
                         }
+                    }
+                    cv[c] = v;
+                }
+                const unsigned char *ph = xb + (size_t)xbuf * xbuf_bytes + (size_t)rl * 16;
+                const unsigned char *pl = ph + xhi_bytes;
+                float s = 0.f;
+#pragma unroll
+                for (int c = 0; c < NCH_MAX; ++c) {
+                    if (c < nch) {
+                        const float4 h = *reinterpret_cast<const float4 *>(ph + (size_t)c * 2048);
+                        const float4 l = *reinterpret_cast<const float4 *>(pl + (size_t)c * 2048);
+                        const float4 cc = cv[c];
+                        float df;
+                        df = (h.x + l.x) - cc.x; s = fmaf(df, df, s);
+                        df = (h.y + l.y) - cc.y; s = fmaf(df, df, s);
+                        df = (h.z + l.z) - cc.z; s = fmaf(df, df, s);
+                        df = (h.w + l.w) - cc.w; s = fmaf(df, df, s);
                     }
                 }
                 labels[row] = bi;
                 if (mind2) mind2[row] = s;
                 if (flag_rows) {
-                    const float thr = bound_scale * (xn[rt] + cmax);
-                    if (second[rt] - best[rt] <= thr) {
+                    const float thr = bound_scale * (xn_buf[xbuf] + cmax);
+                    if (second - best <= thr) {
                         const int pos = atomicAdd(flag_count, 1);
                         flag_rows[pos] = (int32_t)row;
                     }
@@ -395,8 +446,8 @@ int km_launch_assign_tc(const float *X, int64_t n, int d, int64_t ldx, const voi
     const unsigned char *pk = static_cast<const unsigned char *>(pack);
     const int kpad = km_tc_kpad(d);
     const int nch = kpad / 4;
-    const size_t smem = 2 * (size_t)(nch + 2) * 128 * 16 + 2 * (size_t)nch * 128 * 16 +
-                        TC_BSTAGES * km_tc_tile_bytes(d) + sizeof(TcBars) + 64;
+    const size_t smem = 2 * ((size_t)(nch + 2) * 128 * 16 + (size_t)nch * 128 * 16) +
+                        (size_t)TC_BSTAGES * TC_STAGE_BYTES + sizeof(TcBars) + 64;
     const bool vec = (d % 4 == 0) && (ldx % 4 == 0) && ((reinterpret_cast<uintptr_t>(X) & 15) == 0);
     static bool attr_v[KM_MAX_DEVICES] = {}, attr_s[KM_MAX_DEVICES] = {};
     if (int rc = km_set_smem_once(assign_tc_f32_kernel<true>, 227 * 1024, attr_v)) return rc;

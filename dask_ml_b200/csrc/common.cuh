@@ -46,15 +46,18 @@ static inline int km_set_smem_once(Kern kern, int bytes, bool *flags) {
 // ---------------------------------------------------------------------------------------------
 constexpr int KM_TILE_N = 128;  // centroid tile width of the tiled assign kernel
 
-// tcgen05 (3xTF32) image: per 64-centroid column tile, chunk-major no-swizzle K-major operand
-//   hi part: (kpad/4 + 2) chunks x 64 rows x 16 B   (last two chunks = augmented K-step carrying ||c||^2)
-//   lo part:  kpad/4      chunks x 64 rows x 16 B
-constexpr int KM_TC_BN = 64;
+// tcgen05 (3xTF32) image of the centres: per 256-centroid column tile a sequence of blocks in the
+// UMMA no-swizzle K-major operand layout ([16-byte K chunk][256 rows][16 B]):
+//   block 0      : aug[2 chunks]                  8192 B  (the K-step that adds ||c||^2)
+//   block 1 + ks : hi[2 chunks] | lo[2 chunks]   16384 B  (K-step ks = 8 features of -2c, TF32 hi / lo parts)
+constexpr int KM_TC_BN = 256;
 constexpr int KM_TC_MAX_D = 64;
+constexpr int KM_TC_AUG_BYTES = 2 * KM_TC_BN * 16;
+constexpr int KM_TC_KS_BYTES = 4 * KM_TC_BN * 16;
 __host__ __device__ inline int km_tc_kpad(int d) { return (d + 7) & ~7; }
-__host__ __device__ inline size_t km_tc_hi_bytes(int d) { return (size_t)KM_TC_BN * 16 * (km_tc_kpad(d) / 4 + 2); }
-__host__ __device__ inline size_t km_tc_lo_bytes(int d) { return (size_t)KM_TC_BN * 16 * (km_tc_kpad(d) / 4); }
-__host__ __device__ inline size_t km_tc_tile_bytes(int d) { return km_tc_hi_bytes(d) + km_tc_lo_bytes(d); }
+__host__ __device__ inline size_t km_tc_tile_bytes(int d) {
+    return (size_t)KM_TC_AUG_BYTES + (size_t)(km_tc_kpad(d) / 8) * KM_TC_KS_BYTES;
+}
 
 struct KmPackLayout {
     size_t off_hdr;   // int32[4]: k, d, ntiles, magic
