@@ -93,7 +93,6 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
         : "memory");
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
-__device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 
 __device__ __forceinline__ float tf32_rna(float x) {
     uint32_t u;
@@ -301,28 +300,28 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
         constexpr int NCH_MAX = KM_TC_MAX_D / 4;
         float xn_buf[2] = {0.f, 0.f};
 
-        // stage the rows of `step` into X buffer `bf`; `use` = how many times that buffer was staged before
-        auto stage = [&](int64_t step, uint32_t bf, uint32_t use) {
-            const int64_t row = step * TC_ROWS + rl;
-            const bool live = row < n;
-            const float *xr = X + (live ? row : 0) * ldx;
-            float4 xv[NCH_MAX];
+        // ---- software-pipelined helpers (loads are issued one epilogue tile before they are used) ----
+        float4 ld[NCH_MAX];                       // in-flight global loads (X rows or a centre row)
+        auto issue_row_loads = [&](const float *src, bool live) {
 #pragma unroll
             for (int c = 0; c < NCH_MAX; ++c) {
                 float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
                 if (c < nch && live) {
                     if (VEC) {
-                        if (c * 4 < d) v = __ldg(reinterpret_cast<const float4 *>(xr) + c);
+                        if (c * 4 < d) v = __ldg(reinterpret_cast<const float4 *>(src) + c);
                     } else {
                         const int f = c * 4;
-                        v.x = f + 0 < d ? __ldg(xr + f + 0) : 0.f;
-                        v.y = f + 1 < d ? __ldg(xr + f + 1) : 0.f;
-                        v.z = f + 2 < d ? __ldg(xr + f + 2) : 0.f;
-                        v.w = f + 3 < d ? __ldg(xr + f + 3) : 0.f;
+                        v.x = f + 0 < d ? __ldg(src + f + 0) : 0.f;
+                        v.y = f + 1 < d ? __ldg(src + f + 1) : 0.f;
+                        v.z = f + 2 < d ? __ldg(src + f + 2) : 0.f;
+                        v.w = f + 3 < d ? __ldg(src + f + 3) : 0.f;
                     }
                 }
-                xv[c] = v;
+                ld[c] = v;
             }
+        };
+        // split ld[] (an X row) into TF32 hi/lo parts in X buffer `bf`; `use` = earlier stagings of that buffer
+        auto stage_store = [&](uint32_t bf, uint32_t use) {
             if (use > 0) mbar_wait_bounded(&bars->x_free[bf], (use - 1) & 1);  // tensor core done with it
             unsigned char *ph = xb + (size_t)bf * xbuf_bytes + (size_t)rl * 16;
             unsigned char *pl = ph + xhi_bytes;
@@ -330,7 +329,7 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
 #pragma unroll
             for (int c = 0; c < NCH_MAX; ++c) {
                 if (c < nch) {
-                    const float4 v = xv[c];
+                    const float4 v = ld[c];
                     s = fmaf(v.x, v.x, s); s = fmaf(v.y, v.y, s); s = fmaf(v.z, v.z, s); s = fmaf(v.w, v.w, s);
                     float4 h, l;
                     h.x = tf32_rna(v.x); h.y = tf32_rna(v.y); h.z = tf32_rna(v.z); h.w = tf32_rna(v.w);
@@ -344,15 +343,61 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
             km_fence_proxy_async();   // generic-proxy smem writes -> visible to the tensor core (async proxy)
             mbar_arrive(&bars->x_ready[bf]);
         };
+        // pending result of the previous step (its outputs are written one tile into the next step)
+        bool pend = false;
+        int64_t p_row = 0;
+        int p_bi = 0;
+        uint32_t p_buf = 0;
+        float p_best = 0.f, p_second = 0.f;
+        // winner distance (direct form, fp32) from ld[] (= centre row), outputs, near-tie flag
+        auto output_pending = [&]() {
+            const unsigned char *ph = xb + (size_t)p_buf * xbuf_bytes + (size_t)rl * 16;
+            const unsigned char *pl = ph + xhi_bytes;
+            float s = 0.f;
+#pragma unroll
+            for (int c = 0; c < NCH_MAX; ++c) {
+                if (c < nch) {
+                    const float4 h = *reinterpret_cast<const float4 *>(ph + (size_t)c * 2048);
+                    const float4 l = *reinterpret_cast<const float4 *>(pl + (size_t)c * 2048);
+                    const float4 cc = ld[c];
+                    float df;
+                    df = (h.x + l.x) - cc.x; s = fmaf(df, df, s);
+                    df = (h.y + l.y) - cc.y; s = fmaf(df, df, s);
+                    df = (h.z + l.z) - cc.z; s = fmaf(df, df, s);
+                    df = (h.w + l.w) - cc.w; s = fmaf(df, df, s);
+                }
+            }
+            labels[p_row] = p_bi;
+            if (mind2) mind2[p_row] = s;
+            if (flag_rows) {
+                const float thr = bound_scale * (xn_buf[p_buf] + cmax);
+                if (p_second - p_best <= thr) {
+                    const int pos = atomicAdd(flag_count, 1);
+                    flag_rows[pos] = (int32_t)p_row;
+                }
+            }
+        };
 
         uint32_t it = 0, li = 0;
-        if ((int64_t)blockIdx.x < nsteps) stage(blockIdx.x, 0, 0);
+        if ((int64_t)blockIdx.x < nsteps) {
+            const int64_t row = (int64_t)blockIdx.x * TC_ROWS + rl;
+            issue_row_loads(X + (row < n ? row : 0) * ldx, row < n);
+            stage_store(0, 0);
+        }
+        const int t_stage = ntc > 1 ? 1 : 0;   // tile after which the NEXT step's rows are staged
         for (int64_t step = blockIdx.x; step < nsteps; step += gridDim.x, ++li) {
             const int64_t row0 = step * TC_ROWS;
             const uint32_t xbuf = li & 1;
+            const bool have_next = step + gridDim.x < nsteps;
+            const int64_t nrow = (step + gridDim.x) * TC_ROWS + rl;
             float best = INFINITY, second = INFINITY;
             int bidx = 0;
             for (int t = 0; t < ntc; ++t, ++it) {
+                // loads issued here land while this tile's scores are being tracked
+                if (t == 0 && pend) issue_row_loads(c32 + (size_t)p_bi * d, true);
+                if (t == t_stage && have_next && !(t == 0 && pend))
+                    issue_row_loads(X + (nrow < n ? nrow : 0) * ldx, nrow < n);
+
                 const int a = it % TC_ASTAGES;
                 const uint32_t aph = (it / TC_ASTAGES) & 1;
                 mbar_wait_bounded(&bars->a_full[a], aph);
@@ -375,59 +420,28 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
                 }
                 tc_fence_before();
                 mbar_arrive(&bars->a_empty[a]);
-                // after the first tile: stage the NEXT step's rows into the other X buffer, so the
-                // tensor core never waits for X at a step boundary
-                if (t == 0 && step + gridDim.x < nsteps) stage(step + gridDim.x, xbuf ^ 1, (li + 1) >> 1);
-            }
 
-            // ---- winner distance (direct form, fp32), outputs, near-tie flags ---------------------
-            const int64_t row = row0 + rl;
-            if (row < n) {
-                const int bi = bidx >= k ? k - 1 : bidx;
-                const float *crow = c32 + (size_t)bi * d;
-                float4 cv[NCH_MAX];
-#pragma unroll
-                for (int c = 0; c < NCH_MAX; ++c) {
-                    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-                    if (c < nch) {
-                        if (VEC) {
-                            if (c * 4 < d) v = __ldg(reinterpret_cast<const float4 *>(crow) + c);
-                        } else {
-                            const int f = c * 4;
-                            v.x = f + 0 < d ? __ldg(crow + f + 0) : 0.f;
-                            v.y = f + 1 < d ? __ldg(crow + f + 1) : 0.f;
-                            v.z = f + 2 < d ? __ldg(crow + f + 2) : 0.f;
-                            v.w = f + 3 < d ? __ldg(crow + f + 3) : 0.f;
-                        }
-                    }
-                    cv[c] = v;
+                if (t == 0 && pend) {          // previous step's outputs (its X buffer is still intact)
+                    output_pending();
+                    pend = false;
+                    if (t_stage == 0 && have_next) issue_row_loads(X + (nrow < n ? nrow : 0) * ldx, nrow < n);
                 }
-                const unsigned char *ph = xb + (size_t)xbuf * xbuf_bytes + (size_t)rl * 16;
-                const unsigned char *pl = ph + xhi_bytes;
-                float s = 0.f;
-#pragma unroll
-                for (int c = 0; c < NCH_MAX; ++c) {
-                    if (c < nch) {
-                        const float4 h = *reinterpret_cast<const float4 *>(ph + (size_t)c * 2048);
-                        const float4 l = *reinterpret_cast<const float4 *>(pl + (size_t)c * 2048);
-                        const float4 cc = cv[c];
-                        float df;
-                        df = (h.x + l.x) - cc.x; s = fmaf(df, df, s);
-                        df = (h.y + l.y) - cc.y; s = fmaf(df, df, s);
-                        df = (h.z + l.z) - cc.z; s = fmaf(df, df, s);
-                        df = (h.w + l.w) - cc.w; s = fmaf(df, df, s);
-                    }
-                }
-                labels[row] = bi;
-                if (mind2) mind2[row] = s;
-                if (flag_rows) {
-                    const float thr = bound_scale * (xn_buf[xbuf] + cmax);
-                    if (second - best <= thr) {
-                        const int pos = atomicAdd(flag_count, 1);
-                        flag_rows[pos] = (int32_t)row;
-                    }
-                }
+                // stage the NEXT step's rows into the other X buffer (free: the previous step is written out),
+                // so the tensor core never waits for X at a step boundary
+                if (t == t_stage && have_next) stage_store(xbuf ^ 1, (li + 1) >> 1);
             }
+            if (row0 + rl < n) {
+                pend = true;
+                p_row = row0 + rl;
+                p_bi = bidx >= k ? k - 1 : bidx;
+                p_buf = xbuf;
+                p_best = best;
+                p_second = second;
+            }
+        }
+        if (pend) {
+            issue_row_loads(c32 + (size_t)p_bi * d, true);
+            output_pending();
         }
     }
 

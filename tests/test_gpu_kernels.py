@@ -51,12 +51,49 @@ def _check_assign(eng, X, C, expect_flags=None):
     return got, eng.flagged_count() if X.dtype == np.float32 else 0
 
 
+@pytest.mark.parametrize("variant", [1, 2], ids=["ffma", "tcgen05"])
 @pytest.mark.parametrize("n,d,k", [(5000, 64, 1024), (3001, 32, 256), (777, 20, 150), (1000, 128, 300),
-                                    (513, 7, 33), (128, 4, 17), (4096, 16, 129), (1, 8, 40), (300, 36, 128)])
-def test_assign_f32_tiled(eng, n, d, k):
+                                    (513, 7, 33), (128, 4, 17), (4096, 16, 129), (1, 8, 40), (300, 36, 128),
+                                    (40000, 64, 257), (129, 64, 600), (20000, 48, 2000), (2500, 13, 70)])
+def test_assign_f32_tiled(eng, n, d, k, variant):
+    """Both K1 float32 kernels (FP32 FFMA tiles; tcgen05 3xTF32 with TMEM accumulators, d <= 64)."""
     X, C = blobs(n, d, k, seed=n + d + k, dtype=np.float32)
     init = (C + 0.3 * np.random.RandomState(1).standard_normal(C.shape))
-    _check_assign(eng, X, init)
+    eng.lib.b200km_set_option(1, variant)
+    try:
+        _check_assign(eng, X, init)
+    finally:
+        eng.lib.b200km_set_option(1, 0)
+
+
+@pytest.mark.parametrize("n,d,k", [(3000, 64, 512), (2000, 32, 100)])
+def test_assign_variants_agree_without_refine(eng, n, d, k):
+    """The two float32 kernels must flag every row on which they could disagree: after removing the
+    flagged rows of either kernel their raw (un-refined) labels are identical."""
+    import torch
+
+    X, C = blobs(n, d, k, seed=11, dtype=np.float32)
+    C = C + 0.5 * np.random.RandomState(2).standard_normal(C.shape)   # split blobs -> many near ties
+    Xd = eng.to_device(X)
+    pack = eng.pack(eng.to_device(C, torch.float64))
+    out = {}
+    for variant in (1, 2):
+        eng.lib.b200km_set_option(1, variant)
+        try:
+            labels = torch.empty(n, dtype=torch.int32, device=eng.device)
+            flags = torch.zeros(n, dtype=torch.int32, device=eng.device)
+            cnt = torch.zeros(1, dtype=torch.int32, device=eng.device)
+            eng._call("b200km_assign_f32", Xd.data_ptr(), n, d, d, pack.buf.data_ptr(), k, labels.data_ptr(), None,
+                      flags.data_ptr(), cnt.data_ptr(), 1, eng._stream())
+            c = int(cnt.item())
+            out[variant] = (labels.cpu().numpy(), set(flags[:c].cpu().numpy().tolist()))
+        finally:
+            eng.lib.b200km_set_option(1, 0)
+    flagged = out[1][1] | out[2][1]
+    keep = np.array([i not in flagged for i in range(n)])
+    ref, _ = orc.pairwise_distances_argmin_min(X, C)
+    npt.assert_array_equal(out[1][0][keep], ref[keep])
+    npt.assert_array_equal(out[2][0][keep], ref[keep])
 
 
 @pytest.mark.parametrize("n,d,k", [(4000, 16, 8), (999, 3, 2), (2000, 32, 16), (500, 200, 40), (700, 64, 5), (50, 2, 1)])
