@@ -475,3 +475,65 @@ extern "C" int b200km_refine_f64(const float *X, int64_t n, int d, int64_t ldx, 
     const double *c64 = reinterpret_cast<const double *>(static_cast<const unsigned char *>(pack) + L.off_c64);
     return launch_rb<float, 32, 8, 8, true>(X, n, d, ldx, c64, k, flag_rows, flag_count, labels, mind2, st);
 }
+
+// =============================================================================================
+// b200km_assign_static_f32 -- K1 with every byte of scratch inside the library
+// =============================================================================================
+// The regular path needs caller-allocated device scratch: the centre pack (b200km_pack_bytes) and
+// an n-entry list for the rows that go to the float64 re-decision.  This variant keeps both in the
+// array below, so a caller that owns nothing but its input and output buffers can still label rows:
+// a plugin whose host framework owns all device memory and hands it exactly those buffers, a
+// latency-critical service thread that must stay out of cudaMalloc (it synchronises the device),
+// or a process that has already spent its device-memory budget.
+//
+// In HOST code `g_static_scratch` is only a stand-in for the symbol, not a device address:
+// handing it to a kernel would fault (or, where the GPU can reach host memory, silently touch
+// the wrong bytes).  The device address comes from cudaGetSymbolAddress, fetched once per device
+// with that device current, and only that pointer is passed on.
+constexpr size_t KM_STATIC_PACK_BYTES = B200KM_STATIC_MAX_PACK_BYTES;
+constexpr size_t KM_STATIC_FLAG_BYTES = sizeof(int32_t) * (size_t)B200KM_STATIC_MAX_ROWS;
+constexpr size_t KM_STATIC_BYTES = KM_STATIC_PACK_BYTES + KM_STATIC_FLAG_BYTES + 256;  // + counter slot
+
+static __device__ __align__(256) unsigned char g_static_scratch[KM_STATIC_BYTES];
+
+static unsigned char *g_static_ptr[KM_MAX_DEVICES] = {};
+
+// Device address of the scratch array for the CURRENT device (looked up on the first call per device).
+static int km_static_scratch(unsigned char **out) {
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return (int)e;
+    if (dev < 0 || dev >= KM_MAX_DEVICES) return B200KM_ETOOBIG;
+    if (!g_static_ptr[dev]) {
+        void *p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_static_scratch);
+        if (e != cudaSuccess) return (int)e;
+        g_static_ptr[dev] = static_cast<unsigned char *>(p);
+    }
+    *out = g_static_ptr[dev];
+    return 0;
+}
+
+extern "C" int b200km_assign_static_f32(const float *X, int64_t n, int d, int64_t ldx, const double *centers_f64,
+                                        int k, int32_t *labels, float *mind2, void *stream) {
+    KM_CHECK_ARG(X && centers_f64 && labels, B200KM_EINVAL);
+    KM_CHECK_ARG(n > 0 && d > 0 && k > 0 && ldx >= d, B200KM_EINVAL);
+    KM_CHECK_ARG(k <= B200KM_MAX_K && d <= B200KM_MAX_D, B200KM_ETOOBIG);
+    // the two limits of the built-in scratch
+    if (n > (int64_t)B200KM_STATIC_MAX_ROWS) return B200KM_ESTATICROWS;
+    if (km_pack_layout(k, d).total > KM_STATIC_PACK_BYTES) return B200KM_ESTATICPACK;
+    unsigned char *base = nullptr;
+    int rc = km_static_scratch(&base);
+    if (rc) return rc;
+    unsigned char *pack = base;
+    int32_t *flag_rows = reinterpret_cast<int32_t *>(base + KM_STATIC_PACK_BYTES);
+    int32_t *flag_count = reinterpret_cast<int32_t *>(base + KM_STATIC_PACK_BYTES + KM_STATIC_FLAG_BYTES);
+    // The array keeps whatever the previous call left: the pack is rewritten in full here and the flag
+    // counter is zeroed by b200km_assign_f32 (reset_flags = 1); stale flag_rows entries beyond the new
+    // count are never read.
+    rc = b200km_pack_centers(centers_f64, k, d, pack, stream);
+    if (rc) return rc;
+    rc = b200km_assign_f32(X, n, d, ldx, pack, k, labels, mind2, flag_rows, flag_count, 1, stream);
+    if (rc) return rc;
+    return b200km_refine_f64(X, n, d, ldx, pack, k, flag_rows, flag_count, labels, mind2, stream);
+}

@@ -259,6 +259,12 @@ extern "C" const char *b200km_error_string(int code) {
         case B200KM_ETOOBIG: return "b200km: size beyond the supported maximum";
         case B200KM_EALIGN: return "b200km: pointer or leading dimension not aligned as documented";
         case B200KM_ECAPACITY: return "b200km: output list capacity exceeded";
+        case B200KM_ESTATICROWS:
+            return "b200km_assign_static_f32: more rows than the built-in scratch holds (B200KM_STATIC_MAX_ROWS = "
+                   "1048576); call it per row slab or use b200km_assign_f32 with your own scratch";
+        case B200KM_ESTATICPACK:
+            return "b200km_assign_static_f32: k and d need a centre pack larger than the built-in "
+                   "B200KM_STATIC_MAX_PACK_BYTES (2 MiB); use b200km_pack_centers + b200km_assign_f32";
         default: break;
     }
     if (code > 0) return cudaGetErrorString((cudaError_t)code);

@@ -35,6 +35,8 @@ extern "C" {
 #define B200KM_ETOOBIG (-2)    /* k or d beyond what the kernels support                  */
 #define B200KM_EALIGN (-3)     /* pointer / ldx not aligned as documented                 */
 #define B200KM_ECAPACITY (-4)  /* an output list overflowed its capacity (count is valid) */
+#define B200KM_ESTATICROWS (-5) /* b200km_assign_static_f32: n > B200KM_STATIC_MAX_ROWS             */
+#define B200KM_ESTATICPACK (-6) /* b200km_assign_static_f32: k, d need more than the built-in pack  */
 
 /* dtype tags */
 #define B200KM_F32 0
@@ -92,6 +94,25 @@ int b200km_assign_f64(const double *X, int64_t n, int d, int64_t ldx, const void
 int b200km_refine_f64(const float *X, int64_t n, int d, int64_t ldx, const void *pack, int k,
                       const int32_t *flag_rows, const int32_t *flag_count, int32_t *labels,
                       float *mind2, void *stream);
+
+/* K1 without caller-provided scratch.  No counterpart in the reference (it has no device memory to
+ * manage); it exists for callers that cannot allocate on the device: plugins confined to the buffers
+ * their host framework hands them, latency-critical threads that must stay out of cudaMalloc (which
+ * synchronises the device), processes whose device-memory budget is already spent.  Same results as b200km_pack_centers + b200km_assign_f32 +
+ * b200km_refine_f64 (labels int32, mind2 nullable), but the centre pack and the re-decision list
+ * live in a fixed array inside the library -- B200KM_STATIC_MAX_PACK_BYTES + 4 * B200KM_STATIC_MAX_ROWS
+ * bytes (6 MiB) of device memory that every GPU loading the library holds until the process exits.
+ *   Limits: n <= B200KM_STATIC_MAX_ROWS (else B200KM_ESTATICROWS; label a larger X in row slabs) and
+ *   b200km_pack_bytes(k, d) <= B200KM_STATIC_MAX_PACK_BYTES (else B200KM_ESTATICPACK; e.g. k = 1024,
+ *   d = 64 fits, k = 8192, d = 128 does not).
+ *   It never calls cudaMalloc / cudaFree or any allocating routine.  The FIRST call on each device looks
+ *   the array's address up (cudaGetSymbolAddress, that device current): make that call before any
+ *   stream capture begins.  All calls on a device share the one array: two calls whose kernels can
+ *   overlap on the GPU (different streams, no ordering) race on it -- serialise them. */
+#define B200KM_STATIC_MAX_ROWS (1 << 20)
+#define B200KM_STATIC_MAX_PACK_BYTES (2 << 20)
+int b200km_assign_static_f32(const float *X, int64_t n, int d, int64_t ldx, const double *centers_f64,
+                             int k, int32_t *labels, float *mind2, void *stream);
 
 /* ------------------------------------------------------------------------------------------
  * K2  per-cluster sum and count (+ inertia = sum of mind2).
