@@ -280,10 +280,21 @@ class CudaEngine:
 
 
 _engines = {}
+_override = None
+
+
+def set_engine_override(engine) -> None:
+    """TEST HOOK ONLY: make ``get_engine`` return ``engine`` (an object with the CudaEngine interface)
+    so the host drivers and the collective plumbing can be exercised on CPU with gloo.  The product
+    never sets it; ``None`` restores the CUDA engine."""
+    global _override
+    _override = engine
 
 
 def get_engine(device=None) -> CudaEngine:
     """Per-device engine singleton.  Raises (never falls back) without CUDA / the library."""
+    if _override is not None:
+        return _override
     key = str(device) if device is not None else (f"cuda:{torch.cuda.current_device()}" if torch.cuda.is_available() else "none")
     eng = _engines.get(key)
     if eng is None:

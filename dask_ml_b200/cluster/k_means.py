@@ -199,7 +199,8 @@ def k_means(X, n_clusters, init="k-means||", precompute_distances="auto", n_init
 # initialisation
 # ---------------------------------------------------------------------------------------------
 def _as_device_matrix(X) -> torch.Tensor:
-    if isinstance(X, torch.Tensor) and X.is_cuda and X.dim() == 2 and X.dtype in (torch.float32, torch.float64):
+    if isinstance(X, torch.Tensor) and X.dim() == 2 and X.dtype in (torch.float32, torch.float64) and \
+            X.device == torch.device(get_engine().device):
         return X
     return _dev(X)
 
