@@ -43,12 +43,14 @@ UNIT = "points/s"
 
 
 def _peaks():
+    """(HBM GB/s, dense bf16 TFLOP/s burst, sustained, source) -- driver-measured, else the recipe's fallback."""
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
             p = json.load(f)
-        return float(p["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+        return (float(p["hbm_gbs"]), float(p["bf16_tflops"]), float(p.get("bf16_tflops_sustained", p["bf16_tflops"])),
+                "measured (MEASURED_PEAKS.json)")
     except Exception:
-        return 6650.0, "fallback (B200_PROFILING.md)"
+        return 6650.0, 1590.0, 1400.0, "fallback (B200_PROFILING.md)"
 
 
 class ClockSampler:
@@ -198,6 +200,7 @@ def run_ours(args):
     from dask_ml_b200.cluster import KMeans
 
     eng = get_engine()
+    eng.lib.b200km_set_option(1, {"auto": 0, "ffma": 1, "tc": 2}[args.k1])
     comm = _comm.default_comm()
     dev = eng.device
     n_local, d, k, dtype_s, desc = WORKLOADS[args.workload]
@@ -276,12 +279,14 @@ def run_ours(args):
         return
 
     # ---- roofline of the dominant kernel (K1), measured live -----------------------------------
-    hbm_peak, peak_src = _peaks()
+    hbm_peak, bf16_peak, bf16_sust, peak_src = _peaks()
     k1_avg_ms = sum(k1_ms) / len(k1_ms)
     flops = 2.0 * n_local * k * d
     bytes_alg = n_local * (d * esize + 4)
     roof = {"kernel": "assign (K1)", "traffic": None}
-    k1_is_ffma = dtype_s == "float32" and k > 16 and d <= 128
+    variant = eng.lib.b200km_get_option(1)
+    k1_is_tc = dtype_s == "float32" and k > 16 and d <= 64 and variant != 1
+    k1_is_ffma = dtype_s == "float32" and k > 16 and d <= 128 and not k1_is_tc
     # FP32 / FP64 pipe peak measured here with the FMA probe (MEASURED_PEAKS.json has HBM + bf16 only)
     sink = torch.zeros(8, dtype=tdtype, device=dev)
     probe = "b200km_probe_ffma" if dtype_s == "float32" else "b200km_probe_dfma"
@@ -295,9 +300,24 @@ def run_ours(args):
         torch.cuda.synchronize()
         best = max(best, 2.0 * 64 * iters * 148 * 2 * 1024 / (pe0.elapsed_time(pe1) * 1e-3) / 1e12)
     fma_peak = best
-    if k1_is_ffma:
+    if k1_is_tc:
+        # tcgen05 kind::tf32 runs at half the bf16 rate; the 3xTF32 scheme executes (3d+8)/d TF32 flops per
+        # algorithmic flop (hi.hi + hi.lo + lo.hi, plus the K-step that adds ||c||^2)
+        kpad = (d + 7) // 8 * 8
+        overhead = (3.0 * kpad + 8.0) / d
         ach = flops / (k1_avg_ms * 1e-3) / 1e12
-        roof.update({"bound": "fp32_ffma_pipe", "achieved": ach, "peak": fma_peak, "unit": "TFLOP/s",
+        peak = bf16_peak / 2.0 / overhead
+        roof.update({"kernel": "assign_tc_f32_kernel (K1, tcgen05 3xTF32, TMEM accumulators)",
+                     "bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
+                     "peak_source": f"{peak_src}: dense bf16 burst {bf16_peak:.0f} TFLOP/s / 2 (TF32 rate) / "
+                                    f"{overhead:.3f} (TF32 flops executed per algorithmic 2Nkd flop)",
+                     "executed_tf32_tflops": ach * overhead,
+                     "frac_of_sustained_peak": ach / (bf16_sust / 2.0 / overhead),
+                     "fp32_ffma_pipe_peak_tflops": fma_peak,
+                     "hbm_frac": bytes_alg / (k1_avg_ms * 1e-3) / 1e9 / hbm_peak})
+    elif k1_is_ffma:
+        ach = flops / (k1_avg_ms * 1e-3) / 1e12
+        roof.update({"kernel": "assign_tiled_f32_kernel (K1, FP32 FFMA)", "bound": "fp32_ffma_pipe", "achieved": ach, "peak": fma_peak, "unit": "TFLOP/s",
                      "frac": ach / fma_peak,
                      "peak_source": "FFMA probe kernel (b200km_probe_ffma) timed in this run; nominal 148 SM x 128 "
                                     "x 2 x 1.965 GHz = 74.5",
@@ -381,6 +401,7 @@ def main():
     ap.add_argument("--ref-rows", type=int, default=0)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--k1", default="auto", choices=["auto", "ffma", "tc"], help="K1 kernel variant (float32)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":
