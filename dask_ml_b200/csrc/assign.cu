@@ -279,9 +279,14 @@ constexpr int RB_DC = 128;  // feature chunk
 
 template <typename TX, int R, int G, int JB, bool INDIRECT>
 __global__ void __launch_bounds__(R *G)
-assign_rb_kernel(const TX *__restrict__ X, int64_t n, int d, int64_t ldx, const double *__restrict__ c64, int k,
+assign_rb_kernel(const TX *__restrict__ X, int64_t n, int d, int64_t ldx, const double *__restrict__ c64,
+                 const double *__restrict__ cn64, int k,
                  const int32_t *__restrict__ rows, const int32_t *__restrict__ nrows_ptr,
                  int32_t *__restrict__ labels, TX *__restrict__ mind2) {
+    // INDIRECT (the refine kernel) decides on the expanded form ||c||^2 - 2 x.c in float64 -- one DFMA per
+    // term, the same arithmetic sklearn's ArgKmin uses -- and recomputes only the winner's distance in
+    // direct form; the direct kernels accumulate (x-c)^2 throughout.
+    constexpr bool NORMFORM = INDIRECT;
     extern __shared__ __align__(16) double smem_d[];
     const int dc_max = d < RB_DC ? d : RB_DC;
     const int xld = dc_max + 1;
@@ -330,15 +335,22 @@ assign_rb_kernel(const TX *__restrict__ X, int64_t n, int d, int64_t ldx, const 
                     const double xv = xr[f];
 #pragma unroll
                     for (int j = 0; j < JB; ++j) {
-                        const double df = xv - cr[(size_t)j * dc_max + f];
-                        acc[j] = fma(df, df, acc[j]);
+                        if (NORMFORM) {
+                            acc[j] = fma(xv, cr[(size_t)j * dc_max + f], acc[j]);
+                        } else {
+                            const double df = xv - cr[(size_t)j * dc_max + f];
+                            acc[j] = fma(df, df, acc[j]);
+                        }
                     }
                 }
             }
 #pragma unroll
             for (int j = 0; j < JB; ++j) {
                 const int col = c0 + g * JB + j;
-                if (col < k && acc[j] < best) { best = acc[j]; bidx = col; }
+                if (col < k) {
+                    const double sc = NORMFORM ? fma(-2.0, acc[j], __ldg(cn64 + col)) : acc[j];
+                    if (sc < best) { best = sc; bidx = col; }
+                }
             }
         }
         if (G > 1) {
@@ -357,13 +369,26 @@ assign_rb_kernel(const TX *__restrict__ X, int64_t n, int d, int64_t ldx, const 
         if (g == 0 && base + r < nrows) {
             const int64_t row = INDIRECT ? (int64_t)rows[base + r] : base + r;
             labels[row] = bidx;
-            if (mind2) mind2[row] = (TX)best;
+            if (mind2) {
+                if (NORMFORM) {
+                    const TX *xr = X + row * ldx;
+                    const double *cr = c64 + (size_t)bidx * d;
+                    double s = 0.0;
+                    for (int f = 0; f < d; ++f) {
+                        const double df = (double)xr[f] - cr[f];
+                        s = fma(df, df, s);
+                    }
+                    best = s;
+                }
+                mind2[row] = (TX)best;
+            }
         }
     }
 }
 
 template <typename TX, int R, int G, int JB, bool INDIRECT>
-static int launch_rb(const TX *X, int64_t n, int d, int64_t ldx, const double *c64, int k, const int32_t *rows,
+static int launch_rb(const TX *X, int64_t n, int d, int64_t ldx, const double *c64, const double *cn64, int k,
+                     const int32_t *rows,
                      const int32_t *nrows_ptr, int32_t *labels, TX *mind2, cudaStream_t st) {
     const int dc_max = d < RB_DC ? d : RB_DC;
     const size_t smem = sizeof(double) * ((size_t)R * (dc_max + 1) + (size_t)G * JB * dc_max + (size_t)G * R) +
@@ -375,7 +400,7 @@ static int launch_rb(const TX *X, int64_t n, int d, int64_t ldx, const double *c
     const int64_t cap = (int64_t)KM_NUM_SMS * 8;
     if (INDIRECT || blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
-    kern<<<(unsigned)blocks, R * G, smem, st>>>(X, n, d, ldx, c64, k, rows, nrows_ptr, labels, mind2);
+    kern<<<(unsigned)blocks, R * G, smem, st>>>(X, n, d, ldx, c64, cn64, k, rows, nrows_ptr, labels, mind2);
     KM_LAUNCH_RET();
 }
 
@@ -427,10 +452,10 @@ extern "C" int b200km_assign_f32(const float *X, int64_t n, int d, int64_t ldx, 
     const double *c64 = reinterpret_cast<const double *>(pk + L.off_c64);
     if (k <= 16 && d <= 32) {
         // HBM-bound regime: fp64 arithmetic is free here, so no flags are ever needed.
-        return launch_rb<float, 256, 1, 8, false>(X, n, d, ldx, c64, k, nullptr, nullptr, labels, mind2, st);
+        return launch_rb<float, 256, 1, 8, false>(X, n, d, ldx, c64, nullptr, k, nullptr, nullptr, labels, mind2, st);
     }
     if (d > 128 || k <= 16) {
-        return launch_rb<float, 32, 8, 8, false>(X, n, d, ldx, c64, k, nullptr, nullptr, labels, mind2, st);
+        return launch_rb<float, 32, 8, 8, false>(X, n, d, ldx, c64, nullptr, k, nullptr, nullptr, labels, mind2, st);
     }
     if (use_tc_path(d, k)) return km_launch_assign_tc(X, n, d, ldx, pack, k, labels, mind2, flag_rows, flag_count, st);
     const int ntiles = (k + KM_TILE_N - 1) / KM_TILE_N;
@@ -460,8 +485,8 @@ extern "C" int b200km_assign_f64(const double *X, int64_t n, int d, int64_t ldx,
     const KmPackLayout L = km_pack_layout(k, d);
     const double *c64 = reinterpret_cast<const double *>(static_cast<const unsigned char *>(pack) + L.off_c64);
     if (k <= 16 && d <= 32)
-        return launch_rb<double, 256, 1, 8, false>(X, n, d, ldx, c64, k, nullptr, nullptr, labels, mind2, st);
-    return launch_rb<double, 32, 8, 8, false>(X, n, d, ldx, c64, k, nullptr, nullptr, labels, mind2, st);
+        return launch_rb<double, 256, 1, 8, false>(X, n, d, ldx, c64, nullptr, k, nullptr, nullptr, labels, mind2, st);
+    return launch_rb<double, 32, 8, 8, false>(X, n, d, ldx, c64, nullptr, k, nullptr, nullptr, labels, mind2, st);
 }
 
 extern "C" int b200km_refine_f64(const float *X, int64_t n, int d, int64_t ldx, const void *pack, int k,
@@ -473,7 +498,8 @@ extern "C" int b200km_refine_f64(const float *X, int64_t n, int d, int64_t ldx, 
     cudaStream_t st = km_stream(stream);
     const KmPackLayout L = km_pack_layout(k, d);
     const double *c64 = reinterpret_cast<const double *>(static_cast<const unsigned char *>(pack) + L.off_c64);
-    return launch_rb<float, 32, 8, 8, true>(X, n, d, ldx, c64, k, flag_rows, flag_count, labels, mind2, st);
+    const double *cn64 = reinterpret_cast<const double *>(static_cast<const unsigned char *>(pack) + L.off_cn64);
+    return launch_rb<float, 32, 8, 8, true>(X, n, d, ldx, c64, cn64, k, flag_rows, flag_count, labels, mind2, st);
 }
 
 // =============================================================================================

@@ -107,7 +107,7 @@ __device__ __forceinline__ void track(float v, int j, float &best, float &second
         "max.f32 t, %0, %3;\n\t"
         "min.f32 %1, %1, t;\n\t"
         "min.f32 %0, %0, %3;\n\t"
-        "selp.b32 %2, %4, %2, p;\n\t}"
+        "@p mov.b32 %2, %4;\n\t}"
         : "+f"(best), "+f"(second), "+r"(jloc)
         : "f"(v), "r"(j));
 }
@@ -390,8 +390,9 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
             const uint32_t xbuf = li & 1;
             const bool have_next = step + gridDim.x < nsteps;
             const int64_t nrow = (step + gridDim.x) * TC_ROWS + rl;
-            float best = INFINITY, second = INFINITY;
-            int bidx = 0;
+            // two independent trackers (even / odd columns) double the ILP of the dependent min/max chains
+            float best2[2] = {INFINITY, INFINITY}, second2[2] = {INFINITY, INFINITY};
+            int bidx2[2] = {0, 0};
             for (int t = 0; t < ntc; ++t, ++it) {
                 // loads issued here land while this tile's scores are being tracked
                 if (t == 0 && pend) issue_row_loads(c32 + (size_t)p_bi * d, true);
@@ -411,11 +412,16 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
                     uint32_t (&cur)[32] = (c & 1) ? rb : ra;
                     uint32_t (&nxt)[32] = (c & 1) ? ra : rb;
                     if (c + 1 < KM_TC_BN / 32) tmem_ld32(tbase + (uint32_t)((c + 1) * 32), nxt);  // flies under this chunk
-                    const float before = best;
-                    int jloc = 0;
+                    const float before0 = best2[0], before1 = best2[1];
+                    int jloc0 = 0, jloc1 = 0;
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) track(__uint_as_float(cur[j]), j, best, second, jloc);
-                    bidx = best < before ? t * KM_TC_BN + c * 32 + jloc : bidx;
+                    for (int j = 0; j < 32; j += 2) {
+                        track(__uint_as_float(cur[j]), j, best2[0], second2[0], jloc0);
+                        track(__uint_as_float(cur[j + 1]), j + 1, best2[1], second2[1], jloc1);
+                    }
+                    const int cb = t * KM_TC_BN + c * 32;
+                    bidx2[0] = best2[0] < before0 ? cb + jloc0 : bidx2[0];
+                    bidx2[1] = best2[1] < before1 ? cb + jloc1 : bidx2[1];
                     if (c + 1 < KM_TC_BN / 32) tmem_ld_wait();
                 }
                 tc_fence_before();
@@ -431,6 +437,11 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
                 if (t == t_stage && have_next) stage_store(xbuf ^ 1, (li + 1) >> 1);
             }
             if (row0 + rl < n) {
+                // merge the two trackers (an exact tie keeps the lower column; it is flagged anyway)
+                const bool takeb = best2[1] < best2[0] || (best2[1] == best2[0] && bidx2[1] < bidx2[0]);
+                const float best = takeb ? best2[1] : best2[0];
+                const int bidx = takeb ? bidx2[1] : bidx2[0];
+                const float second = fminf(fminf(second2[0], second2[1]), takeb ? best2[0] : best2[1]);
                 pend = true;
                 p_row = row0 + rl;
                 p_bi = bidx >= k ? k - 1 : bidx;

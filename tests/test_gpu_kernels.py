@@ -143,7 +143,9 @@ def test_assign_strided_rows(eng):
 
 @pytest.mark.parametrize("n,d,k,dtype", [(5000, 16, 8, np.float64), (6000, 32, 256, np.float32),
                                          (3000, 64, 1024, np.float32), (2047, 5, 3, np.float64),
-                                         (1000, 128, 700, np.float32), (900, 33, 40, np.float64)])
+                                         (1000, 128, 700, np.float32), (900, 33, 40, np.float64),
+                                         (40000, 64, 1024, np.float32), (70001, 24, 3000, np.float64),
+                                         (16384 * 3 + 5, 100, 1500, np.float32), (33000, 130, 8192, np.float32)])
 def test_update_and_finalize(eng, n, d, k, dtype):
     import torch
 
