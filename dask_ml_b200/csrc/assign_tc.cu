@@ -9,11 +9,11 @@
 //      + Xaug.Baug^T                         (one extra K-step that adds ||c||^2 exactly)
 // so the epilogue only has to track (best, second, argmin) per row -- no per-element norm add.
 //
-// CTA = 192 threads, persistent, one per SM, 128 rows (one M=128 row tile) per step:
+// CTA = 320 threads, persistent, one per SM, 128 rows (one M=128 row tile) per step:
 //   warp 0      : producer -- one 1-D bulk async copy (TMA, mbarrier complete_tx) per K-step block of a
 //                 256-centroid column tile (16 KB: hi + lo parts of 8 features)
 //   warp 1      : TMEM allocator + tcgen05.mma issue (M=128, N=256, K=8, kind::tf32, one elected lane)
-//   warps 2..5  : X staging (LDG.128 -> cvt.rna.tf32 split -> STS in the UMMA canonical no-swizzle
+//   warps 2..9  : X staging (LDG.128 -> cvt.rna.tf32 split -> STS in the UMMA canonical no-swizzle
 //                 K-major layout, double-buffered so the next step is staged under the current one) and
 //                 the epilogue (tcgen05.ld 32x32b.x32, double-buffered against the argmin tracking)
 // N = 256 per MMA keeps the tensor core's shared-memory operand fetch (A 4 KB + B 8 KB per K-step) below
@@ -23,7 +23,8 @@
 
 namespace {
 
-constexpr int TC_THREADS = 192;
+constexpr int TC_THREADS = 320;   // producer warp + MMA warp + 8 staging/epilogue warps
+constexpr int TC_EPI = 256;       // staging/epilogue threads: 2 per row (column halves)
 constexpr int TC_ROWS = 128;     // rows per CTA step
 constexpr int TC_BSTAGES = 5;    // ring of K-step blocks
 constexpr int TC_STAGE_BYTES = KM_TC_KS_BYTES;
@@ -119,8 +120,17 @@ struct TcBars {
     uint64_t a_empty[TC_ASTAGES];
     uint64_t x_ready[2];
     uint64_t x_free[2];
+    uint64_t m_ready[2];           // both column halves of a step have published their (best, second, argmin)
+    uint64_t s_ready[2];           // the upper half has published its partial winner distance
     uint32_t tmem_base;
     uint32_t pad;
+    // per step buffer [2], per column half [2], per row [128]
+    float m_best[2][2][128];
+    float m_second[2][2][128];
+    int m_idx[2][2][128];
+    float xn_part[2][2][128];
+    float s_part[2][128];
+    float xn_pub[2][128];
 };
 
 }  // namespace
@@ -201,8 +211,13 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
 
     if (tid == 0) {
         for (int i = 0; i < TC_BSTAGES; ++i) { km_mbar_init(&bars->b_full[i], 1); km_mbar_init(&bars->b_empty[i], 1); }
-        for (int i = 0; i < TC_ASTAGES; ++i) { km_mbar_init(&bars->a_full[i], 1); km_mbar_init(&bars->a_empty[i], 128); }
-        for (int i = 0; i < 2; ++i) { km_mbar_init(&bars->x_ready[i], 128); km_mbar_init(&bars->x_free[i], 1); }
+        for (int i = 0; i < TC_ASTAGES; ++i) { km_mbar_init(&bars->a_full[i], 1); km_mbar_init(&bars->a_empty[i], TC_EPI); }
+        for (int i = 0; i < 2; ++i) {
+            km_mbar_init(&bars->x_ready[i], TC_EPI);
+            km_mbar_init(&bars->x_free[i], 1);
+            km_mbar_init(&bars->m_ready[i], TC_EPI);
+            km_mbar_init(&bars->s_ready[i], TC_EPI / 2);
+        }
         km_fence_mbar_init();
     }
     if (warp == 1) {
@@ -292,25 +307,31 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
             __syncwarp();
         }
     } else {
-        // ================= X staging + epilogue (warps 2..5, 128 threads) =================
+        // ================= X staging + epilogue (warps 2..9, 256 threads) =================
+        // Two threads per row: half g = 0 (warps 2..5) owns columns [0,128) of every 256-column tile and the
+        // lower K chunks of the row, half g = 1 (warps 6..9) the rest.  Two warps per scheduler keep the ALU
+        // pipe busy through the dependent min/max chains and the TMEM-load waits of one another.
+        const int g = (warp - 2) >> 2;           // column / K half
         const int q4 = warp & 3;                 // TMEM lane quarter this warp may access
-        const int rl = q4 * 32 + lane;           // row within the tile == TMEM lane (also staged by this thread)
+        const int rl = q4 * 32 + lane;           // row within the tile == TMEM lane
         const float cmax = __uint_as_float(*cmax_bits);
         const float bound_scale = 2.0f * (float)(d + 8) * 1.1920929e-07f;
-        constexpr int NCH_MAX = KM_TC_MAX_D / 4;
-        float xn_buf[2] = {0.f, 0.f};
+        constexpr int NCH_H = KM_TC_MAX_D / 8;   // K chunks per half (max)
+        const int nch_h = nch / 2;               // nch is even (kpad multiple of 8)
+        const int c_lo = g * nch_h;              // first K chunk of this half
 
         // ---- software-pipelined helpers (loads are issued one epilogue tile before they are used) ----
-        float4 ld[NCH_MAX];                       // in-flight global loads (X rows or a centre row)
+        float4 ld[NCH_H];                         // in-flight global loads (half an X row or half a centre row)
         auto issue_row_loads = [&](const float *src, bool live) {
 #pragma unroll
-            for (int c = 0; c < NCH_MAX; ++c) {
+            for (int c = 0; c < NCH_H; ++c) {
                 float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (c < nch && live) {
+                const int cc = c_lo + c;
+                if (c < nch_h && live) {
                     if (VEC) {
-                        if (c * 4 < d) v = __ldg(reinterpret_cast<const float4 *>(src) + c);
+                        if (cc * 4 < d) v = __ldg(reinterpret_cast<const float4 *>(src) + cc);
                     } else {
-                        const int f = c * 4;
+                        const int f = cc * 4;
                         v.x = f + 0 < d ? __ldg(src + f + 0) : 0.f;
                         v.y = f + 1 < d ? __ldg(src + f + 1) : 0.f;
                         v.z = f + 2 < d ? __ldg(src + f + 2) : 0.f;
@@ -320,26 +341,26 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
                 ld[c] = v;
             }
         };
-        // split ld[] (an X row) into TF32 hi/lo parts in X buffer `bf`; `use` = earlier stagings of that buffer
+        // split ld[] (half an X row) into TF32 hi/lo parts in X buffer `bf`; `use` = earlier stagings of it
         auto stage_store = [&](uint32_t bf, uint32_t use) {
             if (use > 0) mbar_wait_bounded(&bars->x_free[bf], (use - 1) & 1);  // tensor core done with it
             unsigned char *ph = xb + (size_t)bf * xbuf_bytes + (size_t)rl * 16;
             unsigned char *pl = ph + xhi_bytes;
             float s = 0.f;
 #pragma unroll
-            for (int c = 0; c < NCH_MAX; ++c) {
-                if (c < nch) {
+            for (int c = 0; c < NCH_H; ++c) {
+                if (c < nch_h) {
                     const float4 v = ld[c];
                     s = fmaf(v.x, v.x, s); s = fmaf(v.y, v.y, s); s = fmaf(v.z, v.z, s); s = fmaf(v.w, v.w, s);
                     float4 h, l;
                     h.x = tf32_rna(v.x); h.y = tf32_rna(v.y); h.z = tf32_rna(v.z); h.w = tf32_rna(v.w);
                     l.x = tf32_rna(v.x - h.x); l.y = tf32_rna(v.y - h.y);
                     l.z = tf32_rna(v.z - h.z); l.w = tf32_rna(v.w - h.w);
-                    *reinterpret_cast<float4 *>(ph + (size_t)c * 2048) = h;
-                    *reinterpret_cast<float4 *>(pl + (size_t)c * 2048) = l;
+                    *reinterpret_cast<float4 *>(ph + (size_t)(c_lo + c) * 2048) = h;
+                    *reinterpret_cast<float4 *>(pl + (size_t)(c_lo + c) * 2048) = l;
                 }
             }
-            xn_buf[bf] = s;
+            bars->xn_part[bf][g][rl] = s;
             km_fence_proxy_async();   // generic-proxy smem writes -> visible to the tensor core (async proxy)
             mbar_arrive(&bars->x_ready[bf]);
         };
@@ -347,18 +368,31 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
         bool pend = false;
         int64_t p_row = 0;
         int p_bi = 0;
-        uint32_t p_buf = 0;
+        uint32_t p_buf = 0, p_use = 0;
         float p_best = 0.f, p_second = 0.f;
-        // winner distance (direct form, fp32) from ld[] (= centre row), outputs, near-tie flag
+        // merge the two column halves of the pending step (both threads of a row compute the same result)
+        auto merge_pending = [&]() {
+            mbar_wait_bounded(&bars->m_ready[p_buf], p_use & 1);
+            const float b0 = bars->m_best[p_buf][0][rl], b1 = bars->m_best[p_buf][1][rl];
+            const float s0 = bars->m_second[p_buf][0][rl], s1 = bars->m_second[p_buf][1][rl];
+            const int i0 = bars->m_idx[p_buf][0][rl], i1 = bars->m_idx[p_buf][1][rl];
+            const bool take1 = b1 < b0 || (b1 == b0 && i1 < i0);
+            p_best = take1 ? b1 : b0;
+            const int bi = take1 ? i1 : i0;
+            p_second = fminf(fminf(s0, s1), take1 ? b0 : b1);
+            p_bi = bi >= k ? k - 1 : bi;
+        };
+        // partial winner distance (direct form, fp32) over this half's K chunks from ld[] (= centre row half);
+        // the upper half publishes its part, the lower half adds it and writes labels / mind2 / near-tie flag
         auto output_pending = [&]() {
             const unsigned char *ph = xb + (size_t)p_buf * xbuf_bytes + (size_t)rl * 16;
             const unsigned char *pl = ph + xhi_bytes;
             float s = 0.f;
 #pragma unroll
-            for (int c = 0; c < NCH_MAX; ++c) {
-                if (c < nch) {
-                    const float4 h = *reinterpret_cast<const float4 *>(ph + (size_t)c * 2048);
-                    const float4 l = *reinterpret_cast<const float4 *>(pl + (size_t)c * 2048);
+            for (int c = 0; c < NCH_H; ++c) {
+                if (c < nch_h) {
+                    const float4 h = *reinterpret_cast<const float4 *>(ph + (size_t)(c_lo + c) * 2048);
+                    const float4 l = *reinterpret_cast<const float4 *>(pl + (size_t)(c_lo + c) * 2048);
                     const float4 cc = ld[c];
                     float df;
                     df = (h.x + l.x) - cc.x; s = fmaf(df, df, s);
@@ -367,13 +401,24 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
                     df = (h.w + l.w) - cc.w; s = fmaf(df, df, s);
                 }
             }
-            labels[p_row] = p_bi;
-            if (mind2) mind2[p_row] = s;
-            if (flag_rows) {
-                const float thr = bound_scale * (xn_buf[p_buf] + cmax);
-                if (p_second - p_best <= thr) {
-                    const int pos = atomicAdd(flag_count, 1);
-                    flag_rows[pos] = (int32_t)p_row;
+            if (g == 1) {
+                bars->s_part[p_buf][rl] = s;
+                bars->xn_pub[p_buf][rl] = bars->xn_part[p_buf][1][rl];   // before this thread restages the buffer
+                mbar_arrive(&bars->s_ready[p_buf]);
+            } else {
+                mbar_wait_bounded(&bars->s_ready[p_buf], p_use & 1);
+                s += bars->s_part[p_buf][rl];
+                if (p_row < n) {
+                    labels[p_row] = p_bi;
+                    if (mind2) mind2[p_row] = s;
+                    if (flag_rows) {
+                        const float xn = bars->xn_part[p_buf][0][rl] + bars->xn_pub[p_buf][rl];
+                        const float thr = bound_scale * (xn + cmax);
+                        if (p_second - p_best <= thr) {
+                            const int pos = atomicAdd(flag_count, 1);
+                            flag_rows[pos] = (int32_t)p_row;
+                        }
+                    }
                 }
             }
         };
@@ -395,7 +440,10 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
             int bidx2[2] = {0, 0};
             for (int t = 0; t < ntc; ++t, ++it) {
                 // loads issued here land while this tile's scores are being tracked
-                if (t == 0 && pend) issue_row_loads(c32 + (size_t)p_bi * d, true);
+                if (t == 0 && pend) {
+                    merge_pending();
+                    issue_row_loads(c32 + (size_t)p_bi * d, true);
+                }
                 if (t == t_stage && have_next && !(t == 0 && pend))
                     issue_row_loads(X + (nrow < n ? nrow : 0) * ldx, nrow < n);
 
@@ -403,15 +451,15 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
                 const uint32_t aph = (it / TC_ASTAGES) & 1;
                 mbar_wait_bounded(&bars->a_full[a], aph);
                 tc_fence_after();
-                const uint32_t tbase = tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(a * KM_TC_BN);
+                const uint32_t tbase = tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(a * KM_TC_BN + g * 128);
                 uint32_t ra[32], rb[32];
                 tmem_ld32(tbase, ra);
                 tmem_ld_wait();
 #pragma unroll
-                for (int c = 0; c < KM_TC_BN / 32; ++c) {   // 32 columns per chunk
+                for (int c = 0; c < 4; ++c) {   // this half's 4 chunks of 32 columns
                     uint32_t (&cur)[32] = (c & 1) ? rb : ra;
                     uint32_t (&nxt)[32] = (c & 1) ? ra : rb;
-                    if (c + 1 < KM_TC_BN / 32) tmem_ld32(tbase + (uint32_t)((c + 1) * 32), nxt);  // flies under this chunk
+                    if (c + 1 < 4) tmem_ld32(tbase + (uint32_t)((c + 1) * 32), nxt);  // flies under this chunk
                     const float before0 = best2[0], before1 = best2[1];
                     int jloc0 = 0, jloc1 = 0;
 #pragma unroll
@@ -419,10 +467,10 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
                         track(__uint_as_float(cur[j]), j, best2[0], second2[0], jloc0);
                         track(__uint_as_float(cur[j + 1]), j + 1, best2[1], second2[1], jloc1);
                     }
-                    const int cb = t * KM_TC_BN + c * 32;
+                    const int cb = t * KM_TC_BN + g * 128 + c * 32;
                     bidx2[0] = best2[0] < before0 ? cb + jloc0 : bidx2[0];
                     bidx2[1] = best2[1] < before1 ? cb + jloc1 : bidx2[1];
-                    if (c + 1 < KM_TC_BN / 32) tmem_ld_wait();
+                    if (c + 1 < 4) tmem_ld_wait();
                 }
                 tc_fence_before();
                 mbar_arrive(&bars->a_empty[a]);
@@ -436,21 +484,21 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
                 // so the tensor core never waits for X at a step boundary
                 if (t == t_stage && have_next) stage_store(xbuf ^ 1, (li + 1) >> 1);
             }
-            if (row0 + rl < n) {
-                // merge the two trackers (an exact tie keeps the lower column; it is flagged anyway)
+            {
+                // publish this half's result (an exact tie keeps the lower column; it is flagged anyway)
                 const bool takeb = best2[1] < best2[0] || (best2[1] == best2[0] && bidx2[1] < bidx2[0]);
-                const float best = takeb ? best2[1] : best2[0];
-                const int bidx = takeb ? bidx2[1] : bidx2[0];
-                const float second = fminf(fminf(second2[0], second2[1]), takeb ? best2[0] : best2[1]);
+                bars->m_best[xbuf][g][rl] = takeb ? best2[1] : best2[0];
+                bars->m_idx[xbuf][g][rl] = takeb ? bidx2[1] : bidx2[0];
+                bars->m_second[xbuf][g][rl] = fminf(fminf(second2[0], second2[1]), takeb ? best2[0] : best2[1]);
+                mbar_arrive(&bars->m_ready[xbuf]);
                 pend = true;
                 p_row = row0 + rl;
-                p_bi = bidx >= k ? k - 1 : bidx;
                 p_buf = xbuf;
-                p_best = best;
-                p_second = second;
+                p_use = li >> 1;
             }
         }
         if (pend) {
+            merge_pending();
             issue_row_loads(c32 + (size_t)p_bi * d, true);
             output_pending();
         }
