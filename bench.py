@@ -318,7 +318,7 @@ def run_ours(args):
     bytes_alg = n_local * (d * esize + 4)
     roof = {"kernel": "assign (K1)", "traffic": None}
     variant = eng.lib.b200km_get_option(1)
-    k1_is_tc = dtype_s == "float32" and k > 16 and d <= 64 and variant != 1
+    k1_is_tc = dtype_s == "float32" and k > 16 and d <= 128 and variant != 1
     k1_is_ffma = dtype_s == "float32" and k > 16 and d <= 128 and not k1_is_tc
     # FP32 / FP64 pipe peak measured here with the FMA probe (MEASURED_PEAKS.json has HBM + bf16 only)
     sink = torch.zeros(8, dtype=tdtype, device=dev)

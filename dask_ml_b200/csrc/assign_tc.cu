@@ -1,6 +1,6 @@
 // assign_tc.cu -- K1 on the 5th-generation tensor cores: 3xTF32 tcgen05.mma with TMEM accumulators.
 //
-// Same contract as assign_tiled_f32_kernel (labels, winner distance, near-tie flags), for d <= 64.
+// Same contract as assign_tiled_f32_kernel (labels, winner distance, near-tie flags), for d <= 128.
 // Replaces dask_ml.metrics.pairwise_distances_argmin_min (reference dask_ml/metrics/pairwise.py:19-47)
 // on the Lloyd path (dask_ml/cluster/k_means.py:576-579) when k*d makes the FFMA pipe the bound.
 //
@@ -186,7 +186,9 @@ int km_launch_pack_tc(int k, int d, void *pack, cudaStream_t st) {
 // ---------------------------------------------------------------------------------------------
 // the kernel
 // ---------------------------------------------------------------------------------------------
-template <bool VEC>
+// DBUF: two X buffers (d <= 64) so the next step's rows are staged under the current step; for
+// 64 < d <= 128 one buffer fills shared memory and staging happens at the step boundary instead.
+template <bool VEC, bool DBUF>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
                      const unsigned char *__restrict__ tc_img, const float *__restrict__ c32,
@@ -201,8 +203,8 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
     const uint32_t xlo_bytes = (uint32_t)nch * 128 * 16;
     const uint32_t xbuf_bytes = xhi_bytes + xlo_bytes;     // one X buffer: hi part then lo part
     const uint32_t tile_bytes = (uint32_t)km_tc_tile_bytes(d);
-    unsigned char *xb = tc_smem;                           // [2][xbuf_bytes]
-    unsigned char *bst = xb + 2 * xbuf_bytes;              // [TC_BSTAGES][TC_STAGE_BYTES]
+    unsigned char *xb = tc_smem;                           // [DBUF ? 2 : 1][xbuf_bytes]
+    unsigned char *bst = xb + (DBUF ? 2 : 1) * xbuf_bytes; // [TC_BSTAGES][TC_STAGE_BYTES]
     TcBars *bars = reinterpret_cast<TcBars *>(bst + TC_BSTAGES * TC_STAGE_BYTES);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -228,7 +230,7 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     // constant augmented chunks of Xhi: chunk nch = [1,1,1,0], chunk nch+1 = 0 (both X buffers)
-    for (int e = tid; e < 2 * 2 * 128; e += TC_THREADS) {
+    for (int e = tid; e < (DBUF ? 2 : 1) * 2 * 128; e += TC_THREADS) {
         const int bf = e / 256, c = (e / 128) & 1, r = e & 127;
         float4 v = c == 0 ? make_float4(1.f, 1.f, 1.f, 0.f) : make_float4(0.f, 0.f, 0.f, 0.f);
         *reinterpret_cast<float4 *>(xb + (size_t)bf * xbuf_bytes + ((size_t)(nch + c) * 128 + r) * 16) = v;
@@ -270,8 +272,8 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
         const bool leader = elect_one();
         uint32_t it = 0, ita = 0, li = 0;
         for (int64_t step = blockIdx.x; step < nsteps; step += gridDim.x, ++li) {
-            const uint32_t xbuf = li & 1;
-            mbar_wait_bounded(&bars->x_ready[xbuf], (li >> 1) & 1);
+            const uint32_t xbuf = DBUF ? (li & 1) : 0u;
+            mbar_wait_bounded(&bars->x_ready[xbuf], (DBUF ? (li >> 1) : li) & 1);
             tc_fence_after();
             const uint32_t ah = (((xb_a + xbuf * xbuf_bytes) & 0x3FFFFu) >> 4) | a_lbo;
             const uint32_t al = ah + (xhi_bytes >> 4);
@@ -429,10 +431,11 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
             issue_row_loads(X + (row < n ? row : 0) * ldx, row < n);
             stage_store(0, 0);
         }
-        const int t_stage = ntc > 1 ? 1 : 0;   // tile after which the NEXT step's rows are staged
+        // tile after which the NEXT step's rows are staged (never inside the tile loop with one X buffer)
+        const int t_stage = DBUF ? (ntc > 1 ? 1 : 0) : -1;
         for (int64_t step = blockIdx.x; step < nsteps; step += gridDim.x, ++li) {
             const int64_t row0 = step * TC_ROWS;
-            const uint32_t xbuf = li & 1;
+            const uint32_t xbuf = DBUF ? (li & 1) : 0u;
             const bool have_next = step + gridDim.x < nsteps;
             const int64_t nrow = (step + gridDim.x) * TC_ROWS + rl;
             // two independent trackers (even / odd columns) double the ILP of the dependent min/max chains
@@ -494,7 +497,18 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
                 pend = true;
                 p_row = row0 + rl;
                 p_buf = xbuf;
-                p_use = li >> 1;
+                p_use = DBUF ? (li >> 1) : li;
+            }
+            if (!DBUF) {
+                // one X buffer: write this step out now, then restage once the tensor core has let go of it
+                merge_pending();
+                issue_row_loads(c32 + (size_t)p_bi * d, true);
+                output_pending();
+                pend = false;
+                if (have_next) {
+                    issue_row_loads(X + (nrow < n ? nrow : 0) * ldx, nrow < n);
+                    stage_store(0, li + 1);
+                }
             }
         }
         if (pend) {
@@ -519,22 +533,27 @@ int km_launch_assign_tc(const float *X, int64_t n, int d, int64_t ldx, const voi
     const unsigned char *pk = static_cast<const unsigned char *>(pack);
     const int kpad = km_tc_kpad(d);
     const int nch = kpad / 4;
-    const size_t smem = 2 * ((size_t)(nch + 2) * 128 * 16 + (size_t)nch * 128 * 16) +
+    const bool dbuf = d <= 64;
+    const size_t smem = (dbuf ? 2 : 1) * ((size_t)(nch + 2) * 128 * 16 + (size_t)nch * 128 * 16) +
                         (size_t)TC_BSTAGES * TC_STAGE_BYTES + sizeof(TcBars) + 64;
     const bool vec = (d % 4 == 0) && (ldx % 4 == 0) && ((reinterpret_cast<uintptr_t>(X) & 15) == 0);
-    static bool attr_v[KM_MAX_DEVICES] = {}, attr_s[KM_MAX_DEVICES] = {};
-    if (int rc = km_set_smem_once(assign_tc_f32_kernel<true>, 227 * 1024, attr_v)) return rc;
-    if (int rc = km_set_smem_once(assign_tc_f32_kernel<false>, 227 * 1024, attr_s)) return rc;
     int64_t steps = (n + TC_ROWS - 1) / TC_ROWS;
     const int grid = (int)(steps < KM_NUM_SMS ? steps : KM_NUM_SMS);
     const unsigned char *img = pk + L.off_tc;
     const float *c32 = reinterpret_cast<const float *>(pk + L.off_c32);
     const unsigned int *cmax = reinterpret_cast<const unsigned int *>(pk + L.off_cmax);
-    if (vec)
-        assign_tc_f32_kernel<true><<<grid, TC_THREADS, smem, st>>>(X, n, d, ldx, img, c32, cmax, k, labels, mind2,
-                                                                    flag_rows, flag_count);
-    else
-        assign_tc_f32_kernel<false><<<grid, TC_THREADS, smem, st>>>(X, n, d, ldx, img, c32, cmax, k, labels, mind2,
-                                                                     flag_rows, flag_count);
+#define TC_LAUNCH(VEC_, DBUF_)                                                                              \
+    {                                                                                                       \
+        auto kern = assign_tc_f32_kernel<VEC_, DBUF_>;                                                      \
+        static bool attr[KM_MAX_DEVICES] = {};                                                              \
+        if (int rc = km_set_smem_once(kern, 227 * 1024, attr)) return rc;                                   \
+        kern<<<grid, TC_THREADS, smem, st>>>(X, n, d, ldx, img, c32, cmax, k, labels, mind2, flag_rows,     \
+                                             flag_count);                                                   \
+    }
+    if (vec && dbuf) TC_LAUNCH(true, true)
+    else if (vec) TC_LAUNCH(true, false)
+    else if (dbuf) TC_LAUNCH(false, true)
+    else TC_LAUNCH(false, false)
+#undef TC_LAUNCH
     return (int)cudaGetLastError();
 }

@@ -51,7 +51,7 @@ constexpr int KM_TILE_N = 128;  // centroid tile width of the tiled assign kerne
 //   block 0      : aug[2 chunks]                  8192 B  (the K-step that adds ||c||^2)
 //   block 1 + ks : hi[2 chunks] | lo[2 chunks]   16384 B  (K-step ks = 8 features of -2c, TF32 hi / lo parts)
 constexpr int KM_TC_BN = 256;
-constexpr int KM_TC_MAX_D = 64;
+constexpr int KM_TC_MAX_D = 128;
 constexpr int KM_TC_AUG_BYTES = 2 * KM_TC_BN * 16;
 constexpr int KM_TC_KS_BYTES = 4 * KM_TC_BN * 16;
 __host__ __device__ inline int km_tc_kpad(int d) { return (d + 7) & ~7; }

@@ -48,7 +48,7 @@ extern "C" {
 #define B200KM_MINDIST_MAX_M 8 /* candidates per b200km_mindist_update_* launch */
 
 /* options (process-wide; meant for benchmarks and tests) */
-#define B200KM_OPT_K1_VARIANT 1 /* 0 = auto, 1 = FP32 FFMA kernel, 2 = tcgen05 3xTF32 kernel (d <= 64) */
+#define B200KM_OPT_K1_VARIANT 1 /* 0 = auto, 1 = FP32 FFMA kernel, 2 = tcgen05 3xTF32 kernel (d <= 128) */
 int b200km_set_option(int key, int value);
 int b200km_get_option(int key);
 

@@ -54,7 +54,8 @@ def _check_assign(eng, X, C, expect_flags=None):
 @pytest.mark.parametrize("variant", [1, 2], ids=["ffma", "tcgen05"])
 @pytest.mark.parametrize("n,d,k", [(5000, 64, 1024), (3001, 32, 256), (777, 20, 150), (1000, 128, 300),
                                     (513, 7, 33), (128, 4, 17), (4096, 16, 129), (1, 8, 40), (300, 36, 128),
-                                    (40000, 64, 257), (129, 64, 600), (20000, 48, 2000), (2500, 13, 70)])
+                                    (40000, 64, 257), (129, 64, 600), (20000, 48, 2000), (2500, 13, 70),
+                                    (3000, 100, 700), (2000, 128, 4100), (700, 66, 90)])
 def test_assign_f32_tiled(eng, n, d, k, variant):
     """Both K1 float32 kernels (FP32 FFMA tiles; tcgen05 3xTF32 with TMEM accumulators, d <= 64)."""
     X, C = blobs(n, d, k, seed=n + d + k, dtype=np.float32)

@@ -27,9 +27,22 @@ def run(n, d, k, seed=0):
         msg += f"; ffma-vs-f64 {(l1 != ref).sum()}, tc-vs-f64 {(l2 != ref).sum()}; mind2 maxrel {np.abs(out[2][1]-D.min(1)).max()/D.min(1).max():.2e}"
     print(msg, flush=True)
 
-for shape in [(256, 64, 64), (256, 64, 128), (1000, 64, 1024), (5000, 32, 256), (777, 20, 150), (513, 8, 33), (100000, 64, 1024), (3000, 48, 500)]:
+for shape in [(256, 64, 64), (256, 64, 128), (1000, 64, 1024), (5000, 32, 256), (777, 20, 150), (513, 8, 33), (100000, 64, 1024), (3000, 48, 500), (1000, 128, 300), (3000, 100, 700), (2000, 128, 8192), (4000, 72, 1024)]:
     run(*shape)
 # timing
+import itertools
+for n, d, k in [(8_000_000, 64, 1024), (1_000_000, 128, 8192), (16_000_000, 32, 256)]:
+  X = torch.randn(n, d, device=eng.device); C = torch.randn(k, d, dtype=torch.float64, device=eng.device) * 3
+  pack = eng.pack(C)
+  for var in (1, 2):
+    lib.b200km_set_option(1, var)
+    lab, m2 = eng.assign(X, pack, refine=False)
+    torch.cuda.synchronize(); t0 = time.perf_counter()
+    for _ in range(3): eng.assign(X, pack, lab, m2, refine=False)
+    torch.cuda.synchronize(); dt = (time.perf_counter() - t0) / 3
+    print(f"n={n} d={d} k={k} variant {var}: {dt*1e3:.2f} ms  {n/dt/1e6:.1f} Mpts/s  {2*n*k*d/dt/1e12:.1f} TFLOP/s-equivalent", flush=True)
+lib.b200km_set_option(1, 0)
+sys.exit(0)
 n, d, k = 8_000_000, 64, 1024
 X = torch.randn(n, d, device=eng.device); C = torch.randn(k, d, dtype=torch.float64, device=eng.device) * 3
 pack = eng.pack(C)
