@@ -409,16 +409,23 @@ static int launch_rb(const TX *X, int64_t n, int d, int64_t ldx, const double *c
 // =============================================================================================
 
 static int g_k1_variant = 0;  // B200KM_OPT_K1_VARIANT: 0 auto, 1 FFMA, 2 tcgen05 3xTF32
+static int g_k2_variant = 0;  // B200KM_OPT_K2_VARIANT: 0 auto, 1 owner table, 2 chunk sort, 3 global atomics
+int km_k2_variant() { return g_k2_variant; }
 
 extern "C" int b200km_set_option(int key, int value) {
     if (key == B200KM_OPT_K1_VARIANT && value >= 0 && value <= 2) {
         g_k1_variant = value;
         return 0;
     }
+    if (key == B200KM_OPT_K2_VARIANT && value >= 0 && value <= 3) {
+        g_k2_variant = value;
+        return 0;
+    }
     return B200KM_EINVAL;
 }
 extern "C" int b200km_get_option(int key) {
     if (key == B200KM_OPT_K1_VARIANT) return g_k1_variant;
+    if (key == B200KM_OPT_K2_VARIANT) return g_k2_variant;
     return B200KM_EINVAL;
 }
 

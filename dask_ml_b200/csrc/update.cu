@@ -17,6 +17,8 @@
 //       table (L2-resident), counts via one RED per row.
 #include "common.cuh"
 
+int km_k2_variant();  // assign.cu (b200km_set_option)
+
 constexpr int UP_THREADS = 256;
 constexpr int UP_WARPS = UP_THREADS / 32;
 
@@ -255,7 +257,15 @@ static int update_impl(const T *X, int64_t n, int d, int64_t ldx, const int32_t 
     KM_CHECK_ARG(k <= B200KM_MAX_K && d <= B200KM_MAX_D, B200KM_ETOOBIG);
     cudaStream_t st = km_stream(stream);
     const size_t smem = sizeof(double) * (size_t)k * d + sizeof(int) * (size_t)k;
-    if (smem <= 96 * 1024) {
+    const int variant = km_k2_variant();
+    const bool seg_ok = k <= SEG_MAX_K && n >= 4 * (int64_t)k;
+    const bool owner_ok = smem <= 96 * 1024;
+    // auto (measured on B200, tools/upd_check.py): the shared-memory owner table for tiny tables (k*d <= 2048:
+    // C1); chunk sort + run sums while a 16384-row chunk holds >= 8 rows per cluster (k <= 2048: C2, C3);
+    // plain fp64 REDs beyond that (C4: runs of 2 rows do not pay for the sort)
+    const bool use_owner = variant == 1 ? owner_ok : (variant == 0 && owner_ok && (size_t)k * d <= 2048);
+    const bool use_seg = !use_owner && seg_ok && (variant == 2 || (variant == 0 && k <= 2048));
+    if (use_owner) {
         auto kern = update_owner_kernel<T>;
         static bool attr_set[KM_MAX_DEVICES] = {};
         if (int rc = km_set_smem_once(kern, 96 * 1024, attr_set)) return rc;
@@ -263,7 +273,7 @@ static int update_impl(const T *X, int64_t n, int d, int64_t ldx, const int32_t 
         const int64_t cap = (int64_t)KM_NUM_SMS * 2;
         if (blocks > cap) blocks = cap;
         kern<<<(unsigned)blocks, UP_THREADS, smem, st>>>(X, n, d, ldx, labels, mind2, k, acc, scale_sqrt);
-    } else if (k <= SEG_MAX_K && n >= 4 * (int64_t)k) {
+    } else if (use_seg) {
         const size_t seg_smem = sizeof(int) * (size_t)(2 * k + 1) + sizeof(unsigned short) * SEG_R + 16;
         auto kern = update_seg_kernel<T>;
         static bool attr_set[KM_MAX_DEVICES] = {};

@@ -49,6 +49,7 @@ extern "C" {
 
 /* options (process-wide; meant for benchmarks and tests) */
 #define B200KM_OPT_K1_VARIANT 1 /* 0 = auto, 1 = FP32 FFMA kernel, 2 = tcgen05 3xTF32 kernel (d <= 128) */
+#define B200KM_OPT_K2_VARIANT 2 /* 0 = auto, 1 = shared-memory owner table, 2 = chunk sort + run sums, 3 = global atomics */
 int b200km_set_option(int key, int value);
 int b200km_get_option(int key);
 
