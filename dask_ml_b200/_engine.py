@@ -172,6 +172,30 @@ class CudaEngine:
                        1 if sqrt else 0, st)
         return acc
 
+    FUSED_MAX_K, FUSED_MAX_D = 16, 32
+
+    def can_fuse(self, k: int, d: int) -> bool:
+        """True when K1 and K2 run as ONE pass over X (the HBM-bound regime: tiny k and d)."""
+        return k <= self.FUSED_MAX_K and d <= self.FUSED_MAX_D
+
+    def assign_update(self, X: torch.Tensor, centers64: torch.Tensor, labels: torch.Tensor, mind2: torch.Tensor,
+                      acc: torch.Tensor) -> None:
+        """b200km_assign_update_*: labels, mind2 and acc += [sums | counts | inertia] in one pass."""
+        n, d, ldx = self._check_matrix(X)
+        k = centers64.shape[0]
+        sfx = _suffix(X)
+        st = self._stream()
+        for r0 in range(0, n, _MAX_ROWS_PER_CALL):
+            nn = min(_MAX_ROWS_PER_CALL, n - r0)
+            if self.k1_events is not None:
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+            self._call(f"b200km_assign_update_{sfx}", X[r0 : r0 + nn].data_ptr(), nn, d, ldx, centers64.data_ptr(), k,
+                       labels[r0 : r0 + nn].data_ptr(), mind2[r0 : r0 + nn].data_ptr(), acc.data_ptr(), st)
+            if self.k1_events is not None:
+                e1.record()
+                self.k1_events.append((e0, e1))
+
     def finalize(self, acc: torch.Tensor, k: int, d: int, centers_old: torch.Tensor,
                  centers_new: Optional[torch.Tensor] = None, shift: Optional[torch.Tensor] = None):
         if centers_new is None:

@@ -440,12 +440,16 @@ def _kmeans_single_lloyd(X, n_clusters, max_iter=300, init="k-means||", verbose=
     i = -1
     for i in range(max_iter):
         with _timer("Lloyd loop %2d." % i, _logger=logger):
-            pack = eng.pack(centers64, pack)
-            if n_local:
-                eng.assign(X, pack, labels, mind2)  # :576-579
             acc.zero_()
-            if n_local:
-                eng.update(X, labels, mind2, k, acc)  # :582-598, :616
+            if getattr(eng, "can_fuse", lambda *_: False)(k, P):
+                # HBM-bound regime (tiny k, d): labels + sums + counts + inertia in ONE pass over X
+                if n_local:
+                    eng.assign_update(X, centers64, labels, mind2, acc)  # :576-598, :616
+            else:
+                pack = eng.pack(centers64, pack)
+                if n_local:
+                    eng.assign(X, pack, labels, mind2)  # :576-579
+                    eng.update(X, labels, mind2, k, acc)  # :582-598, :616
             comm.allreduce_sum_(acc)  # the chain-sum over blocks / workers (:595-597)
             eng.finalize(acc, k, P, centers64, new64, shift_t)  # :600-605
             shift = float(shift_t.item())  # :602 -- the one round trip per iteration

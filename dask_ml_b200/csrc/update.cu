@@ -361,3 +361,131 @@ extern "C" int b200km_reduce_sum_f32(const float *v, int64_t n, int take_sqrt, d
 extern "C" int b200km_reduce_sum_f64(const double *v, int64_t n, int take_sqrt, double *out, void *stream) {
     return reduce_sum_impl<double>(v, n, take_sqrt, out, stream);
 }
+
+// ---------------------------------------------------------------------------------------------
+// Fused K1+K2 for the HBM-bound regime (k <= 16, d <= 32; BASELINE config C1): ONE pass over X gives
+// labels, min distances, per-cluster sums, counts and inertia.  Replaces the pair
+// pairwise_distances_argmin_min (reference dask_ml/metrics/pairwise.py:19-47) + _centers_dense /
+// bincount (dask_ml/cluster/k_means.py:582-598) that the reference runs as two passes over X.
+//   phase A: thread per row, float64 direct-form distances to the k centres held in shared memory;
+//   phase B: the tile's rows are counting-sorted by label with warp ballots, then thread (c, f) adds the
+//            rows of cluster c into its private float64 register cell -- no atomics until the CTA's
+//            final flush (k*d REDs per CTA).
+// ---------------------------------------------------------------------------------------------
+constexpr int FU_R = 256;        // rows per tile == threads per CTA
+constexpr int FU_MAXK = 16;
+constexpr int FU_MAXD = 32;
+
+template <typename TX>
+__global__ void __launch_bounds__(FU_R)
+assign_update_small_kernel(const TX *__restrict__ X, int64_t n, int d, int64_t ldx, const double *__restrict__ c64,
+                           int k, int32_t *__restrict__ labels, TX *__restrict__ mind2, double *__restrict__ acc) {
+    extern __shared__ __align__(16) double fu_smem[];
+    const int xld = d + 1;
+    double *xs = fu_smem;                            // [FU_R][d+1]
+    double *cs = fu_smem + (size_t)FU_R * xld;       // [k][d]
+    __shared__ unsigned char order[FU_R];            // row slots sorted by label
+    __shared__ int wcnt[FU_R / 32][FU_MAXK];         // per-warp label counts
+    __shared__ int cstart[FU_MAXK + 1];
+    __shared__ double red[32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (int e = tid; e < k * d; e += FU_R) cs[e] = c64[e];
+    // register cells: thread t owns cells t and t + 256 of the k*d table
+    const int ncell = k * d;
+    const int c0 = tid / d, f0 = tid % d;
+    const int c1 = (tid + FU_R) / d, f1 = (tid + FU_R) % d;
+    double cell0 = 0.0, cell1 = 0.0, inert = 0.0;
+    double mycount = 0.0;                             // thread c < k accumulates the count of cluster c
+    __syncthreads();
+
+    for (int64_t base = (int64_t)blockIdx.x * FU_R; base < n; base += (int64_t)gridDim.x * FU_R) {
+        const int rows = (int)((n - base) < FU_R ? (n - base) : FU_R);
+        // stage the tile (coalesced), converted to float64
+        for (int e = tid; e < rows * d; e += FU_R) {
+            const int r = e / d, f = e - r * d;
+            xs[r * xld + f] = (double)X[(base + r) * ldx + f];
+        }
+        __syncthreads();
+        // ---- phase A: argmin (lowest index on ties) -------------------------------------------
+        int lab = -1;
+        if (tid < rows) {
+            double best = INFINITY;
+            for (int c = 0; c < k; ++c) {
+                double s = 0.0;
+                for (int f = 0; f < d; ++f) {
+                    const double df = xs[tid * xld + f] - cs[c * d + f];
+                    s = fma(df, df, s);
+                }
+                if (s < best) { best = s; lab = c; }
+            }
+            labels[base + tid] = lab;
+            if (mind2) mind2[base + tid] = (TX)best;
+            inert += best;
+        }
+        // ---- counting sort of the tile's rows by label (warp ballots) -------------------------
+        int rank_in_warp = 0;
+        for (int c = 0; c < k; ++c) {
+            const unsigned m = __ballot_sync(0xffffffffu, lab == c);
+            if (lab == c) rank_in_warp = __popc(m & ((1u << lane) - 1u));
+            if (lane == 0) wcnt[warp][c] = __popc(m);
+        }
+        __syncthreads();
+        if (tid <= k) {
+            int s = 0;
+            for (int c = 0; c < tid; ++c)
+                for (int w = 0; w < FU_R / 32; ++w) s += wcnt[w][c];
+            cstart[tid] = s;
+            if (tid < k) {
+                int mine = 0;
+                for (int w = 0; w < FU_R / 32; ++w) mine += wcnt[w][tid];
+                mycount += (double)mine;
+            }
+        }
+        __syncthreads();
+        if (lab >= 0) {
+            int pos = cstart[lab] + rank_in_warp;
+            for (int w = 0; w < warp; ++w) pos += wcnt[w][lab];
+            order[pos] = (unsigned char)tid;
+        }
+        __syncthreads();
+        // ---- phase B: thread (c, f) sums the rows of cluster c ---------------------------------
+        if (tid < ncell) {
+            const int s0 = cstart[c0], s1 = cstart[c0 + 1];
+            for (int p = s0; p < s1; ++p) cell0 += xs[order[p] * xld + f0];
+        }
+        if (tid + FU_R < ncell) {
+            const int s0 = cstart[c1], s1 = cstart[c1 + 1];
+            for (int p = s0; p < s1; ++p) cell1 += xs[order[p] * xld + f1];
+        }
+        __syncthreads();
+    }
+    if (tid < ncell && cell0 != 0.0) atomicAdd(acc + tid, cell0);
+    if (tid + FU_R < ncell && cell1 != 0.0) atomicAdd(acc + tid + FU_R, cell1);
+    if (tid < k && mycount != 0.0) atomicAdd(acc + ncell + tid, mycount);
+    km_block_atomic_add(inert, acc + ncell + k, red);
+}
+
+template <typename TX>
+static int assign_update_impl(const TX *X, int64_t n, int d, int64_t ldx, const double *centers_f64, int k,
+                              int32_t *labels, TX *mind2, double *acc, void *stream) {
+    KM_CHECK_ARG(X && centers_f64 && labels && acc, B200KM_EINVAL);
+    KM_CHECK_ARG(n > 0 && d > 0 && k > 0 && ldx >= d, B200KM_EINVAL);
+    KM_CHECK_ARG(k <= FU_MAXK && d <= FU_MAXD, B200KM_ETOOBIG);
+    int64_t blocks = (n + FU_R - 1) / FU_R;
+    const int64_t cap = (int64_t)KM_NUM_SMS * 4;
+    if (blocks > cap) blocks = cap;
+    const size_t smem = sizeof(double) * ((size_t)FU_R * (d + 1) + (size_t)k * d);
+    auto kern = assign_update_small_kernel<TX>;
+    static bool attr_set[KM_MAX_DEVICES] = {};
+    if (int rc = km_set_smem_once(kern, 80 * 1024, attr_set)) return rc;
+    kern<<<(unsigned)blocks, FU_R, smem, km_stream(stream)>>>(X, n, d, ldx, centers_f64, k, labels, mind2, acc);
+    KM_LAUNCH_RET();
+}
+extern "C" int b200km_assign_update_f32(const float *X, int64_t n, int d, int64_t ldx, const double *centers_f64,
+                                        int k, int32_t *labels, float *mind2, double *acc, void *stream) {
+    return assign_update_impl<float>(X, n, d, ldx, centers_f64, k, labels, mind2, acc, stream);
+}
+extern "C" int b200km_assign_update_f64(const double *X, int64_t n, int d, int64_t ldx, const double *centers_f64,
+                                        int k, int32_t *labels, double *mind2, double *acc, void *stream) {
+    return assign_update_impl<double>(X, n, d, ldx, centers_f64, k, labels, mind2, acc, stream);
+}

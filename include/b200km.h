@@ -130,6 +130,17 @@ int b200km_update_f32(const float *X, int64_t n, int d, int64_t ldx, const int32
 int b200km_update_f64(const double *X, int64_t n, int d, int64_t ldx, const int32_t *labels,
                       const double *mind2, int k, double *acc, int scale_sqrt, void *stream);
 
+/* K1+K2 fused into ONE pass over X for the HBM-bound regime: k <= 16 and d <= 32 (else B200KM_ETOOBIG).
+ * labels / mind2 as K1 (float64 arithmetic, so no re-decision is needed), acc += as K2 (squared inertia).
+ * Replaces: the two passes R/dask_ml/cluster/k_means.py:576-598 makes over X per iteration
+ *           (pairwise_distances_argmin_min, then _centers_dense + bincount). */
+#define B200KM_FUSED_MAX_K 16
+#define B200KM_FUSED_MAX_D 32
+int b200km_assign_update_f32(const float *X, int64_t n, int d, int64_t ldx, const double *centers_f64, int k,
+                             int32_t *labels, float *mind2, double *acc, void *stream);
+int b200km_assign_update_f64(const double *X, int64_t n, int d, int64_t ldx, const double *centers_f64, int k,
+                             int32_t *labels, double *mind2, double *acc, void *stream);
+
 /* out[0] += sum_i v[i]  (or sum_i sqrt(v[i]) when take_sqrt != 0), float64; caller zeroes out.
  * Replaces: distances.sum() (R/dask_ml/cluster/k_means.py:616) on the non-squared final pass. */
 int b200km_reduce_sum_f32(const float *v, int64_t n, int take_sqrt, double *out, void *stream);

@@ -253,3 +253,34 @@ def test_make_blobs_statistics(eng):
     # sharding invariance: rows generated with an offset equal the same rows of the full array
     Y = eng.make_blobs(1000, d, centers, 1.0, seed=3, row_offset=5000)
     assert torch.equal(Y, X[5000:6000])
+
+
+@pytest.mark.parametrize("n,d,k,dtype", [(4000, 16, 8, np.float64), (999, 3, 2, np.float32), (70000, 32, 16, np.float32),
+                                         (1, 1, 1, np.float64), (257, 5, 3, np.float64), (100000, 16, 8, np.float32)])
+def test_assign_update_fused(eng, n, d, k, dtype):
+    """K1+K2 in one pass (HBM-bound regime, k <= 16, d <= 32) against the oracle's two passes."""
+    import torch
+
+    X, C = blobs(n, d, k, seed=n + k, dtype=dtype)
+    C = C + 0.2
+    Xd = eng.to_device(X)
+    Cd = eng.to_device(C, torch.float64)
+    labels = torch.full((n,), -1, dtype=torch.int32, device=eng.device)
+    mind2 = torch.zeros(n, dtype=Xd.dtype, device=eng.device)
+    acc = torch.zeros(eng.acc_len(k, d), dtype=torch.float64, device=eng.device)
+    assert eng.can_fuse(k, d)
+    eng.assign_update(Xd, Cd, labels, mind2, acc)
+    lab_ref, d_ref = orc.pairwise_distances_argmin_min(X, C, metric_kwargs={"squared": True})
+    got = labels.cpu().numpy()
+    diff = got != lab_ref
+    assert not (diff & ~_near_tie_mask(X, C, 1e-12)).any()
+    tol = RTOL[dtype]
+    npt.assert_allclose(mind2.cpu().numpy().astype(np.float64), d_ref, rtol=3 * tol, atol=tol * max(d_ref.max(), 1e-30))
+    a = acc.cpu().numpy()
+    sums = orc.centers_dense(X, got.astype(np.int32), k)
+    npt.assert_allclose(a[: k * d].reshape(k, d), sums, rtol=1e-12, atol=1e-9 * max(np.abs(sums).max(), 1.0))
+    npt.assert_array_equal(a[k * d : k * d + k], np.bincount(got, minlength=k))
+    npt.assert_allclose(a[-1], mind2.double().sum().item(), rtol=1e-6 if dtype == np.float32 else 1e-12)
+    with pytest.raises(ValueError):
+        eng.assign_update(eng.to_device(np.zeros((4, 40), dtype)), eng.to_device(np.zeros((2, 40)), torch.float64),
+                          labels[:4], mind2[:4], acc)
