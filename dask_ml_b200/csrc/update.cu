@@ -376,20 +376,27 @@ constexpr int FU_R = 256;        // rows per tile == threads per CTA
 constexpr int FU_MAXK = 16;
 constexpr int FU_MAXD = 32;
 
-template <typename TX>
-__global__ void __launch_bounds__(FU_R)
+template <typename TX, int DMAX>
+__global__ void __launch_bounds__(FU_R, 3)
 assign_update_small_kernel(const TX *__restrict__ X, int64_t n, int d, int64_t ldx, const double *__restrict__ c64,
                            int k, int32_t *__restrict__ labels, TX *__restrict__ mind2, double *__restrict__ acc) {
     extern __shared__ __align__(16) double fu_smem[];
     const int xld = d + 1;
     double *xs = fu_smem;                            // [FU_R][d+1]
-    double *cs = fu_smem + (size_t)FU_R * xld;       // [k][d]
+    const int dpad = (d + 1) & ~1;                   // centres padded to an even length (zeros)
+    int lg_dp = 0;
+    while ((1 << lg_dp) < d) ++lg_dp;                // dp = smallest power of two >= d (<= 32)
+    const int dp = 1 << lg_dp;
+    double *cs = fu_smem + (size_t)FU_R * xld + ((FU_R * xld) & 1);  // [k][dpad], 16-byte aligned
     __shared__ unsigned char order[FU_R];            // row slots sorted by label
     __shared__ int wcnt[FU_R / 32][FU_MAXK];         // per-warp label counts
     __shared__ int cstart[FU_MAXK + 1];
     __shared__ double red[32];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    for (int e = tid; e < k * d; e += FU_R) cs[e] = c64[e];
+    for (int e = tid; e < k * dpad; e += FU_R) {
+        const int c = e / dpad, f = e - c * dpad;
+        cs[e] = f < d ? c64[(size_t)c * d + f] : 0.0;
+    }
     // register cells: thread t owns cells t and t + 256 of the k*d table
     const int ncell = k * d;
     const int c0 = tid / d, f0 = tid % d;
@@ -400,22 +407,52 @@ assign_update_small_kernel(const TX *__restrict__ X, int64_t n, int d, int64_t l
 
     for (int64_t base = (int64_t)blockIdx.x * FU_R; base < n; base += (int64_t)gridDim.x * FU_R) {
         const int rows = (int)((n - base) < FU_R ? (n - base) : FU_R);
-        // stage the tile (coalesced), converted to float64
-        for (int e = tid; e < rows * d; e += FU_R) {
-            const int r = e / d, f = e - r * d;
-            xs[r * xld + f] = (double)X[(base + r) * ldx + f];
+        // stage the tile, converted to float64.  Lanes = features (padded to a power of two so the row /
+        // feature split is shifts, not divisions), 32/dp rows per warp instruction; all of a thread's loads
+        // are issued before the first store so the tile costs one memory latency.
+        {
+            const int sub = lane >> lg_dp, f = lane & (dp - 1);
+            const int rpi = 32 >> lg_dp;                       // rows per warp instruction
+            const int r_first = warp * rpi + sub;
+            const int r_step = (FU_R / 32) * rpi;
+            const bool fok = f < d;
+            for (int i0 = 0; i0 * r_step < FU_R; i0 += 8) {    // batches of 8 loads in flight per thread
+                TX v[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const int r = r_first + (i0 + i) * r_step;
+                    v[i] = (TX)0;
+                    if (fok && r < rows) v[i] = __ldg(X + (base + r) * ldx + f);
+                }
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const int r = r_first + (i0 + i) * r_step;
+                    if (fok && r < rows) xs[r * xld + f] = (double)v[i];
+                }
+            }
         }
         __syncthreads();
         // ---- phase A: argmin (lowest index on ties) -------------------------------------------
         int lab = -1;
         if (tid < rows) {
+            // the row lives in registers (d <= 32); centres are broadcast 16-byte shared-memory loads
+            double xr[DMAX];
+#pragma unroll
+            for (int f = 0; f < DMAX; ++f) xr[f] = f < d ? xs[tid * xld + f] : 0.0;
             double best = INFINITY;
             for (int c = 0; c < k; ++c) {
-                double s = 0.0;
-                for (int f = 0; f < d; ++f) {
-                    const double df = xs[tid * xld + f] - cs[c * d + f];
-                    s = fma(df, df, s);
+                const double *cr = cs + c * dpad;
+                double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+                for (int f = 0; f < DMAX; f += 2) {
+                    if (f < d) {
+                        const double2 cv = *reinterpret_cast<const double2 *>(cr + f);
+                        const double d0 = xr[f] - cv.x, d1 = xr[f + 1] - cv.y;
+                        s0 = fma(d0, d0, s0);
+                        s1 = fma(d1, d1, s1);
+                    }
                 }
+                const double s = s0 + s1;
                 if (s < best) { best = s; lab = c; }
             }
             labels[base + tid] = lab;
@@ -474,11 +511,18 @@ static int assign_update_impl(const TX *X, int64_t n, int d, int64_t ldx, const 
     int64_t blocks = (n + FU_R - 1) / FU_R;
     const int64_t cap = (int64_t)KM_NUM_SMS * 4;
     if (blocks > cap) blocks = cap;
-    const size_t smem = sizeof(double) * ((size_t)FU_R * (d + 1) + (size_t)k * d);
-    auto kern = assign_update_small_kernel<TX>;
-    static bool attr_set[KM_MAX_DEVICES] = {};
-    if (int rc = km_set_smem_once(kern, 80 * 1024, attr_set)) return rc;
-    kern<<<(unsigned)blocks, FU_R, smem, km_stream(stream)>>>(X, n, d, ldx, centers_f64, k, labels, mind2, acc);
+    const size_t smem = sizeof(double) * ((size_t)FU_R * (d + 1) + 1 + (size_t)k * (d + 1));
+    if (d <= 16) {
+        auto kern = assign_update_small_kernel<TX, 16>;
+        static bool attr_set[KM_MAX_DEVICES] = {};
+        if (int rc = km_set_smem_once(kern, 80 * 1024, attr_set)) return rc;
+        kern<<<(unsigned)blocks, FU_R, smem, km_stream(stream)>>>(X, n, d, ldx, centers_f64, k, labels, mind2, acc);
+    } else {
+        auto kern = assign_update_small_kernel<TX, FU_MAXD>;
+        static bool attr_set[KM_MAX_DEVICES] = {};
+        if (int rc = km_set_smem_once(kern, 80 * 1024, attr_set)) return rc;
+        kern<<<(unsigned)blocks, FU_R, smem, km_stream(stream)>>>(X, n, d, ldx, centers_f64, k, labels, mind2, acc);
+    }
     KM_LAUNCH_RET();
 }
 extern "C" int b200km_assign_update_f32(const float *X, int64_t n, int d, int64_t ldx, const double *centers_f64,
