@@ -37,6 +37,15 @@ def _dev(X, eng=None, dtype=None) -> torch.Tensor:
     return t
 
 
+def _check_same_features(Xd: torch.Tensor, Yd: torch.Tensor) -> None:
+    """The reference fails inside da.dot / sklearn with a ValueError when the feature counts differ."""
+    if Xd.shape[1] != Yd.shape[1]:
+        raise ValueError(
+            "Incompatible dimension for X and Y matrices: X.shape[1] == %d while Y.shape[1] == %d"
+            % (Xd.shape[1], Yd.shape[1])
+        )
+
+
 def pairwise_distances_argmin_min(X, Y, axis: int = 1, metric="euclidean", batch_size: Optional[int] = None,
                                   metric_kwargs: Optional[Dict[str, Any]] = None):
     """reference dask_ml/metrics/pairwise.py:19-47.
@@ -58,11 +67,7 @@ def pairwise_distances_argmin_min(X, Y, axis: int = 1, metric="euclidean", batch
     eng = get_engine()
     Xd = _dev(X, eng)
     Yd = _dev(Y, eng, torch.float64)
-    if Xd.shape[1] != Yd.shape[1]:
-        raise ValueError(
-            "Incompatible dimension for X and Y matrices: X.shape[1] == %d while Y.shape[1] == %d"
-            % (Xd.shape[1], Yd.shape[1])
-        )
+    _check_same_features(Xd, Yd)
     pack = eng.pack(Yd)
     labels, mind2 = eng.assign(Xd, pack, want_mind2=True)
     mins = mind2.to(torch.float64)
@@ -80,6 +85,7 @@ def pairwise_distances(X, Y, metric="euclidean", n_jobs: Optional[int] = None, *
     eng = get_engine()
     Xd = _dev(X, eng)
     Yd = _dev(Y, eng)
+    _check_same_features(Xd, Yd)
     if Yd.dtype != Xd.dtype:
         Xd, Yd = Xd.to(torch.float64), Yd.to(torch.float64)
     squared = metric == "sqeuclidean" or bool(kwargs.get("squared", False))
@@ -93,6 +99,7 @@ def euclidean_distances(X, Y=None, Y_norm_squared=None, squared: bool = False, X
     Xd = _dev(X, eng)
     same = Y is None or Y is X
     Yd = Xd if same else _dev(Y, eng)
+    _check_same_features(Xd, Yd)
     if Yd.dtype != Xd.dtype:  # numpy promotion of -2 * dot(X, Y.T) + XX + YY (:101)
         Xd, Yd = Xd.to(torch.float64), Yd.to(torch.float64)
     xn = yn = None

@@ -37,6 +37,30 @@ def replace(a, old, new):
 
 
 # ---- the reference's own tests, replayed on the CUDA path --------------------------------------
+def test_check_estimator():  # reference tests/test_kmeans.py:25-33
+    import warnings
+
+    from sklearn.utils.estimator_checks import check_estimator
+
+    with warnings.catch_warnings(record=True):
+        warnings.simplefilter("ignore")
+        check_estimator(
+            _km()(),
+            expected_failed_checks={
+                "check_n_features_in_after_fitting": "https://github.com/dask/dask-ml/pull/1008"
+            },
+        )
+
+
+def test_feature_mismatch_raises():
+    X = np.random.RandomState(0).uniform(size=(40, 4))
+    km = _km()(n_clusters=3, random_state=0).fit(X)
+    with pytest.raises(ValueError):
+        km.transform(X[:, :3])
+    with pytest.raises(ValueError):
+        km.predict(X[:, :2])
+
+
 def test_row_norms(X_blobs):  # reference tests/test_kmeans.py:36-39
     from dask_ml_b200._engine import get_engine
     from dask_ml_b200.utils import row_norms
