@@ -408,12 +408,13 @@ static int launch_rb(const TX *X, int64_t n, int d, int64_t ldx, const double *c
 // entry points
 // =============================================================================================
 
-static int g_k1_variant = 0;  // B200KM_OPT_K1_VARIANT: 0 auto, 1 FFMA, 2 tcgen05 3xTF32
+static int g_k1_variant = 0;  // B200KM_OPT_K1_VARIANT: 0 auto, 1 FFMA, 2 tcgen05 (one CTA), 3 tcgen05 (CTA pair)
+bool km_tc_pair_mode() { return g_k1_variant == 3; }
 static int g_k2_variant = 0;  // B200KM_OPT_K2_VARIANT: 0 auto, 1 owner table, 2 chunk sort, 3 global atomics
 int km_k2_variant() { return g_k2_variant; }
 
 extern "C" int b200km_set_option(int key, int value) {
-    if (key == B200KM_OPT_K1_VARIANT && value >= 0 && value <= 2) {
+    if (key == B200KM_OPT_K1_VARIANT && value >= 0 && value <= 3) {
         g_k1_variant = value;
         return 0;
     }
@@ -432,7 +433,7 @@ extern "C" int b200km_get_option(int key) {
 static bool use_tc_path(int d, int k) {
     if (d > KM_TC_MAX_D) return false;
     if (g_k1_variant == 1) return false;
-    if (g_k1_variant == 2) return true;
+    if (g_k1_variant >= 2) return true;
     return true;   // auto: tensor cores whenever the shape allows (d <= 128)
 }
 static int check_pack_args(const void *X, int64_t n, int d, int64_t ldx, const void *pack, int k, const void *labels) {

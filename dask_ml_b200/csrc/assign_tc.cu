@@ -26,8 +26,7 @@ namespace {
 constexpr int TC_THREADS = 320;   // producer warp + MMA warp + 8 staging/epilogue warps
 constexpr int TC_EPI = 256;       // staging/epilogue threads: 2 per row (column halves)
 constexpr int TC_ROWS = 128;     // rows per CTA step
-constexpr int TC_BSTAGES = 5;    // ring of K-step blocks
-constexpr int TC_STAGE_BYTES = KM_TC_KS_BYTES;
+constexpr int TC_BSTAGES_MAX = 8;   // ring of K-step blocks: 5 x 16 KB (one CTA) or 8 x 8 KB (CTA pair)
 constexpr int TC_ASTAGES = 2;    // accumulator stages: 2 x 256 = 512 TMEM columns
 constexpr uint32_t TC_SPIN_LIMIT = 1u << 27;
 
@@ -66,6 +65,43 @@ __device__ __forceinline__ void mma_tf32(uint32_t tmem_d, uint32_t adesc_lo, uin
         "mov.b64 db, {%2, %3};\n\t"
         "tcgen05.mma.cta_group::1.kind::tf32 [%0], da, db, %4, {%6, %6, %6, %6}, p;\n\t}"
         ::"r"(tmem_d), "r"(adesc_lo), "r"(bdesc_lo), "r"(desc_hi), "r"(idesc), "r"(accumulate), "r"(0u)
+        : "memory");
+}
+// the same MMA spanning a CTA pair (cta_group::2): M = 256 (128 rows from each CTA), N split likewise
+__device__ __forceinline__ void mma_tf32_pair(uint32_t tmem_d, uint32_t adesc_lo, uint32_t bdesc_lo, uint32_t desc_hi,
+                                              uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\t"
+        "setp.ne.b32 p, %5, 0;\n\t"
+        "mov.b64 da, {%1, %3};\n\t"
+        "mov.b64 db, {%2, %3};\n\t"
+        "tcgen05.mma.cta_group::2.kind::tf32 [%0], da, db, %4, {%6, %6, %6, %6, %6, %6, %6, %6}, p;\n\t}"
+        ::"r"(tmem_d), "r"(adesc_lo), "r"(bdesc_lo), "r"(desc_hi), "r"(idesc), "r"(accumulate), "r"(0u)
+        : "memory");
+}
+__device__ __forceinline__ void mma_commit_pair(uint64_t *bar) {   // arrives on `bar` in BOTH CTAs of the pair
+    asm volatile(
+        "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+            km_smem_u32(bar)),
+        "h"((unsigned short)3)
+        : "memory");
+}
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// arrive on the barrier at the same shared-memory offset in CTA `rank` of the cluster
+__device__ __forceinline__ void mbar_arrive_remote(uint64_t *bar, uint32_t rank) {
+    asm volatile(
+        "{\n\t.reg .b32 ra;\n\t"
+        "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
+        "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n\t}" ::"r"(km_smem_u32(bar)),
+        "r"(rank)
         : "memory");
 }
 __device__ __forceinline__ bool elect_one() {
@@ -114,8 +150,8 @@ __device__ __forceinline__ void track(float v, int j, float &best, float &second
 }
 
 struct TcBars {
-    uint64_t b_full[TC_BSTAGES];
-    uint64_t b_empty[TC_BSTAGES];
+    uint64_t b_full[TC_BSTAGES_MAX];
+    uint64_t b_empty[TC_BSTAGES_MAX];
     uint64_t a_full[TC_ASTAGES];
     uint64_t a_empty[TC_ASTAGES];
     uint64_t x_ready[2];
@@ -138,24 +174,30 @@ struct TcBars {
 // ---------------------------------------------------------------------------------------------
 // TC image of the centres (runs after pack_centers_kernel on the same stream)
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(64) pack_tc_kernel(int k, int d, unsigned char *__restrict__ pack) {
+__global__ void __launch_bounds__(64) pack_tc_kernel(int k, int d, unsigned char *__restrict__ pack, int pair) {
+    // pair != 0: each 256-column tile is stored as two 128-column halves (one per CTA of the pair), each
+    // half = [aug | K-step blocks]; otherwise as one 256-row operand.  BR = operand rows per block.
     const KmPackLayout L = km_pack_layout(k, d);
     const float *c32 = reinterpret_cast<const float *>(pack + L.off_c32);
     const float *cn32 = reinterpret_cast<const float *>(pack + L.off_cn32);
     const int j = blockIdx.x;
     const int tile = j / KM_TC_BN, jj = j % KM_TC_BN;
     const int kpad = km_tc_kpad(d);
-    unsigned char *img = pack + L.off_tc + (size_t)tile * km_tc_tile_bytes(d);
+    const int BR = pair ? KM_TC_BN / 2 : KM_TC_BN;
+    const int half = pair ? jj / BR : 0, jr = jj - half * BR;
+    const size_t aug_bytes = (size_t)2 * BR * 16, ks_bytes = (size_t)4 * BR * 16;
+    unsigned char *img = pack + L.off_tc + (size_t)tile * km_tc_tile_bytes(d) +
+                         (size_t)half * (aug_bytes + (size_t)(kpad / 8) * ks_bytes);
     for (int f = threadIdx.x; f < kpad; f += blockDim.x) {
         float v = 0.f;
         if (j < k && f < d) v = -2.f * c32[(size_t)j * d + f];
         const float h = tf32_rna(v);
         const float l = tf32_rna(v - h);
         const int ks = f >> 3, fc = f & 7;
-        unsigned char *blk = img + KM_TC_AUG_BYTES + (size_t)ks * KM_TC_KS_BYTES;
-        const size_t o = ((size_t)(fc >> 2) * KM_TC_BN + jj) * 4 + (fc & 3);
+        unsigned char *blk = img + aug_bytes + (size_t)ks * ks_bytes;
+        const size_t o = ((size_t)(fc >> 2) * BR + jr) * 4 + (fc & 3);
         reinterpret_cast<float *>(blk)[o] = h;
-        reinterpret_cast<float *>(blk + KM_TC_KS_BYTES / 2)[o] = l;
+        reinterpret_cast<float *>(blk + ks_bytes / 2)[o] = l;
     }
     if (threadIdx.x < 8) {
         // augmented K-step: chunk 0 = [cn_h, cn_m, cn_l, 0], chunk 1 = 0
@@ -172,14 +214,16 @@ __global__ void __launch_bounds__(64) pack_tc_kernel(int k, int d, unsigned char
             }
         }
         const int f = threadIdx.x;
-        reinterpret_cast<float *>(img)[((size_t)(f >> 2) * KM_TC_BN + jj) * 4 + (f & 3)] = v;
+        reinterpret_cast<float *>(img)[((size_t)(f >> 2) * BR + jr) * 4 + (f & 3)] = v;
     }
 }
+
+bool km_tc_pair_mode();  // assign.cu: true when K1 runs on CTA pairs (cta_group::2)
 
 int km_launch_pack_tc(int k, int d, void *pack, cudaStream_t st) {
     if (d > KM_TC_MAX_D) return 0;
     const int ntc = (k + KM_TC_BN - 1) / KM_TC_BN;
-    pack_tc_kernel<<<ntc * KM_TC_BN, 64, 0, st>>>(k, d, static_cast<unsigned char *>(pack));
+    pack_tc_kernel<<<ntc * KM_TC_BN, 64, 0, st>>>(k, d, static_cast<unsigned char *>(pack), km_tc_pair_mode() ? 1 : 0);
     return (int)cudaGetLastError();
 }
 
@@ -188,7 +232,10 @@ int km_launch_pack_tc(int k, int d, void *pack, cudaStream_t st) {
 // ---------------------------------------------------------------------------------------------
 // DBUF: two X buffers (d <= 64) so the next step's rows are staged under the current step; for
 // 64 < d <= 128 one buffer fills shared memory and staging happens at the step boundary instead.
-template <bool VEC, bool DBUF>
+// PAIR: the kernel runs on clusters of two CTAs (one SM pair); one tcgen05.mma.cta_group::2 of M = 256 covers
+// 128 rows of each CTA, and each CTA streams only ITS 128-column half of every centroid tile -- half the
+// TMA writes and half the B operand reads per SM, which is what keeps shared memory from capping the pipe.
+template <bool VEC, bool DBUF, bool PAIR>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
                      const unsigned char *__restrict__ tc_img, const float *__restrict__ c32,
@@ -203,19 +250,32 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
     const uint32_t xlo_bytes = (uint32_t)nch * 128 * 16;
     const uint32_t xbuf_bytes = xhi_bytes + xlo_bytes;     // one X buffer: hi part then lo part
     const uint32_t tile_bytes = (uint32_t)km_tc_tile_bytes(d);
+    constexpr int TC_BSTAGES = PAIR ? 8 : 5;
+    constexpr uint32_t BROWS = PAIR ? KM_TC_BN / 2 : KM_TC_BN;   // B operand rows held by this CTA
+    constexpr uint32_t TC_STAGE_BYTES = 4 * BROWS * 16;           // one K-step block: hi + lo, 2 chunks each
+    constexpr uint32_t AUG_BYTES = 2 * BROWS * 16;
     unsigned char *xb = tc_smem;                           // [DBUF ? 2 : 1][xbuf_bytes]
     unsigned char *bst = xb + (DBUF ? 2 : 1) * xbuf_bytes; // [TC_BSTAGES][TC_STAGE_BYTES]
     TcBars *bars = reinterpret_cast<TcBars *>(bst + TC_BSTAGES * TC_STAGE_BYTES);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int ntc = (k + KM_TC_BN - 1) / KM_TC_BN;
-    const int64_t nsteps = (n + TC_ROWS - 1) / TC_ROWS;
+    const uint32_t crank = PAIR ? cluster_ctarank() : 0u;          // 0 = leader of the pair
+    const int64_t step_rows = PAIR ? 2 * TC_ROWS : TC_ROWS;        // rows per step of the CTA (pair)
+    const int64_t nsteps = (n + step_rows - 1) / step_rows;
+    const int64_t step0 = PAIR ? blockIdx.x / 2 : blockIdx.x;
+    const int64_t step_inc = PAIR ? gridDim.x / 2 : gridDim.x;
 
     if (tid == 0) {
-        for (int i = 0; i < TC_BSTAGES; ++i) { km_mbar_init(&bars->b_full[i], 1); km_mbar_init(&bars->b_empty[i], 1); }
-        for (int i = 0; i < TC_ASTAGES; ++i) { km_mbar_init(&bars->a_full[i], 1); km_mbar_init(&bars->a_empty[i], TC_EPI); }
+        // pair mode: the leader's b_full / a_empty / x_ready also collect the peer CTA's arrivals
+        const uint32_t np = PAIR ? 2u : 1u;
+        for (int i = 0; i < TC_BSTAGES; ++i) {
+            km_mbar_init(&bars->b_full[i], (PAIR && crank == 0) ? 2 : 1);
+            km_mbar_init(&bars->b_empty[i], 1);
+        }
+        for (int i = 0; i < TC_ASTAGES; ++i) { km_mbar_init(&bars->a_full[i], 1); km_mbar_init(&bars->a_empty[i], np * TC_EPI); }
         for (int i = 0; i < 2; ++i) {
-            km_mbar_init(&bars->x_ready[i], TC_EPI);
+            km_mbar_init(&bars->x_ready[i], np * TC_EPI);
             km_mbar_init(&bars->x_free[i], 1);
             km_mbar_init(&bars->m_ready[i], TC_EPI);
             km_mbar_init(&bars->s_ready[i], TC_EPI / 2);
@@ -223,11 +283,19 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
         km_fence_mbar_init();
     }
     if (warp == 1) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
-                         km_smem_u32(&bars->tmem_base)),
-                     "r"(512u)
-                     : "memory");
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        if (PAIR) {
+            asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                             km_smem_u32(&bars->tmem_base)),
+                         "r"(512u)
+                         : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+        } else {
+            asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                             km_smem_u32(&bars->tmem_base)),
+                         "r"(512u)
+                         : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        }
     }
     // constant augmented chunks of Xhi: chunk nch = [1,1,1,0], chunk nch+1 = 0 (both X buffers)
     for (int e = tid; e < (DBUF ? 2 : 1) * 2 * 128; e += TC_THREADS) {
@@ -238,6 +306,7 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
     km_fence_proxy_async();
     tc_fence_before();
     __syncthreads();
+    if (PAIR) cluster_sync_all();   // both CTAs' barriers are initialised before any remote arrive / multicast commit
     tc_fence_after();
     const uint32_t tmem_base = bars->tmem_base;
 
@@ -245,13 +314,14 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
         // ================= producer =================
         if (lane == 0) {
             uint32_t it = 0;
-            for (int64_t step = blockIdx.x; step < nsteps; step += gridDim.x) {
+            for (int64_t step = step0; step < nsteps; step += step_inc) {
                 for (int t = 0; t < ntc; ++t) {
-                    const unsigned char *src = tc_img + (size_t)t * tile_bytes;
+                    // pair mode: this CTA streams only its 128-column half of the tile
+                    const unsigned char *src = tc_img + (size_t)t * tile_bytes + (size_t)crank * (tile_bytes / 2);
                     for (int b = 0; b <= nks; ++b, ++it) {
                         const int s = it % TC_BSTAGES;
                         const uint32_t ph = (it / TC_BSTAGES) & 1;
-                        const uint32_t bytes = b == 0 ? (uint32_t)KM_TC_AUG_BYTES : (uint32_t)KM_TC_KS_BYTES;
+                        const uint32_t bytes = b == 0 ? AUG_BYTES : TC_STAGE_BYTES;
                         mbar_wait_bounded(&bars->b_empty[s], ph ^ 1);
                         km_mbar_expect_tx(&bars->b_full[s], bytes);
                         km_bulk_g2s(bst + (size_t)s * TC_STAGE_BYTES, src, bytes, &bars->b_full[s]);
@@ -260,18 +330,30 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
                 }
             }
         }
+    } else if (warp == 1 && PAIR && crank != 0) {
+        // ================= peer CTA: relay "my half of block b has landed" to the leader =============
+        if (lane == 0) {
+            uint32_t it = 0;
+            for (int64_t step = step0; step < nsteps; step += step_inc)
+                for (int t = 0; t < ntc; ++t)
+                    for (int b = 0; b <= nks; ++b, ++it) {
+                        const int s = it % TC_BSTAGES;
+                        mbar_wait_bounded(&bars->b_full[s], (it / TC_BSTAGES) & 1);
+                        mbar_arrive_remote(&bars->b_full[s], 0);
+                    }
+        }
     } else if (warp == 1) {
         // ================= MMA issuer (warp-uniform control flow, one elected lane issues) =======
-        // instruction descriptor: D=F32, A=B=TF32, both K-major, N=256, M=128
+        // instruction descriptor: D=F32, A=B=TF32, both K-major, N=256, M=128 (256 across a CTA pair)
         const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(KM_TC_BN >> 3) << 17) |
-                               ((uint32_t)(128 >> 4) << 24);
+                               ((uint32_t)((PAIR ? 256 : 128) >> 4) << 24);
         const uint32_t desc_hi = (128u >> 4) | (1u << 14);           // SBO = 128 B, version = 1
         const uint32_t a_lbo = (2048u >> 4) << 16;                   // A: 128 rows x 16 B per K chunk
-        const uint32_t b_lbo = ((uint32_t)(KM_TC_BN * 16) >> 4) << 16;  // B: 256 rows x 16 B per K chunk
+        const uint32_t b_lbo = ((BROWS * 16) >> 4) << 16;            // B: BROWS rows x 16 B per K chunk
         const uint32_t xb_a = km_smem_u32(xb), bst_a = km_smem_u32(bst);
         const bool leader = elect_one();
         uint32_t it = 0, ita = 0, li = 0;
-        for (int64_t step = blockIdx.x; step < nsteps; step += gridDim.x, ++li) {
+        for (int64_t step = step0; step < nsteps; step += step_inc, ++li) {
             const uint32_t xbuf = DBUF ? (li & 1) : 0u;
             mbar_wait_bounded(&bars->x_ready[xbuf], (DBUF ? (li >> 1) : li) & 1);
             tc_fence_after();
@@ -289,23 +371,37 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
                     tc_fence_after();
                     const uint32_t bh = (((bst_a + s * TC_STAGE_BYTES) & 0x3FFFFu) >> 4) | b_lbo;
                     if (leader) {
-                        if (b == 0) {
-                            // augmented step first (overwrites the accumulator): + ||c||^2
-                            mma_tf32(dcol, ah + (uint32_t)nch * 128u, bh, desc_hi, idesc, 0u);
+                        const uint32_t ao = (uint32_t)(b - 1) * 256u;
+                        const uint32_t bl = bh + ((TC_STAGE_BYTES / 2) >> 4);
+                        if (PAIR) {
+                            if (b == 0) {
+                                mma_tf32_pair(dcol, ah + (uint32_t)nch * 128u, bh, desc_hi, idesc, 0u);
+                            } else {
+                                mma_tf32_pair(dcol, al + ao, bh, desc_hi, idesc, 1u);
+                                mma_tf32_pair(dcol, ah + ao, bl, desc_hi, idesc, 1u);
+                                mma_tf32_pair(dcol, ah + ao, bh, desc_hi, idesc, 1u);
+                            }
+                            mma_commit_pair(&bars->b_empty[s]);
+                            if (b == nks) mma_commit_pair(&bars->a_full[a]);
                         } else {
-                            const uint32_t ao = (uint32_t)(b - 1) * 256u;
-                            const uint32_t bl = bh + ((uint32_t)(KM_TC_KS_BYTES / 2) >> 4);
-                            mma_tf32(dcol, al + ao, bh, desc_hi, idesc, 1u);
-                            mma_tf32(dcol, ah + ao, bl, desc_hi, idesc, 1u);
-                            mma_tf32(dcol, ah + ao, bh, desc_hi, idesc, 1u);
+                            if (b == 0) {
+                                // augmented step first (overwrites the accumulator): + ||c||^2
+                                mma_tf32(dcol, ah + (uint32_t)nch * 128u, bh, desc_hi, idesc, 0u);
+                            } else {
+                                mma_tf32(dcol, al + ao, bh, desc_hi, idesc, 1u);
+                                mma_tf32(dcol, ah + ao, bl, desc_hi, idesc, 1u);
+                                mma_tf32(dcol, ah + ao, bh, desc_hi, idesc, 1u);
+                            }
+                            mma_commit(&bars->b_empty[s]);  // smem stage reusable once these MMAs retire
+                            if (b == nks) mma_commit(&bars->a_full[a]);  // accumulator ready for the epilogue
                         }
-                        mma_commit(&bars->b_empty[s]);  // smem stage reusable once these MMAs retire
-                        if (b == nks) mma_commit(&bars->a_full[a]);  // accumulator ready for the epilogue
                     }
                     __syncwarp();
                 }
             }
-            if (leader) mma_commit(&bars->x_free[xbuf]);  // X buffer no longer read by the tensor core
+            if (leader) {   // X buffer no longer read by the tensor core
+                if (PAIR) mma_commit_pair(&bars->x_free[xbuf]); else mma_commit(&bars->x_free[xbuf]);
+            }
             __syncwarp();
         }
     } else {
@@ -364,7 +460,7 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
             }
             bars->xn_part[bf][g][rl] = s;
             km_fence_proxy_async();   // generic-proxy smem writes -> visible to the tensor core (async proxy)
-            mbar_arrive(&bars->x_ready[bf]);
+            if (PAIR) mbar_arrive_remote(&bars->x_ready[bf], 0); else mbar_arrive(&bars->x_ready[bf]);
         };
         // pending result of the previous step (its outputs are written one tile into the next step)
         bool pend = false;
@@ -426,18 +522,18 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
         };
 
         uint32_t it = 0, li = 0;
-        if ((int64_t)blockIdx.x < nsteps) {
-            const int64_t row = (int64_t)blockIdx.x * TC_ROWS + rl;
+        if (step0 < nsteps) {
+            const int64_t row = step0 * step_rows + crank * TC_ROWS + rl;
             issue_row_loads(X + (row < n ? row : 0) * ldx, row < n);
             stage_store(0, 0);
         }
         // tile after which the NEXT step's rows are staged (never inside the tile loop with one X buffer)
         const int t_stage = DBUF ? (ntc > 1 ? 1 : 0) : -1;
-        for (int64_t step = blockIdx.x; step < nsteps; step += gridDim.x, ++li) {
-            const int64_t row0 = step * TC_ROWS;
+        for (int64_t step = step0; step < nsteps; step += step_inc, ++li) {
+            const int64_t row0 = step * step_rows + crank * TC_ROWS;
             const uint32_t xbuf = DBUF ? (li & 1) : 0u;
-            const bool have_next = step + gridDim.x < nsteps;
-            const int64_t nrow = (step + gridDim.x) * TC_ROWS + rl;
+            const bool have_next = step + step_inc < nsteps;
+            const int64_t nrow = (step + step_inc) * step_rows + crank * TC_ROWS + rl;
             // two independent trackers (even / odd columns) double the ILP of the dependent min/max chains
             float best2[2] = {INFINITY, INFINITY}, second2[2] = {INFINITY, INFINITY};
             int bidx2[2] = {0, 0};
@@ -476,7 +572,7 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
                     if (c + 1 < 4) tmem_ld_wait();
                 }
                 tc_fence_before();
-                mbar_arrive(&bars->a_empty[a]);
+                if (PAIR) mbar_arrive_remote(&bars->a_empty[a], 0); else mbar_arrive(&bars->a_empty[a]);
 
                 if (t == 0 && pend) {          // previous step's outputs (its X buffer is still intact)
                     output_pending();
@@ -520,9 +616,13 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
 
     tc_fence_before();
     __syncthreads();
+    if (PAIR) cluster_sync_all();   // neither CTA may leave (or free TMEM) while the pair's MMAs / arrivals are in flight
     if (warp == 1) {
         tc_fence_after();
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
+        if (PAIR)
+            asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
+        else
+            asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
     }
 }
 
@@ -534,26 +634,47 @@ int km_launch_assign_tc(const float *X, int64_t n, int d, int64_t ldx, const voi
     const int kpad = km_tc_kpad(d);
     const int nch = kpad / 4;
     const bool dbuf = d <= 64;
+    const bool pair = km_tc_pair_mode();
+    const size_t stage_bytes = pair ? 8192 : 16384;
+    const int nstages = pair ? 8 : 5;
     const size_t smem = (dbuf ? 2 : 1) * ((size_t)(nch + 2) * 128 * 16 + (size_t)nch * 128 * 16) +
-                        (size_t)TC_BSTAGES * TC_STAGE_BYTES + sizeof(TcBars) + 64;
+                        (size_t)nstages * stage_bytes + sizeof(TcBars) + 64;
     const bool vec = (d % 4 == 0) && (ldx % 4 == 0) && ((reinterpret_cast<uintptr_t>(X) & 15) == 0);
-    int64_t steps = (n + TC_ROWS - 1) / TC_ROWS;
-    const int grid = (int)(steps < KM_NUM_SMS ? steps : KM_NUM_SMS);
+    const int64_t step_rows = pair ? 2 * TC_ROWS : TC_ROWS;
+    int64_t steps = (n + step_rows - 1) / step_rows;
+    const int max_units = pair ? KM_NUM_SMS / 2 : KM_NUM_SMS;
+    const int units = (int)(steps < max_units ? steps : max_units);
     const unsigned char *img = pk + L.off_tc;
     const float *c32 = reinterpret_cast<const float *>(pk + L.off_c32);
     const unsigned int *cmax = reinterpret_cast<const unsigned int *>(pk + L.off_cmax);
-#define TC_LAUNCH(VEC_, DBUF_)                                                                              \
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(pair ? 2 * units : units);
+    cfg.blockDim = dim3(TC_THREADS);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr1[1];
+    attr1[0].id = cudaLaunchAttributeClusterDimension;
+    attr1[0].val.clusterDim.x = 2;
+    attr1[0].val.clusterDim.y = 1;
+    attr1[0].val.clusterDim.z = 1;
+    cfg.attrs = attr1;
+    cfg.numAttrs = pair ? 1 : 0;
+#define TC_LAUNCH(VEC_, DBUF_, PAIR_)                                                                      \
     {                                                                                                       \
-        auto kern = assign_tc_f32_kernel<VEC_, DBUF_>;                                                      \
+        auto kern = assign_tc_f32_kernel<VEC_, DBUF_, PAIR_>;                                               \
         static bool attr[KM_MAX_DEVICES] = {};                                                              \
         if (int rc = km_set_smem_once(kern, 227 * 1024, attr)) return rc;                                   \
-        kern<<<grid, TC_THREADS, smem, st>>>(X, n, d, ldx, img, c32, cmax, k, labels, mind2, flag_rows,     \
-                                             flag_count);                                                   \
+        cudaError_t le = cudaLaunchKernelEx(&cfg, kern, X, n, d, ldx, img, c32, cmax, k, labels, mind2,     \
+                                            flag_rows, flag_count);                                         \
+        if (le != cudaSuccess) return (int)le;                                                              \
     }
-    if (vec && dbuf) TC_LAUNCH(true, true)
-    else if (vec) TC_LAUNCH(true, false)
-    else if (dbuf) TC_LAUNCH(false, true)
-    else TC_LAUNCH(false, false)
+#define TC_LAUNCH_VD(PAIR_)                     \
+    if (vec && dbuf) TC_LAUNCH(true, true, PAIR_) \
+    else if (vec) TC_LAUNCH(true, false, PAIR_)   \
+    else if (dbuf) TC_LAUNCH(false, true, PAIR_)  \
+    else TC_LAUNCH(false, false, PAIR_)
+    if (pair) { TC_LAUNCH_VD(true) } else { TC_LAUNCH_VD(false) }
+#undef TC_LAUNCH_VD
 #undef TC_LAUNCH
     return (int)cudaGetLastError();
 }

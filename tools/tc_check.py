@@ -14,14 +14,15 @@ def run(n, d, k, seed=0):
     Xd = eng.to_device(X); pack = eng.pack(eng.to_device(Cq, torch.float64))
     D = ((X.astype(np.float64)[:, None, :] - Cq[None]) ** 2).sum(-1) if n * k <= 4e7 else None
     out = {}
-    for var in (1, 2):
+    for var in (1, 2, 3):
         lib.b200km_set_option(1, var)
+        pack = eng.pack(eng.to_device(Cq, torch.float64))   # the tcgen05 image layout depends on the variant
         lab, m2 = eng.assign(Xd, pack, refine=False)
         torch.cuda.synchronize()
         out[var] = (lab.cpu().numpy().copy(), m2.cpu().numpy().copy())
     lib.b200km_set_option(1, 0)
     l1, l2 = out[1][0], out[2][0]
-    msg = f"n={n} d={d} k={k}: ffma-vs-tc label mismatches {int((l1 != l2).sum())}"
+    msg = f"n={n} d={d} k={k}: ffma-vs-tc label mismatches {int((l1 != l2).sum())}, ffma-vs-pair {int((l1 != out[3][0]).sum())}"
     if D is not None:
         ref = D.argmin(1)
         msg += f"; ffma-vs-f64 {(l1 != ref).sum()}, tc-vs-f64 {(l2 != ref).sum()}; mind2 maxrel {np.abs(out[2][1]-D.min(1)).max()/D.min(1).max():.2e}"
@@ -33,9 +34,9 @@ for shape in [(256, 64, 64), (256, 64, 128), (1000, 64, 1024), (5000, 32, 256), 
 import itertools
 for n, d, k in [(8_000_000, 64, 1024), (1_000_000, 128, 8192), (16_000_000, 32, 256)]:
   X = torch.randn(n, d, device=eng.device); C = torch.randn(k, d, dtype=torch.float64, device=eng.device) * 3
-  pack = eng.pack(C)
-  for var in (1, 2):
+  for var in (1, 2, 3):
     lib.b200km_set_option(1, var)
+    pack = eng.pack(C)
     lab, m2 = eng.assign(X, pack, refine=False)
     torch.cuda.synchronize(); t0 = time.perf_counter()
     for _ in range(3): eng.assign(X, pack, lab, m2, refine=False)
