@@ -38,6 +38,13 @@ WORKLOADS = {
     "c1": (1_000_000, 16, 8, "float64", "C1: N=1e6 rows per GPU, d=16, k=8, float64 blobs"),
     "c4": (25_000_000, 128, 8192, "float32", "C4 shard: N=2e8/8=2.5e7 rows per GPU, d=128, k=8192, float32 blobs"),
 }
+# DRAM traffic of the dominant kernel per row, from the committed `ncu --set full` captures
+# (dram__bytes_read.sum + dram__bytes_write.sum of one launch / rows of that launch); scaled by the rows of a
+# bench launch to fill roofline.traffic.  Source files under profiles/.
+NCU_TRAFFIC_BYTES_PER_ROW = {
+    ("c3", "tc"): ((1.024942e9 + 33.665792e6) / 4_000_000, "profiles/r1_k1_tcgen05_ncu_full_raw.csv"),
+    ("c3", "ffma"): ((1.025531e9 + 33.185536e6) / 4_000_000, "profiles/r1_k1_ffma_ncu_full_raw.csv"),
+}
 METRIC = "lloyd_points_per_sec"
 UNIT = "points/s"
 
@@ -364,6 +371,11 @@ def run_ours(args):
         ach = bytes_alg / (k1_avg_ms * 1e-3) / 1e9
         roof.update({"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
                      "peak_source": peak_src, "fma_pipe_peak_tflops": fma_peak})
+    tkey = (args.workload, "tc" if k1_is_tc else ("ffma" if k1_is_ffma else "other"))
+    if tkey in NCU_TRAFFIC_BYTES_PER_ROW:
+        bpr, src = NCU_TRAFFIC_BYTES_PER_ROW[tkey]
+        roof["traffic"] = bpr * n_local
+        roof["traffic_source"] = f"{src}: {bpr:.1f} B/row measured by ncu on a 4e6-row launch of this kernel, x rows"
     roof["k1_ms_per_launch"] = k1_avg_ms
     roof["k1_share_of_step"] = k1_avg_ms / ms_per_step
     roof["alg_bytes_per_launch"] = bytes_alg

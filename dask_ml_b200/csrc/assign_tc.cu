@@ -104,6 +104,17 @@ __device__ __forceinline__ void mbar_arrive_remote(uint64_t *bar, uint32_t rank)
         "r"(rank)
         : "memory");
 }
+// the same without release semantics (no cluster-scope fence): for arrivals that only pass on an event whose
+// ordering is already established elsewhere (TMA completion observed on a local barrier; TMEM reads ordered
+// by tcgen05.fence)
+__device__ __forceinline__ void mbar_arrive_remote_relaxed(uint64_t *bar, uint32_t rank) {
+    asm volatile(
+        "{\n\t.reg .b32 ra;\n\t"
+        "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
+        "mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [ra];\n\t}" ::"r"(km_smem_u32(bar)),
+        "r"(rank)
+        : "memory");
+}
 __device__ __forceinline__ bool elect_one() {
     uint32_t pred;
     asm volatile(
@@ -339,7 +350,7 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
                     for (int b = 0; b <= nks; ++b, ++it) {
                         const int s = it % TC_BSTAGES;
                         mbar_wait_bounded(&bars->b_full[s], (it / TC_BSTAGES) & 1);
-                        mbar_arrive_remote(&bars->b_full[s], 0);
+                        mbar_arrive_remote_relaxed(&bars->b_full[s], 0);
                     }
         }
     } else if (warp == 1) {
@@ -572,7 +583,7 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
                     if (c + 1 < 4) tmem_ld_wait();
                 }
                 tc_fence_before();
-                if (PAIR) mbar_arrive_remote(&bars->a_empty[a], 0); else mbar_arrive(&bars->a_empty[a]);
+                if (PAIR) mbar_arrive_remote_relaxed(&bars->a_empty[a], 0); else mbar_arrive(&bars->a_empty[a]);
 
                 if (t == 0 && pend) {          // previous step's outputs (its X buffer is still intact)
                     output_pending();
