@@ -49,6 +49,7 @@ class CudaEngine:
         self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
         self.launches = 0  # kernels launched through this engine (bench.py reports it)
         self.k1_events = None  # bench.py: set to a list to collect (start, end) CUDA events around K1
+        self.trace = None      # tools/: set to a list to collect (entry point, event) per launch
         self._scratch = {}
 
     # ---- plumbing -------------------------------------------------------------------------
@@ -59,6 +60,10 @@ class CudaEngine:
         rc = getattr(self.lib, name)(*args)
         _lib.check(rc, name)
         self.launches += launches
+        if self.trace is not None:   # tools/: (entry point, CUDA event recorded right after its launch)
+            ev = torch.cuda.Event(enable_timing=True)
+            ev.record(torch.cuda.current_stream(self.device))
+            self.trace.append((name, ev))
 
     def _buf(self, key, shape, dtype) -> torch.Tensor:
         """Reusable scratch tensor (grown on demand) -- keeps the Lloyd loop allocation-free."""
@@ -77,6 +82,57 @@ class CudaEngine:
         if dtype is not None and t.dtype != dtype:
             t = t.to(dtype)
         return t.to(self.device, non_blocking=True).contiguous()
+
+    STREAM_MIN_BYTES = 64 << 20   # host inputs at least this big are uploaded in overlapped row chunks
+    STREAM_CHUNKS = 8
+
+    def to_device_streamed(self, a) -> torch.Tensor:
+        """Device tensor for a 2-D HOST array whose upload is deferred: ``start_upload`` later issues the copy in
+        row chunks on a side stream and attaches ``_b200_pending = [(r0, r1, event), ...]``; a consumer makes its
+        stream wait for a chunk's event and can compute on the first rows while the rest is still crossing
+        PCIe (the first Lloyd pass and the NaN/inf scan do exactly that).  The start is deferred so that the
+        caller's small host->device copies (initial centres) are queued on the copy engine BEFORE the big
+        one -- H2D copies execute in issue order whatever their stream."""
+        t = a if isinstance(a, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(a))
+        t = t.contiguous()
+        dst = torch.empty(t.shape, dtype=t.dtype, device=self.device)
+        dst._b200_host = t
+        dst._b200_pending = None
+        return dst
+
+    def start_upload(self, dst: torch.Tensor) -> None:
+        t = getattr(dst, "_b200_host", None)
+        if t is None:
+            return
+        n = t.shape[0]
+        if not hasattr(self, "_copy_stream"):
+            self._copy_stream = torch.cuda.Stream(device=self.device)
+        cs = self._copy_stream
+        cs.wait_stream(torch.cuda.current_stream(self.device))
+        # (no dst.record_stream: every consumer waits for the chunk events on the compute stream, so the
+        #  tensor's last use is ordered after the copies and the caching allocator may recycle it normally)
+        pending = []
+        step = -(-n // self.STREAM_CHUNKS)
+        with torch.cuda.stream(cs):
+            for r0 in range(0, n, step):
+                r1 = min(n, r0 + step)
+                dst[r0:r1].copy_(t[r0:r1], non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(cs)
+                pending.append((r0, r1, ev))
+        dst._b200_pending = pending
+        dst._b200_host = None
+        dst._b200_src = t   # keep the (possibly temporary) host buffer alive until the copies are done
+
+    def wait_pending(self, X: torch.Tensor) -> None:
+        """Start (if needed) and make the current stream wait for every upload chunk of X (no host sync)."""
+        self.start_upload(X)
+        pending = getattr(X, "_b200_pending", None)
+        if pending:
+            cur = torch.cuda.current_stream(self.device)
+            for _, _, ev in pending:
+                cur.wait_event(ev)
+            X._b200_pending = None
 
     @staticmethod
     def _check_matrix(X: torch.Tensor):
@@ -286,12 +342,17 @@ class CudaEngine:
                        self._stream())
         return out
 
-    def has_nonfinite(self, X: torch.Tensor) -> bool:
+    def nonfinite_flag(self, X: torch.Tensor, bad: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """Device flag (int32[1]) that becomes non-zero when X holds a NaN / inf; no host sync."""
         n, d, ldx = self._check_matrix(X)
-        bad = torch.zeros(1, dtype=torch.int32, device=self.device)
+        if bad is None:
+            bad = torch.zeros(1, dtype=torch.int32, device=self.device)
         if n and d:
             self._call(f"b200km_count_nonfinite_{_suffix(X)}", X.data_ptr(), n, d, ldx, bad.data_ptr(), self._stream())
-        return bool(bad.item())
+        return bad
+
+    def has_nonfinite(self, X: torch.Tensor) -> bool:
+        return bool(self.nonfinite_flag(X).item())
 
     def make_blobs(self, n: int, d: int, centers: torch.Tensor, cluster_std: float = 1.0, seed: int = 0,
                    row_offset: int = 0, dtype=torch.float32, out: Optional[torch.Tensor] = None) -> torch.Tensor:

@@ -134,9 +134,17 @@ class KMeans(TransformerMixin, BaseEstimator):
         self.copy_x = copy_x
         self.n_init = n_init
 
+    _NONFINITE_MSG = "Input contains NaN, infinity or a value too large for dtype('float64')."
+
     @_timed(_logger=logger)
-    def _check_array(self, X):
-        """reference :171-202 -> a (n, d) float32/float64 tensor on the device."""
+    def _check_array(self, X, defer=False):
+        """reference :171-202 -> a (n, d) float32/float64 tensor on the device.
+
+        ``defer=True`` (used by ``fit``): a large HOST input is uploaded in row chunks on a side stream and the
+        NaN/inf scan runs chunk by chunk behind the copies; the tensor comes back with the outstanding chunks
+        attached so the first Lloyd pass can start on the first rows while the rest is still crossing PCIe.
+        The scan's verdict is read -- and the reference's ValueError raised -- at the first host
+        synchronisation of the fit (end of Lloyd iteration 0)."""
         try:
             import pandas as pd
 
@@ -149,14 +157,21 @@ class KMeans(TransformerMixin, BaseEstimator):
         X = check_array(X, accept_dask_dataframe=False, accept_unknown_chunks=False, accept_sparse=False,
                         remove_zero_chunks=True, ensure_all_finite=False)
         eng = get_engine()
+        host = isinstance(X, np.ndarray) or (isinstance(X, torch.Tensor) and not X.is_cuda)
+        if (defer and host and hasattr(eng, "to_device_streamed") and X.ndim == 2
+                and str(X.dtype).replace("torch.", "") in ("float32", "float64")
+                and X.shape[0] * X.shape[1] * (4 if "32" in str(X.dtype) else 8) >= eng.STREAM_MIN_BYTES):
+            Xd = eng.to_device_streamed(X)
+            # the scan itself (:195-201) is interleaved with Lloyd iteration 0, chunk by chunk
+            Xd._b200_bad = torch.zeros(1, dtype=torch.int32, device=eng.device)
+            return Xd
         Xd = _dev(X, eng)  # int32 -> float32, int64 -> float64 (:187-190)
         if Xd.shape[0] and eng.has_nonfinite(Xd):  # :195-201
-            msg = "Input contains NaN, infinity or a value too large for dtype('float64')."
-            raise ValueError(msg)
+            raise ValueError(self._NONFINITE_MSG)
         return Xd
 
     def fit(self, X, y=None):
-        X = self._check_array(X)
+        X = self._check_array(X, defer=True)
         labels, centroids, inertia, n_iter = k_means(
             X, self.n_clusters, oversampling_factor=self.oversampling_factor, random_state=self.random_state,
             init=self.init, return_n_iter=True, max_iter=self.max_iter, init_max_iter=self.init_max_iter,
@@ -424,6 +439,13 @@ def _kmeans_single_lloyd(X, n_clusters, max_iter=300, init="k-means||", verbose=
     X = _as_device_matrix(X)
     eng = get_engine(X.device)
     comm = _comm.default_comm()
+    streamed = getattr(X, "_b200_host", None) is not None   # deferred upload (KMeans._check_array(defer=True))
+    if streamed and not isinstance(init, (np.ndarray, torch.Tensor)):
+        eng.wait_pending(X)                        # the initialisers read all of X: no overlap, scan it now
+        streamed = False
+        X._b200_bad = None
+        if eng.has_nonfinite(X):
+            raise ValueError(KMeans._NONFINITE_MSG)
     centers = k_init(X, n_clusters, init=init, oversampling_factor=oversampling_factor, random_state=random_state,
                      max_iter=init_max_iter, n_init=n_init)
     dt = X.dtype
@@ -438,21 +460,44 @@ def _kmeans_single_lloyd(X, n_clusters, max_iter=300, init="k-means||", verbose=
     pack = None
     shift = None
     i = -1
+    pending = None
+    if streamed:
+        # every small host->device copy of the set-up is queued by now: start the big one behind them
+        eng.start_upload(X)
+        pending = X._b200_pending
     for i in range(max_iter):
         with _timer("Lloyd loop %2d." % i, _logger=logger):
             acc.zero_()
-            if getattr(eng, "can_fuse", lambda *_: False)(k, P):
-                # HBM-bound regime (tiny k, d): labels + sums + counts + inertia in ONE pass over X
-                if n_local:
-                    eng.assign_update(X, centers64, labels, mind2, acc)  # :576-598, :616
-            else:
+            fused = getattr(eng, "can_fuse", lambda *_: False)(k, P)
+            if not fused:
                 pack = eng.pack(centers64, pack)
-                if n_local:
-                    eng.assign(X, pack, labels, mind2)  # :576-579
-                    eng.update(X, labels, mind2, k, acc)  # :582-598, :616
+            # iteration 0 of a streamed upload runs chunk by chunk behind the copy engine; afterwards one span
+            spans = [(0, n_local, None)] if not pending else pending
+            for r0, r1, ev in spans:
+                if r1 <= r0:
+                    continue
+                if ev is not None:
+                    torch.cuda.current_stream(eng.device).wait_event(ev)
+                Xs, ls, ms = X[r0:r1], labels[r0:r1], mind2[r0:r1]
+                if ev is not None:
+                    eng.nonfinite_flag(Xs, X._b200_bad)  # the deferred NaN/inf scan (:195-201)
+                if fused:
+                    # HBM-bound regime (tiny k, d): labels + sums + counts + inertia in ONE pass over X
+                    eng.assign_update(Xs, centers64, ls, ms, acc)  # :576-598, :616
+                else:
+                    eng.assign(Xs, pack, ls, ms)  # :576-579
+                    eng.update(Xs, ls, ms, k, acc)  # :582-598, :616
+            if pending:
+                pending = None
+                X._b200_pending = None
             comm.allreduce_sum_(acc)  # the chain-sum over blocks / workers (:595-597)
             eng.finalize(acc, k, P, centers64, new64, shift_t)  # :600-605
             shift = float(shift_t.item())  # :602 -- the one round trip per iteration
+            bad = getattr(X, "_b200_bad", None)
+            if bad is not None:            # deferred NaN/inf verdict of a streamed upload (:195-201)
+                X._b200_bad = None
+                if int(bad.item()):
+                    raise ValueError(KMeans._NONFINITE_MSG)
             logger.info("Shift: %0.4f", shift)
             if shift < tol:
                 break

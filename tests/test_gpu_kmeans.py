@@ -296,3 +296,28 @@ def test_kmeans_parallel_init_quality():
         ours.append(_km()(n_clusters=10, random_state=seed, max_iter=30).fit(X).inertia_)
         theirs.append(orc.KMeansOracle(n_clusters=10, random_state=seed, max_iter=30, chunks=(len(X),)).fit(X).inertia_)
     assert np.median(ours) < 1.3 * np.median(theirs)
+
+
+def test_streamed_upload_fit_matches_plain_fit(monkeypatch):
+    """fit() on a large HOST array uploads in overlapped chunks and runs Lloyd iteration 0 behind the copies;
+    results must equal the fit on the same data already resident on the device, and a NaN must still raise."""
+    import torch
+    from dask_ml_b200._engine import CudaEngine
+
+    monkeypatch.setattr(CudaEngine, "STREAM_MIN_BYTES", 1 << 16)
+    X, _ = blobs(30011, 16, 40, seed=5, dtype=np.float32)
+    init = X[:40].copy()
+    a = _km()(n_clusters=40, init=init, max_iter=3, tol=0.0).fit(X)                       # streamed (host ndarray)
+    b = _km()(n_clusters=40, init=init, max_iter=3, tol=0.0).fit(torch.from_numpy(X).cuda())  # resident
+    npt.assert_array_equal(a.labels_.compute(), b.labels_.compute())
+    npt.assert_allclose(a.cluster_centers_, b.cluster_centers_, rtol=1e-6)
+    npt.assert_allclose(a.inertia_, b.inertia_, rtol=1e-9)
+    c = _km()(n_clusters=8, random_state=0, max_iter=2).fit(X)                             # k-means|| waits for all chunks
+    assert np.isfinite(c.inertia_)
+    Xbad = X.copy()
+    Xbad[29000, 3] = np.inf
+    with pytest.raises(ValueError, match="Input contains NaN, infinity"):
+        _km()(n_clusters=40, init=init, max_iter=3, tol=0.0).fit(Xbad)
+    pinned = torch.from_numpy(X).pin_memory()
+    d_ = _km()(n_clusters=40, init=init, max_iter=3, tol=0.0).fit(pinned)
+    npt.assert_array_equal(d_.labels_.compute(), b.labels_.compute())
