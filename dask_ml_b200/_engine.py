@@ -355,12 +355,14 @@ class CudaEngine:
         return bool(self.nonfinite_flag(X).item())
 
     def make_blobs(self, n: int, d: int, centers: torch.Tensor, cluster_std: float = 1.0, seed: int = 0,
-                   row_offset: int = 0, dtype=torch.float32, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+                   row_offset: int = 0, dtype=torch.float32, out: Optional[torch.Tensor] = None,
+                   y: Optional[torch.Tensor] = None) -> torch.Tensor:
         if out is None:
             out = torch.empty(n, d, dtype=dtype, device=self.device)
         centers = centers.to(device=self.device, dtype=out.dtype).contiguous()
         self._call(f"b200km_make_blobs_{_suffix(out)}", out.data_ptr(), n, d, d, centers.data_ptr(), centers.shape[0],
-                   float(cluster_std), int(seed), int(row_offset), self._stream())
+                   float(cluster_std), int(seed) & (2**64 - 1), int(row_offset), (y.data_ptr() if y is not None else None),
+                   self._stream())
         return out
 
 

@@ -58,8 +58,8 @@ PROTOTYPES = {
     "b200km_row_norms_f64": (c_int, [_P, c_int64, c_int, c_int64, _P, c_int, _P]),
     "b200km_count_nonfinite_f32": (c_int, [_P, c_int64, c_int, c_int64, _P, _P]),
     "b200km_count_nonfinite_f64": (c_int, [_P, c_int64, c_int, c_int64, _P, _P]),
-    "b200km_make_blobs_f32": (c_int, [_P, c_int64, c_int, c_int64, _P, c_int, c_float, c_uint64, c_int64, _P]),
-    "b200km_make_blobs_f64": (c_int, [_P, c_int64, c_int, c_int64, _P, c_int, c_double, c_uint64, c_int64, _P]),
+    "b200km_make_blobs_f32": (c_int, [_P, c_int64, c_int, c_int64, _P, c_int, c_float, c_uint64, c_int64, _P, _P]),
+    "b200km_make_blobs_f64": (c_int, [_P, c_int64, c_int, c_int64, _P, c_int, c_double, c_uint64, c_int64, _P, _P]),
     "b200km_probe_ffma": (c_int, [_P, c_int, c_int, c_int, _P]),
     "b200km_probe_dfma": (c_int, [_P, c_int, c_int, c_int, _P]),
 }

@@ -170,7 +170,7 @@ extern "C" int b200km_count_nonfinite_f64(const double *X, int64_t n, int d, int
 template <typename T>
 __global__ void __launch_bounds__(256)
 blobs_kernel(T *__restrict__ X, int64_t n, int d, int64_t ldx, const T *__restrict__ centers, int k_true, T cluster_std,
-             uint32_t k0, uint32_t k1, int64_t row_offset) {
+             uint32_t k0, uint32_t k1, int64_t row_offset, int32_t *__restrict__ y) {
     const int dq = (d + 3) / 4;
     const int64_t total = n * (int64_t)dq;
     for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
@@ -179,6 +179,7 @@ blobs_kernel(T *__restrict__ X, int64_t n, int d, int64_t ldx, const T *__restri
         const uint64_t g = (uint64_t)(row_offset + r);
         const KmPhilox4 cw = km_philox4x32_10((uint32_t)g, (uint32_t)(g >> 32), 0u, 0x626c6f62u, k0, k1);
         const int cls = (int)(cw.x % (uint32_t)k_true);
+        if (y && q == 0) y[r] = cls;
         const KmPhilox4 w = km_philox4x32_10((uint32_t)g, (uint32_t)(g >> 32), (uint32_t)q + 1u, 0x626c6f62u, k0, k1);
         // two Box-Muller pairs
         const float u0 = ((float)(w.x >> 8) + 0.5f) * (1.0f / 16777216.0f);
@@ -200,21 +201,21 @@ blobs_kernel(T *__restrict__ X, int64_t n, int d, int64_t ldx, const T *__restri
 
 template <typename T>
 static int blobs_impl(T *X, int64_t n, int d, int64_t ldx, const T *centers, int k_true, T cluster_std, uint64_t seed,
-                      int64_t row_offset, void *stream) {
+                      int64_t row_offset, int32_t *y, void *stream) {
     KM_CHECK_ARG(X && centers && n > 0 && d > 0 && k_true > 0 && ldx >= d, B200KM_EINVAL);
     int64_t blocks = (n * (int64_t)((d + 3) / 4) + 255) / 256;
     if (blocks > KM_NUM_SMS * 32) blocks = KM_NUM_SMS * 32;
     blobs_kernel<T><<<(unsigned)blocks, 256, 0, km_stream(stream)>>>(X, n, d, ldx, centers, k_true, cluster_std,
-                                                                     (uint32_t)seed, (uint32_t)(seed >> 32), row_offset);
+                                                                     (uint32_t)seed, (uint32_t)(seed >> 32), row_offset, y);
     KM_LAUNCH_RET();
 }
 extern "C" int b200km_make_blobs_f32(float *X, int64_t n, int d, int64_t ldx, const float *centers, int k_true,
-                                     float cluster_std, uint64_t seed, int64_t row_offset, void *stream) {
-    return blobs_impl<float>(X, n, d, ldx, centers, k_true, cluster_std, seed, row_offset, stream);
+                                     float cluster_std, uint64_t seed, int64_t row_offset, int32_t *y, void *stream) {
+    return blobs_impl<float>(X, n, d, ldx, centers, k_true, cluster_std, seed, row_offset, y, stream);
 }
 extern "C" int b200km_make_blobs_f64(double *X, int64_t n, int d, int64_t ldx, const double *centers, int k_true,
-                                     double cluster_std, uint64_t seed, int64_t row_offset, void *stream) {
-    return blobs_impl<double>(X, n, d, ldx, centers, k_true, cluster_std, seed, row_offset, stream);
+                                     double cluster_std, uint64_t seed, int64_t row_offset, int32_t *y, void *stream) {
+    return blobs_impl<double>(X, n, d, ldx, centers, k_true, cluster_std, seed, row_offset, y, stream);
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -213,14 +213,16 @@ int b200km_count_nonfinite_f64(const double *X, int64_t n, int d, int64_t ldx, i
 
 /* ------------------------------------------------------------------------------------------
  * Synthetic blobs on the device (benchmark input):
- *   X[i,:] = centers[(row_offset+i) % k_true, :] + cluster_std * N(0,1)   (Philox + Box-Muller)
+ *   X[i,:] = centers[class(row_offset+i), :] + cluster_std * N(0,1)   (Philox + Box-Muller; the class of a
+ *   row is a Philox hash of its GLOBAL index, so any sharding generates the same array); y (nullable,
+ *   int32) receives the class of every row.
  * Mirrors the distribution of dask_ml.datasets.make_blobs (R/dask_ml/datasets.py:78-205): equal
  * points per centre, isotropic Gaussian; NOT its bit stream.
  * ---------------------------------------------------------------------------------------- */
 int b200km_make_blobs_f32(float *X, int64_t n, int d, int64_t ldx, const float *centers, int k_true,
-                          float cluster_std, uint64_t seed, int64_t row_offset, void *stream);
+                          float cluster_std, uint64_t seed, int64_t row_offset, int32_t *y, void *stream);
 int b200km_make_blobs_f64(double *X, int64_t n, int d, int64_t ldx, const double *centers, int k_true,
-                          double cluster_std, uint64_t seed, int64_t row_offset, void *stream);
+                          double cluster_std, uint64_t seed, int64_t row_offset, int32_t *y, void *stream);
 
 /* FP32 FFMA / FP64 DFMA pipe microbenchmarks (roofline denominators that MEASURED_PEAKS.json
  * lacks).  Runs `iters` dependent-chain FMA bundles on every SM; writes a checksum to `sink`

@@ -284,3 +284,23 @@ def test_assign_update_fused(eng, n, d, k, dtype):
     with pytest.raises(ValueError):
         eng.assign_update(eng.to_device(np.zeros((4, 40), dtype)), eng.to_device(np.zeros((2, 40)), torch.float64),
                           labels[:4], mind2[:4], acc)
+
+
+def test_datasets_make_blobs_api(eng):
+    """dask_ml_b200.datasets.make_blobs: reference signature (dask_ml/datasets.py:78-205), device output."""
+    from dask_ml_b200.datasets import make_blobs
+
+    X, y = make_blobs(n_samples=60000, n_features=5, centers=4, cluster_std=0.5, random_state=0, chunks=1000)
+    assert X.shape == (60000, 5) and X.dtype == np.float64 and y.shape == (60000,) and y.dtype == np.int64
+    Xh, yh = X.compute(), y.compute()
+    assert set(np.unique(yh)) == {0, 1, 2, 3}
+    c = np.random.RandomState(0).uniform(-10, 10, size=(4, 5))      # the centres sklearn would draw first
+    for j in range(4):
+        npt.assert_allclose(Xh[yh == j].mean(0), c[j], atol=0.02)
+        assert abs((Xh[yh == j] - c[j]).std() - 0.5) < 0.01
+    X2, y2 = make_blobs(n_samples=100, n_features=5, centers=4, cluster_std=0.5, random_state=0, row_offset=500)
+    npt.assert_array_equal(X2.compute(), Xh[500:600])                # shard invariance
+    npt.assert_array_equal(y2.compute(), yh[500:600])
+    Xc, _ = make_blobs(n_samples=10, centers=np.array([[-7.0, -7.0], [0.0, 0.0], [7.0, 7.0]]), cluster_std=0.1,
+                       random_state=0, dtype="f4")
+    assert Xc.shape == (10, 2) and Xc.dtype == np.float32
