@@ -216,6 +216,19 @@ update_seg_kernel(const T *__restrict__ X, int64_t n, int d, int64_t ldx, const 
                 const int fa = f0 + lane, fb = f0 + 32 + lane;
                 double a0 = 0.0, a1 = 0.0;
                 int p = s0;
+                for (; p + 8 <= s1; p += 8) {   // 8 rows (16 loads per lane) in flight
+                    T v[8], w[8];
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) {
+                        const int64_t ro = (int64_t)order[p + u] * ldx;
+                        v[u] = fa < d ? __ldg(Xb + ro + fa) : (T)0;
+                        w[u] = fb < d ? __ldg(Xb + ro + fb) : (T)0;
+                    }
+                    a0 += (((double)v[0] + (double)v[1]) + ((double)v[2] + (double)v[3])) +
+                          (((double)v[4] + (double)v[5]) + ((double)v[6] + (double)v[7]));
+                    a1 += (((double)w[0] + (double)w[1]) + ((double)w[2] + (double)w[3])) +
+                          (((double)w[4] + (double)w[5]) + ((double)w[6] + (double)w[7]));
+                }
                 for (; p + 4 <= s1; p += 4) {
                     const int r0 = order[p], r1 = order[p + 1], r2 = order[p + 2], r3 = order[p + 3];
                     T v0 = (T)0, v1 = (T)0, v2 = (T)0, v3 = (T)0, w0 = (T)0, w1 = (T)0, w2 = (T)0, w3 = (T)0;
@@ -279,7 +292,7 @@ static int update_impl(const T *X, int64_t n, int d, int64_t ldx, const int32_t 
         static bool attr_set[KM_MAX_DEVICES] = {};
         if (int rc = km_set_smem_once(kern, 110 * 1024, attr_set)) return rc;
         int64_t blocks = (n + SEG_R - 1) / SEG_R;
-        const int64_t cap = (int64_t)KM_NUM_SMS * 2;
+        const int64_t cap = (int64_t)KM_NUM_SMS * 4;   // several CTAs per SM: one sorts while another gathers
         if (blocks > cap) blocks = cap;
         kern<<<(unsigned)blocks, SEG_THREADS, seg_smem, st>>>(X, n, d, ldx, labels, mind2, k, acc, scale_sqrt);
     } else {
