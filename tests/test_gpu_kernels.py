@@ -304,3 +304,23 @@ def test_datasets_make_blobs_api(eng):
     Xc, _ = make_blobs(n_samples=10, centers=np.array([[-7.0, -7.0], [0.0, 0.0], [7.0, 7.0]]), cluster_std=0.1,
                        random_state=0, dtype="f4")
     assert Xc.shape == (10, 2) and Xc.dtype == np.float32
+
+
+def test_assign_random_shapes_fuzz(eng):
+    """Many random (n, d, k) shapes through every K1 path (tcgen05, FFMA, row-block fp64) against the oracle."""
+    import torch
+
+    rs = np.random.RandomState(123)
+    for trial in range(36):
+        d = int(rs.choice([1, 2, 3, 5, 8, 12, 16, 24, 31, 40, 64, 65, 96, 128, 130, 200]))
+        k = int(rs.choice([1, 2, 7, 16, 17, 40, 100, 255, 256, 257, 513, 1000]))
+        n = int(rs.choice([1, 5, 127, 128, 129, 255, 256, 257, 1000, 4097]))
+        dtype = np.float32 if trial % 3 else np.float64
+        X, C = blobs(n, d, k, seed=1000 + trial, dtype=dtype)
+        C = C + 0.3 * rs.standard_normal(C.shape)
+        variant = 1 + trial % 3 if dtype == np.float32 else 0
+        eng.lib.b200km_set_option(1, variant)
+        try:
+            _check_assign(eng, X, C)
+        finally:
+            eng.lib.b200km_set_option(1, 0)

@@ -321,3 +321,51 @@ def test_streamed_upload_fit_matches_plain_fit(monkeypatch):
     pinned = torch.from_numpy(X).pin_memory()
     d_ = _km()(n_clusters=40, init=init, max_iter=3, tol=0.0).fit(pinned)
     npt.assert_array_equal(d_.labels_.compute(), b.labels_.compute())
+
+
+def test_random_and_pp_init_paths():
+    """init='random' (reference :426-432) and init='k-means++' (:404-423, sklearn on a host copy) run and give
+    sane clusterings; the upstream tests for these are skipped, so only behaviour is pinned here."""
+    X, true = blobs(6000, 5, 6, seed=21, dtype=np.float32)
+    base = orc.KMeansOracle(n_clusters=6, random_state=0, chunks=(len(X),)).fit(X).inertia_
+    for init in ("random", "k-means++"):
+        km = _km()(n_clusters=6, init=init, random_state=0, max_iter=50).fit(X)
+        assert km.cluster_centers_.shape == (6, 5) and km.labels_.compute().max() < 6
+        assert km.inertia_ < 3.0 * base
+    # reproducible for a fixed seed
+    a = _km()(n_clusters=6, init="random", random_state=7, max_iter=5).fit(X).cluster_centers_
+    b = _km()(n_clusters=6, init="random", random_state=7, max_iter=5).fit(X).cluster_centers_
+    npt.assert_array_equal(a, b)
+
+
+def test_kmeans_parallel_is_reproducible_and_seed_dependent():
+    X, _ = blobs(8000, 6, 12, seed=3, dtype=np.float32)
+    a = _km()(n_clusters=12, random_state=5, max_iter=3).fit(X)
+    b = _km()(n_clusters=12, random_state=5, max_iter=3).fit(X)
+    c = _km()(n_clusters=12, random_state=6, max_iter=3).fit(X)
+    npt.assert_array_equal(a.cluster_centers_, b.cluster_centers_)
+    assert not np.array_equal(a.cluster_centers_, c.cluster_centers_)
+
+
+def test_degenerate_inputs():
+    """Duplicated rows, duplicated centres, a single row, a single feature, constant data, large magnitudes."""
+    rs = np.random.RandomState(0)
+    # every row duplicated 3x and init drawn from duplicates -> exact ties everywhere
+    base = rs.standard_normal((300, 7)).astype(np.float32)
+    X = np.repeat(base, 3, axis=0)
+    init = X[:20].copy()
+    _lloyd_vs_oracle(X, 20, init, 3, 0.0, 1e-5)
+    # one feature, two clusters
+    X1 = np.concatenate([rs.normal(-5, 1, 500), rs.normal(5, 1, 500)]).reshape(-1, 1)
+    _lloyd_vs_oracle(X1, 2, X1[[0, 999]].copy(), 10, 0.0, 1e-10)
+    # constant data: all distances equal -> label 0 everywhere (lowest index), other clusters go to the origin
+    Xc = np.full((64, 3), 2.5, np.float32)
+    km = _km()(n_clusters=3, init=np.array([[2.5, 2.5, 2.5], [2.5, 2.5, 2.5], [0, 0, 0]], np.float32), max_iter=2, tol=0.0).fit(Xc)
+    assert (km.labels_.compute() == 0).all()
+    # large magnitudes (float32): the rounding bound scales with the norms, parity must hold
+    Xb, _ = blobs(4000, 24, 50, seed=8, dtype=np.float32)
+    Xb = (Xb * 1e4).astype(np.float32)
+    _lloyd_vs_oracle(Xb, 50, Xb[:50].copy(), 2, 0.0, 1e-5)
+    # a single row
+    km = _km()(n_clusters=1, init=np.zeros((1, 4)), max_iter=2).fit(np.ones((1, 4)))
+    npt.assert_allclose(km.cluster_centers_, np.ones((1, 4)))
