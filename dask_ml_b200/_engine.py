@@ -334,6 +334,20 @@ class CudaEngine:
                        self._stream())
         return out
 
+    KERNEL_KINDS = {"rbf": 2, "linear": 3, "polynomial": 4, "sigmoid": 5}
+
+    def pairwise_kernel(self, X: torch.Tensor, Y: torch.Tensor, kind: str, gamma: float = 1.0, coef0: float = 1.0,
+                        degree: int = 3) -> torch.Tensor:
+        """(n, k) kernel matrix between the rows of X and Y (b200km_pairwise_kernel_*)."""
+        n, d, ldx = self._check_matrix(X)
+        Y = Y.contiguous()
+        k = Y.shape[0]
+        out = torch.empty(n, k, dtype=X.dtype, device=self.device)
+        if n and k:
+            self._call(f"b200km_pairwise_kernel_{_suffix(X)}", X.data_ptr(), n, d, ldx, Y.data_ptr(), k, out.data_ptr(),
+                       self.KERNEL_KINDS[kind], float(gamma), float(coef0), int(degree), self._stream())
+        return out
+
     def row_norms(self, X: torch.Tensor, squared: bool = False) -> torch.Tensor:
         n, d, ldx = self._check_matrix(X)
         out = torch.empty(n, dtype=X.dtype, device=self.device)

@@ -54,6 +54,8 @@ PROTOTYPES = {
     "b200km_gather_rows_f64": (c_int, [_P, c_int64, c_int, c_int64, _P, c_int, _P, _P]),
     "b200km_cdist_f32": (c_int, [_P, c_int64, c_int, c_int64, _P, c_int, _P, _P, _P, c_int, _P]),
     "b200km_cdist_f64": (c_int, [_P, c_int64, c_int, c_int64, _P, c_int, _P, _P, _P, c_int, _P]),
+    "b200km_pairwise_kernel_f32": (c_int, [_P, c_int64, c_int, c_int64, _P, c_int, _P, c_int, c_double, c_double, c_int, _P]),
+    "b200km_pairwise_kernel_f64": (c_int, [_P, c_int64, c_int, c_int64, _P, c_int, _P, c_int, c_double, c_double, c_int, _P]),
     "b200km_row_norms_f32": (c_int, [_P, c_int64, c_int, c_int64, _P, c_int, _P]),
     "b200km_row_norms_f64": (c_int, [_P, c_int64, c_int, c_int64, _P, c_int, _P]),
     "b200km_count_nonfinite_f32": (c_int, [_P, c_int64, c_int, c_int64, _P, _P]),

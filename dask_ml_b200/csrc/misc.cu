@@ -10,10 +10,15 @@
 // ---------------------------------------------------------------------------------------------
 constexpr int CD_T = 64, CD_KC = 16;
 
+// epilogue modes of the tile kernel: the distance matrix itself, or one of dask-ml's pairwise kernels
+// (reference dask_ml/metrics/pairwise.py:135-191) applied to the same X.Y^T tile
+enum CdMode { CD_DIST = 0, CD_SQDIST = 1, CD_RBF = 2, CD_LINEAR = 3, CD_POLY = 4, CD_SIGMOID = 5 };
+
 template <typename T>
 __global__ void __launch_bounds__(256)
 cdist_kernel(const T *__restrict__ X, int64_t n, int d, int64_t ldx, const T *__restrict__ Y, int k,
-             const T *__restrict__ xnorm2, const T *__restrict__ ynorm2, T *__restrict__ out, int squared) {
+             const T *__restrict__ xnorm2, const T *__restrict__ ynorm2, T *__restrict__ out, int mode,
+             T gamma, T coef0, int degree) {
     __shared__ T As[CD_KC][CD_T + 4];
     __shared__ T Bs[CD_KC][CD_T + 4];
     const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
@@ -63,16 +68,29 @@ cdist_kernel(const T *__restrict__ X, int64_t n, int d, int64_t ldx, const T *__
             const int col = col0 + tx * 4 + j;
             if (col >= k) continue;
             const T yn = ynorm2 ? ynorm2[col] : yy[j];
-            T v = ((T)(-2) * acc[i][j] + xn) + yn;
-            v = v > (T)0 ? v : (T)0;
-            out[row * (int64_t)k + col] = squared ? v : sqrt(v);
+            T v;
+            if (mode <= CD_RBF) {
+                v = ((T)(-2) * acc[i][j] + xn) + yn;   // pairwise.py:101
+                v = v > (T)0 ? v : (T)0;               // :102
+                if (mode == CD_DIST) v = sqrt(v);
+                else if (mode == CD_RBF) v = exp(-gamma * v);   // rbf_kernel :143-151
+            } else if (mode == CD_LINEAR) {
+                v = acc[i][j];                          // linear_kernel :135-138
+            } else if (mode == CD_POLY) {
+                const T b = gamma * acc[i][j] + coef0;  // polynomial_kernel :154-167
+                v = (T)1;
+                for (int e = 0; e < degree; ++e) v *= b;
+            } else {
+                v = tanh(gamma * acc[i][j] + coef0);    // sigmoid_kernel :170-185
+            }
+            out[row * (int64_t)k + col] = v;
         }
     }
 }
 
 template <typename T>
 static int cdist_impl(const T *X, int64_t n, int d, int64_t ldx, const T *Y, int k, const T *xnorm2, const T *ynorm2,
-                      T *out, int squared, void *stream) {
+                      T *out, int mode, T gamma, T coef0, int degree, void *stream) {
     KM_CHECK_ARG(X && Y && out && n > 0 && d > 0 && k > 0 && ldx >= d, B200KM_EINVAL);
     const int64_t gy = (n + CD_T - 1) / CD_T;
     KM_CHECK_ARG(gy <= 65535LL * 65535LL, B200KM_ETOOBIG);
@@ -84,18 +102,30 @@ static int cdist_impl(const T *X, int64_t n, int d, int64_t ldx, const T *Y, int
         const int64_t nn = (n - r0) < nt * CD_T ? (n - r0) : nt * CD_T;
         dim3 grid((k + CD_T - 1) / CD_T, (unsigned)nt);
         cdist_kernel<T><<<grid, 256, 0, st>>>(X + r0 * ldx, nn, d, ldx, Y, k, xnorm2 ? xnorm2 + r0 : nullptr, ynorm2,
-                                              out + r0 * (int64_t)k, squared);
+                                              out + r0 * (int64_t)k, mode, gamma, coef0, degree);
     }
     KM_LAUNCH_RET();
 }
 
 extern "C" int b200km_cdist_f32(const float *X, int64_t n, int d, int64_t ldx, const float *Y, int k,
                                 const float *xnorm2, const float *ynorm2, float *out, int squared, void *stream) {
-    return cdist_impl<float>(X, n, d, ldx, Y, k, xnorm2, ynorm2, out, squared, stream);
+    return cdist_impl<float>(X, n, d, ldx, Y, k, xnorm2, ynorm2, out, squared ? CD_SQDIST : CD_DIST, 0.f, 0.f, 0, stream);
 }
 extern "C" int b200km_cdist_f64(const double *X, int64_t n, int d, int64_t ldx, const double *Y, int k,
                                 const double *xnorm2, const double *ynorm2, double *out, int squared, void *stream) {
-    return cdist_impl<double>(X, n, d, ldx, Y, k, xnorm2, ynorm2, out, squared, stream);
+    return cdist_impl<double>(X, n, d, ldx, Y, k, xnorm2, ynorm2, out, squared ? CD_SQDIST : CD_DIST, 0.0, 0.0, 0, stream);
+}
+
+// pairwise kernels on the same tile kernel (the SpectralClustering tail)
+extern "C" int b200km_pairwise_kernel_f32(const float *X, int64_t n, int d, int64_t ldx, const float *Y, int k,
+                                          float *out, int kind, double gamma, double coef0, int degree, void *stream) {
+    KM_CHECK_ARG(kind >= B200KM_KERNEL_RBF && kind <= B200KM_KERNEL_SIGMOID && degree >= 0, B200KM_EINVAL);
+    return cdist_impl<float>(X, n, d, ldx, Y, k, nullptr, nullptr, out, kind, (float)gamma, (float)coef0, degree, stream);
+}
+extern "C" int b200km_pairwise_kernel_f64(const double *X, int64_t n, int d, int64_t ldx, const double *Y, int k,
+                                          double *out, int kind, double gamma, double coef0, int degree, void *stream) {
+    KM_CHECK_ARG(kind >= B200KM_KERNEL_RBF && kind <= B200KM_KERNEL_SIGMOID && degree >= 0, B200KM_EINVAL);
+    return cdist_impl<double>(X, n, d, ldx, Y, k, nullptr, nullptr, out, kind, gamma, coef0, degree, stream);
 }
 
 // ---------------------------------------------------------------------------------------------

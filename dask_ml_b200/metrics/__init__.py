@@ -1,3 +1,8 @@
-from .pairwise import euclidean_distances, pairwise_distances, pairwise_distances_argmin_min  # noqa: F401
+from .pairwise import (  # noqa: F401
+    euclidean_distances,
+    pairwise_distances,
+    pairwise_distances_argmin_min,
+    pairwise_kernels,
+)
 
-__all__ = ["euclidean_distances", "pairwise_distances", "pairwise_distances_argmin_min"]
+__all__ = ["euclidean_distances", "pairwise_distances", "pairwise_distances_argmin_min", "pairwise_kernels"]

@@ -15,7 +15,8 @@ import torch
 from .._engine import get_engine
 from ..utils import DeviceArray
 
-__all__ = ["pairwise_distances_argmin_min", "pairwise_distances", "euclidean_distances"]
+__all__ = ["pairwise_distances_argmin_min", "pairwise_distances", "euclidean_distances", "pairwise_kernels",
+           "rbf_kernel", "linear_kernel", "polynomial_kernel", "sigmoid_kernel", "PAIRWISE_KERNEL_FUNCTIONS"]
 
 
 def _dev(X, eng=None, dtype=None) -> torch.Tensor:
@@ -120,3 +121,74 @@ def euclidean_distances(X, Y=None, Y_norm_squared=None, squared: bool = False, X
             raise ValueError("Incompatible dimensions for Y and Y_norm_squared")
         yn = eng.to_device(YY.reshape(-1), Xd.dtype)
     return DeviceArray(eng.cdist(Xd, Yd, squared=squared, xnorm2=xn, ynorm2=yn))
+
+
+# ----------------
+# Kernel functions (reference dask_ml/metrics/pairwise.py:135-226) -- the affinity blocks of
+# SpectralClustering's Nystrom embedding, the only in-tree caller of KMeans
+# ----------------
+def _kernel(X, Y, kind, gamma=None, coef0=1.0, degree=3):
+    eng = get_engine()
+    Xd = _dev(X, eng)
+    Yd = Xd if Y is None else _dev(Y, eng)
+    _check_same_features(Xd, Yd)  # check_pairwise_arrays (:108-128)
+    if Yd.dtype != Xd.dtype:
+        Xd, Yd = Xd.to(torch.float64), Yd.to(torch.float64)
+    if gamma is None:
+        gamma = 1.0 / Xd.shape[1]
+    return DeviceArray(eng.pairwise_kernel(Xd, Yd, kind, gamma=gamma, coef0=coef0, degree=degree))
+
+
+def linear_kernel(X, Y=None):
+    """reference :135-138 -- ``dot(X, Y.T)``."""
+    return _kernel(X, Y, "linear")
+
+
+def rbf_kernel(X, Y=None, gamma=None):
+    """reference :141-151 -- ``exp(-gamma * euclidean_distances(X, Y, squared=True))``, gamma default 1/d."""
+    return _kernel(X, Y, "rbf", gamma=gamma)
+
+
+def polynomial_kernel(X, Y=None, degree=3, gamma=None, coef0=1):
+    """reference :154-167 -- ``(gamma * dot(X, Y.T) + coef0) ** degree``."""
+    return _kernel(X, Y, "polynomial", gamma=gamma, coef0=coef0, degree=degree)
+
+
+def sigmoid_kernel(X, Y=None, gamma=None, coef0=1):
+    """reference :170-185 -- ``tanh(gamma * dot(X, Y.T) + coef0)``."""
+    return _kernel(X, Y, "sigmoid", gamma=gamma, coef0=coef0)
+
+
+PAIRWISE_KERNEL_FUNCTIONS = {
+    "rbf": rbf_kernel,
+    "linear": linear_kernel,
+    "polynomial": polynomial_kernel,
+    "sigmoid": sigmoid_kernel,
+}
+
+
+def pairwise_kernels(X, Y=None, metric="linear", filter_params=False, n_jobs=1, **kwds):
+    """reference :199-226 (same dispatch, same errors)."""
+    from sklearn.gaussian_process.kernels import Kernel as GPKernel
+    from sklearn.metrics.pairwise import KERNEL_PARAMS
+
+    if metric == "precomputed":
+        Xd = _dev(X)
+        Yn = Xd.shape[0] if Y is None else _dev(Y).shape[0]
+        if Xd.shape[1] != Yn:
+            raise ValueError(
+                "Precomputed metric requires shape (n_queries, n_indexed). Got (%d, %d) for %d indexed."
+                % (Xd.shape[0], Xd.shape[1], Yn)
+            )
+        return DeviceArray(Xd)
+    elif isinstance(metric, GPKernel):
+        raise NotImplementedError()
+    elif isinstance(metric, str) and metric in PAIRWISE_KERNEL_FUNCTIONS:
+        if filter_params:
+            kwds = dict((k, kwds[k]) for k in kwds if k in KERNEL_PARAMS[metric])
+        func = PAIRWISE_KERNEL_FUNCTIONS[metric]
+    elif callable(metric):
+        raise NotImplementedError()
+    else:
+        raise ValueError("Unknown kernel %r" % metric)
+    return func(X, Y, **kwds)

@@ -202,6 +202,20 @@ int b200km_cdist_f32(const float *X, int64_t n, int d, int64_t ldx, const float 
 int b200km_cdist_f64(const double *X, int64_t n, int d, int64_t ldx, const double *Y, int k,
                      const double *xnorm2, const double *ynorm2, double *out, int squared, void *stream);
 
+/* Kernel matrices on the same tile kernel: out[i,j] = kernel(x_i, y_j) in the input precision.
+ * Replaces: dask_ml.metrics.pairwise.{rbf,linear,polynomial,sigmoid}_kernel / pairwise_kernels
+ *           (R/dask_ml/metrics/pairwise.py:135-226), the affinity blocks of SpectralClustering's Nystrom
+ *           embedding (R/dask_ml/cluster/spectral.py:312-336) -- the only in-tree caller of KMeans.
+ *   kind: RBF exp(-gamma ||x-y||^2), LINEAR x.y, POLY (gamma x.y + coef0)^degree, SIGMOID tanh(gamma x.y + coef0) */
+#define B200KM_KERNEL_RBF 2
+#define B200KM_KERNEL_LINEAR 3
+#define B200KM_KERNEL_POLY 4
+#define B200KM_KERNEL_SIGMOID 5
+int b200km_pairwise_kernel_f32(const float *X, int64_t n, int d, int64_t ldx, const float *Y, int k, float *out,
+                               int kind, double gamma, double coef0, int degree, void *stream);
+int b200km_pairwise_kernel_f64(const double *X, int64_t n, int d, int64_t ldx, const double *Y, int k, double *out,
+                               int kind, double gamma, double coef0, int degree, void *stream);
+
 /* row_norms(X, squared) -- R/dask_ml/utils.py:83-88. */
 int b200km_row_norms_f32(const float *X, int64_t n, int d, int64_t ldx, float *out, int squared, void *stream);
 int b200km_row_norms_f64(const double *X, int64_t n, int d, int64_t ldx, double *out, int squared, void *stream);

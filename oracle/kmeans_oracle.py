@@ -554,3 +554,51 @@ class KMeansOracle:
 
     def fit_transform(self, X, y=None):
         return self.fit(X).transform(X)
+
+
+# --------------------------------------------------------------------------------------
+# SpectralClustering's Nystrom embedding (the in-tree caller of KMeans)
+# --------------------------------------------------------------------------------------
+def _pairwise_kernel(X, Y, metric, gamma=None, degree=3, coef0=1):
+    """R/dask_ml/metrics/pairwise.py:135-191 in numpy (gamma default 1/d)."""
+    if gamma is None:
+        gamma = 1.0 / X.shape[1]
+    if metric == "rbf":
+        return np.exp(-gamma * euclidean_distances(X, Y, squared=True))
+    if metric == "linear":
+        return X @ Y.T
+    if metric == "polynomial":
+        return (gamma * (X @ Y.T) + coef0) ** degree
+    if metric == "sigmoid":
+        return np.tanh(gamma * (X @ Y.T) + coef0)
+    raise ValueError("Unknown kernel %r" % metric)
+
+
+def spectral_embedding(X, keep, n_clusters, metric="rbf", gamma=1.0, degree=3, coef0=1):
+    """R/dask_ml/cluster/spectral.py:226-288 with ``keep`` (the sorted sampled row indices) supplied.
+    Returns (U2 (n, n_clusters) in the ORIGINAL row order, leading singular values)."""
+    from scipy.linalg import pinv, svd
+
+    X = np.asarray(X, dtype=float)  # :157
+    n = len(X)
+    n_components = len(keep)
+    inds = np.arange(n)
+    rest = ~np.isin(inds, keep)  # :231
+    X_keep, X_rest = X[keep], X[rest]
+    A = _pairwise_kernel(X_keep, X_keep, metric, gamma, degree, coef0)  # :318-319
+    B = _pairwise_kernel(X_keep, X_rest, metric, gamma, degree, coef0)  # :320-322
+    a = A.sum(0)  # :246-248
+    b1 = B.sum(1)
+    b2 = B.sum(0)
+    A_inv = pinv(A)  # :251
+    inner = A_inv.dot(b1)  # :253
+    d1_si = 1 / np.sqrt(a + b1)  # :254
+    d2_si = 1 / np.sqrt(b2 + B.T.dot(inner))  # :256
+    A2 = d1_si.reshape(-1, 1) * A * d1_si.reshape(1, -1)  # :260
+    B2 = d1_si.reshape(-1, 1) * B * d2_si.reshape(1, -1)  # :264
+    U_A, S_A, V_A = svd(A2)  # :267
+    V2 = np.sqrt(float(n_components) / n) * np.vstack([A2, B2.T]).dot(U_A[:, :n_clusters]).dot(
+        np.diag(1.0 / np.sqrt(S_A[:n_clusters])))  # :272-275
+    U2 = (V2.T / np.sqrt((V2 ** 2).sum(1))).T  # :283
+    idx = np.argsort(np.concatenate([keep, inds[rest]]))  # :288 (_slice_mostly_sorted)
+    return U2[idx], S_A[:n_clusters]
