@@ -404,6 +404,118 @@ static int launch_rb(const TX *X, int64_t n, int d, int64_t ldx, const double *c
     KM_LAUNCH_RET();
 }
 
+
+// =============================================================================================
+// tiled FP64 kernel (DFMA): float64 X with k > 16, d <= 128
+// =============================================================================================
+// Same structure as the FFMA kernel in double precision: 64 rows x 64 centroids per CTA step, 4x4 register
+// tile per thread, scores ||c||^2 - 2 x.c (sklearn's own float64 arithmetic), winner distance recomputed in
+// direct form.  float64 needs no re-decision pass.  Centroid tiles are staged from the pack's float64 copy
+// with coalesced loads (the next tile is prefetched into registers while the current one is multiplied).
+constexpr int AD_BM = 128, AD_BN = 64, AD_THREADS = 256;   // 8 x 4 register tile per thread
+constexpr int AD_XLD = AD_BM + 2;
+
+__global__ void __launch_bounds__(AD_THREADS, 2)
+assign_tiled_f64_kernel(const double *__restrict__ X, int64_t n, int d, int64_t ldx, const double *__restrict__ c64,
+                        const double *__restrict__ cn64, int k, int32_t *__restrict__ labels,
+                        double *__restrict__ mind2) {
+    extern __shared__ __align__(16) double smd[];
+    double *Xs = smd;                               // [d][AD_XLD]   (transposed X tile)
+    double *Cs = smd + (size_t)d * AD_XLD;          // [d][AD_BN]    (transposed centroid tile)
+    double *cns = Cs + (size_t)d * AD_BN;           // [AD_BN]
+    const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+    const int64_t row0 = (int64_t)blockIdx.x * AD_BM;
+    const int ntiles = (k + AD_BN - 1) / AD_BN;
+
+    for (int e = tid; e < AD_BM * d; e += AD_THREADS) {
+        const int m = e / d, f = e - m * d;
+        Xs[(size_t)f * AD_XLD + m] = row0 + m < n ? X[(row0 + m) * ldx + f] : 0.0;
+    }
+    double best[8];
+    int bidx[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { best[i] = INFINITY; bidx[i] = 0; }
+
+    for (int t = 0; t < ntiles; ++t) {
+        __syncthreads();   // previous tile fully consumed (also orders the Xs stores before the first use)
+        // stage the centroid tile transposed: element e -> centroid jj = e / d, feature f = e % d (coalesced)
+        for (int e = tid; e < AD_BN * d; e += AD_THREADS) {
+            const int jj = e / d, f = e - jj * d;
+            const int col = t * AD_BN + jj;
+            Cs[(size_t)f * AD_BN + jj] = col < k ? __ldg(c64 + (size_t)col * d + f) : 0.0;
+        }
+        if (tid < AD_BN) {
+            const int col = t * AD_BN + tid;
+            cns[tid] = col < k ? __ldg(cn64 + col) : INFINITY;
+        }
+        __syncthreads();
+        double acc[8][4];
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) acc[i][j] = 0.0;
+#pragma unroll 2
+        for (int f = 0; f < d; ++f) {
+            const double *xp = Xs + (size_t)f * AD_XLD + ty * 8;
+            const double *cp = Cs + (size_t)f * AD_BN + tx * 4;
+            const double2 x0 = *reinterpret_cast<const double2 *>(xp), x1 = *reinterpret_cast<const double2 *>(xp + 2);
+            const double2 x2 = *reinterpret_cast<const double2 *>(xp + 4), x3 = *reinterpret_cast<const double2 *>(xp + 6);
+            const double2 ca = *reinterpret_cast<const double2 *>(cp), cb = *reinterpret_cast<const double2 *>(cp + 2);
+            const double xr[8] = {x0.x, x0.y, x1.x, x1.y, x2.x, x2.y, x3.x, x3.y};
+            const double cr[4] = {ca.x, ca.y, cb.x, cb.y};
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) acc[i][j] = fma(xr[i], cr[j], acc[i][j]);
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const double v = fma(-2.0, acc[i][j], cns[tx * 4 + j]);
+                if (v < best[i]) { best[i] = v; bidx[i] = t * AD_BN + tx * 4 + j; }
+            }
+    }
+    // merge the 16 column threads of each row group (lowest index on exact ties)
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+#pragma unroll
+        for (int o = 1; o < 16; o <<= 1) {
+            const double ob = __shfl_xor_sync(0xffffffffu, best[i], o);
+            const int oi = __shfl_xor_sync(0xffffffffu, bidx[i], o);
+            if (ob < best[i] || (ob == best[i] && oi < bidx[i])) { best[i] = ob; bidx[i] = oi; }
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int m = ty * 8 + i;
+        int bi = bidx[i];
+        if (bi >= k) bi = k - 1;
+        const double *crow = c64 + (size_t)bi * d;
+        double s = 0.0;
+        for (int f = tx; f < d; f += 16) {
+            const double df = Xs[(size_t)f * AD_XLD + m] - __ldg(crow + f);
+            s = fma(df, df, s);
+        }
+#pragma unroll
+        for (int o = 1; o < 16; o <<= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        if (tx == i && row0 + m < n) {
+            labels[row0 + m] = bi;
+            if (mind2) mind2[row0 + m] = s;
+        }
+    }
+}
+
+static int launch_tiled_f64(const double *X, int64_t n, int d, int64_t ldx, const double *c64, const double *cn64,
+                            int k, int32_t *labels, double *mind2, cudaStream_t st) {
+    const size_t smem = sizeof(double) * ((size_t)d * AD_XLD + (size_t)d * AD_BN + AD_BN);
+    static bool attr_set[KM_MAX_DEVICES] = {};
+    if (int rc = km_set_smem_once(assign_tiled_f64_kernel, 200 * 1024, attr_set)) return rc;
+    const int64_t blocks = (n + AD_BM - 1) / AD_BM;
+    assign_tiled_f64_kernel<<<(unsigned)blocks, AD_THREADS, smem, st>>>(X, n, d, ldx, c64, cn64, k, labels, mind2);
+    KM_LAUNCH_RET();
+}
+
 // =============================================================================================
 // entry points
 // =============================================================================================
@@ -494,6 +606,10 @@ extern "C" int b200km_assign_f64(const double *X, int64_t n, int d, int64_t ldx,
     const double *c64 = reinterpret_cast<const double *>(static_cast<const unsigned char *>(pack) + L.off_c64);
     if (k <= 16 && d <= 32)
         return launch_rb<double, 256, 1, 8, false>(X, n, d, ldx, c64, nullptr, k, nullptr, nullptr, labels, mind2, st);
+    if (k > 16 && d <= 128 && g_k1_variant != 1) {   // the DFMA tile kernel (variant 1 keeps the row-block kernel)
+        const double *cn64 = reinterpret_cast<const double *>(static_cast<const unsigned char *>(pack) + L.off_cn64);
+        return launch_tiled_f64(X, n, d, ldx, c64, cn64, k, labels, mind2, st);
+    }
     return launch_rb<double, 32, 8, 8, false>(X, n, d, ldx, c64, nullptr, k, nullptr, nullptr, labels, mind2, st);
 }
 
