@@ -415,21 +415,31 @@ static int launch_rb(const TX *X, int64_t n, int d, int64_t ldx, const double *c
 constexpr int AD_BM = 128, AD_BN = 64, AD_THREADS = 256;   // 8 x 4 register tile per thread
 constexpr int AD_XLD = AD_BM + 2;
 
+// TX = storage type of X (float for the refine use); INDIRECT: the rows are rows[0 .. *nrows_ptr) (the flagged rows
+// of a float32 pass -- count read on the device) and the CTAs stride over them persistently.
+template <typename TX, bool INDIRECT>
 __global__ void __launch_bounds__(AD_THREADS, 2)
-assign_tiled_f64_kernel(const double *__restrict__ X, int64_t n, int d, int64_t ldx, const double *__restrict__ c64,
-                        const double *__restrict__ cn64, int k, int32_t *__restrict__ labels,
-                        double *__restrict__ mind2) {
+assign_tiled_f64_kernel(const TX *__restrict__ X, int64_t n, int d, int64_t ldx, const double *__restrict__ c64,
+                        const double *__restrict__ cn64, int k, const int32_t *__restrict__ rows,
+                        const int32_t *__restrict__ nrows_ptr, int32_t *__restrict__ labels,
+                        TX *__restrict__ mind2) {
     extern __shared__ __align__(16) double smd[];
     double *Xs = smd;                               // [d][AD_XLD]   (transposed X tile)
     double *Cs = smd + (size_t)d * AD_XLD;          // [d][AD_BN]    (transposed centroid tile)
     double *cns = Cs + (size_t)d * AD_BN;           // [AD_BN]
     const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
-    const int64_t row0 = (int64_t)blockIdx.x * AD_BM;
     const int ntiles = (k + AD_BN - 1) / AD_BN;
-
+    const int64_t nrows = INDIRECT ? (int64_t)(*nrows_ptr) : n;
+  for (int64_t row0 = (int64_t)blockIdx.x * AD_BM; row0 < nrows; row0 += (int64_t)gridDim.x * AD_BM) {
+    __syncthreads();   // (persistent INDIRECT loop) the previous row tile is fully written out
     for (int e = tid; e < AD_BM * d; e += AD_THREADS) {
         const int m = e / d, f = e - m * d;
-        Xs[(size_t)f * AD_XLD + m] = row0 + m < n ? X[(row0 + m) * ldx + f] : 0.0;
+        double v = 0.0;
+        if (row0 + m < nrows) {
+            const int64_t r = INDIRECT ? (int64_t)rows[row0 + m] : row0 + m;
+            v = (double)X[r * ldx + f];
+        }
+        Xs[(size_t)f * AD_XLD + m] = v;
     }
     double best[8];
     int bidx[8];
@@ -499,20 +509,26 @@ assign_tiled_f64_kernel(const double *__restrict__ X, int64_t n, int d, int64_t 
         }
 #pragma unroll
         for (int o = 1; o < 16; o <<= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-        if (tx == i && row0 + m < n) {
-            labels[row0 + m] = bi;
-            if (mind2) mind2[row0 + m] = s;
+        if (tx == i && row0 + m < nrows) {
+            const int64_t r = INDIRECT ? (int64_t)rows[row0 + m] : row0 + m;
+            labels[r] = bi;
+            if (mind2) mind2[r] = (TX)s;
         }
     }
+  }
 }
 
-static int launch_tiled_f64(const double *X, int64_t n, int d, int64_t ldx, const double *c64, const double *cn64,
-                            int k, int32_t *labels, double *mind2, cudaStream_t st) {
+template <typename TX, bool INDIRECT>
+static int launch_tiled_f64(const TX *X, int64_t n, int d, int64_t ldx, const double *c64, const double *cn64, int k,
+                            const int32_t *rows, const int32_t *nrows_ptr, int32_t *labels, TX *mind2,
+                            cudaStream_t st) {
     const size_t smem = sizeof(double) * ((size_t)d * AD_XLD + (size_t)d * AD_BN + AD_BN);
+    auto kern = assign_tiled_f64_kernel<TX, INDIRECT>;
     static bool attr_set[KM_MAX_DEVICES] = {};
-    if (int rc = km_set_smem_once(assign_tiled_f64_kernel, 200 * 1024, attr_set)) return rc;
-    const int64_t blocks = (n + AD_BM - 1) / AD_BM;
-    assign_tiled_f64_kernel<<<(unsigned)blocks, AD_THREADS, smem, st>>>(X, n, d, ldx, c64, cn64, k, labels, mind2);
+    if (int rc = km_set_smem_once(kern, 200 * 1024, attr_set)) return rc;
+    int64_t blocks = (n + AD_BM - 1) / AD_BM;
+    if (INDIRECT) blocks = (int64_t)KM_NUM_SMS * 2;   // persistent: the row count lives on the device
+    kern<<<(unsigned)blocks, AD_THREADS, smem, st>>>(X, n, d, ldx, c64, cn64, k, rows, nrows_ptr, labels, mind2);
     KM_LAUNCH_RET();
 }
 
@@ -608,7 +624,7 @@ extern "C" int b200km_assign_f64(const double *X, int64_t n, int d, int64_t ldx,
         return launch_rb<double, 256, 1, 8, false>(X, n, d, ldx, c64, nullptr, k, nullptr, nullptr, labels, mind2, st);
     if (k > 16 && d <= 128 && g_k1_variant != 1) {   // the DFMA tile kernel (variant 1 keeps the row-block kernel)
         const double *cn64 = reinterpret_cast<const double *>(static_cast<const unsigned char *>(pack) + L.off_cn64);
-        return launch_tiled_f64(X, n, d, ldx, c64, cn64, k, labels, mind2, st);
+        return launch_tiled_f64<double, false>(X, n, d, ldx, c64, cn64, k, nullptr, nullptr, labels, mind2, st);
     }
     return launch_rb<double, 32, 8, 8, false>(X, n, d, ldx, c64, nullptr, k, nullptr, nullptr, labels, mind2, st);
 }
@@ -623,6 +639,8 @@ extern "C" int b200km_refine_f64(const float *X, int64_t n, int d, int64_t ldx, 
     const KmPackLayout L = km_pack_layout(k, d);
     const double *c64 = reinterpret_cast<const double *>(static_cast<const unsigned char *>(pack) + L.off_c64);
     const double *cn64 = reinterpret_cast<const double *>(static_cast<const unsigned char *>(pack) + L.off_cn64);
+    // (measured: with ~0.2-0.5 % of the rows flagged, the row-block kernel's 32-row groups spread over more CTAs
+    //  and beat the DFMA tile kernel's 128-row tiles at every BASELINE size, so it stays the refine kernel)
     return launch_rb<float, 32, 8, 8, true>(X, n, d, ldx, c64, cn64, k, flag_rows, flag_count, labels, mind2, st);
 }
 
