@@ -538,6 +538,7 @@ static int launch_tiled_f64(const TX *X, int64_t n, int d, int64_t ldx, const do
 
 static int g_k1_variant = 0;  // B200KM_OPT_K1_VARIANT: 0 auto, 1 FFMA, 2 tcgen05 (one CTA), 3 tcgen05 (CTA pair)
 bool km_tc_pair_mode() { return g_k1_variant == 3; }
+bool km_tc_small_enabled() { return g_k1_variant == 0; }   // auto only: variant 2 keeps the general tcgen05 kernel
 static int g_k2_variant = 0;  // B200KM_OPT_K2_VARIANT: 0 auto, 1 owner table, 2 chunk sort, 3 global atomics
 int km_k2_variant() { return g_k2_variant; }
 

@@ -49,6 +49,18 @@ __device__ __forceinline__ void mbar_wait_bounded(uint64_t *bar, uint32_t parity
         if (!done && ++spins > TC_SPIN_LIMIT) __trap();
     } while (!done);
 }
+// non-blocking probe of a barrier phase
+__device__ __forceinline__ bool mbar_test(uint64_t *bar, uint32_t parity) {
+    uint32_t done;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(km_smem_u32(bar)), "r"(parity)
+        : "memory");
+    return done != 0;
+}
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 
@@ -203,7 +215,7 @@ __global__ void __launch_bounds__(64) pack_tc_kernel(int k, int d, unsigned char
         float v = 0.f;
         if (j < k && f < d) v = -2.f * c32[(size_t)j * d + f];
         const float h = tf32_rna(v);
-        const float l = tf32_rna(v - h);
+        const float l = v - h;            // exact; read by the tensor core as TF32 (low 13 bits ignored)
         const int ks = f >> 3, fc = f & 7;
         unsigned char *blk = img + aug_bytes + (size_t)ks * ks_bytes;
         const size_t o = ((size_t)(fc >> 2) * BR + jr) * 4 + (fc & 3);
@@ -230,6 +242,7 @@ __global__ void __launch_bounds__(64) pack_tc_kernel(int k, int d, unsigned char
 }
 
 bool km_tc_pair_mode();  // assign.cu: true when K1 runs on CTA pairs (cta_group::2)
+bool km_tc_small_enabled();   // assign.cu: false when the small-k kernel is switched off (variant 2 forces the general one)
 
 int km_launch_pack_tc(int k, int d, void *pack, cudaStream_t st) {
     if (d > KM_TC_MAX_D) return 0;
@@ -424,14 +437,15 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
         const int q4 = warp & 3;                 // TMEM lane quarter this warp may access
         const int rl = q4 * 32 + lane;           // row within the tile == TMEM lane
         const float cmax = __uint_as_float(*cmax_bits);
-        const float bound_scale = 2.0f * (float)(d + 8) * 1.1920929e-07f;
-        constexpr int NCH_H = KM_TC_MAX_D / 8;   // K chunks per half (max)
+        const float bound_scale = 2.0f * (float)(d + 12) * 1.1920929e-07f;
+        constexpr int NCH_H = DBUF ? KM_TC_MAX_D / 16 : KM_TC_MAX_D / 8;   // K chunks per half (max; d <= 64 when DBUF)
         const int nch_h = nch / 2;               // nch is even (kpad multiple of 8)
         const int c_lo = g * nch_h;              // first K chunk of this half
 
         // ---- software-pipelined helpers (loads are issued one epilogue tile before they are used) ----
-        float4 ld[NCH_H];                         // in-flight global loads (half an X row or half a centre row)
-        auto issue_row_loads = [&](const float *src, bool live) {
+        using LdRegs = float4[NCH_H];             // in-flight global loads (half an X row or half a centre row)
+        LdRegs ld;
+        auto issue_row_loads = [&](LdRegs &ld, const float *src, bool live) {
 #pragma unroll
             for (int c = 0; c < NCH_H; ++c) {
                 float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -451,7 +465,7 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
             }
         };
         // split ld[] (half an X row) into TF32 hi/lo parts in X buffer `bf`; `use` = earlier stagings of it
-        auto stage_store = [&](uint32_t bf, uint32_t use) {
+        auto stage_store = [&](const LdRegs &ld, uint32_t bf, uint32_t use) {
             if (use > 0) mbar_wait_bounded(&bars->x_free[bf], (use - 1) & 1);  // tensor core done with it
             unsigned char *ph = xb + (size_t)bf * xbuf_bytes + (size_t)rl * 16;
             unsigned char *pl = ph + xhi_bytes;
@@ -463,8 +477,9 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
                     s = fmaf(v.x, v.x, s); s = fmaf(v.y, v.y, s); s = fmaf(v.z, v.z, s); s = fmaf(v.w, v.w, s);
                     float4 h, l;
                     h.x = tf32_rna(v.x); h.y = tf32_rna(v.y); h.z = tf32_rna(v.z); h.w = tf32_rna(v.w);
-                    l.x = tf32_rna(v.x - h.x); l.y = tf32_rna(v.y - h.y);
-                    l.z = tf32_rna(v.z - h.z); l.w = tf32_rna(v.w - h.w);
+                    // low parts are stored exactly (fp32): the tensor core ignores the 13 low mantissa bits of a
+                    // TF32 operand, and h + l == x lets the epilogue rebuild the row without error
+                    l.x = v.x - h.x; l.y = v.y - h.y; l.z = v.z - h.z; l.w = v.w - h.w;
                     *reinterpret_cast<float4 *>(ph + (size_t)(c_lo + c) * 2048) = h;
                     *reinterpret_cast<float4 *>(pl + (size_t)(c_lo + c) * 2048) = l;
                 }
@@ -493,7 +508,7 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
         };
         // partial winner distance (direct form, fp32) over this half's K chunks from ld[] (= centre row half);
         // the upper half publishes its part, the lower half adds it and writes labels / mind2 / near-tie flag
-        auto output_pending = [&]() {
+        auto output_pending = [&](const LdRegs &ld) {
             const unsigned char *ph = xb + (size_t)p_buf * xbuf_bytes + (size_t)rl * 16;
             const unsigned char *pl = ph + xhi_bytes;
             float s = 0.f;
@@ -532,44 +547,29 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
             }
         };
 
-        uint32_t it = 0, li = 0;
-        if (step0 < nsteps) {
-            const int64_t row = step0 * step_rows + crank * TC_ROWS + rl;
-            issue_row_loads(X + (row < n ? row : 0) * ldx, row < n);
-            stage_store(0, 0);
-        }
-        // tile after which the NEXT step's rows are staged (never inside the tile loop with one X buffer)
-        const int t_stage = DBUF ? (ntc > 1 ? 1 : 0) : -1;
-        for (int64_t step = step0; step < nsteps; step += step_inc, ++li) {
-            const int64_t row0 = step * step_rows + crank * TC_ROWS;
-            const uint32_t xbuf = DBUF ? (li & 1) : 0u;
-            const bool have_next = step + step_inc < nsteps;
-            const int64_t nrow = (step + step_inc) * step_rows + crank * TC_ROWS + rl;
-            // two independent trackers (even / odd columns) double the ILP of the dependent min/max chains
-            float best2[2] = {INFINITY, INFINITY}, second2[2] = {INFINITY, INFINITY};
-            int bidx2[2] = {0, 0};
-            for (int t = 0; t < ntc; ++t, ++it) {
-                // loads issued here land while this tile's scores are being tracked
-                if (t == 0 && pend) {
-                    merge_pending();
-                    issue_row_loads(c32 + (size_t)p_bi * d, true);
-                }
-                if (t == t_stage && have_next && !(t == 0 && pend))
-                    issue_row_loads(X + (nrow < n ? nrow : 0) * ldx, nrow < n);
-
-                const int a = it % TC_ASTAGES;
-                const uint32_t aph = (it / TC_ASTAGES) & 1;
-                mbar_wait_bounded(&bars->a_full[a], aph);
-                tc_fence_after();
-                const uint32_t tbase = tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(a * KM_TC_BN + g * 128);
-                uint32_t ra[32], rb[32];
-                tmem_ld32(tbase, ra);
-                tmem_ld_wait();
+        // two independent trackers (even / odd columns) double the ILP of the dependent min/max chains
+        float best2[2], second2[2];
+        int bidx2[2];
+        // this thread's 128-column half of column tile t (accumulator stage of ring position `it`):
+        // TMEM -> registers -> trackers, 4 chunks of 32 columns
+        auto track_tile = [&](int t, uint32_t it) {
+            constexpr int NC = 4;
+            const int col0 = g * 128;
+            const int a = it % TC_ASTAGES;
+            const uint32_t aph = (it / TC_ASTAGES) & 1;
+            mbar_wait_bounded(&bars->a_full[a], aph);
+            tc_fence_after();
+            const uint32_t tbase = tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(a * KM_TC_BN + col0);
+            uint32_t ra[32], rb[32];
+            tmem_ld32(tbase, ra);
+            tmem_ld_wait();
 #pragma unroll
-                for (int c = 0; c < 4; ++c) {   // this half's 4 chunks of 32 columns
-                    uint32_t (&cur)[32] = (c & 1) ? rb : ra;
-                    uint32_t (&nxt)[32] = (c & 1) ? ra : rb;
-                    if (c + 1 < 4) tmem_ld32(tbase + (uint32_t)((c + 1) * 32), nxt);  // flies under this chunk
+            for (int c = 0; c < NC; ++c) {
+                uint32_t (&cur)[32] = (c & 1) ? rb : ra;
+                uint32_t (&nxt)[32] = (c & 1) ? ra : rb;
+                if (c + 1 < NC) tmem_ld32(tbase + (uint32_t)((c + 1) * 32), nxt);  // flies under this chunk
+                const int cb = t * KM_TC_BN + col0 + c * 32;
+                if (cb < k) {               // chunks made of padding columns only cannot win (warp-uniform)
                     const float before0 = best2[0], before1 = best2[1];
                     int jloc0 = 0, jloc1 = 0;
 #pragma unroll
@@ -577,51 +577,109 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
                         track(__uint_as_float(cur[j]), j, best2[0], second2[0], jloc0);
                         track(__uint_as_float(cur[j + 1]), j + 1, best2[1], second2[1], jloc1);
                     }
-                    const int cb = t * KM_TC_BN + g * 128 + c * 32;
                     bidx2[0] = best2[0] < before0 ? cb + jloc0 : bidx2[0];
                     bidx2[1] = best2[1] < before1 ? cb + jloc1 : bidx2[1];
-                    if (c + 1 < 4) tmem_ld_wait();
                 }
-                tc_fence_before();
-                if (PAIR) mbar_arrive_remote_relaxed(&bars->a_empty[a], 0); else mbar_arrive(&bars->a_empty[a]);
+                if (c + 1 < NC) tmem_ld_wait();
+            }
+            tc_fence_before();
+            if (PAIR) mbar_arrive_remote_relaxed(&bars->a_empty[a], 0); else mbar_arrive(&bars->a_empty[a]);
+        };
+        // publish this half's result of a step (an exact tie keeps the lower column; it is flagged anyway)
+        auto publish = [&](uint32_t xbuf, int64_t row, uint32_t use) {
+            const bool takeb = best2[1] < best2[0] || (best2[1] == best2[0] && bidx2[1] < bidx2[0]);
+            bars->m_best[xbuf][g][rl] = takeb ? best2[1] : best2[0];
+            bars->m_idx[xbuf][g][rl] = takeb ? bidx2[1] : bidx2[0];
+            bars->m_second[xbuf][g][rl] = fminf(fminf(second2[0], second2[1]), takeb ? best2[0] : best2[1]);
+            mbar_arrive(&bars->m_ready[xbuf]);
+            pend = true;
+            p_row = row;
+            p_buf = xbuf;
+            p_use = use;
+        };
 
-                if (t == 0 && pend) {          // previous step's outputs (its X buffer is still intact)
-                    output_pending();
-                    pend = false;
-                    if (t_stage == 0 && have_next) issue_row_loads(X + (nrow < n ? nrow : 0) * ldx, nrow < n);
-                }
-                // stage the NEXT step's rows into the other X buffer (free: the previous step is written out),
-                // so the tensor core never waits for X at a step boundary
-                if (t == t_stage && have_next) stage_store(xbuf ^ 1, (li + 1) >> 1);
-            }
-            {
-                // publish this half's result (an exact tie keeps the lower column; it is flagged anyway)
-                const bool takeb = best2[1] < best2[0] || (best2[1] == best2[0] && bidx2[1] < bidx2[0]);
-                bars->m_best[xbuf][g][rl] = takeb ? best2[1] : best2[0];
-                bars->m_idx[xbuf][g][rl] = takeb ? bidx2[1] : bidx2[0];
-                bars->m_second[xbuf][g][rl] = fminf(fminf(second2[0], second2[1]), takeb ? best2[0] : best2[1]);
-                mbar_arrive(&bars->m_ready[xbuf]);
-                pend = true;
-                p_row = row0 + rl;
-                p_buf = xbuf;
-                p_use = DBUF ? (li >> 1) : li;
-            }
-            if (!DBUF) {
-                // one X buffer: write this step out now, then restage once the tensor core has let go of it
-                merge_pending();
-                issue_row_loads(c32 + (size_t)p_bi * d, true);
-                output_pending();
-                pend = false;
-                if (have_next) {
-                    issue_row_loads(X + (nrow < n ? nrow : 0) * ldx, nrow < n);
-                    stage_store(0, li + 1);
-                }
-            }
+        uint32_t it = 0, li = 0;
+        if (step0 < nsteps) {
+            const int64_t row = step0 * step_rows + crank * TC_ROWS + rl;
+            issue_row_loads(ld, X + (row < n ? row : 0) * ldx, row < n);
+            stage_store(ld, 0, 0);
         }
-        if (pend) {
-            merge_pending();
-            issue_row_loads(c32 + (size_t)p_bi * d, true);
-            output_pending();
+        if (DBUF && ntc == 1) {
+            // ---- one column tile per step (k <= 256): nothing inside a step to hide the step boundary under, so
+            // the pipeline runs one step deeper -- step s+1 is staged BEFORE the scores of step s are tracked
+            // (its MMAs then run under that epilogue) and the rows of step s+2 are already in flight.
+            LdRegs ldc;                       // winner's centre row of the pending step
+            if (step0 + step_inc < nsteps) {
+                const int64_t row = (step0 + step_inc) * step_rows + crank * TC_ROWS + rl;
+                issue_row_loads(ld, X + (row < n ? row : 0) * ldx, row < n);
+            }
+            for (int64_t step = step0; step < nsteps; step += step_inc, ++li, ++it) {
+                const uint32_t xbuf = li & 1;
+                const bool have_next = step + step_inc < nsteps;
+                const bool have_next2 = step + 2 * step_inc < nsteps;
+                if (pend) {                   // step s-1 leaves X buffer xbuf^1 ...
+                    output_pending(ldc);
+                    pend = false;
+                }
+                if (have_next) stage_store(ld, xbuf ^ 1, (li + 1) >> 1);   // ... and step s+1 moves in
+                if (have_next2) {
+                    const int64_t row = (step + 2 * step_inc) * step_rows + crank * TC_ROWS + rl;
+                    issue_row_loads(ld, X + (row < n ? row : 0) * ldx, row < n);
+                }
+                best2[0] = best2[1] = second2[0] = second2[1] = INFINITY;
+                bidx2[0] = bidx2[1] = 0;
+                track_tile(0, it);
+                publish(xbuf, step * step_rows + crank * TC_ROWS + rl, li >> 1);
+                merge_pending();
+                issue_row_loads(ldc, c32 + (size_t)p_bi * d, true);
+            }
+            if (pend) output_pending(ldc);
+        } else {
+            // tile after which the NEXT step's rows are staged (never inside the tile loop with one X buffer)
+            const int t_stage = DBUF ? (ntc > 1 ? 1 : 0) : -1;
+            for (int64_t step = step0; step < nsteps; step += step_inc, ++li) {
+                const int64_t row0 = step * step_rows + crank * TC_ROWS;
+                const uint32_t xbuf = DBUF ? (li & 1) : 0u;
+                const bool have_next = step + step_inc < nsteps;
+                const int64_t nrow = (step + step_inc) * step_rows + crank * TC_ROWS + rl;
+                best2[0] = best2[1] = second2[0] = second2[1] = INFINITY;
+                bidx2[0] = bidx2[1] = 0;
+                for (int t = 0; t < ntc; ++t, ++it) {
+                    // loads issued here land while this tile's scores are being tracked
+                    if (t == 0 && pend) {
+                        merge_pending();
+                        issue_row_loads(ld, c32 + (size_t)p_bi * d, true);
+                    }
+                    if (t == t_stage && have_next && !(t == 0 && pend))
+                        issue_row_loads(ld, X + (nrow < n ? nrow : 0) * ldx, nrow < n);
+                    track_tile(t, it);
+                    if (t == 0 && pend) {          // previous step's outputs (its X buffer is still intact)
+                        output_pending(ld);
+                        pend = false;
+                        if (t_stage == 0 && have_next) issue_row_loads(ld, X + (nrow < n ? nrow : 0) * ldx, nrow < n);
+                    }
+                    // stage the NEXT step's rows into the other X buffer (free: the previous step is written
+                    // out), so the tensor core never waits for X at a step boundary
+                    if (t == t_stage && have_next) stage_store(ld, xbuf ^ 1, (li + 1) >> 1);
+                }
+                publish(xbuf, row0 + rl, DBUF ? (li >> 1) : li);
+                if (!DBUF) {
+                    // one X buffer: write this step out now, then restage once the tensor core has let go of it
+                    merge_pending();
+                    issue_row_loads(ld, c32 + (size_t)p_bi * d, true);
+                    output_pending(ld);
+                    pend = false;
+                    if (have_next) {
+                        issue_row_loads(ld, X + (nrow < n ? nrow : 0) * ldx, nrow < n);
+                        stage_store(ld, 0, li + 1);
+                    }
+                }
+            }
+            if (pend) {
+                merge_pending();
+                issue_row_loads(ld, c32 + (size_t)p_bi * d, true);
+                output_pending(ld);
+            }
         }
     }
 
@@ -637,6 +695,336 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// small-k variant: k <= 256 (one column tile per step) and d <= 32
+// ---------------------------------------------------------------------------------------------
+// With a single column tile there is nothing inside a step to overlap the step boundary with, and the whole
+// centre image (<= 72 KB) fits in shared memory next to four X buffers.  So: the image is loaded ONCE per CTA
+// (no per-step re-streaming from L2), and the eight staging/epilogue warps form two groups that own alternate
+// 128-row steps end to end -- one thread per row: it stages the row, tracks all 256 columns of the step's
+// accumulator (TMEM stage = group), and writes the row's outputs with no cross-thread merge.  The groups run
+// out of phase, so one group's waits (row loads, centre-row gather, barriers) sit under the other's tracking.
+#ifdef KM_TC_TRACE
+// debug build only (make EXTRA=-DKM_TC_TRACE): CTA 0 stamps clock64 into a fixed slot per (role, step, event) --
+// plain stores, no atomics, so the stamps barely disturb the schedule.  roles: 0/1 = row groups, 2/3 = MMAs of group 0/1
+__device__ long long g_tc_trace[4 * 256 * 8];
+__device__ __forceinline__ void tc_trace(int role, int step, int ev) {
+    if (blockIdx.x != 0 || step >= 256) return;
+    g_tc_trace[(role * 256 + step) * 8 + ev] = clock64();
+}
+extern "C" int b200km_debug_read_trace(long long *host, int max_events) {
+    cudaDeviceSynchronize();
+    cudaMemcpyFromSymbol(host, g_tc_trace, sizeof(long long) * 4 * 256 * 8);
+    return 4 * 256 * 8;
+}
+#define TC_TRACE(role, step, ev) do { if (lane == 0) tc_trace(role, (int)(step), ev); } while (0)
+#else
+#define TC_TRACE(role, step, ev) do { } while (0)
+#endif
+
+struct TcSmallBars {
+    uint64_t b_ready;
+    uint64_t a_full[2];
+    uint64_t a_empty[2];
+    uint64_t x_ready[2][2];        // [group][buffer]
+    uint64_t x_free[2][2];
+    uint64_t turn[2];              // tracking token: turn[g] completes when the OTHER group has finished a step
+    uint32_t tmem_base;
+    uint32_t pad;
+    float xn[2][2][128];           // ||x||^2 of the staged rows
+};
+
+template <bool VEC>
+__global__ void __launch_bounds__(TC_THREADS, 1)
+assign_tc_small_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
+                       const unsigned char *__restrict__ tc_img, const float *__restrict__ c32,
+                       const unsigned int *__restrict__ cmax_bits, int k,
+                       int32_t *__restrict__ labels, float *__restrict__ mind2,
+                       int32_t *__restrict__ flag_rows, int32_t *__restrict__ flag_count) {
+    extern __shared__ __align__(1024) unsigned char tc_smem[];
+    constexpr int NCH = 8;                                 // 16-byte K chunks of a row at d = 32
+    const int kpad = km_tc_kpad(d);
+    const int nch = kpad / 4;
+    const int nks = kpad / 8;
+    const uint32_t xhi_bytes = (uint32_t)(nch + 2) * 128 * 16;
+    const uint32_t xlo_bytes = (uint32_t)nch * 128 * 16;
+    const uint32_t xbuf_bytes = xhi_bytes + xlo_bytes;
+    const uint32_t img_bytes = (uint32_t)km_tc_tile_bytes(d);
+    unsigned char *xb = tc_smem;                           // [group][buffer][xbuf_bytes]
+    unsigned char *bimg = xb + 4 * xbuf_bytes;             // [aug | K-step blocks], resident
+    TcSmallBars *bars = reinterpret_cast<TcSmallBars *>(bimg + img_bytes);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int64_t ntiles = (n + TC_ROWS - 1) / TC_ROWS;
+    const int64_t my_tiles =
+        (int64_t)blockIdx.x < ntiles ? (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;   // tile = bid + li * grid
+
+    if (tid == 0) {
+        km_mbar_init(&bars->b_ready, 1);
+        for (int g = 0; g < 2; ++g) {
+            km_mbar_init(&bars->a_full[g], 1);
+            km_mbar_init(&bars->a_empty[g], TC_EPI / 2);
+            km_mbar_init(&bars->turn[g], TC_EPI / 2);
+            for (int b = 0; b < 2; ++b) {
+                km_mbar_init(&bars->x_ready[g][b], TC_EPI / 2);
+                km_mbar_init(&bars->x_free[g][b], 1);
+            }
+        }
+        km_fence_mbar_init();
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                         km_smem_u32(&bars->tmem_base)),
+                     "r"(512u)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    // constant augmented chunks of Xhi in all four buffers: chunk nch = [1,1,1,0], chunk nch+1 = 0
+    for (int e = tid; e < 4 * 2 * 128; e += TC_THREADS) {
+        const int bf = e / 256, c = (e / 128) & 1, r = e & 127;
+        float4 v = c == 0 ? make_float4(1.f, 1.f, 1.f, 0.f) : make_float4(0.f, 0.f, 0.f, 0.f);
+        *reinterpret_cast<float4 *>(xb + (size_t)bf * xbuf_bytes + ((size_t)(nch + c) * 128 + r) * 16) = v;
+    }
+    km_fence_proxy_async();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = bars->tmem_base;
+
+    if (warp == 0) {
+        // ================= the centre image, once =================
+        if (lane == 0 && my_tiles > 0) {
+            km_mbar_expect_tx(&bars->b_ready, img_bytes);
+            km_bulk_g2s(bimg, tc_img, KM_TC_AUG_BYTES, &bars->b_ready);
+            for (int b = 0; b < nks; ++b)
+                km_bulk_g2s(bimg + KM_TC_AUG_BYTES + (size_t)b * KM_TC_KS_BYTES,
+                            tc_img + KM_TC_AUG_BYTES + (size_t)b * KM_TC_KS_BYTES, KM_TC_KS_BYTES, &bars->b_ready);
+        }
+    } else if (warp == 1) {
+        // ================= MMA issuer for both groups =================
+        const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(KM_TC_BN >> 3) << 17) |
+                               ((uint32_t)(128 >> 4) << 24);
+        const uint32_t desc_hi = (128u >> 4) | (1u << 14);           // SBO = 128 B, version = 1
+        const uint32_t a_lbo = (2048u >> 4) << 16;
+        const uint32_t b_lbo = ((KM_TC_BN * 16) >> 4) << 16;
+        const uint32_t xb_a = km_smem_u32(xb), bimg_a = km_smem_u32(bimg);
+        const bool leader = elect_one();
+        if (my_tiles > 0) {
+            mbar_wait_bounded(&bars->b_ready, 0);
+            tc_fence_after();
+        }
+        // Serve whichever group is ready (its next rows staged, its accumulator drained): strict alternation
+        // would hold one group's MMAs behind the other group's tracking.
+        const uint32_t nj0 = (uint32_t)((my_tiles + 1) / 2), nj1 = (uint32_t)(my_tiles / 2);
+        uint32_t j0 = 0, j1 = 0, g = 0, spins = 0;
+        while (j0 < nj0 || j1 < nj1) {
+            const uint32_t j = g ? j1 : j0, buf = j & 1;
+            const bool more = g ? (j1 < nj1) : (j0 < nj0);
+            const bool ready = more && mbar_test(&bars->x_ready[g][buf], (j >> 1) & 1) &&
+                               mbar_test(&bars->a_empty[g], (j & 1) ^ 1);
+            if (!ready) {
+                g ^= 1;
+                if (++spins > TC_SPIN_LIMIT) __trap();
+                continue;
+            }
+            spins = 0;
+            tc_fence_after();
+            TC_TRACE(2 + (int)g, j, 0);
+            const uint32_t ah = (((xb_a + (g * 2 + buf) * xbuf_bytes) & 0x3FFFFu) >> 4) | a_lbo;
+            const uint32_t al = ah + (xhi_bytes >> 4);
+            const uint32_t dcol = tmem_base + g * (uint32_t)KM_TC_BN;
+            if (leader) {
+                const uint32_t baug = ((bimg_a & 0x3FFFFu) >> 4) | b_lbo;
+                mma_tf32(dcol, ah + (uint32_t)nch * 128u, baug, desc_hi, idesc, 0u);   // + ||c||^2, overwrites
+                for (int b = 0; b < nks; ++b) {
+                    const uint32_t bh =
+                        (((bimg_a + KM_TC_AUG_BYTES + (uint32_t)b * KM_TC_KS_BYTES) & 0x3FFFFu) >> 4) | b_lbo;
+                    const uint32_t bl = bh + ((KM_TC_KS_BYTES / 2) >> 4);
+                    const uint32_t ao = (uint32_t)b * 256u;
+                    mma_tf32(dcol, al + ao, bh, desc_hi, idesc, 1u);
+                    mma_tf32(dcol, ah + ao, bl, desc_hi, idesc, 1u);
+                    mma_tf32(dcol, ah + ao, bh, desc_hi, idesc, 1u);
+                }
+                mma_commit(&bars->a_full[g]);
+                mma_commit(&bars->x_free[g][buf]);
+            }
+            __syncwarp();
+            if (g) ++j1; else ++j0;
+            g ^= 1;
+        }
+    } else {
+        // ================= the two row groups (warps 2..5 and 6..9) =================
+        // Tracking and outputs: one thread per row (row rl of the tile == TMEM lane).  Staging: the warp's 32 rows
+        // are loaded cooperatively -- lane (r8, cq) takes rows r8, r8+8, r8+16, r8+24 and the 16-byte chunks cq and
+        // cq+4 -- so a load instruction touches 8 rows x 64 contiguous bytes instead of 32 separate lines, and a
+        // quarter-warp's shared-memory stores are 128 contiguous bytes.
+        const int g = (warp - 2) >> 2;
+        const int q4 = warp & 3;                 // TMEM lane quarter this warp may access
+        const int rl = q4 * 32 + lane;           // row within the tile == TMEM lane
+        const int r8 = lane & 7, cq = lane >> 3;
+        const float cmax = __uint_as_float(*cmax_bits);
+        const float bound_scale = 2.0f * (float)(d + 12) * 1.1920929e-07f;
+        const int64_t nj = my_tiles > g ? (my_tiles - g + 1) / 2 : 0;      // this group's steps: li = 2j + g
+        auto tile_row0 = [&](int64_t j) { return ((int64_t)blockIdx.x + (2 * j + g) * (int64_t)gridDim.x) * TC_ROWS; };
+        using LdRegs = float4[NCH];
+        auto issue_x = [&](LdRegs &ld, int64_t j) {
+            const int64_t base = tile_row0(j) + q4 * 32 + r8;
+#pragma unroll
+            for (int i = 0; i < NCH; ++i) {
+                const int64_t row = base + 8 * (i & 3);
+                const int c = 4 * (i >> 2) + cq;
+                float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (c < nch && row < n) {
+                    const float *src = X + row * ldx;
+                    if (VEC) {
+                        if (c * 4 < d) v = __ldg(reinterpret_cast<const float4 *>(src) + c);
+                    } else {
+                        const int f = c * 4;
+                        v.x = f + 0 < d ? __ldg(src + f + 0) : 0.f;
+                        v.y = f + 1 < d ? __ldg(src + f + 1) : 0.f;
+                        v.z = f + 2 < d ? __ldg(src + f + 2) : 0.f;
+                        v.w = f + 3 < d ? __ldg(src + f + 3) : 0.f;
+                    }
+                }
+                ld[i] = v;
+            }
+        };
+        // split the pieces in ld[] into TF32 hi / exact lo parts in this group's buffer j & 1
+        auto stage = [&](const LdRegs &ld, int64_t j) {
+            const uint32_t bf = (uint32_t)(j & 1), use = (uint32_t)(j >> 1);
+            if (use > 0) mbar_wait_bounded(&bars->x_free[g][bf], (use - 1) & 1);   // tensor core done with it
+            __syncwarp();             // every lane is done with this buffer's previous rows (output of step j-2)
+            unsigned char *ph = xb + (size_t)(g * 2 + bf) * xbuf_bytes + (size_t)(q4 * 32 + r8) * 16;
+            unsigned char *pl = ph + xhi_bytes;
+            float s4[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+            for (int i = 0; i < NCH; ++i) {
+                const int c = 4 * (i >> 2) + cq;
+                if (c < nch) {
+                    const float4 v = ld[i];
+                    float s = s4[i & 3];
+                    s = fmaf(v.x, v.x, s); s = fmaf(v.y, v.y, s); s = fmaf(v.z, v.z, s); s = fmaf(v.w, v.w, s);
+                    s4[i & 3] = s;
+                    float4 h, l;
+                    h.x = tf32_rna(v.x); h.y = tf32_rna(v.y); h.z = tf32_rna(v.z); h.w = tf32_rna(v.w);
+                    l.x = v.x - h.x; l.y = v.y - h.y; l.z = v.z - h.z; l.w = v.w - h.w;   // exact: h + l == x
+                    const size_t o = (size_t)c * 2048 + (size_t)(8 * (i & 3)) * 16;
+                    *reinterpret_cast<float4 *>(ph + o) = h;
+                    *reinterpret_cast<float4 *>(pl + o) = l;
+                }
+            }
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {         // row norms: the row's chunks sit in the 4 lanes with the same r8
+                float s = s4[q];
+                s += __shfl_xor_sync(0xffffffffu, s, 8);
+                s += __shfl_xor_sync(0xffffffffu, s, 16);
+                if (cq == 0) bars->xn[g][bf][q4 * 32 + 8 * q + r8] = s;
+            }
+            km_fence_proxy_async();   // generic-proxy smem writes -> visible to the tensor core (async proxy)
+            mbar_arrive(&bars->x_ready[g][bf]);
+            __syncwarp();             // xn[] written by other lanes of this warp is read in output()
+        };
+        // labels / winner distance / near-tie flag of row rl of step j.  The winner's centre row comes from the
+        // resident image: -(hi + lo) / 2 is the float32 centre exactly (lo is stored unrounded).
+        auto output = [&](int64_t j, float best, float second, int bi) {
+            const uint32_t bf = (uint32_t)(j & 1);
+            const unsigned char *ph = xb + (size_t)(g * 2 + bf) * xbuf_bytes + (size_t)rl * 16;
+            const unsigned char *pl = ph + xhi_bytes;
+            const unsigned char *pc = bimg + KM_TC_AUG_BYTES + (size_t)bi * 16;
+            float s = 0.f;
+#pragma unroll
+            for (int c = 0; c < NCH; ++c) {
+                if (c < nch) {
+                    const float4 h = *reinterpret_cast<const float4 *>(ph + (size_t)c * 2048);
+                    const float4 l = *reinterpret_cast<const float4 *>(pl + (size_t)c * 2048);
+                    const unsigned char *pk = pc + (size_t)(c >> 1) * KM_TC_KS_BYTES + (size_t)(c & 1) * (KM_TC_BN * 16);
+                    const float4 ch = *reinterpret_cast<const float4 *>(pk);
+                    const float4 cl = *reinterpret_cast<const float4 *>(pk + KM_TC_KS_BYTES / 2);
+                    float df;
+                    df = fmaf(0.5f, ch.x + cl.x, h.x + l.x); s = fmaf(df, df, s);
+                    df = fmaf(0.5f, ch.y + cl.y, h.y + l.y); s = fmaf(df, df, s);
+                    df = fmaf(0.5f, ch.z + cl.z, h.z + l.z); s = fmaf(df, df, s);
+                    df = fmaf(0.5f, ch.w + cl.w, h.w + l.w); s = fmaf(df, df, s);
+                }
+            }
+            const int64_t row = tile_row0(j) + rl;
+            if (row < n) {
+                labels[row] = bi;
+                if (mind2) mind2[row] = s;
+                if (flag_rows) {
+                    const float thr = bound_scale * (bars->xn[g][bf][rl] + cmax);
+                    if (second - best <= thr) {
+                        const int pos = atomicAdd(flag_count, 1);
+                        flag_rows[pos] = (int32_t)row;
+                    }
+                }
+            }
+        };
+
+        LdRegs ld;
+        if (nj > 0) {
+            issue_x(ld, 0);
+            stage(ld, 0);
+            if (nj > 1) issue_x(ld, 1);
+        }
+        const uint32_t tbase = tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(g * KM_TC_BN);
+        for (int64_t j = 0; j < nj; ++j) {
+            if (q4 == 2) TC_TRACE(g, j, 1);
+            if (j + 1 < nj) stage(ld, j + 1);       // its MMAs run under the tracking below
+            if (j + 2 < nj) issue_x(ld, j + 2);
+            if (q4 == 2) TC_TRACE(g, j, 3);
+            // ---- scores of step j: all 256 columns of this group's accumulator stage ----
+            float best2[2] = {INFINITY, INFINITY}, second2[2] = {INFINITY, INFINITY};
+            int bidx2[2] = {0, 0};
+            mbar_wait_bounded(&bars->a_full[g], (uint32_t)(j & 1));
+            // The groups track strictly in turn (0, 1, 0, 1, ...).  Left alone they fall into lockstep -- both
+            // tracking at once on a shared ALU pipe, then both idle while their MMAs queue on the tensor core.
+            if (g == 1) mbar_wait_bounded(&bars->turn[1], (uint32_t)(j & 1));
+            else if (j > 0) mbar_wait_bounded(&bars->turn[0], (uint32_t)((j - 1) & 1));
+            tc_fence_after();
+            if (q4 == 2) TC_TRACE(g, j, 4);
+            uint32_t ra[32], rb[32];
+            tmem_ld32(tbase, ra);
+            tmem_ld_wait();
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                uint32_t (&cur)[32] = (c & 1) ? rb : ra;
+                uint32_t (&nxt)[32] = (c & 1) ? ra : rb;
+                if (c + 1 < 8) tmem_ld32(tbase + (uint32_t)((c + 1) * 32), nxt);  // flies under this chunk
+                const int cb = c * 32;
+                if (cb < k) {               // chunks made of padding columns only cannot win (warp-uniform)
+                    const float before0 = best2[0], before1 = best2[1];
+                    int jloc0 = 0, jloc1 = 0;
+#pragma unroll
+                    for (int jj = 0; jj < 32; jj += 2) {
+                        track(__uint_as_float(cur[jj]), jj, best2[0], second2[0], jloc0);
+                        track(__uint_as_float(cur[jj + 1]), jj + 1, best2[1], second2[1], jloc1);
+                    }
+                    bidx2[0] = best2[0] < before0 ? cb + jloc0 : bidx2[0];
+                    bidx2[1] = best2[1] < before1 ? cb + jloc1 : bidx2[1];
+                }
+                if (c + 1 < 8) tmem_ld_wait();
+            }
+            tc_fence_before();
+            mbar_arrive(&bars->a_empty[g]);
+            mbar_arrive(&bars->turn[g ^ 1]);
+            if (q4 == 2) TC_TRACE(g, j, 5);
+            // an exact tie keeps the lower column; it is flagged anyway
+            const bool takeb = best2[1] < best2[0] || (best2[1] == best2[0] && bidx2[1] < bidx2[0]);
+            const int bi = takeb ? bidx2[1] : bidx2[0];
+            output(j, takeb ? best2[1] : best2[0], fminf(fminf(second2[0], second2[1]), takeb ? best2[0] : best2[1]),
+                   bi >= k ? k - 1 : bi);
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
+    }
+}
+
 // host-side launcher, called from b200km_assign_f32
 int km_launch_assign_tc(const float *X, int64_t n, int d, int64_t ldx, const void *pack, int k, int32_t *labels,
                         float *mind2, int32_t *flag_rows, int32_t *flag_count, cudaStream_t st) {
@@ -646,18 +1034,35 @@ int km_launch_assign_tc(const float *X, int64_t n, int d, int64_t ldx, const voi
     const int nch = kpad / 4;
     const bool dbuf = d <= 64;
     const bool pair = km_tc_pair_mode();
+    const bool vec = (d % 4 == 0) && (ldx % 4 == 0) && ((reinterpret_cast<uintptr_t>(X) & 15) == 0);
+    const unsigned char *img = pk + L.off_tc;
+    const float *c32 = reinterpret_cast<const float *>(pk + L.off_c32);
+    const unsigned int *cmax = reinterpret_cast<const unsigned int *>(pk + L.off_cmax);
+    if (!pair && k <= KM_TC_BN && d <= 32 && km_tc_small_enabled()) {
+        // one column tile, resident centre image, two row groups (assign_tc_small_kernel)
+        const size_t xbuf = (size_t)(nch + 2) * 128 * 16 + (size_t)nch * 128 * 16;
+        const size_t smem_s = 4 * xbuf + km_tc_tile_bytes(d) + sizeof(TcSmallBars) + 64;
+        const int64_t tiles = (n + TC_ROWS - 1) / TC_ROWS;
+        const unsigned grid = (unsigned)(tiles < KM_NUM_SMS ? tiles : KM_NUM_SMS);
+        static bool attr_v[KM_MAX_DEVICES] = {}, attr_s[KM_MAX_DEVICES] = {};
+        if (int rc = km_set_smem_once(assign_tc_small_kernel<true>, 227 * 1024, attr_v)) return rc;
+        if (int rc = km_set_smem_once(assign_tc_small_kernel<false>, 227 * 1024, attr_s)) return rc;
+        if (vec)
+            assign_tc_small_kernel<true><<<grid, TC_THREADS, smem_s, st>>>(X, n, d, ldx, img, c32, cmax, k, labels, mind2,
+                                                                          flag_rows, flag_count);
+        else
+            assign_tc_small_kernel<false><<<grid, TC_THREADS, smem_s, st>>>(X, n, d, ldx, img, c32, cmax, k, labels, mind2,
+                                                                           flag_rows, flag_count);
+        return (int)cudaGetLastError();
+    }
     const size_t stage_bytes = pair ? 8192 : 16384;
     const int nstages = pair ? 8 : 5;
     const size_t smem = (dbuf ? 2 : 1) * ((size_t)(nch + 2) * 128 * 16 + (size_t)nch * 128 * 16) +
                         (size_t)nstages * stage_bytes + sizeof(TcBars) + 64;
-    const bool vec = (d % 4 == 0) && (ldx % 4 == 0) && ((reinterpret_cast<uintptr_t>(X) & 15) == 0);
     const int64_t step_rows = pair ? 2 * TC_ROWS : TC_ROWS;
     int64_t steps = (n + step_rows - 1) / step_rows;
     const int max_units = pair ? KM_NUM_SMS / 2 : KM_NUM_SMS;
     const int units = (int)(steps < max_units ? steps : max_units);
-    const unsigned char *img = pk + L.off_tc;
-    const float *c32 = reinterpret_cast<const float *>(pk + L.off_c32);
-    const unsigned int *cmax = reinterpret_cast<const unsigned int *>(pk + L.off_cmax);
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(pair ? 2 * units : units);
     cfg.blockDim = dim3(TC_THREADS);
