@@ -324,3 +324,72 @@ def test_assign_random_shapes_fuzz(eng):
             _check_assign(eng, X, C)
         finally:
             eng.lib.b200km_set_option(1, 0)
+
+
+@pytest.mark.parametrize("n,d,k", [(150001, 32, 256), (40000, 32, 200), (77777, 16, 100), (60000, 7, 17),
+                                    (130, 24, 33), (100000, 13, 256), (38017, 32, 64), (1, 4, 20),
+                                    (300000, 8, 255)])
+def test_assign_f32_small_k_kernel(eng, n, d, k):
+    """The small-k tcgen05 kernel (auto variant, k <= 256 and d <= 32: resident centre image, two row groups)
+    against the oracle, and against the general tcgen05 kernel on the same rows (several steps per CTA and group,
+    ragged tails, d not a multiple of 4)."""
+    import torch
+
+    X, C = blobs(n, d, k, seed=7 * n + d + k, dtype=np.float32)
+    init = (C + 0.3 * np.random.RandomState(2).standard_normal(C.shape))
+    assert eng.lib.b200km_get_option(1) == 0
+    got, _ = _check_assign(eng, X, init)
+    eng.lib.b200km_set_option(1, 2)
+    try:
+        Xd = eng.to_device(X)
+        pack = eng.pack(eng.to_device(init, torch.float64))
+        lab2, m2 = eng.assign(Xd, pack)
+    finally:
+        eng.lib.b200km_set_option(1, 0)
+    npt.assert_array_equal(got, lab2.cpu().numpy())
+
+
+def test_assign_f32_small_k_strided(eng):
+    """Row stride > d (a column slice of a wider matrix) through the small-k kernel's scalar-load path."""
+    import torch
+
+    rs = np.random.RandomState(5)
+    wide = rs.standard_normal((50000, 37)).astype(np.float32) * 3
+    Xd = eng.to_device(wide)[:, 3:30]                    # d = 27, ldx = 37, base pointer not 16-byte aligned
+    C = wide[:150, 3:30].astype(np.float64) + 0.1
+    pack = eng.pack(eng.to_device(C, torch.float64))
+    labels, mind2 = eng.assign(Xd, pack)
+    lab_ref, d_ref = orc.pairwise_distances_argmin_min(wide[:, 3:30], C, metric_kwargs={"squared": True})
+    got = labels.cpu().numpy()
+    diff = got != lab_ref
+    assert not (diff & ~_near_tie_mask(wide[:, 3:30], C)).any()
+    npt.assert_allclose(mind2.cpu().numpy().astype(np.float64), d_ref, rtol=3e-5, atol=1e-5 * d_ref.max())
+
+
+@pytest.mark.parametrize("variant", [0, 1, 2], ids=["auto", "ffma", "tcgen05"])
+@pytest.mark.parametrize("n,d,k,offset", [(20000, 32, 64, 1000.0), (20000, 64, 300, 300.0)])
+def test_assign_f32_far_from_origin(eng, n, d, k, offset, variant):
+    """Data far from the origin: labels stay exact (most rows go through the float64 re-decision) and the winner
+    distance keeps float32 accuracy (it is rebuilt in direct form from the exact row)."""
+    import torch
+
+    rs = np.random.RandomState(11)
+    cen = rs.uniform(-10, 10, size=(k, d))
+    X = (cen[rs.randint(0, k, n)] + rs.standard_normal((n, d)) + offset).astype(np.float32)
+    C = X[:k].astype(np.float64)
+    X64 = X.astype(np.float64)
+    D = (X64 ** 2).sum(1)[:, None] - 2.0 * X64 @ C.T + (C ** 2).sum(1)[None, :]
+    lab_ref = D.argmin(1)
+    m_ref = ((X64 - C[lab_ref]) ** 2).sum(1)
+    eng.lib.b200km_set_option(1, variant)
+    try:
+        pack = eng.pack(eng.to_device(C, torch.float64))
+        labels, mind2 = eng.assign(eng.to_device(X), pack)
+    finally:
+        eng.lib.b200km_set_option(1, 0)
+    got = labels.cpu().numpy()
+    diff = got != lab_ref
+    assert not (diff & ~_near_tie_mask(X, C, rel=1e-9)).any()
+    m = mind2.cpu().numpy().astype(np.float64)
+    nz = m_ref > 0
+    assert (np.abs(m[nz] - m_ref[nz]) / m_ref[nz]).max() < 2e-6
