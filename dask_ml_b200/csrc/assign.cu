@@ -24,9 +24,33 @@ int km_launch_assign_tc(const float *X, int64_t n, int d, int64_t ldx, const voi
 // =============================================================================================
 // centre pack
 // =============================================================================================
+// mu[f] = mean_j c64[j][f], rounded to fp32 (block f; features d .. kpad(d)-1 are zero padding)
+__global__ void __launch_bounds__(128) pack_mu_kernel(const double *__restrict__ c64in, int k, int d,
+                                                      unsigned char *__restrict__ pack) {
+    const KmPackLayout L = km_pack_layout(k, d);
+    float *mu = reinterpret_cast<float *>(pack + L.off_mu);
+    const int f = blockIdx.x;
+    __shared__ double red[4];
+    if (f >= d) {
+        if (threadIdx.x == 0) mu[f] = 0.f;
+        return;
+    }
+    double s = 0.0;
+    for (int j = threadIdx.x; j < k; j += blockDim.x) s += c64in[(size_t)j * d + f];
+    s = km_warp_sum(s);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const double m = (red[0] + red[1] + red[2] + red[3]) / (double)k;
+        const float mf = (float)m;
+        mu[f] = isfinite(mf) ? mf : 0.f;
+    }
+}
+
 __global__ void __launch_bounds__(128) pack_centers_kernel(const double *__restrict__ c64in, int k, int d,
                                                            unsigned char *__restrict__ pack) {
     const KmPackLayout L = km_pack_layout(k, d);
+    const float *mu = reinterpret_cast<const float *>(pack + L.off_mu);
     const int j = blockIdx.x;  // 0 .. ntiles*128
     float *c32 = reinterpret_cast<float *>(pack + L.off_c32);
     float *cn32 = reinterpret_cast<float *>(pack + L.off_cn32);
@@ -49,7 +73,7 @@ __global__ void __launch_bounds__(128) pack_centers_kernel(const double *__restr
     double s64 = 0.0, s32 = 0.0;
     for (int f = threadIdx.x; f < d; f += blockDim.x) {
         const double v = c64in[(size_t)j * d + f];
-        const float vf = (float)v;
+        const float vf = (float)(v - (double)mu[f]);   // centred, then rounded
         c64[(size_t)j * d + f] = v;
         c32[(size_t)j * d + f] = vf;
         ctile[(size_t)f * KM_TILE_N + jj] = vf;
@@ -90,6 +114,9 @@ extern "C" int b200km_pack_centers(const double *centers_f64, int k, int d, void
     cudaError_t e = cudaMemsetAsync(static_cast<unsigned char *>(pack) + L.off_cmax, 0, 4, st);
     if (e != cudaSuccess) return (int)e;
     const int ntiles = (k + KM_TILE_N - 1) / KM_TILE_N;
+    pack_mu_kernel<<<(d + 7) & ~7, 128, 0, st>>>(centers_f64, k, d, static_cast<unsigned char *>(pack));
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return (int)e;
     pack_centers_kernel<<<ntiles * KM_TILE_N, 128, 0, st>>>(centers_f64, k, d, static_cast<unsigned char *>(pack));
     e = cudaGetLastError();
     if (e != cudaSuccess) return (int)e;
@@ -114,7 +141,7 @@ template <bool VEC>
 __global__ void __launch_bounds__(AT_THREADS, 2)
 assign_tiled_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
                         const float *__restrict__ ct, const float *__restrict__ c32,
-                        const unsigned int *__restrict__ cmax_bits, int k, int ntiles,
+                        const float *__restrict__ mu, const unsigned int *__restrict__ cmax_bits, int k, int ntiles,
                         int32_t *__restrict__ labels, float *__restrict__ mind2,
                         int32_t *__restrict__ flag_rows, int32_t *__restrict__ flag_count) {
     extern __shared__ __align__(128) float smem[];
@@ -154,6 +181,8 @@ assign_tiled_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t l
             if (q < d4) {
                 float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
                 if (row0 + m < n) v = __ldg(reinterpret_cast<const float4 *>(X + (row0 + m) * ldx) + q);
+                const float4 mq = __ldg(reinterpret_cast<const float4 *>(mu) + q);   // the kernel works on x - mu
+                v.x -= mq.x; v.y -= mq.y; v.z -= mq.z; v.w -= mq.w;
                 float *dst = Xs + (size_t)(4 * q) * AT_XLD + m;
                 dst[0] = v.x; dst[AT_XLD] = v.y; dst[2 * AT_XLD] = v.z; dst[3 * AT_XLD] = v.w;
             }
@@ -163,7 +192,7 @@ assign_tiled_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t l
             const int m = e / d, f = e - m * d;
             float v = 0.f;
             if (row0 + m < n) v = __ldg(X + (row0 + m) * ldx + f);
-            Xs[(size_t)f * AT_XLD + m] = v;
+            Xs[(size_t)f * AT_XLD + m] = v - __ldg(mu + f);
         }
     }
     __syncthreads();
@@ -241,7 +270,7 @@ assign_tiled_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t l
 
     // ---- winner distance in direct form, outputs, near-tie flags --------------------------------
     const float cmax = __uint_as_float(*cmax_bits);
-    const float bound_scale = (float)(d + 8) * 1.1920929e-07f;  // (d+8) * 2^-23
+    const float bound_scale = (float)(d + 10) * 1.1920929e-07f;  // (d+10) * 2^-23
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
         const int m = (i < 4 ? ty * 4 + i : 60 + ty * 4 + i);
@@ -602,15 +631,16 @@ extern "C" int b200km_assign_f32(const float *X, int64_t n, int d, int64_t ldx, 
     const float *ct = reinterpret_cast<const float *>(pk + L.off_ct);
     const float *c32 = reinterpret_cast<const float *>(pk + L.off_c32);
     const unsigned int *cmax = reinterpret_cast<const unsigned int *>(pk + L.off_cmax);
+    const float *mu = reinterpret_cast<const float *>(pk + L.off_mu);
     static bool attr_v[KM_MAX_DEVICES] = {}, attr_s[KM_MAX_DEVICES] = {};
     if (int rc2 = km_set_smem_once(assign_tiled_f32_kernel<true>, 220 * 1024, attr_v)) return rc2;
     if (int rc2 = km_set_smem_once(assign_tiled_f32_kernel<false>, 220 * 1024, attr_s)) return rc2;
     if (vec)
         assign_tiled_f32_kernel<true><<<(unsigned)blocks, AT_THREADS, smem, st>>>(
-            X, n, d, ldx, ct, c32, cmax, k, ntiles, labels, mind2, flag_rows, flag_count);
+            X, n, d, ldx, ct, c32, mu, cmax, k, ntiles, labels, mind2, flag_rows, flag_count);
     else
         assign_tiled_f32_kernel<false><<<(unsigned)blocks, AT_THREADS, smem, st>>>(
-            X, n, d, ldx, ct, c32, cmax, k, ntiles, labels, mind2, flag_rows, flag_count);
+            X, n, d, ldx, ct, c32, mu, cmax, k, ntiles, labels, mind2, flag_rows, flag_count);
     KM_LAUNCH_RET();
 }
 

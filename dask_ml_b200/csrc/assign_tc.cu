@@ -190,6 +190,7 @@ struct TcBars {
     float xn_part[2][2][128];
     float s_part[2][128];
     float xn_pub[2][128];
+    alignas(16) float mu[KM_TC_MAX_D];   // the pack's centring vector (zero padded), read as float4
 };
 
 }  // namespace
@@ -263,7 +264,7 @@ template <bool VEC, bool DBUF, bool PAIR>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
                      const unsigned char *__restrict__ tc_img, const float *__restrict__ c32,
-                     const unsigned int *__restrict__ cmax_bits, int k,
+                     const float *__restrict__ mu, const unsigned int *__restrict__ cmax_bits, int k,
                      int32_t *__restrict__ labels, float *__restrict__ mind2,
                      int32_t *__restrict__ flag_rows, int32_t *__restrict__ flag_count) {
     extern __shared__ __align__(1024) unsigned char tc_smem[];
@@ -321,6 +322,7 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
             asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
         }
     }
+    for (int f = tid; f < kpad; f += TC_THREADS) bars->mu[f] = __ldg(mu + f);
     // constant augmented chunks of Xhi: chunk nch = [1,1,1,0], chunk nch+1 = 0 (both X buffers)
     for (int e = tid; e < (DBUF ? 2 : 1) * 2 * 128; e += TC_THREADS) {
         const int bf = e / 256, c = (e / 128) & 1, r = e & 127;
@@ -437,7 +439,7 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
         const int q4 = warp & 3;                 // TMEM lane quarter this warp may access
         const int rl = q4 * 32 + lane;           // row within the tile == TMEM lane
         const float cmax = __uint_as_float(*cmax_bits);
-        const float bound_scale = 2.0f * (float)(d + 12) * 1.1920929e-07f;
+        const float bound_scale = 2.0f * (float)(d + 14) * 1.1920929e-07f;
         constexpr int NCH_H = DBUF ? KM_TC_MAX_D / 16 : KM_TC_MAX_D / 8;   // K chunks per half (max; d <= 64 when DBUF)
         const int nch_h = nch / 2;               // nch is even (kpad multiple of 8)
         const int c_lo = g * nch_h;              // first K chunk of this half
@@ -473,7 +475,9 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
 #pragma unroll
             for (int c = 0; c < NCH_H; ++c) {
                 if (c < nch_h) {
-                    const float4 v = ld[c];
+                    float4 v = ld[c];
+                    const float4 mq = *reinterpret_cast<const float4 *>(&bars->mu[(c_lo + c) * 4]);   // x - mu
+                    v.x -= mq.x; v.y -= mq.y; v.z -= mq.z; v.w -= mq.w;
                     s = fmaf(v.x, v.x, s); s = fmaf(v.y, v.y, s); s = fmaf(v.z, v.z, s); s = fmaf(v.w, v.w, s);
                     float4 h, l;
                     h.x = tf32_rna(v.x); h.y = tf32_rna(v.y); h.z = tf32_rna(v.z); h.w = tf32_rna(v.w);
@@ -738,7 +742,7 @@ template <bool VEC>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 assign_tc_small_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
                        const unsigned char *__restrict__ tc_img, const float *__restrict__ c32,
-                       const unsigned int *__restrict__ cmax_bits, int k,
+                       const float *__restrict__ mu, const unsigned int *__restrict__ cmax_bits, int k,
                        int32_t *__restrict__ labels, float *__restrict__ mind2,
                        int32_t *__restrict__ flag_rows, int32_t *__restrict__ flag_count) {
     extern __shared__ __align__(1024) unsigned char tc_smem[];
@@ -863,7 +867,11 @@ assign_tc_small_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ld
         const int rl = q4 * 32 + lane;           // row within the tile == TMEM lane
         const int r8 = lane & 7, cq = lane >> 3;
         const float cmax = __uint_as_float(*cmax_bits);
-        const float bound_scale = 2.0f * (float)(d + 12) * 1.1920929e-07f;
+        const float bound_scale = 2.0f * (float)(d + 14) * 1.1920929e-07f;
+        // the centring vector's two chunks this lane stages (mu is zero padded to kpad)
+        const float4 mu0 = cq < nch ? __ldg(reinterpret_cast<const float4 *>(mu) + cq) : make_float4(0.f, 0.f, 0.f, 0.f);
+        const float4 mu1 =
+            4 + cq < nch ? __ldg(reinterpret_cast<const float4 *>(mu) + 4 + cq) : make_float4(0.f, 0.f, 0.f, 0.f);
         const int64_t nj = my_tiles > g ? (my_tiles - g + 1) / 2 : 0;      // this group's steps: li = 2j + g
         auto tile_row0 = [&](int64_t j) { return ((int64_t)blockIdx.x + (2 * j + g) * (int64_t)gridDim.x) * TC_ROWS; };
         using LdRegs = float4[NCH];
@@ -901,7 +909,9 @@ assign_tc_small_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ld
             for (int i = 0; i < NCH; ++i) {
                 const int c = 4 * (i >> 2) + cq;
                 if (c < nch) {
-                    const float4 v = ld[i];
+                    float4 v = ld[i];
+                    const float4 mq = (i >> 2) ? mu1 : mu0;                      // x - mu
+                    v.x -= mq.x; v.y -= mq.y; v.z -= mq.z; v.w -= mq.w;
                     float s = s4[i & 3];
                     s = fmaf(v.x, v.x, s); s = fmaf(v.y, v.y, s); s = fmaf(v.z, v.z, s); s = fmaf(v.w, v.w, s);
                     s4[i & 3] = s;
@@ -1038,6 +1048,7 @@ int km_launch_assign_tc(const float *X, int64_t n, int d, int64_t ldx, const voi
     const unsigned char *img = pk + L.off_tc;
     const float *c32 = reinterpret_cast<const float *>(pk + L.off_c32);
     const unsigned int *cmax = reinterpret_cast<const unsigned int *>(pk + L.off_cmax);
+    const float *mu = reinterpret_cast<const float *>(pk + L.off_mu);
     if (!pair && k <= KM_TC_BN && d <= 32 && km_tc_small_enabled()) {
         // one column tile, resident centre image, two row groups (assign_tc_small_kernel)
         const size_t xbuf = (size_t)(nch + 2) * 128 * 16 + (size_t)nch * 128 * 16;
@@ -1048,10 +1059,10 @@ int km_launch_assign_tc(const float *X, int64_t n, int d, int64_t ldx, const voi
         if (int rc = km_set_smem_once(assign_tc_small_kernel<true>, 227 * 1024, attr_v)) return rc;
         if (int rc = km_set_smem_once(assign_tc_small_kernel<false>, 227 * 1024, attr_s)) return rc;
         if (vec)
-            assign_tc_small_kernel<true><<<grid, TC_THREADS, smem_s, st>>>(X, n, d, ldx, img, c32, cmax, k, labels, mind2,
+            assign_tc_small_kernel<true><<<grid, TC_THREADS, smem_s, st>>>(X, n, d, ldx, img, c32, mu, cmax, k, labels, mind2,
                                                                           flag_rows, flag_count);
         else
-            assign_tc_small_kernel<false><<<grid, TC_THREADS, smem_s, st>>>(X, n, d, ldx, img, c32, cmax, k, labels, mind2,
+            assign_tc_small_kernel<false><<<grid, TC_THREADS, smem_s, st>>>(X, n, d, ldx, img, c32, mu, cmax, k, labels, mind2,
                                                                            flag_rows, flag_count);
         return (int)cudaGetLastError();
     }
@@ -1080,7 +1091,7 @@ int km_launch_assign_tc(const float *X, int64_t n, int d, int64_t ldx, const voi
         auto kern = assign_tc_f32_kernel<VEC_, DBUF_, PAIR_>;                                               \
         static bool attr[KM_MAX_DEVICES] = {};                                                              \
         if (int rc = km_set_smem_once(kern, 227 * 1024, attr)) return rc;                                   \
-        cudaError_t le = cudaLaunchKernelEx(&cfg, kern, X, n, d, ldx, img, c32, cmax, k, labels, mind2,     \
+        cudaError_t le = cudaLaunchKernelEx(&cfg, kern, X, n, d, ldx, img, c32, mu, cmax, k, labels, mind2,     \
                                             flag_rows, flag_count);                                         \
         if (le != cudaSuccess) return (int)le;                                                              \
     }

@@ -61,12 +61,15 @@ __host__ __device__ inline size_t km_tc_tile_bytes(int d) {
 
 struct KmPackLayout {
     size_t off_hdr;   // int32[4]: k, d, ntiles, magic
-    size_t off_cmax;  // uint32: bits of max_j ||c_j||^2 (fp32, non-negative)
-    size_t off_c32;   // float[k*d]        row-major fp32 centres
-    size_t off_cn32;  // float[ntiles*128] ||c32_j||^2, +inf padded
+    size_t off_cmax;  // uint32: bits of max_j ||c32_j||^2 (fp32, non-negative)
+    size_t off_mu;    // float[kpad(d)]    mu = mean of the centres (fp32, zero padded): the float32 kernels work on
+                      //                   x - mu and c - mu, so their rounding bounds scale with the spread of the data
+                      //                   around the centres, not with its distance from the origin
+    size_t off_c32;   // float[k*d]        row-major fp32 centres, CENTRED: fl32(c64 - mu)
+    size_t off_cn32;  // float[ntiles*128] ||c32_j||^2 (centred), +inf padded
     size_t off_cn64;  // double[k]         ||c64_j||^2
     size_t off_c64;   // double[k*d]       copy of the fp64 master
-    size_t off_ct;    // float[ntiles][d+1][128] column-tiled fp32 centres (zero padded); row d = norms
+    size_t off_ct;    // float[ntiles][d+1][128] column-tiled centred fp32 centres (zero padded); row d = norms
     size_t off_tc;    // tcgen05 image: ceil(k/64) tiles of km_tc_tile_bytes(d) (absent when d > KM_TC_MAX_D)
     size_t total;
 };
@@ -79,6 +82,7 @@ __host__ __device__ inline KmPackLayout km_pack_layout(int k, int d) {
     size_t o = 0;
     L.off_hdr = o;  o = km_align256(o + 16);
     L.off_cmax = o; o = km_align256(o + 4);
+    L.off_mu = o;   o = km_align256(o + sizeof(float) * (size_t)((d + 7) & ~7));
     L.off_c32 = o;  o = km_align256(o + sizeof(float) * (size_t)k * d);
     L.off_cn32 = o; o = km_align256(o + sizeof(float) * ntiles * KM_TILE_N);
     L.off_cn64 = o; o = km_align256(o + sizeof(double) * (size_t)k);
