@@ -352,7 +352,9 @@ def run_ours(args):
         overhead = (3.0 * kpad + 8.0) / d
         ach = flops / (k1_avg_ms * 1e-3) / 1e12
         peak = bf16_peak / 2.0 / overhead
-        roof.update({"kernel": "assign_tc_f32_kernel (K1, tcgen05 3xTF32, TMEM accumulators)",
+        small = k <= 256 and d <= 32 and args.k1 == "auto"
+        roof.update({"kernel": ("assign_tc_small_kernel (K1, tcgen05 3xTF32, resident centre image, two row groups)"
+                                if small else "assign_tc_f32_kernel (K1, tcgen05 3xTF32, TMEM accumulators)"),
                      "bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
                      "peak_source": f"{peak_src}: dense bf16 burst {bf16_peak:.0f} TFLOP/s / 2 (TF32 rate) / "
                                     f"{overhead:.3f} (TF32 flops executed per algorithmic 2Nkd flop)",

@@ -49,6 +49,7 @@ class CudaEngine:
         self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
         self.launches = 0  # kernels launched through this engine (bench.py reports it)
         self.k1_events = None  # bench.py: set to a list to collect (start, end) CUDA events around K1
+        self.pruned_refine = True   # tests flip this to compare with the full float64 scan
         self.trace = None      # tools/: set to a list to collect (entry point, event) per launch
         self._scratch = {}
 
@@ -190,8 +191,12 @@ class CudaEngine:
                     if self.k1_events is not None:
                         e1.record()
                         self.k1_events.append((e0, e1))
-                    self._call("b200km_refine_f64", xs.data_ptr(), nn, d, ldx, pack.buf.data_ptr(), pack.k,
-                               flags.data_ptr(), fcnt.data_ptr(), ls.data_ptr(), mp, st, launches=1)
+                    # float64 re-decision of the flagged rows; with the winner distances at hand the tensor cores
+                    # first list each row's possible winners (4 launches, 2 of them gated off on the device)
+                    fn = "b200km_refine_pruned_f64" if (mp is not None and self.pruned_refine) else "b200km_refine_f64"
+                    self._call(fn, xs.data_ptr(), nn, d, ldx, pack.buf.data_ptr(), pack.k,
+                               flags.data_ptr(), fcnt.data_ptr(), ls.data_ptr(), mp, st,
+                               launches=4 if fn.endswith("pruned_f64") else 1)
                 else:
                     self._call("b200km_assign_f32", xs.data_ptr(), nn, d, ldx, pack.buf.data_ptr(), pack.k,
                                ls.data_ptr(), mp, None, None, 0, st, launches=1)

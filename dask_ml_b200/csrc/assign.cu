@@ -311,7 +311,13 @@ __global__ void __launch_bounds__(R *G)
 assign_rb_kernel(const TX *__restrict__ X, int64_t n, int d, int64_t ldx, const double *__restrict__ c64,
                  const double *__restrict__ cn64, int k,
                  const int32_t *__restrict__ rows, const int32_t *__restrict__ nrows_ptr,
-                 int32_t *__restrict__ labels, TX *__restrict__ mind2) {
+                 int32_t *__restrict__ labels, TX *__restrict__ mind2,
+                 const int32_t *__restrict__ gate_ptr = nullptr, int64_t gate_max = 0, int gate_run_if_le = 0) {
+    // optional gate (pruned re-decision): run only if *gate_ptr <= gate_max (or > gate_max); uniform over the grid
+    if (gate_ptr) {
+        const int64_t c = (int64_t)(*gate_ptr);
+        if (gate_run_if_le ? (c > gate_max) : (c <= gate_max)) return;
+    }
     // INDIRECT (the refine kernel) decides on the expanded form ||c||^2 - 2 x.c in float64 -- one DFMA per
     // term, the same arithmetic sklearn's ArgKmin uses -- and recomputes only the winner's distance in
     // direct form; the direct kernels accumulate (x-c)^2 throughout.
@@ -418,7 +424,8 @@ assign_rb_kernel(const TX *__restrict__ X, int64_t n, int d, int64_t ldx, const 
 template <typename TX, int R, int G, int JB, bool INDIRECT>
 static int launch_rb(const TX *X, int64_t n, int d, int64_t ldx, const double *c64, const double *cn64, int k,
                      const int32_t *rows,
-                     const int32_t *nrows_ptr, int32_t *labels, TX *mind2, cudaStream_t st) {
+                     const int32_t *nrows_ptr, int32_t *labels, TX *mind2, cudaStream_t st,
+                     const int32_t *gate_ptr = nullptr, int64_t gate_max = 0, int gate_run_if_le = 0) {
     const int dc_max = d < RB_DC ? d : RB_DC;
     const size_t smem = sizeof(double) * ((size_t)R * (dc_max + 1) + (size_t)G * JB * dc_max + (size_t)G * R) +
                         sizeof(int) * (size_t)G * R;
@@ -429,7 +436,8 @@ static int launch_rb(const TX *X, int64_t n, int d, int64_t ldx, const double *c
     const int64_t cap = (int64_t)KM_NUM_SMS * 8;
     if (INDIRECT || blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
-    kern<<<(unsigned)blocks, R * G, smem, st>>>(X, n, d, ldx, c64, cn64, k, rows, nrows_ptr, labels, mind2);
+    kern<<<(unsigned)blocks, R * G, smem, st>>>(X, n, d, ldx, c64, cn64, k, rows, nrows_ptr, labels, mind2, gate_ptr,
+                                                gate_max, gate_run_if_le);
     KM_LAUNCH_RET();
 }
 
@@ -673,6 +681,88 @@ extern "C" int b200km_refine_f64(const float *X, int64_t n, int d, int64_t ldx, 
     // (measured: with ~0.2-0.5 % of the rows flagged, the row-block kernel's 32-row groups spread over more CTAs
     //  and beat the DFMA tile kernel's 128-row tiles at every BASELINE size, so it stays the refine kernel)
     return launch_rb<float, 32, 8, 8, true>(X, n, d, ldx, c64, cn64, k, flag_rows, flag_count, labels, mind2, st);
+}
+
+// =============================================================================================
+// pruned float64 re-decision: only the centres the candidate kernel listed
+// =============================================================================================
+constexpr int KM_CAND_CAP = 6;   // == TC_CAND_CAP (assign_tc.cu)
+int km_launch_cand_tc(const float *X, int64_t n, int d, int64_t ldx, const void *pack, int k, int32_t *flag_rows,
+                      const int32_t *flag_count, const float *mind2, cudaStream_t st);
+
+// One thread per flagged row: the listed columns are scored exactly as assign_rb_kernel<INDIRECT> scores them
+// (cn64 - 2 * sum_f x_f c_f, one DFMA per term in feature order, strict < then lowest index), so the two paths
+// give the same labels bit for bit.  A row with more than KM_CAND_CAP listed columns (duplicate centres, e.g.
+// several empty clusters parked at the origin) goes to the overflow list and gets the full scan.
+__global__ void __launch_bounds__(128)
+refine_cand_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx, const double *__restrict__ c64,
+                   const double *__restrict__ cn64, int32_t *__restrict__ F, const int32_t *__restrict__ flag_count,
+                   int32_t *__restrict__ labels, float *__restrict__ mind2) {
+    const int64_t M = (n - 1) / (KM_CAND_CAP + 3);
+    const int64_t cnt = (int64_t)(*flag_count);
+    if (cnt > M) return;
+    const int32_t *cand = F + M;
+    int32_t *ovf = F + M * (KM_CAND_CAP + 2);
+    for (int64_t pos = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; pos < cnt;
+         pos += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t row = (int64_t)F[pos];
+        const int32_t *cl = cand + pos * (KM_CAND_CAP + 1);
+        const int nc = cl[0];
+        if (nc > KM_CAND_CAP || nc <= 0) {   // (0 cannot happen: the winner itself is always within the threshold)
+            const int q = atomicAdd(F + (n - 1), 1);
+            ovf[q] = (int32_t)row;
+            continue;
+        }
+        const float *xr = X + row * ldx;
+        double best = INFINITY;
+        int bidx = 0;
+        for (int q = 0; q < nc; ++q) {
+            const int col = cl[1 + q];
+            const double *cr = c64 + (size_t)col * d;
+            double a = 0.0;
+            for (int f = 0; f < d; ++f) a = fma((double)__ldg(xr + f), cr[f], a);
+            const double sc = fma(-2.0, a, __ldg(cn64 + col));
+            if (sc < best || (sc == best && col < bidx)) { best = sc; bidx = col; }
+        }
+        labels[row] = bidx;
+        if (mind2) {
+            const double *cr = c64 + (size_t)bidx * d;
+            double s = 0.0;
+            for (int f = 0; f < d; ++f) {
+                const double df = (double)__ldg(xr + f) - cr[f];
+                s = fma(df, df, s);
+            }
+            mind2[row] = (float)s;
+        }
+    }
+}
+
+extern "C" int b200km_refine_pruned_f64(const float *X, int64_t n, int d, int64_t ldx, const void *pack, int k,
+                                        int32_t *flag_rows, const int32_t *flag_count, int32_t *labels,
+                                        float *mind2, void *stream) {
+    int rc = check_pack_args(X, n, d, ldx, pack, k, labels);
+    if (rc) return rc;
+    KM_CHECK_ARG(flag_rows && flag_count, B200KM_EINVAL);
+    // the candidate pass needs the tensor-core image (d <= 128, one-CTA layout) and the winner distances
+    if (d > KM_TC_MAX_D || km_tc_pair_mode() || !mind2 || n < 4096)
+        return b200km_refine_f64(X, n, d, ldx, pack, k, flag_rows, flag_count, labels, mind2, stream);
+    cudaStream_t st = km_stream(stream);
+    const KmPackLayout L = km_pack_layout(k, d);
+    const double *c64 = reinterpret_cast<const double *>(static_cast<const unsigned char *>(pack) + L.off_c64);
+    const double *cn64 = reinterpret_cast<const double *>(static_cast<const unsigned char *>(pack) + L.off_cn64);
+    const int64_t M = (n - 1) / (KM_CAND_CAP + 3);
+    // more flagged rows than the scratch layout holds: the full scan, gated on the device-side count
+    rc = launch_rb<float, 32, 8, 8, true>(X, n, d, ldx, c64, cn64, k, flag_rows, flag_count, labels, mind2, st,
+                                          flag_count, M, 0);
+    if (rc) return rc;
+    rc = km_launch_cand_tc(X, n, d, ldx, pack, k, flag_rows, flag_count, mind2, st);
+    if (rc) return rc;
+    refine_cand_kernel<<<KM_NUM_SMS * 4, 128, 0, st>>>(X, n, d, ldx, c64, cn64, flag_rows, flag_count, labels, mind2);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return (int)e;
+    // rows with too many candidates: the full scan over the overflow list (its size is flag_rows[n-1])
+    return launch_rb<float, 32, 8, 8, true>(X, n, d, ldx, c64, cn64, k, flag_rows + M * (KM_CAND_CAP + 2),
+                                            flag_rows + (n - 1), labels, mind2, st, flag_count, M, 1);
 }
 
 // =============================================================================================

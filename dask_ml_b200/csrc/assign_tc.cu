@@ -1035,6 +1035,261 @@ assign_tc_small_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ld
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// candidate kernel: which centres can still win a flagged row?
+// ---------------------------------------------------------------------------------------------
+// Second, small tensor-core pass over the rows K1 flagged (0.2-0.5 % of the rows).  A flagged row's float64
+// winner has a float32 score within the rounding bound of the row's best score, so instead of re-scanning all k
+// centres in float64 the row's scores are recomputed here (same 3xTF32 MMAs, rows gathered through flag_rows) and
+// every column with  score <= (mind2 - ||x'||^2) + 2 * bound  is listed: typically 2-3 columns.  The float64
+// re-decision then looks at those only (refine_cand_kernel).  (mind2 - ||x'||^2 is the winner's score up to the
+// bound, so the threshold needs nothing stored by K1.)
+// Scratch: the unused tail of flag_rows (n entries, *flag_count used), laid out by capacity M = (n-1) / (CAP + 3):
+//   [0, M) row indices | [M, M + M*(CAP+1)) per flagged row: count, CAP columns | then the overflow list | [n-1] its size
+// Runs only when *flag_count <= M; otherwise the full re-decision kernel does the work.
+constexpr int TC_CAND_CAP = 6;
+
+struct TcCandBars {
+    uint64_t b_full[5];
+    uint64_t b_empty[5];
+    uint64_t a_full[TC_ASTAGES];
+    uint64_t a_empty[TC_ASTAGES];
+    uint64_t x_ready;
+    uint64_t x_free;
+    uint64_t l_done;               // both column halves of a step have finished listing
+    uint32_t tmem_base;
+    uint32_t pad;
+    alignas(16) float mu[KM_TC_MAX_D];
+    float xn_part[2][128];
+    int ccnt[128];
+    int clist[128][TC_CAND_CAP];
+};
+
+template <bool VEC>
+__global__ void __launch_bounds__(TC_THREADS, 1)
+cand_tc_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx, const unsigned char *__restrict__ tc_img,
+               const float *__restrict__ mu, const unsigned int *__restrict__ cmax_bits, int k,
+               int32_t *__restrict__ F, const int32_t *__restrict__ flag_count, const float *__restrict__ mind2) {
+    extern __shared__ __align__(1024) unsigned char tc_smem[];
+    const int64_t M = (n - 1) / (TC_CAND_CAP + 3);
+    const int64_t cnt = (int64_t)(*flag_count);
+    if (cnt > M) return;                                   // uniform: the full re-decision handles this call
+    if (blockIdx.x == 0 && threadIdx.x == 0) F[n - 1] = 0; // size of the overflow list
+    if (cnt <= 0) return;
+    const int kpad = km_tc_kpad(d);
+    const int nch = kpad / 4;
+    const int nks = kpad / 8;
+    const uint32_t xhi_bytes = (uint32_t)(nch + 2) * 128 * 16;
+    const uint32_t xlo_bytes = (uint32_t)nch * 128 * 16;
+    const uint32_t xbuf_bytes = xhi_bytes + xlo_bytes;
+    const uint32_t tile_bytes = (uint32_t)km_tc_tile_bytes(d);
+    constexpr int NST = 5;
+    constexpr uint32_t STAGE = KM_TC_KS_BYTES, AUG = KM_TC_AUG_BYTES;
+    unsigned char *xb = tc_smem;
+    unsigned char *bst = xb + xbuf_bytes;
+    TcCandBars *bars = reinterpret_cast<TcCandBars *>(bst + NST * STAGE);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int ntc = (k + KM_TC_BN - 1) / KM_TC_BN;
+    const int64_t nsteps = (cnt + TC_ROWS - 1) / TC_ROWS;
+    int32_t *cand = F + M;
+
+    if (tid == 0) {
+        for (int i = 0; i < NST; ++i) { km_mbar_init(&bars->b_full[i], 1); km_mbar_init(&bars->b_empty[i], 1); }
+        for (int i = 0; i < TC_ASTAGES; ++i) { km_mbar_init(&bars->a_full[i], 1); km_mbar_init(&bars->a_empty[i], TC_EPI); }
+        km_mbar_init(&bars->x_ready, TC_EPI);
+        km_mbar_init(&bars->x_free, 1);
+        km_mbar_init(&bars->l_done, TC_EPI);
+        km_fence_mbar_init();
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                         km_smem_u32(&bars->tmem_base)),
+                     "r"(512u)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    for (int f = tid; f < kpad; f += TC_THREADS) bars->mu[f] = __ldg(mu + f);
+    for (int e = tid; e < 2 * 128; e += TC_THREADS) {
+        const int c = e / 128, r = e & 127;
+        float4 v = c == 0 ? make_float4(1.f, 1.f, 1.f, 0.f) : make_float4(0.f, 0.f, 0.f, 0.f);
+        *reinterpret_cast<float4 *>(xb + ((size_t)(nch + c) * 128 + r) * 16) = v;
+    }
+    km_fence_proxy_async();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = bars->tmem_base;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            uint32_t it = 0;
+            for (int64_t step = blockIdx.x; step < nsteps; step += gridDim.x)
+                for (int t = 0; t < ntc; ++t) {
+                    const unsigned char *src = tc_img + (size_t)t * tile_bytes;
+                    for (int b = 0; b <= nks; ++b, ++it) {
+                        const int s = it % NST;
+                        const uint32_t bytes = b == 0 ? AUG : STAGE;
+                        mbar_wait_bounded(&bars->b_empty[s], ((it / NST) & 1) ^ 1);
+                        km_mbar_expect_tx(&bars->b_full[s], bytes);
+                        km_bulk_g2s(bst + (size_t)s * STAGE, src, bytes, &bars->b_full[s]);
+                        src += bytes;
+                    }
+                }
+        }
+    } else if (warp == 1) {
+        const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(KM_TC_BN >> 3) << 17) |
+                               ((uint32_t)(128 >> 4) << 24);
+        const uint32_t desc_hi = (128u >> 4) | (1u << 14);
+        const uint32_t a_lbo = (2048u >> 4) << 16;
+        const uint32_t b_lbo = ((KM_TC_BN * 16) >> 4) << 16;
+        const uint32_t xb_a = km_smem_u32(xb), bst_a = km_smem_u32(bst);
+        const bool leader = elect_one();
+        uint32_t it = 0, ita = 0, li = 0;
+        for (int64_t step = blockIdx.x; step < nsteps; step += gridDim.x, ++li) {
+            mbar_wait_bounded(&bars->x_ready, li & 1);
+            tc_fence_after();
+            const uint32_t ah = ((xb_a & 0x3FFFFu) >> 4) | a_lbo;
+            const uint32_t al = ah + (xhi_bytes >> 4);
+            for (int t = 0; t < ntc; ++t, ++ita) {
+                const int a = ita % TC_ASTAGES;
+                mbar_wait_bounded(&bars->a_empty[a], ((ita / TC_ASTAGES) & 1) ^ 1);
+                const uint32_t dcol = tmem_base + (uint32_t)(a * KM_TC_BN);
+                for (int b = 0; b <= nks; ++b, ++it) {
+                    const int s = it % NST;
+                    mbar_wait_bounded(&bars->b_full[s], (it / NST) & 1);
+                    tc_fence_after();
+                    const uint32_t bh = (((bst_a + s * STAGE) & 0x3FFFFu) >> 4) | b_lbo;
+                    if (leader) {
+                        const uint32_t ao = (uint32_t)(b - 1) * 256u;
+                        const uint32_t bl = bh + ((STAGE / 2) >> 4);
+                        if (b == 0) {
+                            mma_tf32(dcol, ah + (uint32_t)nch * 128u, bh, desc_hi, idesc, 0u);
+                        } else {
+                            mma_tf32(dcol, al + ao, bh, desc_hi, idesc, 1u);
+                            mma_tf32(dcol, ah + ao, bl, desc_hi, idesc, 1u);
+                            mma_tf32(dcol, ah + ao, bh, desc_hi, idesc, 1u);
+                        }
+                        mma_commit(&bars->b_empty[s]);
+                        if (b == nks) mma_commit(&bars->a_full[a]);
+                    }
+                    __syncwarp();
+                }
+            }
+            if (leader) mma_commit(&bars->x_free);
+            __syncwarp();
+        }
+    } else {
+        const int g = (warp - 2) >> 2;
+        const int q4 = warp & 3;
+        const int rl = q4 * 32 + lane;
+        const float cmax = __uint_as_float(*cmax_bits);
+        const float bound_scale = 2.0f * (float)(d + 14) * 1.1920929e-07f;
+        const int nch_h = nch / 2, c_lo = g * nch_h;
+        uint32_t it = 0, li = 0;
+        for (int64_t step = blockIdx.x; step < nsteps; step += gridDim.x, ++li) {
+            const int64_t pos = step * TC_ROWS + rl;
+            const bool live = pos < cnt;
+            const int64_t row = live ? (int64_t)__ldg(F + pos) : 0;
+            const float *src = X + row * ldx;
+            if (li > 0) mbar_wait_bounded(&bars->x_free, (li - 1) & 1);    // tensor core done with the previous rows
+            if (g == 0) bars->ccnt[rl] = 0;
+            {
+                unsigned char *ph = xb + (size_t)rl * 16;
+                unsigned char *pl = ph + xhi_bytes;
+                float s = 0.f;
+                for (int c = 0; c < nch_h; ++c) {
+                    const int cc = c_lo + c;
+                    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (live) {
+                        if (VEC) {
+                            if (cc * 4 < d) v = __ldg(reinterpret_cast<const float4 *>(src) + cc);
+                        } else {
+                            const int f = cc * 4;
+                            v.x = f + 0 < d ? __ldg(src + f + 0) : 0.f;
+                            v.y = f + 1 < d ? __ldg(src + f + 1) : 0.f;
+                            v.z = f + 2 < d ? __ldg(src + f + 2) : 0.f;
+                            v.w = f + 3 < d ? __ldg(src + f + 3) : 0.f;
+                        }
+                    }
+                    const float4 mq = *reinterpret_cast<const float4 *>(&bars->mu[cc * 4]);
+                    v.x -= mq.x; v.y -= mq.y; v.z -= mq.z; v.w -= mq.w;
+                    s = fmaf(v.x, v.x, s); s = fmaf(v.y, v.y, s); s = fmaf(v.z, v.z, s); s = fmaf(v.w, v.w, s);
+                    float4 h, l;
+                    h.x = tf32_rna(v.x); h.y = tf32_rna(v.y); h.z = tf32_rna(v.z); h.w = tf32_rna(v.w);
+                    l.x = v.x - h.x; l.y = v.y - h.y; l.z = v.z - h.z; l.w = v.w - h.w;
+                    *reinterpret_cast<float4 *>(ph + (size_t)cc * 2048) = h;
+                    *reinterpret_cast<float4 *>(pl + (size_t)cc * 2048) = l;
+                }
+                bars->xn_part[g][rl] = s;
+                km_fence_proxy_async();
+                mbar_arrive(&bars->x_ready);
+            }
+            // both halves of the row are staged once x_ready completes: the row's threshold
+            mbar_wait_bounded(&bars->x_ready, li & 1);
+            const float xn = bars->xn_part[0][rl] + bars->xn_part[1][rl];
+            const float T = live ? (__ldg(mind2 + row) - xn) + 2.0f * bound_scale * (xn + cmax) : -INFINITY;
+            for (int t = 0; t < ntc; ++t, ++it) {
+                const int a = it % TC_ASTAGES;
+                mbar_wait_bounded(&bars->a_full[a], (it / TC_ASTAGES) & 1);
+                tc_fence_after();
+                const uint32_t tbase = tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(a * KM_TC_BN + g * 128);
+                for (int c = 0; c < 4; ++c) {
+                    uint32_t r[32];
+                    tmem_ld32(tbase + (uint32_t)(c * 32), r);
+                    tmem_ld_wait();
+                    const int cb = t * KM_TC_BN + g * 128 + c * 32;
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        if (__uint_as_float(r[j]) <= T && cb + j < k) {
+                            const int q = atomicAdd(&bars->ccnt[rl], 1);
+                            if (q < TC_CAND_CAP) bars->clist[rl][q] = cb + j;
+                        }
+                    }
+                }
+                tc_fence_before();
+                mbar_arrive(&bars->a_empty[a]);
+            }
+            mbar_arrive(&bars->l_done);
+            mbar_wait_bounded(&bars->l_done, li & 1);
+            if (g == 0 && live) {
+                int32_t *out = cand + pos * (TC_CAND_CAP + 1);
+                const int c = bars->ccnt[rl];
+                out[0] = c;
+                for (int q = 0; q < TC_CAND_CAP; ++q) out[1 + q] = q < c ? bars->clist[rl][q] : 0;
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
+    }
+}
+
+int km_launch_cand_tc(const float *X, int64_t n, int d, int64_t ldx, const void *pack, int k, int32_t *flag_rows,
+                      const int32_t *flag_count, const float *mind2, cudaStream_t st) {
+    const KmPackLayout L = km_pack_layout(k, d);
+    const unsigned char *pk = static_cast<const unsigned char *>(pack);
+    const int nch = km_tc_kpad(d) / 4;
+    const size_t smem = (size_t)(nch + 2) * 128 * 16 + (size_t)nch * 128 * 16 + 5 * (size_t)KM_TC_KS_BYTES +
+                        sizeof(TcCandBars) + 64;
+    const bool vec = (d % 4 == 0) && (ldx % 4 == 0) && ((reinterpret_cast<uintptr_t>(X) & 15) == 0);
+    const unsigned char *img = pk + L.off_tc;
+    const float *mu = reinterpret_cast<const float *>(pk + L.off_mu);
+    const unsigned int *cmax = reinterpret_cast<const unsigned int *>(pk + L.off_cmax);
+    static bool attr_v[KM_MAX_DEVICES] = {}, attr_s[KM_MAX_DEVICES] = {};
+    if (int rc = km_set_smem_once(cand_tc_kernel<true>, 227 * 1024, attr_v)) return rc;
+    if (int rc = km_set_smem_once(cand_tc_kernel<false>, 227 * 1024, attr_s)) return rc;
+    if (vec)
+        cand_tc_kernel<true><<<KM_NUM_SMS, TC_THREADS, smem, st>>>(X, n, d, ldx, img, mu, cmax, k, flag_rows, flag_count, mind2);
+    else
+        cand_tc_kernel<false><<<KM_NUM_SMS, TC_THREADS, smem, st>>>(X, n, d, ldx, img, mu, cmax, k, flag_rows, flag_count, mind2);
+    return (int)cudaGetLastError();
+}
+
 // host-side launcher, called from b200km_assign_f32
 int km_launch_assign_tc(const float *X, int64_t n, int d, int64_t ldx, const void *pack, int k, int32_t *labels,
                         float *mind2, int32_t *flag_rows, int32_t *flag_count, cudaStream_t st) {

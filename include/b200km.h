@@ -98,6 +98,19 @@ int b200km_assign_f64(const double *X, int64_t n, int d, int64_t ldx, const void
 int b200km_refine_f64(const float *X, int64_t n, int d, int64_t ldx, const void *pack, int k,
                       const int32_t *flag_rows, const int32_t *flag_count, int32_t *labels,
                       float *mind2, void *stream);
+/* The same re-decision, pruned: a flagged row's float64 winner has a float32 score within the rounding bound of
+ * the row's best, so a second, small tensor-core pass over the flagged rows (gathered through flag_rows) lists
+ * the columns with score <= (mind2 - ||x||^2) + 2 * bound -- typically 2-3 of k -- and only those are scored in
+ * float64 (same arithmetic and tie rule as b200km_refine_f64: identical labels).  Rows with more than 6 listed
+ * columns (duplicate centres) get the full scan.
+ *   flag_rows: the n-entry buffer b200km_assign_f32 filled; entries from *flag_count on are used as scratch
+ *   (hence not const).  mind2 must hold b200km_assign_f32's output for these rows.
+ *   Falls back to b200km_refine_f64 when mind2 == NULL, d > 128, n < 4096 or K1 variant 3 is selected, and -- decided
+ *   on the device, no host synchronisation -- when more than (n-1)/9 rows are flagged.
+ * Replaces: nothing in the reference (see b200km_refine_f64). */
+int b200km_refine_pruned_f64(const float *X, int64_t n, int d, int64_t ldx, const void *pack, int k,
+                             int32_t *flag_rows, const int32_t *flag_count, int32_t *labels,
+                             float *mind2, void *stream);
 
 /* K1 without caller-provided scratch.  No counterpart in the reference (it has no device memory to
  * manage); it exists for callers that cannot allocate on the device: plugins confined to the buffers

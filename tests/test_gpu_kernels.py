@@ -396,3 +396,64 @@ def test_assign_f32_far_from_origin(eng, n, d, k, offset, variant):
     m = mind2.cpu().numpy().astype(np.float64)
     nz = m_ref > 0
     assert (np.abs(m[nz] - m_ref[nz]) / m_ref[nz]).max() < 2e-6
+
+
+def _assign_both_refines(eng, X, C):
+    import torch
+
+    out = []
+    Xd = eng.to_device(X)
+    pack = eng.pack(eng.to_device(C, torch.float64))
+    for pruned in (True, False):
+        eng.pruned_refine = pruned
+        try:
+            labels, mind2 = eng.assign(Xd, pack)
+            out.append((labels.cpu().numpy(), mind2.cpu().numpy(), eng.flagged_count()))
+        finally:
+            eng.pruned_refine = True
+    return out
+
+
+@pytest.mark.parametrize("n,d,k", [(60000, 64, 1024), (50000, 32, 256), (30000, 128, 700), (20000, 20, 90),
+                                    (5000, 64, 300), (4096, 8, 40)])
+def test_refine_pruned_equals_full_scan(eng, n, d, k):
+    """The pruned float64 re-decision (tensor-core candidate pass + float64 on the listed centres) gives the labels
+    and distances of the full float64 scan bit for bit; centres = data rows, so near-ties are plentiful."""
+    X, _ = blobs(n, d, max(4, k // 8), seed=n + k, dtype=np.float32)
+    C = X[:k].astype(np.float64)
+    (lp, mp, fp), (lf, mf, ff) = _assign_both_refines(eng, X, C)
+    assert fp == ff and fp > 0
+    npt.assert_array_equal(lp, lf)
+    npt.assert_array_equal(mp, mf)
+    lab_ref, _ = orc.pairwise_distances_argmin_min(X, C, metric_kwargs={"squared": True})
+    diff = lp != lab_ref
+    assert not (diff & ~_near_tie_mask(X, C)).any()
+
+
+def test_refine_pruned_duplicate_centres_overflow(eng):
+    """More than six centres tie for a row (duplicates, as when several empty clusters are parked at the origin):
+    those rows overflow the candidate list and take the full scan; the lowest index must win."""
+    rs = np.random.RandomState(3)
+    n, d, k = 30000, 16, 64
+    X = rs.standard_normal((n, d)).astype(np.float32)
+    C = rs.standard_normal((k, d)) * 3
+    C[5:17] = 0.0                                           # twelve centres at the origin
+    (lp, mp, fp), (lf, mf, ff) = _assign_both_refines(eng, X, C)
+    npt.assert_array_equal(lp, lf)
+    npt.assert_array_equal(mp, mf)
+    assert not np.isin(lp, np.arange(6, 17)).any()          # of the duplicates only index 5 can be a label
+    assert (lp == 5).sum() > 100
+
+
+def test_refine_pruned_falls_back_when_most_rows_are_flagged(eng):
+    """All centres equal: every row is flagged, more than the scratch layout holds, so the device-side gate runs the
+    full scan instead (and the pruned kernels return at once)."""
+    rs = np.random.RandomState(4)
+    n, d, k = 20000, 32, 24
+    X = rs.standard_normal((n, d)).astype(np.float32)
+    C = np.tile(rs.standard_normal((1, d)), (k, 1))
+    (lp, mp, fp), (lf, mf, ff) = _assign_both_refines(eng, X, C)
+    assert fp == n
+    npt.assert_array_equal(lp, lf)
+    assert (lp == 0).all()
+    npt.assert_array_equal(mp, mf)
