@@ -140,14 +140,14 @@ update_atomic_kernel(const T *__restrict__ X, int64_t n, int d, int64_t ldx, con
 // float64 RED per (cluster, feature) per chunk instead of one per (row, feature): SEG_R/k times fewer
 // L2 atomics than update_atomic_kernel (16x at k = 1024).  Counts come from the histogram.
 // ---------------------------------------------------------------------------------------------
-constexpr int SEG_R = 16384;       // rows per CTA chunk (row offsets fit uint16)
+constexpr int SEG_R_MAX = 65536;   // rows per CTA chunk: row offsets fit uint16
 constexpr int SEG_THREADS = 512;
 constexpr int SEG_MAX_K = 8192;
 
 template <typename T>
 __global__ void __launch_bounds__(SEG_THREADS)
 update_seg_kernel(const T *__restrict__ X, int64_t n, int d, int64_t ldx, const int32_t *__restrict__ labels,
-                  const T *__restrict__ mind2, int k, double *__restrict__ acc, int scale_sqrt) {
+                  const T *__restrict__ mind2, int k, double *__restrict__ acc, int scale_sqrt, int SEG_R) {
     extern __shared__ __align__(16) unsigned char seg_smem[];
     int *start = reinterpret_cast<int *>(seg_smem);              // [k+1] histogram, then exclusive starts
     int *cursor = start + (k + 1);                               // [k]
@@ -287,14 +287,20 @@ static int update_impl(const T *X, int64_t n, int d, int64_t ldx, const int32_t 
         if (blocks > cap) blocks = cap;
         kern<<<(unsigned)blocks, UP_THREADS, smem, st>>>(X, n, d, ldx, labels, mind2, k, acc, scale_sqrt);
     } else if (use_seg) {
-        const size_t seg_smem = sizeof(int) * (size_t)(2 * k + 1) + sizeof(unsigned short) * SEG_R + 16;
+        // rows per chunk: longer runs per cluster (fewer REDs, less loop overhead) against fewer resident CTAs and a
+        // longer sort phase; measured optimum (sweep in profiles/r1_hbm_kernels_summary.md): 8192 rows for narrow rows,
+        // 32768 around d = 64, 16384 for wide rows
+        int SEG_R = d <= 32 ? 8192 : (d < 96 ? 32768 : 16384);
+        if (SEG_R > SEG_R_MAX) SEG_R = SEG_R_MAX;
+        while (SEG_R > 4096 && sizeof(int) * (size_t)(2 * k + 1) + sizeof(unsigned short) * (size_t)SEG_R + 16 > 200 * 1024) SEG_R /= 2;
+        const size_t seg_smem = sizeof(int) * (size_t)(2 * k + 1) + sizeof(unsigned short) * (size_t)SEG_R + 16;
         auto kern = update_seg_kernel<T>;
         static bool attr_set[KM_MAX_DEVICES] = {};
-        if (int rc = km_set_smem_once(kern, 110 * 1024, attr_set)) return rc;
+        if (int rc = km_set_smem_once(kern, 200 * 1024, attr_set)) return rc;
         int64_t blocks = (n + SEG_R - 1) / SEG_R;
         const int64_t cap = (int64_t)KM_NUM_SMS * 4;   // several CTAs per SM: one sorts while another gathers
         if (blocks > cap) blocks = cap;
-        kern<<<(unsigned)blocks, SEG_THREADS, seg_smem, st>>>(X, n, d, ldx, labels, mind2, k, acc, scale_sqrt);
+        kern<<<(unsigned)blocks, SEG_THREADS, seg_smem, st>>>(X, n, d, ldx, labels, mind2, k, acc, scale_sqrt, SEG_R);
     } else {
         int64_t blocks = (n + 4 * UP_WARPS - 1) / (4 * UP_WARPS);
         const int64_t cap = (int64_t)KM_NUM_SMS * 8;
