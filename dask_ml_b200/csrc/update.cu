@@ -288,9 +288,8 @@ static int update_impl(const T *X, int64_t n, int d, int64_t ldx, const int32_t 
         kern<<<(unsigned)blocks, UP_THREADS, smem, st>>>(X, n, d, ldx, labels, mind2, k, acc, scale_sqrt);
     } else if (use_seg) {
         // rows per chunk: longer runs per cluster (fewer REDs, less loop overhead) against fewer resident CTAs and a
-        // longer sort phase; measured optimum (sweep in profiles/r1_hbm_kernels_summary.md): 8192 rows for narrow rows,
-        // 32768 around d = 64, 16384 for wide rows
-        int SEG_R = d <= 32 ? 8192 : (d < 96 ? 32768 : 16384);
+        // longer sort phase; measured (sweep in profiles/r1_hbm_kernels_summary.md): 32768 around d = 64, else 16384
+        int SEG_R = (d > 32 && d < 96) ? 32768 : 16384;
         if (SEG_R > SEG_R_MAX) SEG_R = SEG_R_MAX;
         while (SEG_R > 4096 && sizeof(int) * (size_t)(2 * k + 1) + sizeof(unsigned short) * (size_t)SEG_R + 16 > 200 * 1024) SEG_R /= 2;
         const size_t seg_smem = sizeof(int) * (size_t)(2 * k + 1) + sizeof(unsigned short) * (size_t)SEG_R + 16;
