@@ -35,6 +35,7 @@ from sklearn.utils.validation import check_is_fitted
 from .. import _comm
 from .._engine import get_engine
 from ..metrics.pairwise import _dev, euclidean_distances, pairwise_distances_argmin_min
+from .._hostmatrix import HostMatrix, row_chunks
 from ..utils import DeviceArray, _timed, _timer, check_array
 
 logger = logging.getLogger(__name__)
@@ -158,6 +159,11 @@ class KMeans(TransformerMixin, BaseEstimator):
                         remove_zero_chunks=True, ensure_all_finite=False)
         eng = get_engine()
         host = isinstance(X, np.ndarray) or (isinstance(X, torch.Tensor) and not X.is_cuda)
+        if host and getattr(X, "ndim", 0) == 2 and str(X.dtype).replace("torch.", "") in ("float32", "float64") \
+                and _out_of_core(eng, X):
+            # larger than the device can hold: X stays in (page-locked) host memory and every pass streams it;
+            # the NaN/inf scan (:195-201) rides on the first pass
+            return HostMatrix(X, eng, nonfinite_msg=self._NONFINITE_MSG)
         if (defer and host and hasattr(eng, "to_device_streamed") and X.ndim == 2
                 and str(X.dtype).replace("torch.", "") in ("float32", "float64")
                 and X.shape[0] * X.shape[1] * (4 if "32" in str(X.dtype) else 8) >= eng.STREAM_MIN_BYTES):
@@ -187,12 +193,22 @@ class KMeans(TransformerMixin, BaseEstimator):
     def transform(self, X, y=None):
         check_is_fitted(self, "cluster_centers_")
         X = self._check_array(X)
+        if isinstance(X, HostMatrix):
+            raise NotImplementedError("transform() of a matrix that does not fit on the device: the (n, n_clusters) "
+                                      "result would not fit either; transform row blocks instead")
         return euclidean_distances(X, self.cluster_centers_)
 
     def predict(self, X):
         """Index of the closest centre for every row (int32), reference :230-251."""
         check_is_fitted(self, "cluster_centers_")
         X = self._check_array(X)
+        if isinstance(X, HostMatrix):   # streamed: the same K1 calls block by block
+            eng = get_engine()
+            pack = eng.pack(eng.to_device(np.ascontiguousarray(self.cluster_centers_), torch.float64))
+            out = torch.empty(X.shape[0], dtype=torch.int32, device=eng.device)
+            for r0, r1, Xs in row_chunks(X):
+                eng.assign(Xs, pack, out[r0:r1], None, want_mind2=True)
+            return DeviceArray(out)
         labels = pairwise_distances_argmin_min(X, self.cluster_centers_)[0].astype(np.int32)
         return labels
 
@@ -210,10 +226,29 @@ def k_means(X, n_clusters, init="k-means||", precompute_distances="auto", n_init
     return labels, centers, inertia
 
 
+def _out_of_core(eng, X) -> bool:
+    """Does a host matrix have to stay on the host?  ``B200KM_OUT_OF_CORE=1`` / ``0`` forces the answer; otherwise
+    X plus its per-row outputs (labels, distances, flag list: 12 bytes a row) must fit in 80 % of the free device
+    memory."""
+    import os
+
+    env = os.environ.get("B200KM_OUT_OF_CORE")
+    if env is not None and env != "":
+        return env not in ("0", "false", "no")
+    if not hasattr(eng, "device") or not torch.cuda.is_available():
+        return False
+    itemsize = 4 if "32" in str(X.dtype) else 8
+    need = X.shape[0] * (X.shape[1] * itemsize + 12)
+    free, _total = torch.cuda.mem_get_info(torch.device(eng.device))
+    return need > 0.8 * free
+
+
 # ---------------------------------------------------------------------------------------------
 # initialisation
 # ---------------------------------------------------------------------------------------------
 def _as_device_matrix(X) -> torch.Tensor:
+    if isinstance(X, HostMatrix):   # stays on the host; every pass streams it (row_chunks)
+        return X
     if isinstance(X, torch.Tensor) and X.dim() == 2 and X.dtype in (torch.float32, torch.float64) and \
             X.device == torch.device(get_engine().device):
         return X
@@ -278,7 +313,7 @@ def _gather_global_rows(X: torch.Tensor, gidx, comm, row0: int) -> torch.Tensor:
     n_local = X.shape[0]
     mine = (g >= row0) & (g < row0 + n_local)
     loc = torch.from_numpy(g[mine] - row0)
-    rows = eng.gather(X, loc)
+    rows = X.rows(loc) if isinstance(X, HostMatrix) else eng.gather(X, loc)
     if comm.world > 1:
         # ranks own increasing, disjoint row ranges and gidx is sorted, so rank-order
         # concatenation IS index order
@@ -293,7 +328,8 @@ def init_pp(X, n_clusters, random_state):
     from sklearn.cluster import kmeans_plusplus
 
     logger.info("Initializing with k-means++")
-    Xh = _as_device_matrix(X).cpu().numpy()
+    Xd = _as_device_matrix(X)
+    Xh = Xd.host.numpy() if isinstance(Xd, HostMatrix) else Xd.cpu().numpy()
     with _timer("initialization of %2d centers" % n_clusters, _logger=logger):
         centers, _ = kmeans_plusplus(Xh, n_clusters, random_state=random_state)
     return centers
@@ -310,6 +346,17 @@ def init_random(X, n_clusters, random_state):
     return _gather_global_rows(X, idx, comm, row0).cpu().numpy()
 
 
+def _mindist_pass(eng, X, C, mind2, init: bool) -> torch.Tensor:
+    """K4 over all rows of X (resident: one launch sequence; HostMatrix: block by block) -> cost (1-element tensor)."""
+    cost = None
+    for r0, r1, Xs in row_chunks(X):
+        c = eng.mindist_update(Xs, C, mind2[r0:r1], init=init)
+        cost = c.clone() if cost is None else cost.add_(c)
+    if cost is None:
+        cost = torch.zeros(1, dtype=torch.float64, device=eng.device)
+    return cost
+
+
 def evaluate_cost(X, centers):
     """phi_X(C) = sum_i min_j ||x_i - c_j||^2  (reference :516-519).  Returns a Python float
     (the reference returns a lazy scalar that its only caller computes at once, :456)."""
@@ -318,7 +365,7 @@ def evaluate_cost(X, centers):
     comm = _comm.default_comm()
     C = eng.to_device(np.asarray(centers) if not isinstance(centers, torch.Tensor) else centers, X.dtype)
     mind2 = eng._buf("mind2_init", (X.shape[0],), X.dtype)
-    cost = eng.mindist_update(X, C, mind2, init=True)
+    cost = _mindist_pass(eng, X, C, mind2, True)
     comm.allreduce_sum_(cost)
     return float(cost.item())
 
@@ -352,7 +399,7 @@ def _sample_points(X, centers, oversampling_factor, random_state):
     row0, n_total = comm.row_range(X.shape[0])
     C = eng.to_device(np.asarray(centers) if not isinstance(centers, torch.Tensor) else centers, X.dtype)
     mind2 = eng._buf("mind2_init", (X.shape[0],), X.dtype)
-    cost = eng.mindist_update(X, C, mind2, init=True)
+    cost = _mindist_pass(eng, X, C, mind2, True)
     comm.allreduce_sum_(cost)
     if isinstance(random_state, np.random.RandomState):
         random_state = _NumpyRandomState(random_state)
@@ -387,7 +434,7 @@ def init_scalable(X, n_clusters, random_state=None, max_iter=None, oversampling_
 
     # Step 2: Initialize cost (:456)
     mind2 = eng._buf("mind2_init", (n_local,), X.dtype)
-    cost_t = eng.mindist_update(X, new_rows, mind2, init=True)
+    cost_t = _mindist_pass(eng, X, new_rows, mind2, True)
     comm.allreduce_sum_(cost_t)
     cost = float(cost_t.item())
 
@@ -406,7 +453,7 @@ def init_scalable(X, n_clusters, random_state=None, max_iter=None, oversampling_
             c_idx |= set(fresh)
             if fresh:
                 new_rows = _gather_global_rows(X, fresh, comm, row0)
-                cost_t = eng.mindist_update(X, new_rows, mind2, init=False)
+                cost_t = _mindist_pass(eng, X, new_rows, mind2, False)
                 comm.allreduce_sum_(cost_t)
                 cost = float(cost_t.item())
     centers = _gather_global_rows(X, sorted(c_idx), comm, row0).cpu().numpy()  # :479
@@ -471,14 +518,18 @@ def _kmeans_single_lloyd(X, n_clusters, max_iter=300, init="k-means||", verbose=
             fused = getattr(eng, "can_fuse", lambda *_: False)(k, P)
             if not fused:
                 pack = eng.pack(centers64, pack)
-            # iteration 0 of a streamed upload runs chunk by chunk behind the copy engine; afterwards one span
-            spans = [(0, n_local, None)] if not pending else pending
-            for r0, r1, ev in spans:
+            # iteration 0 of a streamed upload runs chunk by chunk behind the copy engine; a HostMatrix is streamed
+            # block by block on EVERY pass; a resident X is one span
+            if pending:
+                spans = ((r0, r1, X[r0:r1], ev) for r0, r1, ev in pending)
+            else:
+                spans = ((r0, r1, Xs, None) for r0, r1, Xs in row_chunks(X))
+            for r0, r1, Xs, ev in spans:
                 if r1 <= r0:
                     continue
                 if ev is not None:
                     torch.cuda.current_stream(eng.device).wait_event(ev)
-                Xs, ls, ms = X[r0:r1], labels[r0:r1], mind2[r0:r1]
+                ls, ms = labels[r0:r1], mind2[r0:r1]
                 if ev is not None:
                     eng.nonfinite_flag(Xs, X._b200_bad)  # the deferred NaN/inf scan (:195-201)
                 if fused:
@@ -505,8 +556,9 @@ def _kmeans_single_lloyd(X, n_clusters, max_iter=300, init="k-means||", verbose=
 
     if shift > 1e-7:  # :612-614 -- labels and NON-squared distances w.r.t. the current centres
         pack = eng.pack(centers64, pack)
-        if n_local:
-            eng.assign(X, pack, labels, mind2)
+        for r0, r1, Xs in row_chunks(X):
+            if r1 > r0:
+                eng.assign(Xs, pack, labels[r0:r1], mind2[r0:r1])
         inertia_t = eng.reduce_sum(mind2, sqrt=True)
         comm.allreduce_sum_(inertia_t)
     else:

@@ -13,7 +13,7 @@ import numpy as np
 import torch
 
 from .._engine import get_engine
-from ..utils import DeviceArray
+from ..utils import DeviceArray, _adopt_device_buffer
 
 __all__ = ["pairwise_distances_argmin_min", "pairwise_distances", "euclidean_distances", "pairwise_kernels",
            "rbf_kernel", "linear_kernel", "polynomial_kernel", "sigmoid_kernel", "PAIRWISE_KERNEL_FUNCTIONS"]
@@ -26,6 +26,8 @@ def _dev(X, eng=None, dtype=None) -> torch.Tensor:
         X = X.tensor
     if hasattr(X, "compute") and not isinstance(X, torch.Tensor):  # a dask collection
         X = X.compute()
+    if not isinstance(X, (torch.Tensor, np.ndarray)):
+        X = _adopt_device_buffer(X)   # CuPy / Numba / JAX device arrays: zero-copy through DLPack
     if not isinstance(X, torch.Tensor):
         X = np.asarray(X)
         if X.dtype not in (np.float32, np.float64):

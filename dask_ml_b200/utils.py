@@ -105,6 +105,25 @@ def row_norms(X, squared=False):
     return DeviceArray(get_engine(t.device).row_norms(t, squared=squared))
 
 
+def _adopt_device_buffer(array):
+    """Zero-copy view of a foreign DEVICE array (CuPy, Numba, JAX, another framework's tensor) as a torch tensor:
+    ``__dlpack__`` when the producer says the buffer lives on a CUDA device, else ``__cuda_array_interface__``.
+    Host-side DLPack producers and everything else are returned unchanged (sklearn's validation handles them).
+    SURVEY section 8(f).3: the reference takes such blocks only inside dask arrays."""
+    dev = getattr(array, "__dlpack_device__", None)
+    if dev is not None and hasattr(array, "__dlpack__"):
+        try:
+            kind = int(dev()[0])
+        except Exception:  # pragma: no cover - a producer that cannot report its device
+            kind = -1
+        if kind in (2, 13):  # kDLCUDA, kDLCUDAManaged
+            return torch.from_dlpack(array)
+        return array
+    if hasattr(array, "__cuda_array_interface__"):
+        return torch.as_tensor(array, device="cuda")
+    return array
+
+
 def check_array(array, *args, accept_dask_array=True, accept_dask_dataframe=False, accept_unknown_chunks=False,
                 accept_multiple_blocks=False, preserve_pandas_dataframe=False, remove_zero_chunks=True, **kwargs):
     """reference dask_ml/utils.py:123-214.
@@ -114,6 +133,8 @@ def check_array(array, *args, accept_dask_array=True, accept_dask_dataframe=Fals
     ``da.Array``, :187-197) and returned unchanged; everything else goes to sklearn's
     ``check_array``.  dask collections are accepted when dask is importable.
     """
+    if not isinstance(array, (torch.Tensor, DeviceArray, np.ndarray)):
+        array = _adopt_device_buffer(array)
     if isinstance(array, (torch.Tensor, DeviceArray)):
         t = array.tensor if isinstance(array, DeviceArray) else array
         shape = tuple(t.shape)

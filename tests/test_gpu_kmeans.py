@@ -369,3 +369,51 @@ def test_degenerate_inputs():
     # a single row
     km = _km()(n_clusters=1, init=np.zeros((1, 4)), max_iter=2).fit(np.ones((1, 4)))
     npt.assert_allclose(km.cluster_centers_, np.ones((1, 4)))
+
+
+class _ForeignDeviceArray:
+    """Stand-in for a CuPy / Numba / JAX device array: exposes only the DLPack protocol."""
+
+    def __init__(self, t):
+        self._t = t
+        self.shape = tuple(t.shape)
+        self.dtype = str(t.dtype).replace("torch.", "")
+        self.ndim = t.ndim
+
+    def __dlpack__(self, stream=None):
+        return self._t.__dlpack__()
+
+    def __dlpack_device__(self):
+        return self._t.__dlpack_device__()
+
+
+class _ForeignCAI:
+    """Stand-in exposing only ``__cuda_array_interface__``."""
+
+    def __init__(self, t):
+        self._t = t
+        self.shape = tuple(t.shape)
+        self.ndim = t.ndim
+
+    @property
+    def __cuda_array_interface__(self):
+        return self._t.__cuda_array_interface__
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("wrap", [_ForeignDeviceArray, _ForeignCAI], ids=["dlpack", "cuda_array_interface"])
+def test_fit_accepts_foreign_device_arrays(wrap):
+    """A device array from another framework is adopted without a copy (DLPack / __cuda_array_interface__) and
+    gives the same model as the torch tensor it wraps."""
+    import torch
+    from dask_ml_b200.cluster import KMeans
+
+    rs = np.random.RandomState(0)
+    Xh = np.vstack([rs.normal(c, 0.3, size=(400, 5)) for c in (-4.0, 0.0, 4.0)]).astype(np.float32)
+    Xt = torch.from_numpy(Xh).cuda()
+    init = Xh[[0, 400, 800]].astype(np.float64)
+    a = KMeans(n_clusters=3, init=init, random_state=0).fit(Xt)
+    b = KMeans(n_clusters=3, init=init, random_state=0).fit(wrap(Xt))
+    npt.assert_array_equal(a.labels_.compute(), b.labels_.compute())
+    npt.assert_allclose(a.cluster_centers_, b.cluster_centers_)
+    npt.assert_array_equal(b.predict(wrap(Xt)), a.predict(Xt))
