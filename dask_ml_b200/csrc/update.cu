@@ -395,7 +395,7 @@ constexpr int FU_MAXK = 16;
 constexpr int FU_MAXD = 32;
 
 template <typename TX, int DMAX>
-__global__ void __launch_bounds__(FU_R, 3)
+__global__ void __launch_bounds__(FU_R, DMAX <= 16 ? 2 : 3)   // the prefetching variant trades a resident CTA for registers
 assign_update_small_kernel(const TX *__restrict__ X, int64_t n, int d, int64_t ldx, const double *__restrict__ c64,
                            int k, int32_t *__restrict__ labels, TX *__restrict__ mind2, double *__restrict__ acc) {
     extern __shared__ __align__(16) double fu_smem[];
@@ -423,29 +423,51 @@ assign_update_small_kernel(const TX *__restrict__ X, int64_t n, int d, int64_t l
     double mycount = 0.0;                             // thread c < k accumulates the count of cluster c
     __syncthreads();
 
+    // Tile staging.  Lanes = features (padded to a power of two so the row / feature split is shifts, not
+    // divisions), 32/dp rows per warp instruction, dp loads per thread and tile.  For d <= 16 the NEXT tile's loads
+    // are issued into registers before the current tile is worked on (they land under phases A-C), so a tile no
+    // longer costs a full memory latency on top of its compute; wider rows keep the batched in-place staging.
+    constexpr bool PREFETCH = DMAX <= 16;
+    const int sub = lane >> lg_dp, fl = lane & (dp - 1);
+    const int rpi = 32 >> lg_dp;                       // rows per warp instruction
+    const int r_first = warp * rpi + sub;
+    const int r_step = (FU_R / 32) * rpi;              // FU_R / r_step == dp loads per thread
+    const bool fok = fl < d;
+    TX pre[PREFETCH ? DMAX : 1];
+    auto prefetch = [&](int64_t base) {
+        const int64_t left = n - base;
+#pragma unroll
+        for (int i = 0; i < (PREFETCH ? DMAX : 1); ++i) {
+            const int r = r_first + i * r_step;
+            pre[i] = (TX)0;
+            if (i < dp && fok && r < left) pre[i] = __ldg(X + (base + r) * ldx + fl);
+        }
+    };
+    if (PREFETCH && (int64_t)blockIdx.x * FU_R < n) prefetch((int64_t)blockIdx.x * FU_R);
+
     for (int64_t base = (int64_t)blockIdx.x * FU_R; base < n; base += (int64_t)gridDim.x * FU_R) {
         const int rows = (int)((n - base) < FU_R ? (n - base) : FU_R);
-        // stage the tile, converted to float64.  Lanes = features (padded to a power of two so the row /
-        // feature split is shifts, not divisions), 32/dp rows per warp instruction; all of a thread's loads
-        // are issued before the first store so the tile costs one memory latency.
-        {
-            const int sub = lane >> lg_dp, f = lane & (dp - 1);
-            const int rpi = 32 >> lg_dp;                       // rows per warp instruction
-            const int r_first = warp * rpi + sub;
-            const int r_step = (FU_R / 32) * rpi;
-            const bool fok = f < d;
+        if (PREFETCH) {
+#pragma unroll
+            for (int i = 0; i < (PREFETCH ? DMAX : 1); ++i) {
+                const int r = r_first + i * r_step;
+                if (i < dp && fok && r < rows) xs[r * xld + fl] = (double)pre[i];
+            }
+            const int64_t nbase = base + (int64_t)gridDim.x * FU_R;
+            if (nbase < n) prefetch(nbase);
+        } else {
             for (int i0 = 0; i0 * r_step < FU_R; i0 += 8) {    // batches of 8 loads in flight per thread
                 TX v[8];
 #pragma unroll
                 for (int i = 0; i < 8; ++i) {
                     const int r = r_first + (i0 + i) * r_step;
                     v[i] = (TX)0;
-                    if (fok && r < rows) v[i] = __ldg(X + (base + r) * ldx + f);
+                    if (fok && r < rows) v[i] = __ldg(X + (base + r) * ldx + fl);
                 }
 #pragma unroll
                 for (int i = 0; i < 8; ++i) {
                     const int r = r_first + (i0 + i) * r_step;
-                    if (fok && r < rows) xs[r * xld + f] = (double)v[i];
+                    if (fok && r < rows) xs[r * xld + fl] = (double)v[i];
                 }
             }
         }
@@ -527,7 +549,7 @@ static int assign_update_impl(const TX *X, int64_t n, int d, int64_t ldx, const 
     KM_CHECK_ARG(n > 0 && d > 0 && k > 0 && ldx >= d, B200KM_EINVAL);
     KM_CHECK_ARG(k <= FU_MAXK && d <= FU_MAXD, B200KM_ETOOBIG);
     int64_t blocks = (n + FU_R - 1) / FU_R;
-    const int64_t cap = (int64_t)KM_NUM_SMS * 4;
+    const int64_t cap = (int64_t)KM_NUM_SMS * (d <= 16 ? 2 : 4);   // resident CTAs per SM of the two variants
     if (blocks > cap) blocks = cap;
     const size_t smem = sizeof(double) * ((size_t)FU_R * (d + 1) + 1 + (size_t)k * (d + 1));
     if (d <= 16) {
