@@ -300,6 +300,23 @@ class CudaEngine:
             first = False
         return cost
 
+    def mindist_pots(self, X: torch.Tensor, cand: torch.Tensor, mind2: torch.Tensor) -> torch.Tensor:
+        """k-means++ trial potentials: (m,) float64, pots[j] = sum_i min(mind2[i], ||x_i - cand_j||^2)."""
+        n, d, ldx = self._check_matrix(X)
+        sfx = _suffix(X)
+        cand = cand.to(X.dtype).contiguous()
+        m = cand.shape[0]
+        per = max(1, min(self.MINDIST_MAX_M, (96 * 1024) // (d * X.element_size())))
+        pots = torch.zeros(m, dtype=torch.float64, device=self.device)
+        st = self._stream()
+        for j0 in range(0, m, per):
+            cj = cand[j0 : j0 + per]
+            for r0 in range(0, n, _MAX_ROWS_PER_CALL):
+                nn = min(_MAX_ROWS_PER_CALL, n - r0)
+                self._call(f"b200km_mindist_pots_{sfx}", X[r0 : r0 + nn].data_ptr(), nn, d, ldx, cj.data_ptr(),
+                           cj.shape[0], mind2[r0 : r0 + nn].data_ptr(), pots[j0 : j0 + per].data_ptr(), st)
+        return pots
+
     def bernoulli(self, mind2: torch.Tensor, scale: float, seed: int, round_: int, row_offset: int,
                   draws: Optional[torch.Tensor] = None, capacity: int = 4096) -> torch.Tensor:
         """Global indices (int64, unsorted) of the rows picked this round."""

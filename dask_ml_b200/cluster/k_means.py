@@ -321,18 +321,67 @@ def _gather_global_rows(X: torch.Tensor, gidx, comm, row0: int) -> torch.Tensor:
     return rows
 
 
-def init_pp(X, n_clusters, random_state):
-    """K-means initialization using k-means++ (reference :404-423: scikit-learn's
-    ``_kmeans_plusplus`` on the fully materialised X -- host-side there too; not a BASELINE
-    config).  X is copied to the host for it."""
-    from sklearn.cluster import kmeans_plusplus
+def _search_cumsum(comm, closest: torch.Tensor, vals: np.ndarray, n_total: int) -> np.ndarray:
+    """``np.searchsorted(stable_cumsum(closest_dist_sq), vals)`` over the row-sharded vector: the global index of
+    the first row whose running total reaches ``vals[j]`` = the number of rows, over all ranks, whose running total
+    is still below it (clipped to the last row as scikit-learn does)."""
+    cs = torch.cumsum(closest.to(torch.float64), 0)
+    total = cs[-1:].clone() if cs.numel() else torch.zeros(1, dtype=torch.float64, device=closest.device)
+    offset = 0.0
+    if comm.world > 1:
+        totals = comm.allgather_varlen(total)
+        offset = float(totals[: comm.rank].sum().item())
+    v = torch.as_tensor(np.asarray(vals, dtype=np.float64) - offset, device=closest.device)
+    counts = torch.searchsorted(cs, v) if cs.numel() else torch.zeros_like(v, dtype=torch.int64)
+    counts = counts.to(torch.float64)          # exact below 2^53; the comm shim reduces floating tensors
+    comm.allreduce_sum_(counts)
+    return np.minimum(counts.cpu().numpy().astype(np.int64), n_total - 1)
 
+
+def init_pp(X, n_clusters, random_state):
+    """K-means initialization using k-means++ (reference :404-423 hands the fully materialised X to scikit-learn's
+    ``_kmeans_plusplus``).  Same algorithm and the same draws from ``random_state`` (one uniform for the first
+    centre, ``2 + int(log(k))`` uniforms per further centre, candidates by searching the running total of the
+    closest squared distances, best candidate by potential), but X stays where it is: the running minimum lives on
+    the device, each step is one pass for the trial potentials (``b200km_mindist_pots``) and one for the update
+    (K4), row-sharded and streamed like every other pass.  SURVEY section 8(f).4."""
     logger.info("Initializing with k-means++")
-    Xd = _as_device_matrix(X)
-    Xh = Xd.host.numpy() if isinstance(Xd, HostMatrix) else Xd.cpu().numpy()
+    X = _as_device_matrix(X)
+    eng = get_engine(X.device)
+    comm = _comm.default_comm()
+    n_local, d = X.shape
+    row0, n_total = comm.row_range(n_local)
+    if not hasattr(eng, "mindist_pots"):   # an engine without the trial-potential kernel: the reference's way
+        from sklearn.cluster import kmeans_plusplus
+
+        Xh = X.host.numpy() if isinstance(X, HostMatrix) else X.cpu().numpy()
+        return kmeans_plusplus(Xh, n_clusters, random_state=random_state)[0]
+    n_local_trials = 2 + int(np.log(n_clusters))
     with _timer("initialization of %2d centers" % n_clusters, _logger=logger):
-        centers, _ = kmeans_plusplus(Xh, n_clusters, random_state=random_state)
-    return centers
+        center_id = min(int(random_state.random_sample() * n_total), n_total - 1)   # choice(n, p=uniform)
+        picked = [_gather_global_rows(X, [center_id], comm, row0)]
+        closest = eng._buf("mind2_init", (n_local,), X.dtype)
+        pot_t = _mindist_pass(eng, X, picked[0], closest, True)
+        comm.allreduce_sum_(pot_t)
+        pot = float(pot_t.item())
+        for _c in range(1, n_clusters):
+            rand_vals = random_state.uniform(size=n_local_trials) * pot
+            cand_ids = _search_cumsum(comm, closest, rand_vals, n_total)
+            uniq = sorted(set(int(g) for g in cand_ids))
+            rows = _gather_global_rows(X, uniq, comm, row0)
+            where = {g: i for i, g in enumerate(uniq)}
+            cand_rows = rows[[where[int(g)] for g in cand_ids]]
+            pots = torch.zeros(len(cand_ids), dtype=torch.float64, device=eng.device)
+            for r0, r1, Xs in row_chunks(X):
+                if r1 > r0:
+                    pots += eng.mindist_pots(Xs, cand_rows, closest[r0:r1])
+            comm.allreduce_sum_(pots)
+            pots_h = pots.cpu().numpy()
+            best = int(np.argmin(pots_h))
+            pot = float(pots_h[best])
+            _mindist_pass(eng, X, cand_rows[best : best + 1], closest, False)
+            picked.append(cand_rows[best : best + 1])
+    return torch.cat(picked).cpu().numpy()
 
 
 @_timed(_logger=logger)

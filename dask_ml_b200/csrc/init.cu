@@ -232,6 +232,111 @@ extern "C" int b200km_mindist_update_f64(const double *X, int64_t n, int d, int6
 }
 
 // ---------------------------------------------------------------------------------------------
+// k-means++ trial potentials: pots[j] = sum_i min(mind2[i], ||x_i - cand_j||^2), mind2 left untouched.
+// Replaces, per k-means++ step, scikit-learn's `distance_to_candidates = euclidean_distances(X[candidate_ids], X)`
+// + `np.minimum(closest_dist_sq, ...)` + `@ sample_weight` (the (trials x n) matrix that the reference's init_pp,
+// dask_ml/cluster/k_means.py:404-423 -> sklearn _kmeans_plusplus, materialises on the host).
+// ---------------------------------------------------------------------------------------------
+template <typename T, int LPR>
+__global__ void __launch_bounds__(MD_THREADS)
+mindist_pots_kernel(const T *__restrict__ X, int64_t n, int d, int64_t ldx, const T *__restrict__ cand, int m,
+                    const T *__restrict__ mind2, double *__restrict__ pots_out) {
+    extern __shared__ __align__(16) unsigned char md_smem[];
+    T *cs = reinterpret_cast<T *>(md_smem);  // [m][d]
+    __shared__ double red[32];
+    for (int e = threadIdx.x; e < m * d; e += MD_THREADS) cs[e] = cand[e];
+    __syncthreads();
+    constexpr int RPW = 32 / LPR;
+    const int lane = threadIdx.x & 31;
+    const int sub = lane / LPR, l = lane % LPR;
+    const int64_t warp_global = ((int64_t)blockIdx.x * MD_THREADS + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * MD_THREADS) >> 5;
+    double pot[MD_MAXM];
+#pragma unroll
+    for (int j = 0; j < MD_MAXM; ++j) pot[j] = 0.0;
+    for (int64_t r0 = warp_global * RPW; r0 < n; r0 += nwarps * RPW) {
+        const int64_t row = r0 + sub;
+        const bool live = row < n;
+        T acc[MD_MAXM];
+#pragma unroll
+        for (int j = 0; j < MD_MAXM; ++j) acc[j] = (T)0;
+        const T *xr = X + (live ? row : 0) * ldx;
+#pragma unroll 4
+        for (int f = l; f < d; f += LPR) {
+            const T xv = live ? __ldg(xr + f) : (T)0;
+#pragma unroll
+            for (int j = 0; j < MD_MAXM; ++j) {
+                if (j < m) {
+                    const T df = xv - cs[j * d + f];
+                    acc[j] = fma(df, df, acc[j]);
+                }
+            }
+        }
+        const T old = (live && l == 0) ? mind2[row] : (T)0;
+#pragma unroll
+        for (int j = 0; j < MD_MAXM; ++j) {
+            if (j < m) {
+                T v = acc[j];
+#pragma unroll
+                for (int o = LPR / 2; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+                if (live && l == 0) pot[j] += (double)(old < v ? old : v);
+            }
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < MD_MAXM; ++j) {
+        if (j < m) {
+            km_block_atomic_add(pot[j], pots_out + j, red);
+            __syncthreads();   // red[] is reused by the next candidate
+        }
+    }
+}
+
+template <typename T>
+static int mindist_pots_impl(const T *X, int64_t n, int d, int64_t ldx, const T *cand, int m, const T *mind2,
+                             double *pots_out, void *stream) {
+    KM_CHECK_ARG(X && cand && mind2 && pots_out, B200KM_EINVAL);
+    KM_CHECK_ARG(n > 0 && d > 0 && m > 0 && ldx >= d, B200KM_EINVAL);
+    KM_CHECK_ARG(m <= MD_MAXM && d <= B200KM_MAX_D, B200KM_ETOOBIG);
+    const size_t smem = sizeof(T) * (size_t)m * d;
+    KM_CHECK_ARG(smem <= 128 * 1024, B200KM_ETOOBIG);
+    cudaStream_t st = km_stream(stream);
+    int lpr = 32;
+    if (d <= 4) lpr = 1; else if (d <= 8) lpr = 2; else if (d <= 16) lpr = 4; else if (d <= 32) lpr = 8;
+    else if (d <= 64) lpr = 16;
+    const int rpw = 32 / lpr;
+    int64_t blocks = (n + (int64_t)rpw * (MD_THREADS / 32) - 1) / ((int64_t)rpw * (MD_THREADS / 32));
+    const int64_t cap = (int64_t)KM_NUM_SMS * 8;
+    if (blocks > cap) blocks = cap;
+#define MDP_LAUNCH(LPR_)                                                                                         \
+    {                                                                                                            \
+        auto kern = mindist_pots_kernel<T, LPR_>;                                                                \
+        static bool attr_set[KM_MAX_DEVICES] = {};                                                               \
+        if (int rc = km_set_smem_once(kern, 128 * 1024, attr_set)) return rc;                                    \
+        kern<<<(unsigned)blocks, MD_THREADS, smem, st>>>(X, n, d, ldx, cand, m, mind2, pots_out);                \
+    }
+    switch (lpr) {
+        case 1: MDP_LAUNCH(1) break;
+        case 2: MDP_LAUNCH(2) break;
+        case 4: MDP_LAUNCH(4) break;
+        case 8: MDP_LAUNCH(8) break;
+        case 16: MDP_LAUNCH(16) break;
+        default: MDP_LAUNCH(32) break;
+    }
+#undef MDP_LAUNCH
+    KM_LAUNCH_RET();
+}
+
+extern "C" int b200km_mindist_pots_f32(const float *X, int64_t n, int d, int64_t ldx, const float *cand, int m,
+                                       const float *mind2, double *pots_out, void *stream) {
+    return mindist_pots_impl<float>(X, n, d, ldx, cand, m, mind2, pots_out, stream);
+}
+extern "C" int b200km_mindist_pots_f64(const double *X, int64_t n, int d, int64_t ldx, const double *cand, int m,
+                                       const double *mind2, double *pots_out, void *stream) {
+    return mindist_pots_impl<double>(X, n, d, ldx, cand, m, mind2, pots_out, stream);
+}
+
+// ---------------------------------------------------------------------------------------------
 // K5 Bernoulli oversampling
 // ---------------------------------------------------------------------------------------------
 template <typename T>

@@ -180,6 +180,14 @@ int b200km_mindist_update_f32(const float *X, int64_t n, int d, int64_t ldx, con
                               int m, float *mind2, int init, double *cost_out, void *stream);
 int b200km_mindist_update_f64(const double *X, int64_t n, int d, int64_t ldx, const double *cand,
                               int m, double *mind2, int init, double *cost_out, void *stream);
+/* k-means++ trial potentials: pots[j] += sum_i min(mind2[i], ||x_i - cand_j||^2) for m <= B200KM_MINDIST_MAX_M
+ * candidates, mind2 untouched (pots must be zeroed by the caller).  Replaces, per k-means++ step, the
+ * (trials x n) distance matrix + np.minimum + potential sums of scikit-learn's _kmeans_plusplus, which the
+ * reference's init_pp calls on the fully materialised X (R/dask_ml/cluster/k_means.py:404-423). */
+int b200km_mindist_pots_f32(const float *X, int64_t n, int d, int64_t ldx, const float *cand, int m,
+                            const float *mind2, double *pots_out, void *stream);
+int b200km_mindist_pots_f64(const double *X, int64_t n, int d, int64_t ldx, const double *cand, int m,
+                            const double *mind2, double *pots_out, void *stream);
 
 /* ------------------------------------------------------------------------------------------
  * K5  Bernoulli oversampling: row i is picked when  scale * mind2[i] > u_i,  scale = l / cost.

@@ -417,3 +417,35 @@ def test_fit_accepts_foreign_device_arrays(wrap):
     npt.assert_array_equal(a.labels_.compute(), b.labels_.compute())
     npt.assert_allclose(a.cluster_centers_, b.cluster_centers_)
     npt.assert_array_equal(b.predict(wrap(Xt)), a.predict(Xt))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+@pytest.mark.parametrize("n,d,k,seed", [(3000, 5, 8, 0), (20000, 16, 40, 1), (777, 2, 3, 2)])
+def test_init_pp_on_device_follows_sklearn(n, d, k, seed, dtype):
+    """k-means++ with the running minimum on the device draws from the RandomState exactly as
+    scikit-learn's _kmeans_plusplus does, so on well-conditioned data it picks the same rows."""
+    from sklearn.cluster import kmeans_plusplus
+    from dask_ml_b200.cluster.k_means import init_pp
+
+    rs = np.random.RandomState(100 + seed)
+    cen = rs.uniform(-10, 10, size=(k, d))
+    X = (cen[rs.randint(0, k, n)] + 0.5 * rs.standard_normal((n, d))).astype(dtype)
+    ref, idx = kmeans_plusplus(X, k, random_state=np.random.RandomState(seed))
+    got = init_pp(X, k, np.random.RandomState(seed))
+    assert got.shape == (k, d)
+    same = (np.abs(got - ref).max(axis=1) < 1e-6).mean()
+    assert same >= (1.0 if dtype == np.float64 else 0.9), f"only {same:.2f} of the centres coincide"
+    # every centre is a data row
+    assert all((np.abs(X - c).max(axis=1) < 1e-6).any() for c in got)
+
+
+@pytest.mark.gpu
+def test_fit_with_kmeanspp_init():
+    from dask_ml_b200.cluster import KMeans
+
+    rs = np.random.RandomState(5)
+    X = np.vstack([rs.normal(c, 0.2, size=(500, 3)) for c in (-5.0, 0.0, 5.0)]).astype(np.float32)
+    km = KMeans(n_clusters=3, init="k-means++", random_state=0).fit(X)
+    sk = SKKMeans(n_clusters=3, init="k-means++", n_init=1, random_state=0).fit(X)
+    npt.assert_allclose(np.sort(km.cluster_centers_[:, 0]), np.sort(sk.cluster_centers_[:, 0]), atol=1e-3)

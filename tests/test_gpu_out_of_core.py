@@ -28,7 +28,7 @@ def _fit(X, **kw):
 
 
 @pytest.mark.parametrize("dtype", [np.float32, np.float64])
-@pytest.mark.parametrize("init", ["array", "k-means||", "random"])
+@pytest.mark.parametrize("init", ["array", "k-means||", "random", "k-means++"])
 def test_streamed_fit_equals_resident_fit(monkeypatch, init, dtype):
     X, cen = _data(dtype=dtype)
     kw = dict(n_clusters=12, random_state=3, max_iter=8, tol=0.0)
