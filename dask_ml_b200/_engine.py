@@ -154,7 +154,7 @@ class CudaEngine:
         out.centers64 = centers64
         # three kernels: the centring vector, the base pack, and the tcgen05 operand image when d <= 128
         self._call("b200km_pack_centers", centers64.data_ptr(), k, d, out.buf.data_ptr(), self._stream(),
-                   launches=3 if d <= 128 else 2)
+                   launches=3 if d <= 2048 else 2)
         return out
 
     def assign(self, X: torch.Tensor, pack: CenterPack, labels: Optional[torch.Tensor] = None,

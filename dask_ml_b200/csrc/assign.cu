@@ -597,7 +597,8 @@ extern "C" int b200km_get_option(int key) {
 }
 
 static bool use_tc_path(int d, int k) {
-    if (d > KM_TC_MAX_D) return false;
+    if (d > KM_TC_WIDE_MAX_D) return false;
+    if (d > KM_TC_MAX_D && g_k1_variant == 3) return false;   // the wide-row kernel has no CTA-pair form
     if (g_k1_variant == 1) return false;
     if (g_k1_variant >= 2) return true;
     return true;   // auto: tensor cores whenever the shape allows (d <= 128)
@@ -628,7 +629,7 @@ extern "C" int b200km_assign_f32(const float *X, int64_t n, int d, int64_t ldx, 
         // HBM-bound regime: fp64 arithmetic is free here, so no flags are ever needed.
         return launch_rb<float, 256, 1, 8, false>(X, n, d, ldx, c64, nullptr, k, nullptr, nullptr, labels, mind2, st);
     }
-    if (d > 128 || k <= 16) {
+    if (k <= 16 || (d > 128 && !use_tc_path(d, k))) {
         return launch_rb<float, 32, 8, 8, false>(X, n, d, ldx, c64, nullptr, k, nullptr, nullptr, labels, mind2, st);
     }
     if (use_tc_path(d, k)) return km_launch_assign_tc(X, n, d, ldx, pack, k, labels, mind2, flag_rows, flag_count, st);

@@ -246,7 +246,7 @@ bool km_tc_pair_mode();  // assign.cu: true when K1 runs on CTA pairs (cta_group
 bool km_tc_small_enabled();   // assign.cu: false when the small-k kernel is switched off (variant 2 forces the general one)
 
 int km_launch_pack_tc(int k, int d, void *pack, cudaStream_t st) {
-    if (d > KM_TC_MAX_D) return 0;
+    if (d > KM_TC_WIDE_MAX_D) return 0;
     const int ntc = (k + KM_TC_BN - 1) / KM_TC_BN;
     pack_tc_kernel<<<ntc * KM_TC_BN, 64, 0, st>>>(k, d, static_cast<unsigned char *>(pack), km_tc_pair_mode() ? 1 : 0);
     return (int)cudaGetLastError();
@@ -1290,6 +1290,310 @@ int km_launch_cand_tc(const float *X, int64_t n, int d, int64_t ldx, const void 
     return (int)cudaGetLastError();
 }
 
+// ---------------------------------------------------------------------------------------------
+// wide rows: 128 < d <= B200KM_MAX_D
+// ---------------------------------------------------------------------------------------------
+// A 128-row tile of X no longer fits in shared memory next to the centre ring (hi + lo parts: 8 bytes per element),
+// so the K dimension is cut into PANELS of 64 features.  The two X buffers of the d <= 64 layout hold alternate
+// panels; for every column tile the staging warps re-stage the step's rows panel by panel (re-read from L2, ntc
+// times per step) while the MMA warp accumulates the tile over all panels in TMEM.  Tracking of tile t-1 is slotted
+// in after the second panel of tile t has been staged -- by then tile t-1's accumulator is complete and the tensor
+// core has two panels queued.  The winner's distance is rebuilt from global memory at the end of the step.
+constexpr int TCW_PF = 64;              // features per panel
+constexpr int TCW_PCH = TCW_PF / 4;     // 16-byte chunks per panel
+constexpr int TCW_PKS = TCW_PF / 8;     // K-steps per panel
+
+template <bool VEC>
+__global__ void __launch_bounds__(TC_THREADS, 1)
+assign_tc_wide_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
+                      const unsigned char *__restrict__ tc_img, const float *__restrict__ c32,
+                      const float *__restrict__ mu, const unsigned int *__restrict__ cmax_bits, int k,
+                      int32_t *__restrict__ labels, float *__restrict__ mind2,
+                      int32_t *__restrict__ flag_rows, int32_t *__restrict__ flag_count) {
+    extern __shared__ __align__(1024) unsigned char tc_smem[];
+    const int kpad = km_tc_kpad(d);
+    const int nks = kpad / 8;                                   // K-steps of a whole row
+    const int npan = (kpad + TCW_PF - 1) / TCW_PF;              // panels per row (>= 3)
+    constexpr uint32_t xhi_bytes = (uint32_t)(TCW_PCH + 2) * 128 * 16;
+    constexpr uint32_t xlo_bytes = (uint32_t)TCW_PCH * 128 * 16;
+    constexpr uint32_t xbuf_bytes = xhi_bytes + xlo_bytes;
+    const uint32_t tile_bytes = (uint32_t)km_tc_tile_bytes(d);
+    constexpr int NST = 5;
+    constexpr uint32_t STAGE = KM_TC_KS_BYTES, AUG = KM_TC_AUG_BYTES;
+    unsigned char *xb = tc_smem;                                // [2][xbuf_bytes]
+    unsigned char *bst = xb + 2 * xbuf_bytes;                   // [NST][STAGE]
+    TcBars *bars = reinterpret_cast<TcBars *>(bst + NST * STAGE);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int ntc = (k + KM_TC_BN - 1) / KM_TC_BN;
+    const int64_t nsteps = (n + TC_ROWS - 1) / TC_ROWS;
+
+    if (tid == 0) {
+        for (int i = 0; i < NST; ++i) { km_mbar_init(&bars->b_full[i], 1); km_mbar_init(&bars->b_empty[i], 1); }
+        for (int i = 0; i < TC_ASTAGES; ++i) { km_mbar_init(&bars->a_full[i], 1); km_mbar_init(&bars->a_empty[i], TC_EPI); }
+        for (int i = 0; i < 2; ++i) {
+            km_mbar_init(&bars->x_ready[i], TC_EPI);
+            km_mbar_init(&bars->x_free[i], 1);
+            km_mbar_init(&bars->m_ready[i], TC_EPI);
+            km_mbar_init(&bars->s_ready[i], TC_EPI / 2);
+        }
+        km_fence_mbar_init();
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                         km_smem_u32(&bars->tmem_base)),
+                     "r"(512u)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    // constant augmented chunks of Xhi in both panel buffers: chunk PCH = [1,1,1,0], chunk PCH+1 = 0
+    for (int e = tid; e < 2 * 2 * 128; e += TC_THREADS) {
+        const int bf = e / 256, c = (e / 128) & 1, r = e & 127;
+        float4 v = c == 0 ? make_float4(1.f, 1.f, 1.f, 0.f) : make_float4(0.f, 0.f, 0.f, 0.f);
+        *reinterpret_cast<float4 *>(xb + (size_t)bf * xbuf_bytes + ((size_t)(TCW_PCH + c) * 128 + r) * 16) = v;
+    }
+    km_fence_proxy_async();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = bars->tmem_base;
+
+    if (warp == 0) {
+        // ================= producer: the centre image, K-step block by K-step block =================
+        if (lane == 0) {
+            uint32_t it = 0;
+            for (int64_t step = blockIdx.x; step < nsteps; step += gridDim.x)
+                for (int t = 0; t < ntc; ++t) {
+                    const unsigned char *src = tc_img + (size_t)t * tile_bytes;
+                    for (int b = 0; b <= nks; ++b, ++it) {
+                        const int s = it % NST;
+                        const uint32_t bytes = b == 0 ? AUG : STAGE;
+                        mbar_wait_bounded(&bars->b_empty[s], ((it / NST) & 1) ^ 1);
+                        km_mbar_expect_tx(&bars->b_full[s], bytes);
+                        km_bulk_g2s(bst + (size_t)s * STAGE, src, bytes, &bars->b_full[s]);
+                        src += bytes;
+                    }
+                }
+        }
+    } else if (warp == 1) {
+        // ================= MMA issuer: a tile accumulates over all panels =================
+        const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(KM_TC_BN >> 3) << 17) |
+                               ((uint32_t)(128 >> 4) << 24);
+        const uint32_t desc_hi = (128u >> 4) | (1u << 14);
+        const uint32_t a_lbo = (2048u >> 4) << 16;
+        const uint32_t b_lbo = ((KM_TC_BN * 16) >> 4) << 16;
+        const uint32_t xb_a = km_smem_u32(xb), bst_a = km_smem_u32(bst);
+        const bool leader = elect_one();
+        uint32_t it = 0, ita = 0, sq = 0;
+        for (int64_t step = blockIdx.x; step < nsteps; step += gridDim.x) {
+            for (int t = 0; t < ntc; ++t, ++ita) {
+                const int a = ita % TC_ASTAGES;
+                mbar_wait_bounded(&bars->a_empty[a], ((ita / TC_ASTAGES) & 1) ^ 1);
+                const uint32_t dcol = tmem_base + (uint32_t)(a * KM_TC_BN);
+                for (int p = 0; p < npan; ++p, ++sq) {
+                    const uint32_t buf = sq & 1;
+                    mbar_wait_bounded(&bars->x_ready[buf], (sq >> 1) & 1);
+                    tc_fence_after();
+                    const uint32_t ah = (((xb_a + buf * xbuf_bytes) & 0x3FFFFu) >> 4) | a_lbo;
+                    const uint32_t al = ah + (xhi_bytes >> 4);
+                    const int ks_p = (nks - p * TCW_PKS) < TCW_PKS ? (nks - p * TCW_PKS) : TCW_PKS;
+                    // panel 0 starts with the augmented K-step (block 0 of the tile image)
+                    for (int b = (p == 0 ? -1 : 0); b < ks_p; ++b, ++it) {
+                        const int s = it % NST;
+                        mbar_wait_bounded(&bars->b_full[s], (it / NST) & 1);
+                        tc_fence_after();
+                        const uint32_t bh = (((bst_a + s * STAGE) & 0x3FFFFu) >> 4) | b_lbo;
+                        if (leader) {
+                            if (b < 0) {
+                                mma_tf32(dcol, ah + (uint32_t)TCW_PCH * 128u, bh, desc_hi, idesc, 0u);
+                            } else {
+                                const uint32_t ao = (uint32_t)b * 256u;
+                                const uint32_t bl = bh + ((STAGE / 2) >> 4);
+                                mma_tf32(dcol, al + ao, bh, desc_hi, idesc, 1u);
+                                mma_tf32(dcol, ah + ao, bl, desc_hi, idesc, 1u);
+                                mma_tf32(dcol, ah + ao, bh, desc_hi, idesc, 1u);
+                            }
+                            mma_commit(&bars->b_empty[s]);
+                        }
+                        __syncwarp();
+                    }
+                    if (leader) {
+                        mma_commit(&bars->x_free[buf]);                       // panel buffer reusable
+                        if (p == npan - 1) mma_commit(&bars->a_full[a]);      // tile complete
+                    }
+                    __syncwarp();
+                }
+            }
+        }
+    } else {
+        // ================= staging + tracking + outputs (warps 2..9; two threads per row) =================
+        const int g = (warp - 2) >> 2;           // half: chunks [8g, 8g+8) of every panel, columns [128g, 128g+128)
+        const int q4 = warp & 3;
+        const int rl = q4 * 32 + lane;
+        const float cmax = __uint_as_float(*cmax_bits);
+        const float bound_scale = 2.0f * (float)(d + 14) * 1.1920929e-07f;
+        constexpr int HCH = TCW_PCH / 2;         // chunks per half panel
+        uint32_t it = 0, sq = 0, li = 0;
+        for (int64_t step = blockIdx.x; step < nsteps; step += gridDim.x, ++li) {
+            const int64_t row = step * TC_ROWS + rl;
+            const bool live = row < n;
+            const float *xrow = X + (live ? row : 0) * ldx;
+            float best2[2] = {INFINITY, INFINITY}, second2[2] = {INFINITY, INFINITY};
+            int bidx2[2] = {0, 0};
+            float xn_half = 0.f;
+            auto track_tile = [&](int t, uint32_t itile) {
+                const int a = itile % TC_ASTAGES;
+                mbar_wait_bounded(&bars->a_full[a], (itile / TC_ASTAGES) & 1);
+                tc_fence_after();
+                const uint32_t tbase = tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(a * KM_TC_BN + g * 128);
+                uint32_t ra[32], rb[32];
+                tmem_ld32(tbase, ra);
+                tmem_ld_wait();
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    uint32_t (&cur)[32] = (c & 1) ? rb : ra;
+                    uint32_t (&nxt)[32] = (c & 1) ? ra : rb;
+                    if (c + 1 < 4) tmem_ld32(tbase + (uint32_t)((c + 1) * 32), nxt);
+                    const int cb = t * KM_TC_BN + g * 128 + c * 32;
+                    if (cb < k) {
+                        const float before0 = best2[0], before1 = best2[1];
+                        int jloc0 = 0, jloc1 = 0;
+#pragma unroll
+                        for (int j = 0; j < 32; j += 2) {
+                            track(__uint_as_float(cur[j]), j, best2[0], second2[0], jloc0);
+                            track(__uint_as_float(cur[j + 1]), j + 1, best2[1], second2[1], jloc1);
+                        }
+                        bidx2[0] = best2[0] < before0 ? cb + jloc0 : bidx2[0];
+                        bidx2[1] = best2[1] < before1 ? cb + jloc1 : bidx2[1];
+                    }
+                    if (c + 1 < 4) tmem_ld_wait();
+                }
+                tc_fence_before();
+                mbar_arrive(&bars->a_empty[a]);
+            };
+            for (int t = 0; t < ntc; ++t) {
+                for (int p = 0; p < npan; ++p, ++sq) {
+                    // ---- stage this half of panel p (features 64p + 32g .. +32) into buffer sq & 1 ----
+                    const uint32_t buf = sq & 1, use = sq >> 1;
+                    float4 v[HCH];
+#pragma unroll
+                    for (int c = 0; c < HCH; ++c) {
+                        const int f = p * TCW_PF + (g * HCH + c) * 4;
+                        float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
+                        if (live && f < d) {
+                            if (VEC) {
+                                x = __ldg(reinterpret_cast<const float4 *>(xrow + f));
+                            } else {
+                                x.x = __ldg(xrow + f);
+                                x.y = f + 1 < d ? __ldg(xrow + f + 1) : 0.f;
+                                x.z = f + 2 < d ? __ldg(xrow + f + 2) : 0.f;
+                                x.w = f + 3 < d ? __ldg(xrow + f + 3) : 0.f;
+                            }
+                        }
+                        v[c] = x;
+                    }
+                    if (use > 0) mbar_wait_bounded(&bars->x_free[buf], (use - 1) & 1);
+                    unsigned char *ph = xb + (size_t)buf * xbuf_bytes + (size_t)rl * 16;
+                    unsigned char *pl = ph + xhi_bytes;
+#pragma unroll
+                    for (int c = 0; c < HCH; ++c) {
+                        const int f = p * TCW_PF + (g * HCH + c) * 4;
+                        float4 x = v[c];
+                        if (f < kpad) {       // mu is zero padded to kpad; beyond kpad the panel's chunks are unused
+                            const float4 mq = __ldg(reinterpret_cast<const float4 *>(mu + f));
+                            x.x -= mq.x; x.y -= mq.y; x.z -= mq.z; x.w -= mq.w;
+                            if (!live) x = make_float4(0.f, 0.f, 0.f, 0.f);
+                            if (f + 3 >= d) {   // padding features of the last chunk stay exactly zero
+                                if (f + 1 >= d) x.y = 0.f;
+                                if (f + 2 >= d) x.z = 0.f;
+                                if (f + 3 >= d) x.w = 0.f;
+                                if (f >= d) x.x = 0.f;
+                            }
+                        } else {
+                            x = make_float4(0.f, 0.f, 0.f, 0.f);
+                        }
+                        if (t == 0) {
+                            xn_half = fmaf(x.x, x.x, xn_half); xn_half = fmaf(x.y, x.y, xn_half);
+                            xn_half = fmaf(x.z, x.z, xn_half); xn_half = fmaf(x.w, x.w, xn_half);
+                        }
+                        float4 h, l;
+                        h.x = tf32_rna(x.x); h.y = tf32_rna(x.y); h.z = tf32_rna(x.z); h.w = tf32_rna(x.w);
+                        l.x = x.x - h.x; l.y = x.y - h.y; l.z = x.z - h.z; l.w = x.w - h.w;
+                        *reinterpret_cast<float4 *>(ph + (size_t)(g * HCH + c) * 2048) = h;
+                        *reinterpret_cast<float4 *>(pl + (size_t)(g * HCH + c) * 2048) = l;
+                    }
+                    km_fence_proxy_async();
+                    mbar_arrive(&bars->x_ready[buf]);
+                    // tile t-1 is complete once this panel's buffer was free again: track it under tile t's MMAs
+                    if (p == 1 && t > 0) { track_tile(t - 1, it); ++it; }
+                }
+            }
+            track_tile(ntc - 1, it); ++it;
+            // ---- merge the two halves, rebuild the winner's distance from global memory, write the row ----
+            {
+                const bool takeb = best2[1] < best2[0] || (best2[1] == best2[0] && bidx2[1] < bidx2[0]);
+                bars->m_best[0][g][rl] = takeb ? best2[1] : best2[0];
+                bars->m_idx[0][g][rl] = takeb ? bidx2[1] : bidx2[0];
+                bars->m_second[0][g][rl] = fminf(fminf(second2[0], second2[1]), takeb ? best2[0] : best2[1]);
+                bars->xn_part[0][g][rl] = xn_half;
+                mbar_arrive(&bars->m_ready[0]);
+                mbar_wait_bounded(&bars->m_ready[0], li & 1);
+                const float b0 = bars->m_best[0][0][rl], b1 = bars->m_best[0][1][rl];
+                const float s0 = bars->m_second[0][0][rl], s1 = bars->m_second[0][1][rl];
+                const int i0 = bars->m_idx[0][0][rl], i1 = bars->m_idx[0][1][rl];
+                const bool take1 = b1 < b0 || (b1 == b0 && i1 < i0);
+                const float p_best = take1 ? b1 : b0;
+                int bi = take1 ? i1 : i0;
+                const float p_second = fminf(fminf(s0, s1), take1 ? b0 : b1);
+                bi = bi >= k ? k - 1 : bi;
+                const float xn = bars->xn_part[0][0][rl] + bars->xn_part[0][1][rl];
+                const float *crow = c32 + (size_t)bi * d;
+                float s = 0.f;
+                if (live) {
+                    for (int p = 0; p < npan; ++p) {
+#pragma unroll
+                        for (int c = 0; c < HCH; ++c) {
+                            const int f = p * TCW_PF + (g * HCH + c) * 4;
+#pragma unroll
+                            for (int e = 0; e < 4; ++e) {
+                                if (f + e < d) {
+                                    const float df = (__ldg(xrow + f + e) - __ldg(mu + f + e)) - __ldg(crow + f + e);
+                                    s = fmaf(df, df, s);
+                                }
+                            }
+                        }
+                    }
+                }
+                if (g == 1) {
+                    bars->s_part[0][rl] = s;
+                    mbar_arrive(&bars->s_ready[0]);
+                } else {
+                    mbar_wait_bounded(&bars->s_ready[0], li & 1);
+                    s += bars->s_part[0][rl];
+                    if (live) {
+                        labels[row] = bi;
+                        if (mind2) mind2[row] = s;
+                        if (flag_rows) {
+                            const float thr = bound_scale * (xn + cmax);
+                            if (p_second - p_best <= thr) {
+                                const int pos = atomicAdd(flag_count, 1);
+                                flag_rows[pos] = (int32_t)row;
+                            }
+                        }
+                    }
+                }
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
+    }
+}
+
 // host-side launcher, called from b200km_assign_f32
 int km_launch_assign_tc(const float *X, int64_t n, int d, int64_t ldx, const void *pack, int k, int32_t *labels,
                         float *mind2, int32_t *flag_rows, int32_t *flag_count, cudaStream_t st) {
@@ -1304,6 +1608,23 @@ int km_launch_assign_tc(const float *X, int64_t n, int d, int64_t ldx, const voi
     const float *c32 = reinterpret_cast<const float *>(pk + L.off_c32);
     const unsigned int *cmax = reinterpret_cast<const unsigned int *>(pk + L.off_cmax);
     const float *mu = reinterpret_cast<const float *>(pk + L.off_mu);
+    if (d > KM_TC_MAX_D) {
+        // wide rows: K cut into 64-feature panels (assign_tc_wide_kernel); same shared-memory footprint as d = 64
+        const size_t xbuf_w = (size_t)(TCW_PCH + 2) * 128 * 16 + (size_t)TCW_PCH * 128 * 16;
+        const size_t smem_w = 2 * xbuf_w + 5 * (size_t)KM_TC_KS_BYTES + sizeof(TcBars) + 64;
+        const int64_t steps_w = (n + TC_ROWS - 1) / TC_ROWS;
+        const unsigned grid = (unsigned)(steps_w < KM_NUM_SMS ? steps_w : KM_NUM_SMS);
+        static bool attr_v[KM_MAX_DEVICES] = {}, attr_s[KM_MAX_DEVICES] = {};
+        if (int rc = km_set_smem_once(assign_tc_wide_kernel<true>, 227 * 1024, attr_v)) return rc;
+        if (int rc = km_set_smem_once(assign_tc_wide_kernel<false>, 227 * 1024, attr_s)) return rc;
+        if (vec)
+            assign_tc_wide_kernel<true><<<grid, TC_THREADS, smem_w, st>>>(X, n, d, ldx, img, c32, mu, cmax, k, labels, mind2,
+                                                                         flag_rows, flag_count);
+        else
+            assign_tc_wide_kernel<false><<<grid, TC_THREADS, smem_w, st>>>(X, n, d, ldx, img, c32, mu, cmax, k, labels, mind2,
+                                                                          flag_rows, flag_count);
+        return (int)cudaGetLastError();
+    }
     if (!pair && k <= KM_TC_BN && d <= 32 && km_tc_small_enabled()) {
         // one column tile, resident centre image, two row groups (assign_tc_small_kernel)
         const size_t xbuf = (size_t)(nch + 2) * 128 * 16 + (size_t)nch * 128 * 16;

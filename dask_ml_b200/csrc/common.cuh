@@ -51,7 +51,8 @@ constexpr int KM_TILE_N = 128;  // centroid tile width of the tiled assign kerne
 //   block 0      : aug[2 chunks]                  8192 B  (the K-step that adds ||c||^2)
 //   block 1 + ks : hi[2 chunks] | lo[2 chunks]   16384 B  (K-step ks = 8 features of -2c, TF32 hi / lo parts)
 constexpr int KM_TC_BN = 256;
-constexpr int KM_TC_MAX_D = 128;
+constexpr int KM_TC_MAX_D = 128;        // a 128-row tile of X (hi + lo parts) stays resident in shared memory up to here
+constexpr int KM_TC_WIDE_MAX_D = 2048;  // beyond it K is cut into panels (assign_tc_wide_kernel); == B200KM_MAX_D
 constexpr int KM_TC_AUG_BYTES = 2 * KM_TC_BN * 16;
 constexpr int KM_TC_KS_BYTES = 4 * KM_TC_BN * 16;
 __host__ __device__ inline int km_tc_kpad(int d) { return (d + 7) & ~7; }
@@ -89,7 +90,7 @@ __host__ __device__ inline KmPackLayout km_pack_layout(int k, int d) {
     L.off_c64 = o;  o = km_align256(o + sizeof(double) * (size_t)k * d);
     L.off_ct = o;   o = km_align256(o + sizeof(float) * ntiles * (size_t)(d + 1) * KM_TILE_N);
     L.off_tc = o;
-    if (d <= KM_TC_MAX_D) o = km_align256(o + (size_t)((k + KM_TC_BN - 1) / KM_TC_BN) * km_tc_tile_bytes(d));
+    if (d <= KM_TC_WIDE_MAX_D) o = km_align256(o + (size_t)((k + KM_TC_BN - 1) / KM_TC_BN) * km_tc_tile_bytes(d));
     L.total = o;
     return L;
 }

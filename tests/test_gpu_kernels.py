@@ -457,3 +457,46 @@ def test_refine_pruned_falls_back_when_most_rows_are_flagged(eng):
     npt.assert_array_equal(lp, lf)
     assert (lp == 0).all()
     npt.assert_array_equal(mp, mf)
+
+
+@pytest.mark.parametrize("n,d,k", [(3000, 129, 300), (5000, 192, 1024), (4097, 256, 513), (2000, 333, 100),
+                                    (1500, 500, 257), (1000, 1024, 64), (600, 2048, 40), (129, 160, 17),
+                                    (40000, 136, 256)])
+def test_assign_f32_wide_rows_kernel(eng, n, d, k):
+    """Rows wider than 128 features: the tcgen05 kernel that cuts K into 64-feature panels (auto variant), against
+    the oracle and against the float64 row-block kernel it replaced for these shapes (variant 1)."""
+    import torch
+
+    X, C = blobs(n, d, max(2, k // 4), seed=3 * n + d + k, dtype=np.float32)
+    init = X[np.random.RandomState(7).randint(0, n, k)].astype(np.float64) + \
+        0.2 * np.random.RandomState(8).standard_normal((k, d))
+    got, flagged = _check_assign(eng, X, init)
+    eng.lib.b200km_set_option(1, 1)
+    try:
+        pack = eng.pack(eng.to_device(init, torch.float64))
+        lab1, _ = eng.assign(eng.to_device(X), pack)
+    finally:
+        eng.lib.b200km_set_option(1, 0)
+    diff = got != lab1.cpu().numpy()
+    assert not (diff & ~_near_tie_mask(X, init)).any()
+
+
+def test_assign_f32_wide_rows_strided_and_far(eng):
+    """Wide rows taken as a column slice (row stride > d, unaligned base) of data far from the origin."""
+    import torch
+
+    rs = np.random.RandomState(9)
+    wide = (rs.standard_normal((6000, 210)) + 400.0).astype(np.float32)
+    Xd = eng.to_device(wide)[:, 5:204]                  # d = 199, ldx = 210
+    Xh = wide[:, 5:204]
+    C = Xh[:90].astype(np.float64) + 0.3
+    pack = eng.pack(eng.to_device(C, torch.float64))
+    labels, mind2 = eng.assign(Xd, pack)
+    X64 = Xh.astype(np.float64)
+    D = np.stack([((X64 - C[j]) ** 2).sum(1) for j in range(90)], axis=1)
+    lab_ref = D.argmin(1)
+    got = labels.cpu().numpy()
+    diff = got != lab_ref
+    assert not (diff & ~_near_tie_mask(Xh, C, rel=1e-9)).any()
+    npt.assert_allclose(mind2.cpu().numpy(), D[np.arange(6000), got], rtol=2e-5)
+    assert eng.flagged_count() < 0.05 * 6000
