@@ -1426,21 +1426,25 @@ assign_tc_wide_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx
             }
         }
     } else {
-        // ================= staging + tracking + outputs (warps 2..9; two threads per row) =================
-        const int g = (warp - 2) >> 2;           // half: chunks [8g, 8g+8) of every panel, columns [128g, 128g+128)
+        // ================= staging + tracking + outputs (warps 2..9) =================
+        // Tracking: one thread per (row, column half): row rl == TMEM lane, half g.  Global loads (staging, and the
+        // winner's distance at the end of the step) are cooperative instead: warp (g, q4) covers its 32 rows and the
+        // 32 features [64p + 32g, +32) of each panel with lane (r8, cq) taking rows r8, r8+8, r8+16, r8+24 and the
+        // 16-byte chunks cq, cq+4 -- a load instruction touches 8 rows x 64 contiguous bytes, not 32 lines.
+        const int g = (warp - 2) >> 2;
         const int q4 = warp & 3;
         const int rl = q4 * 32 + lane;
+        const int r8 = lane & 7, cq = lane >> 3;
         const float cmax = __uint_as_float(*cmax_bits);
         const float bound_scale = 2.0f * (float)(d + 14) * 1.1920929e-07f;
-        constexpr int HCH = TCW_PCH / 2;         // chunks per half panel
+        constexpr int HCH = TCW_PCH / 2;         // chunks per half panel (8): two per lane and row
         uint32_t it = 0, sq = 0, li = 0;
         for (int64_t step = blockIdx.x; step < nsteps; step += gridDim.x, ++li) {
-            const int64_t row = step * TC_ROWS + rl;
-            const bool live = row < n;
-            const float *xrow = X + (live ? row : 0) * ldx;
+            const int64_t row_t = step * TC_ROWS + rl;                    // the row this thread TRACKS
+            const int64_t row_c0 = step * TC_ROWS + q4 * 32 + r8;          // first of the 4 rows this lane LOADS
             float best2[2] = {INFINITY, INFINITY}, second2[2] = {INFINITY, INFINITY};
             int bidx2[2] = {0, 0};
-            float xn_half = 0.f;
+            float xn4[4] = {0.f, 0.f, 0.f, 0.f};
             auto track_tile = [&](int t, uint32_t itile) {
                 const int a = itile % TC_ASTAGES;
                 mbar_wait_bounded(&bars->a_full[a], (itile / TC_ASTAGES) & 1);
@@ -1471,56 +1475,65 @@ assign_tc_wide_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx
                 tc_fence_before();
                 mbar_arrive(&bars->a_empty[a]);
             };
+            // piece i of a half panel: row 8*(i&3) + r8 of the warp's 32, chunk 4*(i>>2) + cq of the half's 8
+            auto load_piece = [&](const float *base, int64_t row, int f) -> float4 {
+                float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (row < n && f < d) {
+                    const float *src = base + f;
+                    if (VEC) {
+                        x = __ldg(reinterpret_cast<const float4 *>(src));
+                    } else {
+                        x.x = __ldg(src);
+                        x.y = f + 1 < d ? __ldg(src + 1) : 0.f;
+                        x.z = f + 2 < d ? __ldg(src + 2) : 0.f;
+                        x.w = f + 3 < d ? __ldg(src + 3) : 0.f;
+                    }
+                }
+                return x;
+            };
             for (int t = 0; t < ntc; ++t) {
                 for (int p = 0; p < npan; ++p, ++sq) {
-                    // ---- stage this half of panel p (features 64p + 32g .. +32) into buffer sq & 1 ----
                     const uint32_t buf = sq & 1, use = sq >> 1;
                     float4 v[HCH];
 #pragma unroll
-                    for (int c = 0; c < HCH; ++c) {
-                        const int f = p * TCW_PF + (g * HCH + c) * 4;
-                        float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
-                        if (live && f < d) {
-                            if (VEC) {
-                                x = __ldg(reinterpret_cast<const float4 *>(xrow + f));
-                            } else {
-                                x.x = __ldg(xrow + f);
-                                x.y = f + 1 < d ? __ldg(xrow + f + 1) : 0.f;
-                                x.z = f + 2 < d ? __ldg(xrow + f + 2) : 0.f;
-                                x.w = f + 3 < d ? __ldg(xrow + f + 3) : 0.f;
-                            }
-                        }
-                        v[c] = x;
+                    for (int i = 0; i < HCH; ++i) {
+                        const int64_t row = row_c0 + 8 * (i & 3);
+                        const int f = p * TCW_PF + (g * HCH + 4 * (i >> 2) + cq) * 4;
+                        v[i] = load_piece(X + (row < n ? row : 0) * ldx, row, f);
+                    }
+                    float4 mq[2];
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        const int f = p * TCW_PF + (g * HCH + 4 * h + cq) * 4;
+                        mq[h] = f < kpad ? __ldg(reinterpret_cast<const float4 *>(mu + f)) : make_float4(0.f, 0.f, 0.f, 0.f);
                     }
                     if (use > 0) mbar_wait_bounded(&bars->x_free[buf], (use - 1) & 1);
-                    unsigned char *ph = xb + (size_t)buf * xbuf_bytes + (size_t)rl * 16;
+                    unsigned char *ph = xb + (size_t)buf * xbuf_bytes + (size_t)(q4 * 32 + r8) * 16;
                     unsigned char *pl = ph + xhi_bytes;
 #pragma unroll
-                    for (int c = 0; c < HCH; ++c) {
-                        const int f = p * TCW_PF + (g * HCH + c) * 4;
-                        float4 x = v[c];
-                        if (f < kpad) {       // mu is zero padded to kpad; beyond kpad the panel's chunks are unused
-                            const float4 mq = __ldg(reinterpret_cast<const float4 *>(mu + f));
-                            x.x -= mq.x; x.y -= mq.y; x.z -= mq.z; x.w -= mq.w;
-                            if (!live) x = make_float4(0.f, 0.f, 0.f, 0.f);
-                            if (f + 3 >= d) {   // padding features of the last chunk stay exactly zero
-                                if (f + 1 >= d) x.y = 0.f;
-                                if (f + 2 >= d) x.z = 0.f;
-                                if (f + 3 >= d) x.w = 0.f;
-                                if (f >= d) x.x = 0.f;
-                            }
-                        } else {
-                            x = make_float4(0.f, 0.f, 0.f, 0.f);
+                    for (int i = 0; i < HCH; ++i) {
+                        const int64_t row = row_c0 + 8 * (i & 3);
+                        const int f = p * TCW_PF + (g * HCH + 4 * (i >> 2) + cq) * 4;
+                        float4 x = v[i];
+                        const float4 m4 = mq[i >> 2];
+                        x.x -= m4.x; x.y -= m4.y; x.z -= m4.z; x.w -= m4.w;
+                        if (row >= n || f >= d) x = make_float4(0.f, 0.f, 0.f, 0.f);
+                        else if (f + 3 >= d) {          // padding features of the row's last chunk stay exactly zero
+                            if (f + 1 >= d) x.y = 0.f;
+                            if (f + 2 >= d) x.z = 0.f;
+                            x.w = 0.f;
                         }
                         if (t == 0) {
-                            xn_half = fmaf(x.x, x.x, xn_half); xn_half = fmaf(x.y, x.y, xn_half);
-                            xn_half = fmaf(x.z, x.z, xn_half); xn_half = fmaf(x.w, x.w, xn_half);
+                            float sx = xn4[i & 3];
+                            sx = fmaf(x.x, x.x, sx); sx = fmaf(x.y, x.y, sx); sx = fmaf(x.z, x.z, sx); sx = fmaf(x.w, x.w, sx);
+                            xn4[i & 3] = sx;
                         }
                         float4 h, l;
                         h.x = tf32_rna(x.x); h.y = tf32_rna(x.y); h.z = tf32_rna(x.z); h.w = tf32_rna(x.w);
                         l.x = x.x - h.x; l.y = x.y - h.y; l.z = x.z - h.z; l.w = x.w - h.w;
-                        *reinterpret_cast<float4 *>(ph + (size_t)(g * HCH + c) * 2048) = h;
-                        *reinterpret_cast<float4 *>(pl + (size_t)(g * HCH + c) * 2048) = l;
+                        const size_t o = (size_t)(g * HCH + 4 * (i >> 2) + cq) * 2048 + (size_t)(8 * (i & 3)) * 16;
+                        *reinterpret_cast<float4 *>(ph + o) = h;
+                        *reinterpret_cast<float4 *>(pl + o) = l;
                     }
                     km_fence_proxy_async();
                     mbar_arrive(&bars->x_ready[buf]);
@@ -1529,56 +1542,81 @@ assign_tc_wide_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx
                 }
             }
             track_tile(ntc - 1, it); ++it;
-            // ---- merge the two halves, rebuild the winner's distance from global memory, write the row ----
+            // ---- merge the two column halves; every thread ends up with its row's winner -------------------
+            float xn_half;
             {
-                const bool takeb = best2[1] < best2[0] || (best2[1] == best2[0] && bidx2[1] < bidx2[0]);
-                bars->m_best[0][g][rl] = takeb ? best2[1] : best2[0];
-                bars->m_idx[0][g][rl] = takeb ? bidx2[1] : bidx2[0];
-                bars->m_second[0][g][rl] = fminf(fminf(second2[0], second2[1]), takeb ? best2[0] : best2[1]);
-                bars->xn_part[0][g][rl] = xn_half;
-                mbar_arrive(&bars->m_ready[0]);
-                mbar_wait_bounded(&bars->m_ready[0], li & 1);
-                const float b0 = bars->m_best[0][0][rl], b1 = bars->m_best[0][1][rl];
-                const float s0 = bars->m_second[0][0][rl], s1 = bars->m_second[0][1][rl];
-                const int i0 = bars->m_idx[0][0][rl], i1 = bars->m_idx[0][1][rl];
-                const bool take1 = b1 < b0 || (b1 == b0 && i1 < i0);
-                const float p_best = take1 ? b1 : b0;
-                int bi = take1 ? i1 : i0;
-                const float p_second = fminf(fminf(s0, s1), take1 ? b0 : b1);
-                bi = bi >= k ? k - 1 : bi;
-                const float xn = bars->xn_part[0][0][rl] + bars->xn_part[0][1][rl];
-                const float *crow = c32 + (size_t)bi * d;
-                float s = 0.f;
-                if (live) {
-                    for (int p = 0; p < npan; ++p) {
 #pragma unroll
-                        for (int c = 0; c < HCH; ++c) {
-                            const int f = p * TCW_PF + (g * HCH + c) * 4;
+                for (int q = 0; q < 4; ++q) {       // the row's pieces sit in the 4 lanes with the same r8
+                    xn4[q] += __shfl_xor_sync(0xffffffffu, xn4[q], 8);
+                    xn4[q] += __shfl_xor_sync(0xffffffffu, xn4[q], 16);
+                }
+                xn_half = cq == 0 ? xn4[0] : (cq == 1 ? xn4[1] : (cq == 2 ? xn4[2] : xn4[3]));   // row 8*cq + r8 == lane
+            }
+            const bool takeb = best2[1] < best2[0] || (best2[1] == best2[0] && bidx2[1] < bidx2[0]);
+            bars->m_best[0][g][rl] = takeb ? best2[1] : best2[0];
+            bars->m_idx[0][g][rl] = takeb ? bidx2[1] : bidx2[0];
+            bars->m_second[0][g][rl] = fminf(fminf(second2[0], second2[1]), takeb ? best2[0] : best2[1]);
+            bars->xn_part[0][g][rl] = xn_half;
+            mbar_arrive(&bars->m_ready[0]);
+            mbar_wait_bounded(&bars->m_ready[0], li & 1);
+            const float b0 = bars->m_best[0][0][rl], b1 = bars->m_best[0][1][rl];
+            const float s0 = bars->m_second[0][0][rl], s1 = bars->m_second[0][1][rl];
+            const int i0 = bars->m_idx[0][0][rl], i1 = bars->m_idx[0][1][rl];
+            const bool take1 = b1 < b0 || (b1 == b0 && i1 < i0);
+            const float p_best = take1 ? b1 : b0;
+            int bi = take1 ? i1 : i0;
+            const float p_second = fminf(fminf(s0, s1), take1 ? b0 : b1);
+            bi = bi >= k ? k - 1 : bi;
+            const float xn = bars->xn_part[0][0][rl] + bars->xn_part[0][1][rl];
+            // ---- the winner's distance in direct form, from global memory, with the cooperative load pattern ---
+            float d4[4] = {0.f, 0.f, 0.f, 0.f};
+            int bi4[4];
 #pragma unroll
-                            for (int e = 0; e < 4; ++e) {
-                                if (f + e < d) {
-                                    const float df = (__ldg(xrow + f + e) - __ldg(mu + f + e)) - __ldg(crow + f + e);
-                                    s = fmaf(df, df, s);
-                                }
-                            }
-                        }
+            for (int q = 0; q < 4; ++q) bi4[q] = __shfl_sync(0xffffffffu, bi, 8 * q + r8);
+            for (int p = 0; p < npan; ++p) {
+                float4 xv[HCH], cv[HCH];
+#pragma unroll
+                for (int i = 0; i < HCH; ++i) {
+                    const int64_t row = row_c0 + 8 * (i & 3);
+                    const int f = p * TCW_PF + (g * HCH + 4 * (i >> 2) + cq) * 4;
+                    xv[i] = load_piece(X + (row < n ? row : 0) * ldx, row, f);
+                    cv[i] = load_piece(c32 + (size_t)bi4[i & 3] * d, row, f);
+                }
+#pragma unroll
+                for (int i = 0; i < HCH; ++i) {
+                    const int f = p * TCW_PF + (g * HCH + 4 * (i >> 2) + cq) * 4;
+                    if (f < d) {
+                        const float4 m4 = __ldg(reinterpret_cast<const float4 *>(mu + f));
+                        float sx = d4[i & 3];
+                        float df;
+                        df = (xv[i].x - m4.x) - cv[i].x; sx = fmaf(df, df, sx);
+                        if (f + 1 < d) { df = (xv[i].y - m4.y) - cv[i].y; sx = fmaf(df, df, sx); }
+                        if (f + 2 < d) { df = (xv[i].z - m4.z) - cv[i].z; sx = fmaf(df, df, sx); }
+                        if (f + 3 < d) { df = (xv[i].w - m4.w) - cv[i].w; sx = fmaf(df, df, sx); }
+                        d4[i & 3] = sx;
                     }
                 }
-                if (g == 1) {
-                    bars->s_part[0][rl] = s;
-                    mbar_arrive(&bars->s_ready[0]);
-                } else {
-                    mbar_wait_bounded(&bars->s_ready[0], li & 1);
-                    s += bars->s_part[0][rl];
-                    if (live) {
-                        labels[row] = bi;
-                        if (mind2) mind2[row] = s;
-                        if (flag_rows) {
-                            const float thr = bound_scale * (xn + cmax);
-                            if (p_second - p_best <= thr) {
-                                const int pos = atomicAdd(flag_count, 1);
-                                flag_rows[pos] = (int32_t)row;
-                            }
+            }
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                d4[q] += __shfl_xor_sync(0xffffffffu, d4[q], 8);
+                d4[q] += __shfl_xor_sync(0xffffffffu, d4[q], 16);
+            }
+            float s = cq == 0 ? d4[0] : (cq == 1 ? d4[1] : (cq == 2 ? d4[2] : d4[3]));   // this thread's row, this half
+            if (g == 1) {
+                bars->s_part[0][rl] = s;
+                mbar_arrive(&bars->s_ready[0]);
+            } else {
+                mbar_wait_bounded(&bars->s_ready[0], li & 1);
+                s += bars->s_part[0][rl];
+                if (row_t < n) {
+                    labels[row_t] = bi;
+                    if (mind2) mind2[row_t] = s;
+                    if (flag_rows) {
+                        const float thr = bound_scale * (xn + cmax);
+                        if (p_second - p_best <= thr) {
+                            const int pos = atomicAdd(flag_count, 1);
+                            flag_rows[pos] = (int32_t)row_t;
                         }
                     }
                 }
