@@ -690,6 +690,8 @@ extern "C" int b200km_refine_f64(const float *X, int64_t n, int d, int64_t ldx, 
 constexpr int KM_CAND_CAP = 6;   // == TC_CAND_CAP (assign_tc.cu)
 int km_launch_cand_tc(const float *X, int64_t n, int d, int64_t ldx, const void *pack, int k, int32_t *flag_rows,
                       const int32_t *flag_count, const float *mind2, cudaStream_t st);
+int km_launch_cand_tc_wide(const float *X, int64_t n, int d, int64_t ldx, const void *pack, int k,
+                           int32_t *flag_rows, const int32_t *flag_count, float *mind2, cudaStream_t st);
 
 // One thread per flagged row: the listed columns are scored exactly as assign_rb_kernel<INDIRECT> scores them
 // (cn64 - 2 * sum_f x_f c_f, one DFMA per term in feature order, strict < then lowest index), so the two paths
@@ -745,7 +747,7 @@ extern "C" int b200km_refine_pruned_f64(const float *X, int64_t n, int d, int64_
     if (rc) return rc;
     KM_CHECK_ARG(flag_rows && flag_count, B200KM_EINVAL);
     // the candidate pass needs the tensor-core image (d <= 128, one-CTA layout) and the winner distances
-    if (d > KM_TC_MAX_D || km_tc_pair_mode() || !mind2 || n < 4096)
+    if (d > KM_TC_WIDE_MAX_D || km_tc_pair_mode() || !mind2 || n < 4096)
         return b200km_refine_f64(X, n, d, ldx, pack, k, flag_rows, flag_count, labels, mind2, stream);
     cudaStream_t st = km_stream(stream);
     const KmPackLayout L = km_pack_layout(k, d);
@@ -756,7 +758,8 @@ extern "C" int b200km_refine_pruned_f64(const float *X, int64_t n, int d, int64_
     rc = launch_rb<float, 32, 8, 8, true>(X, n, d, ldx, c64, cn64, k, flag_rows, flag_count, labels, mind2, st,
                                           flag_count, M, 0);
     if (rc) return rc;
-    rc = km_launch_cand_tc(X, n, d, ldx, pack, k, flag_rows, flag_count, mind2, st);
+    rc = d <= KM_TC_MAX_D ? km_launch_cand_tc(X, n, d, ldx, pack, k, flag_rows, flag_count, mind2, st)
+                          : km_launch_cand_tc_wide(X, n, d, ldx, pack, k, flag_rows, flag_count, mind2, st);
     if (rc) return rc;
     refine_cand_kernel<<<KM_NUM_SMS * 4, 128, 0, st>>>(X, n, d, ldx, c64, cn64, flag_rows, flag_count, labels, mind2);
     cudaError_t e = cudaGetLastError();

@@ -1303,7 +1303,10 @@ constexpr int TCW_PF = 64;              // features per panel
 constexpr int TCW_PCH = TCW_PF / 4;     // 16-byte chunks per panel
 constexpr int TCW_PKS = TCW_PF / 8;     // K-steps per panel
 
-template <bool VEC>
+// CAND: the candidate pass of the pruned re-decision for wide rows -- the rows are flag_rows[0 .. *flag_count)
+// (gathered), the epilogue lists the columns with score <= threshold instead of tracking, nothing else is written
+// (see cand_tc_kernel for the threshold and the scratch layout in the tail of flag_rows).
+template <bool VEC, bool CAND>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 assign_tc_wide_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
                       const unsigned char *__restrict__ tc_img, const float *__restrict__ c32,
@@ -1311,6 +1314,16 @@ assign_tc_wide_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx
                       int32_t *__restrict__ labels, float *__restrict__ mind2,
                       int32_t *__restrict__ flag_rows, int32_t *__restrict__ flag_count) {
     extern __shared__ __align__(1024) unsigned char tc_smem[];
+    int64_t nrows = n;                                          // rows (or flagged rows) to process
+    int64_t cand_M = 0;
+    if (CAND) {
+        cand_M = (n - 1) / (TC_CAND_CAP + 3);
+        const int64_t cnt = (int64_t)(*flag_count);
+        if (cnt > cand_M) return;                               // uniform: the full re-decision handles this call
+        if (blockIdx.x == 0 && threadIdx.x == 0) flag_rows[n - 1] = 0;   // size of the overflow list
+        if (cnt <= 0) return;
+        nrows = cnt;
+    }
     const int kpad = km_tc_kpad(d);
     const int nks = kpad / 8;                                   // K-steps of a whole row
     const int npan = (kpad + TCW_PF - 1) / TCW_PF;              // panels per row (>= 3)
@@ -1326,7 +1339,7 @@ assign_tc_wide_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int ntc = (k + KM_TC_BN - 1) / KM_TC_BN;
-    const int64_t nsteps = (n + TC_ROWS - 1) / TC_ROWS;
+    const int64_t nsteps = (nrows + TC_ROWS - 1) / TC_ROWS;
 
     if (tid == 0) {
         for (int i = 0; i < NST; ++i) { km_mbar_init(&bars->b_full[i], 1); km_mbar_init(&bars->b_empty[i], 1); }
@@ -1440,8 +1453,19 @@ assign_tc_wide_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx
         constexpr int HCH = TCW_PCH / 2;         // chunks per half panel (8): two per lane and row
         uint32_t it = 0, sq = 0, li = 0;
         for (int64_t step = blockIdx.x; step < nsteps; step += gridDim.x, ++li) {
-            const int64_t row_t = step * TC_ROWS + rl;                    // the row this thread TRACKS
-            const int64_t row_c0 = step * TC_ROWS + q4 * 32 + r8;          // first of the 4 rows this lane LOADS
+            // the row this thread TRACKS and the 4 rows this lane LOADS (CAND: through the flagged-row list)
+            const int64_t pos_t = step * TC_ROWS + rl;
+            const bool live_t = pos_t < nrows;
+            const int64_t row_t = CAND ? (live_t ? (int64_t)__ldg(flag_rows + pos_t) : 0) : pos_t;
+            int64_t row4[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int64_t pos = step * TC_ROWS + q4 * 32 + 8 * q + r8;
+                row4[q] = pos < nrows ? (CAND ? (int64_t)__ldg(flag_rows + pos) : pos) : -1;
+            }
+            float cand_T = -INFINITY;
+            int *ccnt = reinterpret_cast<int *>(&bars->m_best[0][0][0]);      // CAND: per-row list length ...
+            int *clist = reinterpret_cast<int *>(&bars->m_second[0][0][0]);   // ... and columns (over m_second, m_idx)
             float best2[2] = {INFINITY, INFINITY}, second2[2] = {INFINITY, INFINITY};
             int bidx2[2] = {0, 0};
             float xn4[4] = {0.f, 0.f, 0.f, 0.f};
@@ -1459,7 +1483,15 @@ assign_tc_wide_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx
                     uint32_t (&nxt)[32] = (c & 1) ? ra : rb;
                     if (c + 1 < 4) tmem_ld32(tbase + (uint32_t)((c + 1) * 32), nxt);
                     const int cb = t * KM_TC_BN + g * 128 + c * 32;
-                    if (cb < k) {
+                    if (CAND) {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) {
+                            if (__uint_as_float(cur[j]) <= cand_T && cb + j < k) {
+                                const int q = atomicAdd(&ccnt[rl], 1);
+                                if (q < TC_CAND_CAP) clist[rl * TC_CAND_CAP + q] = cb + j;
+                            }
+                        }
+                    } else if (cb < k) {
                         const float before0 = best2[0], before1 = best2[1];
                         int jloc0 = 0, jloc1 = 0;
 #pragma unroll
@@ -1478,7 +1510,7 @@ assign_tc_wide_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx
             // piece i of a half panel: row 8*(i&3) + r8 of the warp's 32, chunk 4*(i>>2) + cq of the half's 8
             auto load_piece = [&](const float *base, int64_t row, int f) -> float4 {
                 float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (row < n && f < d) {
+                if (row >= 0 && f < d) {
                     const float *src = base + f;
                     if (VEC) {
                         x = __ldg(reinterpret_cast<const float4 *>(src));
@@ -1497,9 +1529,9 @@ assign_tc_wide_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx
                     float4 v[HCH];
 #pragma unroll
                     for (int i = 0; i < HCH; ++i) {
-                        const int64_t row = row_c0 + 8 * (i & 3);
+                        const int64_t row = row4[i & 3];
                         const int f = p * TCW_PF + (g * HCH + 4 * (i >> 2) + cq) * 4;
-                        v[i] = load_piece(X + (row < n ? row : 0) * ldx, row, f);
+                        v[i] = load_piece(X + (row >= 0 ? row : 0) * ldx, row, f);
                     }
                     float4 mq[2];
 #pragma unroll
@@ -1512,12 +1544,12 @@ assign_tc_wide_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx
                     unsigned char *pl = ph + xhi_bytes;
 #pragma unroll
                     for (int i = 0; i < HCH; ++i) {
-                        const int64_t row = row_c0 + 8 * (i & 3);
+                        const int64_t row = row4[i & 3];
                         const int f = p * TCW_PF + (g * HCH + 4 * (i >> 2) + cq) * 4;
                         float4 x = v[i];
                         const float4 m4 = mq[i >> 2];
                         x.x -= m4.x; x.y -= m4.y; x.z -= m4.z; x.w -= m4.w;
-                        if (row >= n || f >= d) x = make_float4(0.f, 0.f, 0.f, 0.f);
+                        if (row < 0 || f >= d) x = make_float4(0.f, 0.f, 0.f, 0.f);
                         else if (f + 3 >= d) {          // padding features of the row's last chunk stay exactly zero
                             if (f + 1 >= d) x.y = 0.f;
                             if (f + 2 >= d) x.z = 0.f;
@@ -1540,8 +1572,32 @@ assign_tc_wide_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx
                     // tile t-1 is complete once this panel's buffer was free again: track it under tile t's MMAs
                     if (p == 1 && t > 0) { track_tile(t - 1, it); ++it; }
                 }
+                if (CAND && t == 0) {
+                    // every panel of the rows has been staged once: the rows' norms, hence their thresholds
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        xn4[q] += __shfl_xor_sync(0xffffffffu, xn4[q], 8);
+                        xn4[q] += __shfl_xor_sync(0xffffffffu, xn4[q], 16);
+                    }
+                    bars->xn_part[0][g][rl] = cq == 0 ? xn4[0] : (cq == 1 ? xn4[1] : (cq == 2 ? xn4[2] : xn4[3]));
+                    if (g == 0) ccnt[rl] = 0;
+                    mbar_arrive(&bars->m_ready[1]);
+                    mbar_wait_bounded(&bars->m_ready[1], li & 1);
+                    const float xn_c = bars->xn_part[0][0][rl] + bars->xn_part[0][1][rl];
+                    cand_T = live_t ? (__ldg(mind2 + row_t) - xn_c) + 2.0f * bound_scale * (xn_c + cmax) : -INFINITY;
+                }
             }
             track_tile(ntc - 1, it); ++it;
+            if (CAND) {
+                mbar_arrive(&bars->m_ready[0]);                 // both column halves have finished listing
+                mbar_wait_bounded(&bars->m_ready[0], li & 1);
+                if (g == 0 && live_t) {
+                    int32_t *out = flag_rows + cand_M + pos_t * (TC_CAND_CAP + 1);
+                    const int c = ccnt[rl];
+                    out[0] = c;
+                    for (int q = 0; q < TC_CAND_CAP; ++q) out[1 + q] = q < c ? clist[rl * TC_CAND_CAP + q] : 0;
+                }
+            } else {
             // ---- merge the two column halves; every thread ends up with its row's winner -------------------
             float xn_half;
             {
@@ -1577,9 +1633,9 @@ assign_tc_wide_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx
                 float4 xv[HCH], cv[HCH];
 #pragma unroll
                 for (int i = 0; i < HCH; ++i) {
-                    const int64_t row = row_c0 + 8 * (i & 3);
+                    const int64_t row = row4[i & 3];
                     const int f = p * TCW_PF + (g * HCH + 4 * (i >> 2) + cq) * 4;
-                    xv[i] = load_piece(X + (row < n ? row : 0) * ldx, row, f);
+                    xv[i] = load_piece(X + (row >= 0 ? row : 0) * ldx, row, f);
                     cv[i] = load_piece(c32 + (size_t)bi4[i & 3] * d, row, f);
                 }
 #pragma unroll
@@ -1609,7 +1665,7 @@ assign_tc_wide_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx
             } else {
                 mbar_wait_bounded(&bars->s_ready[0], li & 1);
                 s += bars->s_part[0][rl];
-                if (row_t < n) {
+                if (live_t) {
                     labels[row_t] = bi;
                     if (mind2) mind2[row_t] = s;
                     if (flag_rows) {
@@ -1621,6 +1677,7 @@ assign_tc_wide_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx
                     }
                 }
             }
+            }   // !CAND
         }
     }
 
@@ -1630,6 +1687,29 @@ assign_tc_wide_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx
         tc_fence_after();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
     }
+}
+
+int km_launch_cand_tc_wide(const float *X, int64_t n, int d, int64_t ldx, const void *pack, int k,
+                           int32_t *flag_rows, const int32_t *flag_count, float *mind2, cudaStream_t st) {
+    const KmPackLayout L = km_pack_layout(k, d);
+    const unsigned char *pk = static_cast<const unsigned char *>(pack);
+    const size_t xbuf_w = (size_t)(TCW_PCH + 2) * 128 * 16 + (size_t)TCW_PCH * 128 * 16;
+    const size_t smem_w = 2 * xbuf_w + 5 * (size_t)KM_TC_KS_BYTES + sizeof(TcBars) + 64;
+    const bool vec = (d % 4 == 0) && (ldx % 4 == 0) && ((reinterpret_cast<uintptr_t>(X) & 15) == 0);
+    const unsigned char *img = pk + L.off_tc;
+    const float *c32 = reinterpret_cast<const float *>(pk + L.off_c32);
+    const float *mu = reinterpret_cast<const float *>(pk + L.off_mu);
+    const unsigned int *cmax = reinterpret_cast<const unsigned int *>(pk + L.off_cmax);
+    static bool attr_v[KM_MAX_DEVICES] = {}, attr_s[KM_MAX_DEVICES] = {};
+    if (int rc = km_set_smem_once(assign_tc_wide_kernel<true, true>, 227 * 1024, attr_v)) return rc;
+    if (int rc = km_set_smem_once(assign_tc_wide_kernel<false, true>, 227 * 1024, attr_s)) return rc;
+    if (vec)
+        assign_tc_wide_kernel<true, true><<<KM_NUM_SMS, TC_THREADS, smem_w, st>>>(
+            X, n, d, ldx, img, c32, mu, cmax, k, nullptr, mind2, flag_rows, const_cast<int32_t *>(flag_count));
+    else
+        assign_tc_wide_kernel<false, true><<<KM_NUM_SMS, TC_THREADS, smem_w, st>>>(
+            X, n, d, ldx, img, c32, mu, cmax, k, nullptr, mind2, flag_rows, const_cast<int32_t *>(flag_count));
+    return (int)cudaGetLastError();
 }
 
 // host-side launcher, called from b200km_assign_f32
@@ -1653,13 +1733,13 @@ int km_launch_assign_tc(const float *X, int64_t n, int d, int64_t ldx, const voi
         const int64_t steps_w = (n + TC_ROWS - 1) / TC_ROWS;
         const unsigned grid = (unsigned)(steps_w < KM_NUM_SMS ? steps_w : KM_NUM_SMS);
         static bool attr_v[KM_MAX_DEVICES] = {}, attr_s[KM_MAX_DEVICES] = {};
-        if (int rc = km_set_smem_once(assign_tc_wide_kernel<true>, 227 * 1024, attr_v)) return rc;
-        if (int rc = km_set_smem_once(assign_tc_wide_kernel<false>, 227 * 1024, attr_s)) return rc;
+        if (int rc = km_set_smem_once(assign_tc_wide_kernel<true, false>, 227 * 1024, attr_v)) return rc;
+        if (int rc = km_set_smem_once(assign_tc_wide_kernel<false, false>, 227 * 1024, attr_s)) return rc;
         if (vec)
-            assign_tc_wide_kernel<true><<<grid, TC_THREADS, smem_w, st>>>(X, n, d, ldx, img, c32, mu, cmax, k, labels, mind2,
+            assign_tc_wide_kernel<true, false><<<grid, TC_THREADS, smem_w, st>>>(X, n, d, ldx, img, c32, mu, cmax, k, labels, mind2,
                                                                          flag_rows, flag_count);
         else
-            assign_tc_wide_kernel<false><<<grid, TC_THREADS, smem_w, st>>>(X, n, d, ldx, img, c32, mu, cmax, k, labels, mind2,
+            assign_tc_wide_kernel<false, false><<<grid, TC_THREADS, smem_w, st>>>(X, n, d, ldx, img, c32, mu, cmax, k, labels, mind2,
                                                                           flag_rows, flag_count);
         return (int)cudaGetLastError();
     }

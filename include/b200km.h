@@ -105,7 +105,7 @@ int b200km_refine_f64(const float *X, int64_t n, int d, int64_t ldx, const void 
  * columns (duplicate centres) get the full scan.
  *   flag_rows: the n-entry buffer b200km_assign_f32 filled; entries from *flag_count on are used as scratch
  *   (hence not const).  mind2 must hold b200km_assign_f32's output for these rows.
- *   Falls back to b200km_refine_f64 when mind2 == NULL, d > 128, n < 4096 or K1 variant 3 is selected, and -- decided
+ *   Falls back to b200km_refine_f64 when mind2 == NULL, n < 4096 or K1 variant 3 is selected, and -- decided
  *   on the device, no host synchronisation -- when more than (n-1)/9 rows are flagged.
  * Replaces: nothing in the reference (see b200km_refine_f64). */
 int b200km_refine_pruned_f64(const float *X, int64_t n, int d, int64_t ldx, const void *pack, int k,

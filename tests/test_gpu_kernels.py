@@ -415,7 +415,8 @@ def _assign_both_refines(eng, X, C):
 
 
 @pytest.mark.parametrize("n,d,k", [(60000, 64, 1024), (50000, 32, 256), (30000, 128, 700), (20000, 20, 90),
-                                    (5000, 64, 300), (4096, 8, 40)])
+                                    (5000, 64, 300), (4096, 8, 40), (20000, 256, 600), (9000, 333, 100),
+                                    (6000, 1024, 300), (30000, 136, 1024)])
 def test_refine_pruned_equals_full_scan(eng, n, d, k):
     """The pruned float64 re-decision (tensor-core candidate pass + float64 on the listed centres) gives the labels
     and distances of the full float64 scan bit for bit; centres = data rows, so near-ties are plentiful."""
