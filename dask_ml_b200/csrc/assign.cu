@@ -601,7 +601,7 @@ static bool use_tc_path(int d, int k) {
     if (d > KM_TC_MAX_D && g_k1_variant == 3) return false;   // the wide-row kernel has no CTA-pair form
     if (g_k1_variant == 1) return false;
     if (g_k1_variant >= 2) return true;
-    return true;   // auto: tensor cores whenever the shape allows (d <= 128)
+    return true;   // auto: tensor cores whenever the shape allows (d <= 2048)
 }
 static int check_pack_args(const void *X, int64_t n, int d, int64_t ldx, const void *pack, int k, const void *labels) {
     KM_CHECK_ARG(X && pack && labels, B200KM_EINVAL);

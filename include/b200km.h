@@ -48,7 +48,7 @@ extern "C" {
 #define B200KM_MINDIST_MAX_M 8 /* candidates per b200km_mindist_update_* launch */
 
 /* options (process-wide; meant for benchmarks and tests) */
-#define B200KM_OPT_K1_VARIANT 1 /* 0 = auto (tcgen05 3xTF32 for d <= 128; its small-k kernel when k <= 256 and d <= 32),
+#define B200KM_OPT_K1_VARIANT 1 /* 0 = auto (tcgen05 3xTF32 for d <= 2048: small-k kernel when k <= 256 and d <= 32, panel kernel for d > 128),
                                   * 1 = FP32 FFMA kernel, 2 = the general tcgen05 kernel on one CTA per SM,
                                   * 3 = the general tcgen05 kernel on CTA pairs (cta_group::2).
                                   * Set it BEFORE b200km_pack_centers: the tensor-core image differs for 3. */
