@@ -142,6 +142,7 @@ update_atomic_kernel(const T *__restrict__ X, int64_t n, int d, int64_t ldx, con
 // ---------------------------------------------------------------------------------------------
 constexpr int SEG_R_MAX = 65536;   // rows per CTA chunk: row offsets fit uint16
 constexpr int SEG_THREADS = 512;
+constexpr int SEG_LONG = 256;       // runs longer than this are shared out between the CTA's warps
 constexpr int SEG_MAX_K = 8192;
 
 template <typename T>
@@ -154,10 +155,13 @@ update_seg_kernel(const T *__restrict__ X, int64_t n, int d, int64_t ldx, const 
     unsigned short *order = reinterpret_cast<unsigned short *>(cursor + k);  // [SEG_R]
     __shared__ double red[32];
     __shared__ int wsum[SEG_THREADS / 32];
+    __shared__ int nlong;
+    __shared__ int longlist[SEG_R_MAX / SEG_LONG];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr int NW = SEG_THREADS / 32;
     double inert = 0.0;
     double *counts = acc + (size_t)k * d;
+    if (tid == 0) nlong = 0;   // (the first chunk's phase-1 barrier orders this before any use)
 
     for (int64_t base = (int64_t)blockIdx.x * SEG_R; base < n; base += (int64_t)gridDim.x * SEG_R) {
         const int rows = (int)((n - base) < SEG_R ? (n - base) : SEG_R);
@@ -207,11 +211,11 @@ update_seg_kernel(const T *__restrict__ X, int64_t n, int d, int64_t ldx, const 
             order[pos] = (unsigned short)i;
         }
         __syncthreads();
-        // 4. one warp per cluster: sum its rows, one RED per feature
+        // 4. one warp per cluster: sum its rows, one RED per feature.  A run longer than SEG_LONG rows (a dominant
+        //    cluster) would leave one warp with most of the chunk, so it is set aside and then cut into one slice
+        //    per warp (16 REDs per feature for it instead of 1).
         const T *Xb = X + base * ldx;
-        for (int c = warp; c < k; c += NW) {
-            const int s0 = start[c], s1 = start[c + 1];
-            if (s0 == s1) continue;
+        auto sum_run = [&](int c, int s0, int s1) {
             for (int f0 = 0; f0 < d; f0 += 64) {
                 const int fa = f0 + lane, fb = f0 + 32 + lane;
                 double a0 = 0.0, a1 = 0.0;
@@ -251,8 +255,27 @@ update_seg_kernel(const T *__restrict__ X, int64_t n, int d, int64_t ldx, const 
                 if (fa < d) atomicAdd(acc + (size_t)c * d + fa, a0);
                 if (fb < d) atomicAdd(acc + (size_t)c * d + fb, a1);
             }
+        };
+        for (int c = warp; c < k; c += NW) {
+            const int s0 = start[c], s1 = start[c + 1];
+            if (s0 == s1) continue;
+            if (s1 - s0 > SEG_LONG) {
+                if (lane == 0) longlist[atomicAdd(&nlong, 1)] = c;
+                continue;
+            }
+            sum_run(c, s0, s1);
         }
         __syncthreads();
+        const int nl = nlong;
+        for (int i = 0; i < nl; ++i) {
+            const int c = longlist[i];
+            const int s0 = start[c], s1 = start[c + 1];
+            const int per = (s1 - s0 + NW - 1) / NW;
+            const int a = s0 + warp * per, b = (a + per) < s1 ? (a + per) : s1;
+            if (a < b) sum_run(c, a, b);
+        }
+        __syncthreads();
+        if (tid == 0) nlong = 0;
     }
     if (mind2) km_block_atomic_add(inert, acc + (size_t)k * d + k, red);
 }
@@ -273,10 +296,12 @@ static int update_impl(const T *X, int64_t n, int d, int64_t ldx, const int32_t 
     const int variant = km_k2_variant();
     const bool seg_ok = k <= SEG_MAX_K && n >= 4 * (int64_t)k;
     const bool owner_ok = smem <= 96 * 1024;
-    // auto (measured on B200, tools/upd_check.py): the shared-memory owner table for tiny tables (k*d <= 2048:
-    // C1); chunk sort + run sums while a 16384-row chunk holds >= 8 rows per cluster (k <= 2048: C2, C3);
-    // plain fp64 REDs beyond that (C4: runs of 2 rows do not pay for the sort)
-    const bool use_owner = variant == 1 ? owner_ok : (variant == 0 && owner_ok && (size_t)k * d <= 2048);
+    // auto (measured on B200, tools/upd_check.py): chunk sort + run sums while a chunk holds >= 8 rows per cluster
+    // (k <= 2048: C2, C3, and every small table); plain fp64 REDs beyond that (C4: runs of 2 rows do not pay for
+    // the sort)
+    // (the shared-memory owner table, once the choice for tiny tables, loses 3-6x to the chunk-sort kernel on every
+    //  shape measured -- and 14x with one dominant cluster -- so auto takes it only when the chunk sort cannot run)
+    const bool use_owner = variant == 1 ? owner_ok : (variant == 0 && owner_ok && !seg_ok && (size_t)k * d <= 2048);
     const bool use_seg = !use_owner && seg_ok && (variant == 2 || (variant == 0 && k <= 2048));
     if (use_owner) {
         auto kern = update_owner_kernel<T>;
