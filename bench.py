@@ -25,6 +25,13 @@ import subprocess
 import sys
 import time
 
+# OpenBLAS sizes its thread tables from the machine's core count at load time; on boxes with more cores than its
+# compiled-in limit it falls back to an "auxiliary array" path that has aborted the CPU legs here ("BLAS : Bad
+# memory unallocation", "corrupted size vs. prev_size").  The CPU baseline runs one single-threaded BLAS call per
+# row block anyway (the thread pool provides the parallelism), so pin BLAS to one thread BEFORE numpy is imported.
+os.environ.setdefault("OPENBLAS_NUM_THREADS", "1")
+os.environ.setdefault("OMP_NUM_THREADS", "1")
+
 ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)

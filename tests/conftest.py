@@ -1,6 +1,9 @@
 import os
 import sys
 
+# see bench.py: OpenBLAS's thread tables overflow on many-core boxes; the oracle needs one BLAS thread per block
+os.environ.setdefault("OPENBLAS_NUM_THREADS", "1")
+
 import numpy as np
 import pytest
 
