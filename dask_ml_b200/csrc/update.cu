@@ -145,8 +145,10 @@ constexpr int SEG_THREADS = 512;
 constexpr int SEG_LONG = 256;       // runs longer than this are shared out between the CTA's warps
 constexpr int SEG_MAX_K = 8192;
 
-template <typename T>
-__global__ void __launch_bounds__(SEG_THREADS)
+// NARROW (d <= 32): a row is one 32-lane load, so the second feature half (fb, w[]) is compiled out and the
+// registers it frees buy a third resident CTA (C2: 2.39 -> 2.64 TB/s); wider rows do better with two (C3).
+template <typename T, bool NARROW>
+__global__ void __launch_bounds__(SEG_THREADS, NARROW ? 3 : 2)
 update_seg_kernel(const T *__restrict__ X, int64_t n, int d, int64_t ldx, const int32_t *__restrict__ labels,
                   const T *__restrict__ mind2, int k, double *__restrict__ acc, int scale_sqrt, int SEG_R) {
     extern __shared__ __align__(16) unsigned char seg_smem[];
@@ -217,7 +219,7 @@ update_seg_kernel(const T *__restrict__ X, int64_t n, int d, int64_t ldx, const 
         const T *Xb = X + base * ldx;
         auto sum_run = [&](int c, int s0, int s1) {
             for (int f0 = 0; f0 < d; f0 += 64) {
-                const int fa = f0 + lane, fb = f0 + 32 + lane;
+                const int fa = f0 + lane, fb = NARROW ? d : f0 + 32 + lane;   // NARROW: fb >= d, dead code
                 double a0 = 0.0, a1 = 0.0;
                 int p = s0;
                 for (; p + 8 <= s1; p += 8) {   // 8 rows (16 loads per lane) in flight
@@ -226,12 +228,13 @@ update_seg_kernel(const T *__restrict__ X, int64_t n, int d, int64_t ldx, const 
                     for (int u = 0; u < 8; ++u) {
                         const int64_t ro = (int64_t)order[p + u] * ldx;
                         v[u] = fa < d ? __ldg(Xb + ro + fa) : (T)0;
-                        w[u] = fb < d ? __ldg(Xb + ro + fb) : (T)0;
+                        w[u] = (!NARROW && fb < d) ? __ldg(Xb + ro + fb) : (T)0;
                     }
                     a0 += (((double)v[0] + (double)v[1]) + ((double)v[2] + (double)v[3])) +
                           (((double)v[4] + (double)v[5]) + ((double)v[6] + (double)v[7]));
-                    a1 += (((double)w[0] + (double)w[1]) + ((double)w[2] + (double)w[3])) +
-                          (((double)w[4] + (double)w[5]) + ((double)w[6] + (double)w[7]));
+                    if (!NARROW)
+                        a1 += (((double)w[0] + (double)w[1]) + ((double)w[2] + (double)w[3])) +
+                              (((double)w[4] + (double)w[5]) + ((double)w[6] + (double)w[7]));
                 }
                 for (; p + 4 <= s1; p += 4) {
                     const int r0 = order[p], r1 = order[p + 1], r2 = order[p + 2], r3 = order[p + 3];
@@ -240,20 +243,20 @@ update_seg_kernel(const T *__restrict__ X, int64_t n, int d, int64_t ldx, const 
                         v0 = __ldg(Xb + (int64_t)r0 * ldx + fa); v1 = __ldg(Xb + (int64_t)r1 * ldx + fa);
                         v2 = __ldg(Xb + (int64_t)r2 * ldx + fa); v3 = __ldg(Xb + (int64_t)r3 * ldx + fa);
                     }
-                    if (fb < d) {
+                    if (!NARROW && fb < d) {
                         w0 = __ldg(Xb + (int64_t)r0 * ldx + fb); w1 = __ldg(Xb + (int64_t)r1 * ldx + fb);
                         w2 = __ldg(Xb + (int64_t)r2 * ldx + fb); w3 = __ldg(Xb + (int64_t)r3 * ldx + fb);
                     }
                     a0 += ((double)v0 + (double)v1) + ((double)v2 + (double)v3);
-                    a1 += ((double)w0 + (double)w1) + ((double)w2 + (double)w3);
+                    if (!NARROW) a1 += ((double)w0 + (double)w1) + ((double)w2 + (double)w3);
                 }
                 for (; p < s1; ++p) {
                     const int r0 = order[p];
                     if (fa < d) a0 += (double)__ldg(Xb + (int64_t)r0 * ldx + fa);
-                    if (fb < d) a1 += (double)__ldg(Xb + (int64_t)r0 * ldx + fb);
+                    if (!NARROW && fb < d) a1 += (double)__ldg(Xb + (int64_t)r0 * ldx + fb);
                 }
                 if (fa < d) atomicAdd(acc + (size_t)c * d + fa, a0);
-                if (fb < d) atomicAdd(acc + (size_t)c * d + fb, a1);
+                if (!NARROW && fb < d) atomicAdd(acc + (size_t)c * d + fb, a1);
             }
         };
         for (int c = warp; c < k; c += NW) {
@@ -318,13 +321,18 @@ static int update_impl(const T *X, int64_t n, int d, int64_t ldx, const int32_t 
         if (SEG_R > SEG_R_MAX) SEG_R = SEG_R_MAX;
         while (SEG_R > 4096 && sizeof(int) * (size_t)(2 * k + 1) + sizeof(unsigned short) * (size_t)SEG_R + 16 > 200 * 1024) SEG_R /= 2;
         const size_t seg_smem = sizeof(int) * (size_t)(2 * k + 1) + sizeof(unsigned short) * (size_t)SEG_R + 16;
-        auto kern = update_seg_kernel<T>;
-        static bool attr_set[KM_MAX_DEVICES] = {};
-        if (int rc = km_set_smem_once(kern, 200 * 1024, attr_set)) return rc;
+        static bool attr_n[KM_MAX_DEVICES] = {}, attr_w[KM_MAX_DEVICES] = {};
+        if (int rc = km_set_smem_once(update_seg_kernel<T, true>, 200 * 1024, attr_n)) return rc;
+        if (int rc = km_set_smem_once(update_seg_kernel<T, false>, 200 * 1024, attr_w)) return rc;
         int64_t blocks = (n + SEG_R - 1) / SEG_R;
         const int64_t cap = (int64_t)KM_NUM_SMS * 4;   // several CTAs per SM: one sorts while another gathers
         if (blocks > cap) blocks = cap;
-        kern<<<(unsigned)blocks, SEG_THREADS, seg_smem, st>>>(X, n, d, ldx, labels, mind2, k, acc, scale_sqrt, SEG_R);
+        if (d <= 32)
+            update_seg_kernel<T, true><<<(unsigned)blocks, SEG_THREADS, seg_smem, st>>>(X, n, d, ldx, labels, mind2, k, acc,
+                                                                                      scale_sqrt, SEG_R);
+        else
+            update_seg_kernel<T, false><<<(unsigned)blocks, SEG_THREADS, seg_smem, st>>>(X, n, d, ldx, labels, mind2, k,
+                                                                                       acc, scale_sqrt, SEG_R);
     } else {
         int64_t blocks = (n + 4 * UP_WARPS - 1) / (4 * UP_WARPS);
         const int64_t cap = (int64_t)KM_NUM_SMS * 8;
