@@ -50,6 +50,8 @@ class CudaEngine:
         self.launches = 0  # kernels launched through this engine (bench.py reports it)
         self.k1_events = None  # bench.py: set to a list to collect (start, end) CUDA events around K1
         self.pruned_refine = True   # tests flip this to compare with the full float64 scan
+        self.f64_on_tensor_cores = True   # float64 X, k > 16: centre + round, tcgen05 decision, float64 re-decision
+
         self.trace = None      # tools/: set to a list to collect (entry point, event) per launch
         self._scratch = {}
 
@@ -84,6 +86,7 @@ class CudaEngine:
             t = t.to(dtype)
         return t.to(self.device, non_blocking=True).contiguous()
 
+    F64_BLOCK_BYTES = 256 << 20   # float32 scratch of the float64-on-tensor-cores path (rows per block = this / 4d)
     STREAM_MIN_BYTES = 64 << 20   # host inputs at least this big are uploaded in overlapped row chunks
     STREAM_CHUNKS = 8
 
@@ -200,6 +203,32 @@ class CudaEngine:
                 else:
                     self._call("b200km_assign_f32", xs.data_ptr(), nn, d, ldx, pack.buf.data_ptr(), pack.k,
                                ls.data_ptr(), mp, None, None, 0, st, launches=1)
+            elif self.f64_on_tensor_cores and pack.k > 16 and d <= 2048 and self.lib.b200km_get_option(1) in (0, 2):
+                # float64 rows: centred + rounded block by block, decided on the tensor cores with the float32 path's
+                # near-tie flags, re-decided in float64 where flagged, distances rebuilt in float64
+                if self.k1_events is not None:
+                    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    e0.record()
+                blk = max(1, min(nn, self.F64_BLOCK_BYTES // (4 * d)))
+                xc = self._buf("x_centred", (blk, d), torch.float32)
+                flags = self._buf("flag_rows", (blk,), torch.int32)
+                fcnt = self._buf("flag_count", (1,), torch.int32)
+                for b0 in range(0, nn, blk):
+                    bn = min(blk, nn - b0)
+                    xb, lb = xs[b0 : b0 + bn], ls[b0 : b0 + bn]
+                    self._call("b200km_center_convert_f64", xb.data_ptr(), bn, d, ldx, pack.buf.data_ptr(), pack.k,
+                               xc.data_ptr(), st, launches=1)
+                    self._call("b200km_assign_centred_f32", xc.data_ptr(), bn, d, d, pack.buf.data_ptr(), pack.k,
+                               lb.data_ptr(), None, flags.data_ptr(), fcnt.data_ptr(), 1, st, launches=1)
+                    if refine:
+                        self._call("b200km_refine_x64_f64", xb.data_ptr(), bn, d, ldx, pack.buf.data_ptr(), pack.k,
+                                   flags.data_ptr(), fcnt.data_ptr(), lb.data_ptr(), None, st, launches=1)
+                    if mp is not None:
+                        self._call("b200km_rowdist_f64", xb.data_ptr(), bn, d, ldx, pack.buf.data_ptr(), pack.k,
+                                   lb.data_ptr(), mind2[r0 + b0 : r0 + b0 + bn].data_ptr(), st, launches=1)
+                if self.k1_events is not None:
+                    e1.record()
+                    self.k1_events.append((e0, e1))
             else:
                 if self.k1_events is not None:
                     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

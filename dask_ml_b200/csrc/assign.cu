@@ -19,7 +19,7 @@
 
 int km_launch_pack_tc(int k, int d, void *pack, cudaStream_t st);  // assign_tc.cu
 int km_launch_assign_tc(const float *X, int64_t n, int d, int64_t ldx, const void *pack, int k, int32_t *labels,
-                        float *mind2, int32_t *flag_rows, int32_t *flag_count, cudaStream_t st);
+                        float *mind2, int32_t *flag_rows, int32_t *flag_count, cudaStream_t st, bool precentred);
 
 // =============================================================================================
 // centre pack
@@ -30,6 +30,7 @@ __global__ void __launch_bounds__(128) pack_mu_kernel(const double *__restrict__
     const KmPackLayout L = km_pack_layout(k, d);
     float *mu = reinterpret_cast<float *>(pack + L.off_mu);
     const int f = blockIdx.x;
+    if (threadIdx.x == 0) reinterpret_cast<float *>(pack + L.off_zero)[f] = 0.f;
     __shared__ double red[4];
     if (f >= d) {
         if (threadIdx.x == 0) mu[f] = 0.f;
@@ -611,11 +612,13 @@ static int check_pack_args(const void *X, int64_t n, int d, int64_t ldx, const v
     return 0;
 }
 
-extern "C" int b200km_assign_f32(const float *X, int64_t n, int d, int64_t ldx, const void *pack, int k,
-                                 int32_t *labels, float *mind2, int32_t *flag_rows, int32_t *flag_count,
-                                 int reset_flags, void *stream) {
+static int assign_f32_impl(const float *X, int64_t n, int d, int64_t ldx, const void *pack, int k,
+                           int32_t *labels, float *mind2, int32_t *flag_rows, int32_t *flag_count,
+                           int reset_flags, void *stream, bool precentred) {
     int rc = check_pack_args(X, n, d, ldx, pack, k, labels);
     if (rc) return rc;
+    // rows already centred on the pack's mu: only the kernels that work on centred data can take them
+    KM_CHECK_ARG(!precentred || (k > 16 && (d <= 128 || use_tc_path(d, k))), B200KM_EINVAL);
     KM_CHECK_ARG(!flag_rows || flag_count, B200KM_EINVAL);
     cudaStream_t st = km_stream(stream);
     const KmPackLayout L = km_pack_layout(k, d);
@@ -632,7 +635,8 @@ extern "C" int b200km_assign_f32(const float *X, int64_t n, int d, int64_t ldx, 
     if (k <= 16 || (d > 128 && !use_tc_path(d, k))) {
         return launch_rb<float, 32, 8, 8, false>(X, n, d, ldx, c64, nullptr, k, nullptr, nullptr, labels, mind2, st);
     }
-    if (use_tc_path(d, k)) return km_launch_assign_tc(X, n, d, ldx, pack, k, labels, mind2, flag_rows, flag_count, st);
+    if (use_tc_path(d, k))
+        return km_launch_assign_tc(X, n, d, ldx, pack, k, labels, mind2, flag_rows, flag_count, st, precentred);
     const int ntiles = (k + KM_TILE_N - 1) / KM_TILE_N;
     const size_t smem = sizeof(float) * ((size_t)d * AT_XLD + 2 * (size_t)(d + 1) * KM_TILE_N);
     const bool vec = (d % 4 == 0) && (ldx % 4 == 0) && ((reinterpret_cast<uintptr_t>(X) & 15) == 0);
@@ -640,7 +644,7 @@ extern "C" int b200km_assign_f32(const float *X, int64_t n, int d, int64_t ldx, 
     const float *ct = reinterpret_cast<const float *>(pk + L.off_ct);
     const float *c32 = reinterpret_cast<const float *>(pk + L.off_c32);
     const unsigned int *cmax = reinterpret_cast<const unsigned int *>(pk + L.off_cmax);
-    const float *mu = reinterpret_cast<const float *>(pk + L.off_mu);
+    const float *mu = reinterpret_cast<const float *>(pk + (precentred ? L.off_zero : L.off_mu));
     static bool attr_v[KM_MAX_DEVICES] = {}, attr_s[KM_MAX_DEVICES] = {};
     if (int rc2 = km_set_smem_once(assign_tiled_f32_kernel<true>, 220 * 1024, attr_v)) return rc2;
     if (int rc2 = km_set_smem_once(assign_tiled_f32_kernel<false>, 220 * 1024, attr_s)) return rc2;
@@ -651,6 +655,17 @@ extern "C" int b200km_assign_f32(const float *X, int64_t n, int d, int64_t ldx, 
         assign_tiled_f32_kernel<false><<<(unsigned)blocks, AT_THREADS, smem, st>>>(
             X, n, d, ldx, ct, c32, mu, cmax, k, ntiles, labels, mind2, flag_rows, flag_count);
     KM_LAUNCH_RET();
+}
+
+extern "C" int b200km_assign_f32(const float *X, int64_t n, int d, int64_t ldx, const void *pack, int k,
+                                 int32_t *labels, float *mind2, int32_t *flag_rows, int32_t *flag_count,
+                                 int reset_flags, void *stream) {
+    return assign_f32_impl(X, n, d, ldx, pack, k, labels, mind2, flag_rows, flag_count, reset_flags, stream, false);
+}
+extern "C" int b200km_assign_centred_f32(const float *Xc, int64_t n, int d, int64_t ldx, const void *pack, int k,
+                                         int32_t *labels, float *mind2, int32_t *flag_rows, int32_t *flag_count,
+                                         int reset_flags, void *stream) {
+    return assign_f32_impl(Xc, n, d, ldx, pack, k, labels, mind2, flag_rows, flag_count, reset_flags, stream, true);
 }
 
 extern "C" int b200km_assign_f64(const double *X, int64_t n, int d, int64_t ldx, const void *pack, int k,
@@ -682,6 +697,111 @@ extern "C" int b200km_refine_f64(const float *X, int64_t n, int d, int64_t ldx, 
     // (measured: with ~0.2-0.5 % of the rows flagged, the row-block kernel's 32-row groups spread over more CTAs
     //  and beat the DFMA tile kernel's 128-row tiles at every BASELINE size, so it stays the refine kernel)
     return launch_rb<float, 32, 8, 8, true>(X, n, d, ldx, c64, cn64, k, flag_rows, flag_count, labels, mind2, st);
+}
+
+// =============================================================================================
+// float64 X on the tensor cores: centre in float64, round once to float32, decide in float32 with the same
+// near-tie flags, re-decide the flagged rows in float64, then rebuild every winner distance in float64
+// =============================================================================================
+// The reference's arithmetic is float64 for float64 X as well (sklearn ArgKmin, reference pairwise.py:19-47), and the
+// DFMA tile kernel does exactly that at ~16 TFLOP/s.  But the labels only need float64 where the float32 decision is
+// inside its own rounding bound -- the argument that carries the float32 path -- and the bound already contains
+// the one extra rounding here (x - mu computed in float64, then rounded: <= 2^-24 relative to the CENTRED value).
+// So: b200km_center_convert_f64 writes fl32(x - mu) for a block of rows, b200km_assign_centred_f32 runs the
+// tcgen05 kernels on it (mu := 0), b200km_refine_x64_f64 re-decides the flagged rows on the float64 rows, and
+// b200km_rowdist_f64 writes sum_f (x_f - c_f)^2 in float64 for every row (the float32 kernels' distances are
+// only good to ~1e-7, the float64 contract is 1e-10).
+__global__ void __launch_bounds__(256)
+center_convert_kernel(const double *__restrict__ X, int64_t n, int d, int64_t ldx, const float *__restrict__ mu,
+                      float *__restrict__ out) {
+    const int64_t total = n * (int64_t)d;
+    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = e / d;
+        const int f = (int)(e - r * d);
+        out[e] = (float)(X[r * ldx + f] - (double)__ldg(mu + f));
+    }
+}
+
+extern "C" int b200km_center_convert_f64(const double *X, int64_t n, int d, int64_t ldx, const void *pack, int k,
+                                         float *out, void *stream) {
+    KM_CHECK_ARG(X && pack && out, B200KM_EINVAL);
+    KM_CHECK_ARG(n > 0 && d > 0 && k > 0 && ldx >= d, B200KM_EINVAL);
+    KM_CHECK_ARG(k <= B200KM_MAX_K && d <= B200KM_MAX_D, B200KM_ETOOBIG);
+    const KmPackLayout L = km_pack_layout(k, d);
+    const float *mu = reinterpret_cast<const float *>(static_cast<const unsigned char *>(pack) + L.off_mu);
+    int64_t blocks = (n * (int64_t)d + 255) / 256;
+    if (blocks > (int64_t)KM_NUM_SMS * 16) blocks = (int64_t)KM_NUM_SMS * 16;
+    center_convert_kernel<<<(unsigned)blocks, 256, 0, km_stream(stream)>>>(X, n, d, ldx, mu, out);
+    KM_LAUNCH_RET();
+}
+
+// mind2[r] = sum_f (x_rf - c_{label_r, f})^2 in float64; LPR lanes per row (coalesced), centre rows from L2
+template <int LPR>
+__global__ void __launch_bounds__(256)
+rowdist_f64_kernel(const double *__restrict__ X, int64_t n, int d, int64_t ldx, const double *__restrict__ c64,
+                   const int32_t *__restrict__ labels, double *__restrict__ mind2) {
+    constexpr int RPW = 32 / LPR;
+    const int lane = threadIdx.x & 31;
+    const int sub = lane / LPR, l = lane % LPR;
+    const int64_t warp_global = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (int64_t r0 = warp_global * RPW; r0 < n; r0 += nwarps * RPW) {
+        const int64_t row = r0 + sub;
+        const bool live = row < n;
+        const double *xr = X + (live ? row : 0) * ldx;
+        const double *cr = c64 + (size_t)(live ? labels[row] : 0) * d;
+        double s0 = 0.0, s1 = 0.0;
+        int f = l;
+        for (; f + LPR < d; f += 2 * LPR) {
+            const double a = xr[f] - __ldg(cr + f), b = xr[f + LPR] - __ldg(cr + f + LPR);
+            s0 = fma(a, a, s0);
+            s1 = fma(b, b, s1);
+        }
+        if (f < d) { const double a = xr[f] - __ldg(cr + f); s0 = fma(a, a, s0); }
+        double s = s0 + s1;
+#pragma unroll
+        for (int o = LPR / 2; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        if (live && l == 0) mind2[row] = s;
+    }
+}
+
+extern "C" int b200km_rowdist_f64(const double *X, int64_t n, int d, int64_t ldx, const void *pack, int k,
+                                  const int32_t *labels, double *mind2, void *stream) {
+    int rc = check_pack_args(X, n, d, ldx, pack, k, labels);
+    if (rc) return rc;
+    KM_CHECK_ARG(mind2, B200KM_EINVAL);
+    const KmPackLayout L = km_pack_layout(k, d);
+    const double *c64 = reinterpret_cast<const double *>(static_cast<const unsigned char *>(pack) + L.off_c64);
+    cudaStream_t st = km_stream(stream);
+    int lpr = 32;
+    if (d <= 2) lpr = 1; else if (d <= 4) lpr = 2; else if (d <= 8) lpr = 4; else if (d <= 16) lpr = 8;
+    else if (d <= 32) lpr = 16;
+    const int rpw = 32 / lpr;
+    int64_t blocks = (n + (int64_t)rpw * 8 - 1) / ((int64_t)rpw * 8);
+    if (blocks > (int64_t)KM_NUM_SMS * 16) blocks = (int64_t)KM_NUM_SMS * 16;
+    switch (lpr) {
+        case 1: rowdist_f64_kernel<1><<<(unsigned)blocks, 256, 0, st>>>(X, n, d, ldx, c64, labels, mind2); break;
+        case 2: rowdist_f64_kernel<2><<<(unsigned)blocks, 256, 0, st>>>(X, n, d, ldx, c64, labels, mind2); break;
+        case 4: rowdist_f64_kernel<4><<<(unsigned)blocks, 256, 0, st>>>(X, n, d, ldx, c64, labels, mind2); break;
+        case 8: rowdist_f64_kernel<8><<<(unsigned)blocks, 256, 0, st>>>(X, n, d, ldx, c64, labels, mind2); break;
+        case 16: rowdist_f64_kernel<16><<<(unsigned)blocks, 256, 0, st>>>(X, n, d, ldx, c64, labels, mind2); break;
+        default: rowdist_f64_kernel<32><<<(unsigned)blocks, 256, 0, st>>>(X, n, d, ldx, c64, labels, mind2); break;
+    }
+    KM_LAUNCH_RET();
+}
+
+// b200km_refine_f64 for float64 rows (labels updated in place; mind2 nullable -- b200km_rowdist_f64 follows anyway)
+extern "C" int b200km_refine_x64_f64(const double *X, int64_t n, int d, int64_t ldx, const void *pack, int k,
+                                     const int32_t *flag_rows, const int32_t *flag_count, int32_t *labels,
+                                     double *mind2, void *stream) {
+    int rc = check_pack_args(X, n, d, ldx, pack, k, labels);
+    if (rc) return rc;
+    KM_CHECK_ARG(flag_rows && flag_count, B200KM_EINVAL);
+    const KmPackLayout L = km_pack_layout(k, d);
+    const double *c64 = reinterpret_cast<const double *>(static_cast<const unsigned char *>(pack) + L.off_c64);
+    const double *cn64 = reinterpret_cast<const double *>(static_cast<const unsigned char *>(pack) + L.off_cn64);
+    return launch_rb<double, 32, 8, 8, true>(X, n, d, ldx, c64, cn64, k, flag_rows, flag_count, labels, mind2,
+                                             km_stream(stream));
 }
 
 // =============================================================================================

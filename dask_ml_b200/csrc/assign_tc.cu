@@ -1714,7 +1714,7 @@ int km_launch_cand_tc_wide(const float *X, int64_t n, int d, int64_t ldx, const 
 
 // host-side launcher, called from b200km_assign_f32
 int km_launch_assign_tc(const float *X, int64_t n, int d, int64_t ldx, const void *pack, int k, int32_t *labels,
-                        float *mind2, int32_t *flag_rows, int32_t *flag_count, cudaStream_t st) {
+                        float *mind2, int32_t *flag_rows, int32_t *flag_count, cudaStream_t st, bool precentred) {
     const KmPackLayout L = km_pack_layout(k, d);
     const unsigned char *pk = static_cast<const unsigned char *>(pack);
     const int kpad = km_tc_kpad(d);
@@ -1725,7 +1725,7 @@ int km_launch_assign_tc(const float *X, int64_t n, int d, int64_t ldx, const voi
     const unsigned char *img = pk + L.off_tc;
     const float *c32 = reinterpret_cast<const float *>(pk + L.off_c32);
     const unsigned int *cmax = reinterpret_cast<const unsigned int *>(pk + L.off_cmax);
-    const float *mu = reinterpret_cast<const float *>(pk + L.off_mu);
+    const float *mu = reinterpret_cast<const float *>(pk + (precentred ? L.off_zero : L.off_mu));
     if (d > KM_TC_MAX_D) {
         // wide rows: K cut into 64-feature panels (assign_tc_wide_kernel); same shared-memory footprint as d = 64
         const size_t xbuf_w = (size_t)(TCW_PCH + 2) * 128 * 16 + (size_t)TCW_PCH * 128 * 16;

@@ -66,6 +66,8 @@ struct KmPackLayout {
     size_t off_mu;    // float[kpad(d)]    mu = mean of the centres (fp32, zero padded): the float32 kernels work on
                       //                   x - mu and c - mu, so their rounding bounds scale with the spread of the data
                       //                   around the centres, not with its distance from the origin
+    size_t off_zero;  // float[kpad(d)]    zeros: stands in for mu when the caller's rows are already centred
+                      //                   (float64 X converted by b200km_center_convert_f64)
     size_t off_c32;   // float[k*d]        row-major fp32 centres, CENTRED: fl32(c64 - mu)
     size_t off_cn32;  // float[ntiles*128] ||c32_j||^2 (centred), +inf padded
     size_t off_cn64;  // double[k]         ||c64_j||^2
@@ -84,6 +86,7 @@ __host__ __device__ inline KmPackLayout km_pack_layout(int k, int d) {
     L.off_hdr = o;  o = km_align256(o + 16);
     L.off_cmax = o; o = km_align256(o + 4);
     L.off_mu = o;   o = km_align256(o + sizeof(float) * (size_t)((d + 7) & ~7));
+    L.off_zero = o; o = km_align256(o + sizeof(float) * (size_t)((d + 7) & ~7));
     L.off_c32 = o;  o = km_align256(o + sizeof(float) * (size_t)k * d);
     L.off_cn32 = o; o = km_align256(o + sizeof(float) * ntiles * KM_TILE_N);
     L.off_cn64 = o; o = km_align256(o + sizeof(double) * (size_t)k);

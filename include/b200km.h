@@ -91,6 +91,26 @@ int b200km_assign_f32(const float *X, int64_t n, int d, int64_t ldx, const void 
                       int reset_flags, void *stream);
 int b200km_assign_f64(const double *X, int64_t n, int d, int64_t ldx, const void *pack, int k,
                       int32_t *labels, double *mind2, void *stream);
+/* float64 X on the tensor cores (k > 16).  The reference's arithmetic is float64 for float64 input too, but the labels
+ * only need it where the float32 decision is inside its own rounding bound:
+ *   b200km_center_convert_f64   out[i] = fl32(x_i - mu)  (mu = the pack's centring vector; n x d floats, ld = d)
+ *   b200km_assign_centred_f32   b200km_assign_f32 on rows that are ALREADY centred (the kernels use mu = 0);
+ *                               k > 16 only; fills labels / flag_rows exactly like b200km_assign_f32
+ *   b200km_refine_x64_f64       b200km_refine_f64 reading the float64 rows
+ *   b200km_rowdist_f64          mind2[i] = sum_f (x_if - c_{labels[i], f})^2 in float64 (the float32 kernels' distances
+ *                               are good to ~1e-7 only)
+ * Replaces: the same call sites as b200km_assign_f64 (R/dask_ml/metrics/pairwise.py:19-47), 8-10x faster than its
+ * DFMA kernel for k > 16. */
+int b200km_center_convert_f64(const double *X, int64_t n, int d, int64_t ldx, const void *pack, int k, float *out,
+                              void *stream);
+int b200km_assign_centred_f32(const float *Xc, int64_t n, int d, int64_t ldx, const void *pack, int k,
+                              int32_t *labels, float *mind2, int32_t *flag_rows, int32_t *flag_count,
+                              int reset_flags, void *stream);
+int b200km_refine_x64_f64(const double *X, int64_t n, int d, int64_t ldx, const void *pack, int k,
+                          const int32_t *flag_rows, const int32_t *flag_count, int32_t *labels, double *mind2,
+                          void *stream);
+int b200km_rowdist_f64(const double *X, int64_t n, int d, int64_t ldx, const void *pack, int k,
+                       const int32_t *labels, double *mind2, void *stream);
 /* fp64 re-decision of the flagged rows of a float32 X (labels / mind2 updated in place).
  * `flag_count` is read on the device: no host synchronisation is needed between the two calls.
  * Replaces: nothing separate -- it is what makes K1's float32 labels equal the reference's
