@@ -501,3 +501,40 @@ def test_assign_f32_wide_rows_strided_and_far(eng):
     assert not (diff & ~_near_tie_mask(Xh, C, rel=1e-9)).any()
     npt.assert_allclose(mind2.cpu().numpy(), D[np.arange(6000), got], rtol=2e-5)
     assert eng.flagged_count() < 0.05 * 6000
+
+
+@pytest.mark.parametrize("n,d,k,offset", [(30000, 64, 1024, 0.0), (20000, 32, 200, 50.0), (9000, 128, 600, -300.0),
+                                           (5000, 256, 300, 10.0), (4097, 13, 40, 0.0), (2000, 500, 64, 1000.0),
+                                           (150001, 16, 257, 0.0)])
+def test_assign_f64_on_tensor_cores_equals_float64_kernels(eng, n, d, k, offset):
+    """float64 rows decided on the tensor cores (centred, rounded once, flagged rows re-decided in float64) against
+    the all-float64 kernels and the oracle: same labels, distances to float64 accuracy."""
+    import torch
+
+    rs = np.random.RandomState(n + d + k)
+    cen = rs.uniform(-10, 10, size=(max(2, k // 4), d))
+    X = cen[rs.randint(0, len(cen), n)] + rs.standard_normal((n, d)) + offset
+    C = X[rs.randint(0, n, k)] + 0.2 * rs.standard_normal((k, d))
+    Xd = eng.to_device(X)
+    pack = eng.pack(eng.to_device(C, torch.float64))
+    out = {}
+    for tc in (True, False):
+        eng.f64_on_tensor_cores = tc
+        try:
+            lab, m2 = eng.assign(Xd, pack)
+            out[tc] = (lab.cpu().numpy(), m2.cpu().numpy())
+        finally:
+            eng.f64_on_tensor_cores = True
+    diff = out[True][0] != out[False][0]
+    if diff.any():   # only where float64 itself cannot separate the two centres
+        D = np.stack([((X - C[j]) ** 2).sum(1) for j in range(k)], axis=1) if n * k <= 3e7 else None
+        assert D is not None, f"{diff.sum()} labels differ"
+        r = np.arange(n)
+        gap = np.abs(D[r, out[True][0]] - D[r, out[False][0]])
+        assert (gap[diff] <= 1e-9 * D[r, out[False][0]][diff] + 1e-13 * ((X ** 2).sum(1)[diff] + (C ** 2).sum(1).max())).all()
+    same = ~diff
+    npt.assert_allclose(out[True][1][same], out[False][1][same], rtol=1e-12, atol=1e-300)
+    lab_ref, d_ref = orc.pairwise_distances_argmin_min(X, C, metric_kwargs={"squared": True})
+    agree = out[True][0] == lab_ref
+    assert agree.mean() > 0.999
+    npt.assert_allclose(out[True][1][agree], d_ref[agree], rtol=1e-8, atol=1e-9 * ((X ** 2).sum(1).max() + 1))
