@@ -45,9 +45,10 @@ def test_streamed_fit_equals_resident_fit(monkeypatch, init, dtype):
     npt.assert_array_equal(np.asarray(b.predict(X).compute()), np.asarray(a.predict(X).compute()))
 
 
-def test_streamed_fit_tensor_core_path(monkeypatch):
-    """k > 16: K1 on the tensor cores + pruned re-decision + K2, block by block."""
-    X, cen = _data(n=30011, d=24, k=40, seed=5)
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+def test_streamed_fit_tensor_core_path(monkeypatch, dtype):
+    """k > 16: K1 on the tensor cores + re-decision + K2, block by block (float64: the centred / rounded route)."""
+    X, cen = _data(n=30011, d=24, k=40, seed=5, dtype=dtype)
     kw = dict(n_clusters=40, random_state=1, max_iter=5, tol=0.0, init=X[:40].astype(np.float64) + 0.05)
     monkeypatch.setenv("B200KM_OUT_OF_CORE", "0")
     a = _fit(X, **kw)
@@ -55,7 +56,7 @@ def test_streamed_fit_tensor_core_path(monkeypatch):
     monkeypatch.setenv("B200KM_CHUNK_BYTES", str(512 * 1024))
     b = _fit(X, **kw)
     npt.assert_array_equal(a.labels_.compute(), b.labels_.compute())
-    npt.assert_allclose(a.cluster_centers_, b.cluster_centers_, rtol=1e-6)
+    npt.assert_allclose(a.cluster_centers_, b.cluster_centers_, rtol=1e-6 if dtype == np.float32 else 1e-11)
     npt.assert_allclose(a.inertia_, b.inertia_, rtol=1e-9)
 
 
