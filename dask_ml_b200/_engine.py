@@ -86,7 +86,7 @@ class CudaEngine:
             t = t.to(dtype)
         return t.to(self.device, non_blocking=True).contiguous()
 
-    F64_BLOCK_BYTES = 256 << 20   # float32 scratch of the float64-on-tensor-cores path (rows per block = this / 4d)
+    F64_BLOCK_BYTES = 1 << 30     # float32 scratch of the float64-on-tensor-cores path (rows per block = this / 4d)
     STREAM_MIN_BYTES = 64 << 20   # host inputs at least this big are uploaded in overlapped row chunks
     STREAM_CHUNKS = 8
 
