@@ -218,9 +218,15 @@ class CudaEngine:
                     xb, lb = xs[b0 : b0 + bn], ls[b0 : b0 + bn]
                     self._call("b200km_center_convert_f64", xb.data_ptr(), bn, d, ldx, pack.buf.data_ptr(), pack.k,
                                xc.data_ptr(), st, launches=1)
+                    d32 = self._buf("dist32", (blk,), torch.float32) if (refine and self.pruned_refine) else None
                     self._call("b200km_assign_centred_f32", xc.data_ptr(), bn, d, d, pack.buf.data_ptr(), pack.k,
-                               lb.data_ptr(), None, flags.data_ptr(), fcnt.data_ptr(), 1, st, launches=1)
-                    if refine:
+                               lb.data_ptr(), d32.data_ptr() if d32 is not None else None, flags.data_ptr(),
+                               fcnt.data_ptr(), 1, st, launches=1)
+                    if refine and d32 is not None:
+                        self._call("b200km_refine_pruned_x64_f64", xb.data_ptr(), bn, d, ldx, xc.data_ptr(),
+                                   d32.data_ptr(), pack.buf.data_ptr(), pack.k, flags.data_ptr(), fcnt.data_ptr(),
+                                   lb.data_ptr(), None, st, launches=4)
+                    elif refine:
                         self._call("b200km_refine_x64_f64", xb.data_ptr(), bn, d, ldx, pack.buf.data_ptr(), pack.k,
                                    flags.data_ptr(), fcnt.data_ptr(), lb.data_ptr(), None, st, launches=1)
                     if mp is not None:

@@ -1270,7 +1270,7 @@ cand_tc_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx, const
 }
 
 int km_launch_cand_tc(const float *X, int64_t n, int d, int64_t ldx, const void *pack, int k, int32_t *flag_rows,
-                      const int32_t *flag_count, const float *mind2, cudaStream_t st) {
+                      const int32_t *flag_count, const float *mind2, cudaStream_t st, bool precentred) {
     const KmPackLayout L = km_pack_layout(k, d);
     const unsigned char *pk = static_cast<const unsigned char *>(pack);
     const int nch = km_tc_kpad(d) / 4;
@@ -1278,7 +1278,7 @@ int km_launch_cand_tc(const float *X, int64_t n, int d, int64_t ldx, const void 
                         sizeof(TcCandBars) + 64;
     const bool vec = (d % 4 == 0) && (ldx % 4 == 0) && ((reinterpret_cast<uintptr_t>(X) & 15) == 0);
     const unsigned char *img = pk + L.off_tc;
-    const float *mu = reinterpret_cast<const float *>(pk + L.off_mu);
+    const float *mu = reinterpret_cast<const float *>(pk + (precentred ? L.off_zero : L.off_mu));
     const unsigned int *cmax = reinterpret_cast<const unsigned int *>(pk + L.off_cmax);
     static bool attr_v[KM_MAX_DEVICES] = {}, attr_s[KM_MAX_DEVICES] = {};
     if (int rc = km_set_smem_once(cand_tc_kernel<true>, 227 * 1024, attr_v)) return rc;
@@ -1690,7 +1690,7 @@ assign_tc_wide_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx
 }
 
 int km_launch_cand_tc_wide(const float *X, int64_t n, int d, int64_t ldx, const void *pack, int k,
-                           int32_t *flag_rows, const int32_t *flag_count, float *mind2, cudaStream_t st) {
+                           int32_t *flag_rows, const int32_t *flag_count, float *mind2, cudaStream_t st, bool precentred) {
     const KmPackLayout L = km_pack_layout(k, d);
     const unsigned char *pk = static_cast<const unsigned char *>(pack);
     const size_t xbuf_w = (size_t)(TCW_PCH + 2) * 128 * 16 + (size_t)TCW_PCH * 128 * 16;
@@ -1698,7 +1698,7 @@ int km_launch_cand_tc_wide(const float *X, int64_t n, int d, int64_t ldx, const 
     const bool vec = (d % 4 == 0) && (ldx % 4 == 0) && ((reinterpret_cast<uintptr_t>(X) & 15) == 0);
     const unsigned char *img = pk + L.off_tc;
     const float *c32 = reinterpret_cast<const float *>(pk + L.off_c32);
-    const float *mu = reinterpret_cast<const float *>(pk + L.off_mu);
+    const float *mu = reinterpret_cast<const float *>(pk + (precentred ? L.off_zero : L.off_mu));
     const unsigned int *cmax = reinterpret_cast<const unsigned int *>(pk + L.off_cmax);
     static bool attr_v[KM_MAX_DEVICES] = {}, attr_s[KM_MAX_DEVICES] = {};
     if (int rc = km_set_smem_once(assign_tc_wide_kernel<true, true>, 227 * 1024, attr_v)) return rc;

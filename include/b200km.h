@@ -111,6 +111,12 @@ int b200km_refine_x64_f64(const double *X, int64_t n, int d, int64_t ldx, const 
                           void *stream);
 int b200km_rowdist_f64(const double *X, int64_t n, int d, int64_t ldx, const void *pack, int k,
                        const int32_t *labels, double *mind2, void *stream);
+/* b200km_refine_pruned_f64 for float64 rows: the candidate pass reads Xc (the centred float32 block, ld = d) and
+ * dist32 (the distances b200km_assign_centred_f32 wrote for it), the float64 scoring reads X; mind2 (nullable) is
+ * updated for the re-decided rows.  Falls back to b200km_refine_x64_f64 under the same conditions. */
+int b200km_refine_pruned_x64_f64(const double *X, int64_t n, int d, int64_t ldx, const float *Xc, float *dist32,
+                                 const void *pack, int k, int32_t *flag_rows, const int32_t *flag_count,
+                                 int32_t *labels, double *mind2, void *stream);
 /* fp64 re-decision of the flagged rows of a float32 X (labels / mind2 updated in place).
  * `flag_count` is read on the device: no host synchronisation is needed between the two calls.
  * Replaces: nothing separate -- it is what makes K1's float32 labels equal the reference's
