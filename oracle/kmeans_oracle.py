@@ -8,7 +8,7 @@ What this is
 ------------
 A restatement of the reference algorithm with the dask layer removed.  dask and
 distributed are not installable in the build container (no network, no wheel), so
-``import dask_ml`` is impossible; the arithmetic of the path, however, lives in
+a plain ``import dask_ml`` is impossible; the arithmetic of the path, however, lives in
 third-party packages that ARE importable (scikit-learn's Cython ``ArgKmin`` /
 ``euclidean_distances`` and a numba scatter loop) and this module calls those same
 functions per row-block, replacing only dask's chunking / graph execution:
@@ -20,19 +20,22 @@ functions per row-block, replacing only dask's chunking / graph execution:
 * bincount    = ``np.bincount(labels, minlength=k)`` (k_means.py:598)
 * scheduler   = optional ThreadPoolExecutor over blocks (threaded scheduler stand-in)
 
-Parity pin status
------------------
-* ``pairwise_distances_argmin_min`` / ``pairwise_distances`` / ``euclidean_distances`` /
-  ``row_norms`` / the 3-blob ``KMeans`` fit: pinned by replaying the reference's own tests
-  (tests/metrics/test_metrics.py:15-71, tests/test_kmeans.py:36-94, 184-197), whose
-  expectations are computed live from scikit-learn -- see tests/test_oracle_pin.py.
-* Lloyd loop at k > 3, the non-squared-inertia branch, explicit ndarray init, the
-  "found fewer than k" branch, k-means|| sampled indices: the reference has NO test or
-  golden vector for these, and the reference itself cannot be run here:
-  **parity unpinned** for those items (the restatement below follows the source
-  line by line and is the only pin available).
-* ``DaskLikeRandomState`` restates dask's per-chunk MT19937 seeding from memory of
-  dask/array/random.py (dask source is not on this box): **unverified**.
+Parity pin status: PINNED to the reference's own source
+-------------------------------------------------------
+* ``oracle/reference_loader.py`` imports the UNMODIFIED reference modules (dask_ml/cluster/k_means.py,
+  metrics/pairwise.py, utils.py, ...) from /root/reference on top of an eager numpy-backed stand-in for the small
+  dask surface they touch (``oracle/dask_stub``), and ``tests/test_reference_pin.py`` demands that every function
+  here returns what the reference returns on the same inputs: Lloyd at C1-C4 shapes (k up to 1500), both inertia
+  branches, an empty cluster, the ``shift < tol`` exit, k-means|| through the supplement and the re-cluster branch,
+  ``evaluate_cost`` / ``_sample_points`` with shared draws, the three pairwise functions, the estimator end to end --
+  labels / picked rows exact, floats to 1e-12 (bit-equal on this box).  ``tests/golden/*.npz`` are generated from the
+  reference (``tests/golden/make_golden.py``), not from this module.
+* The reference's own tests for the path (tests/metrics/test_metrics.py:15-71, tests/test_kmeans.py:36-94, 184-197;
+  expectations computed live from scikit-learn) are replayed in tests/test_oracle_pin.py.
+* What remains an ASSUMPTION: the stand-in's reading of dask itself, which is not on this box -- per-chunk MT19937
+  seeding of ``da.random.RandomState`` (``DaskLikeRandomState`` below follows the same reading) and the fan-in-4
+  tree of ``Array.sum()`` (``dask_sum``).  Neither touches labels, centres or picked rows beyond the last ulp of a
+  sum, except that the concrete rows k-means|| draws for a given seed depend on the seeding scheme.
 
 Every function cites the reference lines it follows (R/ = /root/reference/).
 """
@@ -51,6 +54,7 @@ from sklearn.utils import extmath as skextmath
 __all__ = [
     "row_chunks",
     "split_blocks",
+    "dask_sum",
     "row_norms",
     "pairwise_distances_argmin_min",
     "pairwise_distances",
@@ -98,6 +102,22 @@ def split_blocks(X: np.ndarray, chunks: Sequence[int]) -> List[np.ndarray]:
         start += c
     assert start == len(X), "chunks must cover X"
     return out
+
+
+def dask_sum(v: np.ndarray, chunks: Sequence[int], split_every: int = 4):
+    """``dask.array.Array.sum()`` of a 1-d array cut into ``chunks``: one ``np.sum(block, dtype=acc)`` per block, then
+    groups of ``split_every`` neighbouring partials are summed until one is left (dask/array/reductions.py
+    ``reduction`` / ``_tree_reduce``; config default ``split_every`` = 4).  The accumulator dtype comes from the
+    array's DECLARED dtype; everything the path sums is declared float64 (``map_blocks(dtype=float)``,
+    R/dask_ml/metrics/pairwise.py:59-66; ``from_delayed(..., "f8")``, :41-43) even where scikit-learn hands back
+    float32 blocks, so float32 values are accumulated in float64."""
+    parts = [np.sum(b, dtype=np.float64, keepdims=True) for b in split_blocks(v, chunks)]
+    if not parts:
+        return np.float64(0.0)
+    while len(parts) > 1:
+        parts = [np.sum(np.concatenate(parts[i : i + split_every]), dtype=np.float64, keepdims=True)
+                 for i in range(0, len(parts), split_every)]
+    return parts[0][0]
 
 
 def _map_blocks(fn: Callable, blocks: Iterable, pool: Optional[ThreadPoolExecutor]):
@@ -269,7 +289,7 @@ def kmeans_single_lloyd(
     if shift > 1e-7:  # :612 (max_iter == 0 raises in the reference too: shift unbound)
         labels, distances = pairwise_distances_argmin_min(X, centers, chunks, pool=pool)  # :613
         labels = labels.astype(np.int32)
-    inertia = float(distances.sum())  # :616
+    inertia = float(dask_sum(distances, chunks))  # :616
     centers = centers.astype(dt)  # :617
     return labels, inertia, centers, i + 1
 
@@ -289,12 +309,11 @@ def _min_dist_sq(X, centers, chunks, pool=None) -> np.ndarray:
 
 
 def evaluate_cost(X: np.ndarray, centers: np.ndarray, chunks: Optional[Sequence[int]] = None, pool=None) -> float:
-    """R/dask_ml/cluster/k_means.py:516-519: ``(pairwise_distances(X, centers).min(1) ** 2).sum()``.
-    The per-block sums are combined as dask's tree-sum would (pairwise); order affects only
-    the last ulp."""
+    """R/dask_ml/cluster/k_means.py:516-519: ``(pairwise_distances(X, centers).min(1) ** 2).sum()`` -- float32
+    blocks for float32 X (scikit-learn), summed in float64 by dask's reduction tree (``dask_sum``)."""
     chunks = chunks if chunks is not None else (len(X),)
     d2 = _min_dist_sq(X, centers, chunks, pool)
-    return float(d2.sum())
+    return float(dask_sum(d2, chunks))
 
 
 def sample_points(
@@ -308,10 +327,11 @@ def sample_points(
 ):
     """R/dask_ml/cluster/k_means.py:522-541 with the uniform ``draws`` vector supplied by the
     caller (one U[0,1) per row).  ``p = l * d2 / d2.sum()`` (:533-535); picked = p > draws
-    (:538); returns the row indices (:540-541)."""
+    (:538); returns the row indices (:540-541).  For float32 X: ``l * d2`` stays float32, the float64 ``denom``
+    (``dask_sum``) promotes the quotient to float64 (numpy >= 2 promotion, which the reference's pins imply)."""
     chunks = chunks if chunks is not None else (len(X),)
     distances = _min_dist_sq(X, centers, chunks, pool)
-    denom = distances.sum()
+    denom = dask_sum(distances, chunks)
     p = oversampling_factor * distances / denom
     (idx,) = np.where(p > draws)
     if return_p:

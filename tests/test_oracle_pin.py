@@ -4,7 +4,8 @@ path against it -- their expectations are computed live from scikit-learn:
   reference tests/metrics/test_metrics.py:15-71   pairwise_distances / argmin_min / euclidean
   reference tests/test_kmeans.py:36-39, 64-94, 184-197   row_norms, 3-blob fit, dtypes
 
-plus the committed golden vectors (tests/golden/*.npz, made by tests/golden/make_golden.py).
+plus the committed golden vectors (tests/golden/*.npz, made by tests/golden/make_golden.py FROM THE REFERENCE run
+through oracle/reference_loader.py; tests/test_reference_pin.py compares oracle and reference directly).
 Runs on CPU (no GPU needed)."""
 import glob
 import os
@@ -145,8 +146,8 @@ def test_quirks():
 
 @pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(HERE, "golden", "*.npz"))))
 def test_golden_vectors(path):
-    """The committed fixtures must still be what the oracle produces (guards against drift of
-    sklearn / numba / numpy versions between the container that made them and this one)."""
+    """The committed fixtures -- the REFERENCE's outputs -- must be what the oracle produces, here and on the GPU box
+    (where the reference tree is absent; also guards against drift of sklearn / numba / numpy versions)."""
     g = np.load(path, allow_pickle=False)
     kind = str(g["kind"])
     if kind == "lloyd":
