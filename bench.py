@@ -214,7 +214,7 @@ def run_ours(args):
     from dask_ml_b200.cluster import KMeans
 
     eng = get_engine()
-    eng.lib.b200km_set_option(1, {"auto": 0, "ffma": 1, "tc": 2}[args.k1])
+    eng.lib.b200km_set_option(_lib.OPT_K1_VARIANT, {"auto": _lib.K1_AUTO, "ffma": _lib.K1_FFMA, "tc": _lib.K1_TCGEN05}[args.k1])
     comm = _comm.default_comm()
     dev = eng.device
     n_local, d, k, dtype_s, desc = WORKLOADS[args.workload]
@@ -336,7 +336,7 @@ def run_ours(args):
     flops = 2.0 * n_local * k * d
     bytes_alg = n_local * (d * esize + 4)
     roof = {"kernel": "assign_update_small_kernel (K1+K2 fused)" if fused else "assign (K1)", "traffic": None}
-    variant = eng.lib.b200km_get_option(1)
+    variant = eng.lib.b200km_get_option(_lib.OPT_K1_VARIANT)
     k1_is_tc = dtype_s == "float32" and k > 16 and d <= 128 and variant != 1
     k1_is_ffma = dtype_s == "float32" and k > 16 and d <= 128 and not k1_is_tc
     # FP32 / FP64 pipe peak measured here with the FMA probe (MEASURED_PEAKS.json has HBM + bf16 only)

@@ -47,6 +47,10 @@ class CudaEngine:
                 "dask_ml_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback."
             )
         self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
+        if self.device.type != "cuda":
+            raise _lib.B200LibraryError(f"dask_ml_b200 runs on CUDA devices only, got {self.device}")
+        if self.device.index is None:
+            self.device = torch.device("cuda", torch.cuda.current_device())
         self.launches = 0  # kernels launched through this engine (bench.py reports it)
         self.k1_events = None  # bench.py: set to a list to collect (start, end) CUDA events around K1
         self.pruned_refine = True   # tests flip this to compare with the full float64 scan
@@ -60,7 +64,13 @@ class CudaEngine:
         return torch.cuda.current_stream(self.device).cuda_stream
 
     def _call(self, name: str, *args, launches: int = 1):
-        rc = getattr(self.lib, name)(*args)
+        # the entry points launch on the CURRENT device (and keep per-device state: shared-memory opt-ins, the SM
+        # count, the static scratch): make this engine's device current for the call, whatever the caller's is
+        if torch.cuda.current_device() != self.device.index:
+            with torch.cuda.device(self.device):
+                rc = getattr(self.lib, name)(*args)
+        else:
+            rc = getattr(self.lib, name)(*args)
         _lib.check(rc, name)
         self.launches += launches
         if self.trace is not None:   # tools/: (entry point, CUDA event recorded right after its launch)
@@ -203,7 +213,7 @@ class CudaEngine:
                 else:
                     self._call("b200km_assign_f32", xs.data_ptr(), nn, d, ldx, pack.buf.data_ptr(), pack.k,
                                ls.data_ptr(), mp, None, None, 0, st, launches=1)
-            elif self.f64_on_tensor_cores and pack.k > 16 and d <= 2048 and self.lib.b200km_get_option(1) in (0, 2):
+            elif self.f64_on_tensor_cores and pack.k > 16 and d <= 2048 and self.lib.b200km_get_option(_lib.OPT_K1_VARIANT) in (_lib.K1_AUTO, _lib.K1_TCGEN05):
                 # float64 rows: centred + rounded block by block, decided on the tensor cores with the float32 path's
                 # near-tie flags, re-decided in float64 where flagged, distances rebuilt in float64
                 if self.k1_events is not None:
@@ -425,7 +435,9 @@ class CudaEngine:
         return bad
 
     def has_nonfinite(self, X: torch.Tensor) -> bool:
-        return bool(self.nonfinite_flag(X).item())
+        """Does X -- or, in a multi-rank fit, ANY rank's shard -- hold a NaN / inf?  The verdict is shared so that
+        every rank raises the reference's ValueError together instead of one rank leaving the others in a collective."""
+        return any_rank_flag(self.nonfinite_flag(X))
 
     def make_blobs(self, n: int, d: int, centers: torch.Tensor, cluster_std: float = 1.0, seed: int = 0,
                    row_offset: int = 0, dtype=torch.float32, out: Optional[torch.Tensor] = None,
@@ -437,6 +449,18 @@ class CudaEngine:
                    float(cluster_std), int(seed) & (2**64 - 1), int(row_offset), (y.data_ptr() if y is not None else None),
                    self._stream())
         return out
+
+
+def any_rank_flag(flag: torch.Tensor) -> bool:
+    """``flag`` (int32[1], non-zero = this rank saw it) -> the OR over all ranks, as a Python bool (synchronises)."""
+    from . import _comm
+
+    comm = _comm.default_comm()
+    if comm.world > 1:
+        f = (flag != 0).to(torch.float64)   # the comm shim reduces floating tensors
+        comm.allreduce_sum_(f)
+        return bool(f.item() > 0)
+    return bool(int(flag.item()))
 
 
 _engines = {}
@@ -455,6 +479,8 @@ def get_engine(device=None) -> CudaEngine:
     """Per-device engine singleton.  Raises (never falls back) without CUDA / the library."""
     if _override is not None:
         return _override
+    if isinstance(device, torch.device) and device.type == "cuda" and device.index is None:
+        device = None
     key = str(device) if device is not None else (f"cuda:{torch.cuda.current_device()}" if torch.cuda.is_available() else "none")
     eng = _engines.get(key)
     if eng is None:

@@ -127,7 +127,9 @@ class HostMatrix:
             free[b] = ev
         if scanning:
             self._scanned = True
-            if int(bad.item()):
+            from ._engine import any_rank_flag
+
+            if any_rank_flag(bad):      # every rank finishes its first pass here: the verdict is shared
                 raise ValueError(self.nonfinite_msg)
 
 

@@ -10,7 +10,8 @@ import ctypes
 import os
 from ctypes import c_char_p, c_double, c_float, c_int, c_int32, c_int64, c_size_t, c_uint32, c_uint64, c_void_p
 
-__all__ = ["load", "check", "B200LibraryError", "B200KernelError", "LIB_PATH", "PROTOTYPES"]
+__all__ = ["load", "check", "B200LibraryError", "B200KernelError", "LIB_PATH", "PROTOTYPES", "OPT_K1_VARIANT",
+           "OPT_K2_VARIANT", "K1_AUTO", "K1_FFMA", "K1_TCGEN05", "K1_TCGEN05_PAIR"]
 
 LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libb200km.so")
 
@@ -22,6 +23,11 @@ class B200LibraryError(RuntimeError):
 class B200KernelError(RuntimeError):
     """An entry point returned a CUDA error (positive code)."""
 
+
+# option keys / values of b200km_set_option / b200km_get_option (include/b200km.h)
+OPT_K1_VARIANT = 1      # B200KM_OPT_K1_VARIANT
+OPT_K2_VARIANT = 2      # B200KM_OPT_K2_VARIANT
+K1_AUTO, K1_FFMA, K1_TCGEN05, K1_TCGEN05_PAIR = 0, 1, 2, 3
 
 _P = c_void_p  # device pointers and the stream are passed as plain addresses
 

@@ -33,7 +33,7 @@ from sklearn.base import BaseEstimator, TransformerMixin
 from sklearn.utils.validation import check_is_fitted
 
 from .. import _comm
-from .._engine import get_engine
+from .._engine import any_rank_flag, get_engine
 from ..metrics.pairwise import _dev, euclidean_distances, pairwise_distances_argmin_min
 from .._hostmatrix import HostMatrix, row_chunks
 from ..utils import DeviceArray, _timed, _timer, check_array
@@ -172,7 +172,12 @@ class KMeans(TransformerMixin, BaseEstimator):
             Xd._b200_bad = torch.zeros(1, dtype=torch.int32, device=eng.device)
             return Xd
         Xd = _dev(X, eng)  # int32 -> float32, int64 -> float64 (:187-190)
-        if Xd.shape[0] and eng.has_nonfinite(Xd):  # :195-201
+        flag = eng.nonfinite_flag(Xd)  # :195-201
+        if defer and _comm.default_comm().world > 1:
+            # multi-rank fit: the verdict is shared at the fit's first exchange step, so that every rank raises
+            # together (a rank raising alone would leave the others waiting in the next collective)
+            Xd._b200_bad = flag
+        elif int(flag.item()):
             raise ValueError(self._NONFINITE_MSG)
         return Xd
 
@@ -351,11 +356,6 @@ def init_pp(X, n_clusters, random_state):
     comm = _comm.default_comm()
     n_local, d = X.shape
     row0, n_total = comm.row_range(n_local)
-    if not hasattr(eng, "mindist_pots"):   # an engine without the trial-potential kernel: the reference's way
-        from sklearn.cluster import kmeans_plusplus
-
-        Xh = X.host.numpy() if isinstance(X, HostMatrix) else X.cpu().numpy()
-        return kmeans_plusplus(Xh, n_clusters, random_state=random_state)[0]
     n_local_trials = 2 + int(np.log(n_clusters))
     with _timer("initialization of %2d centers" % n_clusters, _logger=logger):
         center_id = min(int(random_state.random_sample() * n_total), n_total - 1)   # choice(n, p=uniform)
@@ -536,12 +536,16 @@ def _kmeans_single_lloyd(X, n_clusters, max_iter=300, init="k-means||", verbose=
     eng = get_engine(X.device)
     comm = _comm.default_comm()
     streamed = getattr(X, "_b200_host", None) is not None   # deferred upload (KMeans._check_array(defer=True))
-    if streamed and not isinstance(init, (np.ndarray, torch.Tensor)):
-        eng.wait_pending(X)                        # the initialisers read all of X: no overlap, scan it now
-        streamed = False
-        X._b200_bad = None
-        if eng.has_nonfinite(X):
-            raise ValueError(KMeans._NONFINITE_MSG)
+    if not isinstance(init, (np.ndarray, torch.Tensor)):
+        if streamed:
+            eng.wait_pending(X)                    # the initialisers read all of X: no overlap, scan it now
+            streamed = False
+            X._b200_bad = eng.nonfinite_flag(X)
+        bad = getattr(X, "_b200_bad", None)        # set by fit(): deferred scan, or a multi-rank fit
+        if bad is not None:
+            X._b200_bad = None
+            if any_rank_flag(bad):
+                raise ValueError(KMeans._NONFINITE_MSG)
     centers = k_init(X, n_clusters, init=init, oversampling_factor=oversampling_factor, random_state=random_state,
                      max_iter=init_max_iter, n_init=n_init)
     dt = X.dtype
@@ -549,7 +553,10 @@ def _kmeans_single_lloyd(X, n_clusters, max_iter=300, init="k-means||", verbose=
     k = n_clusters
     centers64 = eng.to_device(np.ascontiguousarray(centers), torch.float64)
     new64 = torch.empty_like(centers64)
-    acc = torch.zeros(eng.acc_len(k, P), dtype=torch.float64, device=eng.device)
+    # one extra slot behind [sums | counts | inertia]: the NaN/inf flag of a deferred scan rides through iteration 0's
+    # allreduce, so every rank learns of a bad value on ANY rank without a collective of its own
+    acc_n = eng.acc_len(k, P)
+    acc = torch.zeros(acc_n + 1, dtype=torch.float64, device=eng.device)
     shift_t = torch.zeros(1, dtype=torch.float64, device=eng.device)
     labels = torch.empty(n_local, dtype=torch.int32, device=eng.device)
     mind2 = torch.empty(n_local, dtype=dt, device=eng.device)
@@ -590,14 +597,15 @@ def _kmeans_single_lloyd(X, n_clusters, max_iter=300, init="k-means||", verbose=
             if pending:
                 pending = None
                 X._b200_pending = None
+            bad = getattr(X, "_b200_bad", None) if i == 0 else None
+            if bad is not None:
+                X._b200_bad = None
+                acc[acc_n:].copy_((bad != 0).to(torch.float64))
             comm.allreduce_sum_(acc)  # the chain-sum over blocks / workers (:595-597)
             eng.finalize(acc, k, P, centers64, new64, shift_t)  # :600-605
             shift = float(shift_t.item())  # :602 -- the one round trip per iteration
-            bad = getattr(X, "_b200_bad", None)
-            if bad is not None:            # deferred NaN/inf verdict of a streamed upload (:195-201)
-                X._b200_bad = None
-                if int(bad.item()):
-                    raise ValueError(KMeans._NONFINITE_MSG)
+            if i == 0 and (bad is not None or comm.world > 1) and float(acc[acc_n].item()) > 0:
+                raise ValueError(KMeans._NONFINITE_MSG)  # NaN/inf verdict (:195-201), the same on every rank
             logger.info("Shift: %0.4f", shift)
             if shift < tol:
                 break
@@ -611,7 +619,7 @@ def _kmeans_single_lloyd(X, n_clusters, max_iter=300, init="k-means||", verbose=
         inertia_t = eng.reduce_sum(mind2, sqrt=True)
         comm.allreduce_sum_(inertia_t)
     else:
-        inertia_t = acc[k * P + k : k * P + k + 1].clone()
+        inertia_t = acc[acc_n - 1 : acc_n].clone()
     inertia = DeviceArray(inertia_t.reshape(()))  # :616
     centers_out = centers64.to(dt).cpu().numpy()  # :617
     return DeviceArray(labels), inertia, centers_out, i + 1

@@ -434,7 +434,7 @@ static int launch_rb(const TX *X, int64_t n, int d, int64_t ldx, const double *c
     static bool attr_set[KM_MAX_DEVICES] = {};
     if (int rc = km_set_smem_once(kern, 200 * 1024, attr_set)) return rc;
     int64_t blocks = (n + R - 1) / R;
-    const int64_t cap = (int64_t)KM_NUM_SMS * 8;
+    const int64_t cap = (int64_t)km_num_sms() * 8;
     if (INDIRECT || blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
     kern<<<(unsigned)blocks, R * G, smem, st>>>(X, n, d, ldx, c64, cn64, k, rows, nrows_ptr, labels, mind2, gate_ptr,
@@ -565,7 +565,7 @@ static int launch_tiled_f64(const TX *X, int64_t n, int d, int64_t ldx, const do
     static bool attr_set[KM_MAX_DEVICES] = {};
     if (int rc = km_set_smem_once(kern, 200 * 1024, attr_set)) return rc;
     int64_t blocks = (n + AD_BM - 1) / AD_BM;
-    if (INDIRECT) blocks = (int64_t)KM_NUM_SMS * 2;   // persistent: the row count lives on the device
+    if (INDIRECT) blocks = (int64_t)km_num_sms() * 2;   // persistent: the row count lives on the device
     kern<<<(unsigned)blocks, AD_THREADS, smem, st>>>(X, n, d, ldx, c64, cn64, k, rows, nrows_ptr, labels, mind2);
     KM_LAUNCH_RET();
 }
@@ -730,7 +730,7 @@ extern "C" int b200km_center_convert_f64(const double *X, int64_t n, int d, int6
     const KmPackLayout L = km_pack_layout(k, d);
     const float *mu = reinterpret_cast<const float *>(static_cast<const unsigned char *>(pack) + L.off_mu);
     int64_t blocks = (n * (int64_t)d + 255) / 256;
-    if (blocks > (int64_t)KM_NUM_SMS * 16) blocks = (int64_t)KM_NUM_SMS * 16;
+    if (blocks > (int64_t)km_num_sms() * 16) blocks = (int64_t)km_num_sms() * 16;
     center_convert_kernel<<<(unsigned)blocks, 256, 0, km_stream(stream)>>>(X, n, d, ldx, mu, out);
     KM_LAUNCH_RET();
 }
@@ -778,7 +778,7 @@ extern "C" int b200km_rowdist_f64(const double *X, int64_t n, int d, int64_t ldx
     else if (d <= 32) lpr = 16;
     const int rpw = 32 / lpr;
     int64_t blocks = (n + (int64_t)rpw * 8 - 1) / ((int64_t)rpw * 8);
-    if (blocks > (int64_t)KM_NUM_SMS * 16) blocks = (int64_t)KM_NUM_SMS * 16;
+    if (blocks > (int64_t)km_num_sms() * 16) blocks = (int64_t)km_num_sms() * 16;
     switch (lpr) {
         case 1: rowdist_f64_kernel<1><<<(unsigned)blocks, 256, 0, st>>>(X, n, d, ldx, c64, labels, mind2); break;
         case 2: rowdist_f64_kernel<2><<<(unsigned)blocks, 256, 0, st>>>(X, n, d, ldx, c64, labels, mind2); break;
@@ -879,7 +879,7 @@ static int refine_pruned_impl(const TX *X, int64_t n, int d, int64_t ldx, const 
              ? km_launch_cand_tc(Xc, n, d, ldxc, pack, k, flag_rows, flag_count, dist32, st, precentred)
              : km_launch_cand_tc_wide(Xc, n, d, ldxc, pack, k, flag_rows, flag_count, dist32, st, precentred);
     if (rc) return rc;
-    refine_cand_kernel<TX><<<KM_NUM_SMS * 4, 128, 0, st>>>(X, n, d, ldx, c64, cn64, flag_rows, flag_count, labels, mind2);
+    refine_cand_kernel<TX><<<km_num_sms() * 4, 128, 0, st>>>(X, n, d, ldx, c64, cn64, flag_rows, flag_count, labels, mind2);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return (int)e;
     // rows with too many candidates: the full scan over the overflow list (its size is flag_rows[n-1])

@@ -28,16 +28,30 @@ constexpr int TC_EPI = 256;       // staging/epilogue threads: 2 per row (column
 constexpr int TC_ROWS = 128;     // rows per CTA step
 constexpr int TC_BSTAGES_MAX = 8;   // ring of K-step blocks: 5 x 16 KB (one CTA) or 8 x 8 KB (CTA pair)
 constexpr int TC_ASTAGES = 2;    // accumulator stages: 2 x 256 = 512 TMEM columns
-constexpr uint32_t TC_SPIN_LIMIT = 1u << 27;
+constexpr unsigned long long TC_WAIT_LIMIT_NS = 30ull * 1000000000ull;   // see km_wait_expired
 
 __device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(km_smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ unsigned long long km_globaltimer() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+// Have 30 s of wall time (%globaltimer) gone by since *t0?  Called every 65536 failed polls of a spin loop; the first
+// call only starts the clock.  A bound in TIME, not in polls: a wait that is merely slow -- time-slicing with another
+// context, MPS co-tenants, a debugger or compute-sanitizer -- must not be taken for a hang.
+__device__ __forceinline__ bool km_wait_expired(unsigned long long &t0) {
+    const unsigned long long now = km_globaltimer();
+    if (t0 == 0) { t0 = now; return false; }
+    return now - t0 > TC_WAIT_LIMIT_NS;
 }
 // bounded wait: a protocol bug traps (launch error) instead of hanging the GPU
 __device__ __forceinline__ void mbar_wait_bounded(uint64_t *bar, uint32_t parity) {
     const uint32_t addr = km_smem_u32(bar);
     uint32_t done;
     uint32_t spins = 0;
+    unsigned long long t0 = 0;
     do {
         asm volatile(
             "{\n\t.reg .pred p;\n\t"
@@ -46,7 +60,7 @@ __device__ __forceinline__ void mbar_wait_bounded(uint64_t *bar, uint32_t parity
             : "=r"(done)
             : "r"(addr), "r"(parity)
             : "memory");
-        if (!done && ++spins > TC_SPIN_LIMIT) __trap();
+        if (!done && ((++spins) & 0xFFFFu) == 0 && km_wait_expired(t0)) __trap();
     } while (!done);
 }
 // non-blocking probe of a barrier phase
@@ -821,6 +835,7 @@ assign_tc_small_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ld
         // would hold one group's MMAs behind the other group's tracking.
         const uint32_t nj0 = (uint32_t)((my_tiles + 1) / 2), nj1 = (uint32_t)(my_tiles / 2);
         uint32_t j0 = 0, j1 = 0, g = 0, spins = 0;
+        unsigned long long wait_t0 = 0;
         while (j0 < nj0 || j1 < nj1) {
             const uint32_t j = g ? j1 : j0, buf = j & 1;
             const bool more = g ? (j1 < nj1) : (j0 < nj0);
@@ -828,10 +843,11 @@ assign_tc_small_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ld
                                mbar_test(&bars->a_empty[g], (j & 1) ^ 1);
             if (!ready) {
                 g ^= 1;
-                if (++spins > TC_SPIN_LIMIT) __trap();
+                if (((++spins) & 0xFFFFu) == 0 && km_wait_expired(wait_t0)) __trap();
                 continue;
             }
             spins = 0;
+            wait_t0 = 0;
             tc_fence_after();
             TC_TRACE(2 + (int)g, j, 0);
             const uint32_t ah = (((xb_a + (g * 2 + buf) * xbuf_bytes) & 0x3FFFFu) >> 4) | a_lbo;
@@ -1284,9 +1300,9 @@ int km_launch_cand_tc(const float *X, int64_t n, int d, int64_t ldx, const void 
     if (int rc = km_set_smem_once(cand_tc_kernel<true>, 227 * 1024, attr_v)) return rc;
     if (int rc = km_set_smem_once(cand_tc_kernel<false>, 227 * 1024, attr_s)) return rc;
     if (vec)
-        cand_tc_kernel<true><<<KM_NUM_SMS, TC_THREADS, smem, st>>>(X, n, d, ldx, img, mu, cmax, k, flag_rows, flag_count, mind2);
+        cand_tc_kernel<true><<<km_num_sms(), TC_THREADS, smem, st>>>(X, n, d, ldx, img, mu, cmax, k, flag_rows, flag_count, mind2);
     else
-        cand_tc_kernel<false><<<KM_NUM_SMS, TC_THREADS, smem, st>>>(X, n, d, ldx, img, mu, cmax, k, flag_rows, flag_count, mind2);
+        cand_tc_kernel<false><<<km_num_sms(), TC_THREADS, smem, st>>>(X, n, d, ldx, img, mu, cmax, k, flag_rows, flag_count, mind2);
     return (int)cudaGetLastError();
 }
 
@@ -1704,10 +1720,10 @@ int km_launch_cand_tc_wide(const float *X, int64_t n, int d, int64_t ldx, const 
     if (int rc = km_set_smem_once(assign_tc_wide_kernel<true, true>, 227 * 1024, attr_v)) return rc;
     if (int rc = km_set_smem_once(assign_tc_wide_kernel<false, true>, 227 * 1024, attr_s)) return rc;
     if (vec)
-        assign_tc_wide_kernel<true, true><<<KM_NUM_SMS, TC_THREADS, smem_w, st>>>(
+        assign_tc_wide_kernel<true, true><<<km_num_sms(), TC_THREADS, smem_w, st>>>(
             X, n, d, ldx, img, c32, mu, cmax, k, nullptr, mind2, flag_rows, const_cast<int32_t *>(flag_count));
     else
-        assign_tc_wide_kernel<false, true><<<KM_NUM_SMS, TC_THREADS, smem_w, st>>>(
+        assign_tc_wide_kernel<false, true><<<km_num_sms(), TC_THREADS, smem_w, st>>>(
             X, n, d, ldx, img, c32, mu, cmax, k, nullptr, mind2, flag_rows, const_cast<int32_t *>(flag_count));
     return (int)cudaGetLastError();
 }
@@ -1731,7 +1747,7 @@ int km_launch_assign_tc(const float *X, int64_t n, int d, int64_t ldx, const voi
         const size_t xbuf_w = (size_t)(TCW_PCH + 2) * 128 * 16 + (size_t)TCW_PCH * 128 * 16;
         const size_t smem_w = 2 * xbuf_w + 5 * (size_t)KM_TC_KS_BYTES + sizeof(TcBars) + 64;
         const int64_t steps_w = (n + TC_ROWS - 1) / TC_ROWS;
-        const unsigned grid = (unsigned)(steps_w < KM_NUM_SMS ? steps_w : KM_NUM_SMS);
+        const unsigned grid = (unsigned)(steps_w < km_num_sms() ? steps_w : km_num_sms());
         static bool attr_v[KM_MAX_DEVICES] = {}, attr_s[KM_MAX_DEVICES] = {};
         if (int rc = km_set_smem_once(assign_tc_wide_kernel<true, false>, 227 * 1024, attr_v)) return rc;
         if (int rc = km_set_smem_once(assign_tc_wide_kernel<false, false>, 227 * 1024, attr_s)) return rc;
@@ -1748,7 +1764,7 @@ int km_launch_assign_tc(const float *X, int64_t n, int d, int64_t ldx, const voi
         const size_t xbuf = (size_t)(nch + 2) * 128 * 16 + (size_t)nch * 128 * 16;
         const size_t smem_s = 4 * xbuf + km_tc_tile_bytes(d) + sizeof(TcSmallBars) + 64;
         const int64_t tiles = (n + TC_ROWS - 1) / TC_ROWS;
-        const unsigned grid = (unsigned)(tiles < KM_NUM_SMS ? tiles : KM_NUM_SMS);
+        const unsigned grid = (unsigned)(tiles < km_num_sms() ? tiles : km_num_sms());
         static bool attr_v[KM_MAX_DEVICES] = {}, attr_s[KM_MAX_DEVICES] = {};
         if (int rc = km_set_smem_once(assign_tc_small_kernel<true>, 227 * 1024, attr_v)) return rc;
         if (int rc = km_set_smem_once(assign_tc_small_kernel<false>, 227 * 1024, attr_s)) return rc;
@@ -1766,7 +1782,7 @@ int km_launch_assign_tc(const float *X, int64_t n, int d, int64_t ldx, const voi
                         (size_t)nstages * stage_bytes + sizeof(TcBars) + 64;
     const int64_t step_rows = pair ? 2 * TC_ROWS : TC_ROWS;
     int64_t steps = (n + step_rows - 1) / step_rows;
-    const int max_units = pair ? KM_NUM_SMS / 2 : KM_NUM_SMS;
+    const int max_units = pair ? km_num_sms() / 2 : km_num_sms();
     const int units = (int)(steps < max_units ? steps : max_units);
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(pair ? 2 * units : units);

@@ -22,11 +22,23 @@
 
 static inline cudaStream_t km_stream(void *s) { return reinterpret_cast<cudaStream_t>(s); }
 
-constexpr int KM_NUM_SMS = 148;  // B200: 2 dies x 74 SMs
+constexpr int KM_MAX_DEVICES = 64;
+// SM count of the current device (148 on B200: 2 dies x 74 SMs), read once per device from the driver; grids of the
+// persistent kernels are sized from it.
+static inline int km_num_sms() {
+    static int cached[KM_MAX_DEVICES];   // zero-initialised; a racing first call writes the same value twice
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= KM_MAX_DEVICES) return 148;
+    int v = cached[dev];
+    if (v <= 0) {
+        if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0) v = 148;
+        cached[dev] = v;
+    }
+    return v;
+}
 
 // Opt a kernel into > 48 KB of dynamic shared memory, once per device per kernel.
 // (cudaFuncSetAttribute is per device; `flags` is a per-kernel static bool[KM_MAX_DEVICES].)
-constexpr int KM_MAX_DEVICES = 64;
 template <typename Kern>
 static inline int km_set_smem_once(Kern kern, int bytes, bool *flags) {
     int dev = 0;
@@ -73,7 +85,7 @@ struct KmPackLayout {
     size_t off_cn64;  // double[k]         ||c64_j||^2
     size_t off_c64;   // double[k*d]       copy of the fp64 master
     size_t off_ct;    // float[ntiles][d+1][128] column-tiled centred fp32 centres (zero padded); row d = norms
-    size_t off_tc;    // tcgen05 image: ceil(k/64) tiles of km_tc_tile_bytes(d) (absent when d > KM_TC_MAX_D)
+    size_t off_tc;    // tcgen05 image: ceil(k/256) column tiles of km_tc_tile_bytes(d) each (absent when d > KM_TC_WIDE_MAX_D)
     size_t total;
 };
 

@@ -173,7 +173,7 @@ static int mindist_impl(const T *X, int64_t n, int d, int64_t ldx, const T *cand
     constexpr int VECW = 16 / sizeof(T);
     if (d % VECW == 0 && ldx % VECW == 0 && (reinterpret_cast<uintptr_t>(X) & 15) == 0) {
         const int dv = d / VECW;
-        int64_t cap = (int64_t)KM_NUM_SMS * 8;
+        int64_t cap = (int64_t)km_num_sms() * 8;
 #define MDV_LAUNCH(LPR_, U_)  /* U_ <= LPR_: every row of a warp step needs an owner lane */                   \
     if (m <= 2) MDV_LAUNCH2(LPR_, (2 * U_ <= LPR_ ? 2 * U_ : U_), 2) else MDV_LAUNCH2(LPR_, U_, MD_MAXM)
 #define MDV_LAUNCH2(LPR_, U_, MM_)                                                                               \
@@ -201,7 +201,7 @@ static int mindist_impl(const T *X, int64_t n, int d, int64_t ldx, const T *cand
     else if (d <= 64) lpr = 16;
     const int rpw = 32 / lpr;
     int64_t blocks = (n + (int64_t)rpw * (MD_THREADS / 32) - 1) / ((int64_t)rpw * (MD_THREADS / 32));
-    const int64_t cap = (int64_t)KM_NUM_SMS * 8;
+    const int64_t cap = (int64_t)km_num_sms() * 8;
     if (blocks > cap) blocks = cap;
 #define MD_LAUNCH(LPR_)                                                                                          \
     {                                                                                                            \
@@ -306,7 +306,7 @@ static int mindist_pots_impl(const T *X, int64_t n, int d, int64_t ldx, const T 
     else if (d <= 64) lpr = 16;
     const int rpw = 32 / lpr;
     int64_t blocks = (n + (int64_t)rpw * (MD_THREADS / 32) - 1) / ((int64_t)rpw * (MD_THREADS / 32));
-    const int64_t cap = (int64_t)KM_NUM_SMS * 8;
+    const int64_t cap = (int64_t)km_num_sms() * 8;
     if (blocks > cap) blocks = cap;
 #define MDP_LAUNCH(LPR_)                                                                                         \
     {                                                                                                            \
@@ -366,7 +366,7 @@ static int bernoulli_impl(const T *mind2, int64_t n, double scale, uint64_t seed
                           const double *draws, int64_t *picked, int32_t *count, int capacity, void *stream) {
     KM_CHECK_ARG(mind2 && picked && count && n > 0 && capacity > 0, B200KM_EINVAL);
     int64_t blocks = (n + 255) / 256;
-    if (blocks > KM_NUM_SMS * 16) blocks = KM_NUM_SMS * 16;
+    if (blocks > km_num_sms() * 16) blocks = km_num_sms() * 16;
     bernoulli_kernel<T><<<(unsigned)blocks, 256, 0, km_stream(stream)>>>(
         mind2, n, scale, (uint32_t)seed, (uint32_t)(seed >> 32), round, row_offset, draws, picked, count, capacity);
     KM_LAUNCH_RET();
@@ -400,7 +400,7 @@ gather_kernel(const T *__restrict__ X, int64_t n, int d, int64_t ldx, const int6
 template <typename T>
 static int gather_impl(const T *X, int64_t n, int d, int64_t ldx, const int64_t *idx, int m, T *out, void *stream) {
     KM_CHECK_ARG(X && idx && out && n > 0 && d > 0 && m > 0 && ldx >= d, B200KM_EINVAL);
-    int blocks = m < KM_NUM_SMS * 16 ? m : KM_NUM_SMS * 16;
+    int blocks = m < km_num_sms() * 16 ? m : km_num_sms() * 16;
     gather_kernel<T><<<blocks, 128, 0, km_stream(stream)>>>(X, n, d, ldx, idx, m, out);
     KM_LAUNCH_RET();
 }

@@ -166,7 +166,7 @@ template <typename T>
 static int row_norms_impl(const T *X, int64_t n, int d, int64_t ldx, T *out, int squared, void *stream) {
     KM_CHECK_ARG(X && out && n > 0 && d > 0 && ldx >= d, B200KM_EINVAL);
     int64_t blocks = (n + 7) / 8;
-    if (blocks > KM_NUM_SMS * 16) blocks = KM_NUM_SMS * 16;
+    if (blocks > km_num_sms() * 16) blocks = km_num_sms() * 16;
     row_norms_kernel<T><<<(unsigned)blocks, 256, 0, km_stream(stream)>>>(X, n, d, ldx, out, squared);
     KM_LAUNCH_RET();
 }
@@ -174,7 +174,7 @@ template <typename T>
 static int nonfinite_impl(const T *X, int64_t n, int d, int64_t ldx, int32_t *bad, void *stream) {
     KM_CHECK_ARG(X && bad && n > 0 && d > 0 && ldx >= d, B200KM_EINVAL);
     int64_t blocks = (n * (int64_t)d + 255) / 256;
-    if (blocks > KM_NUM_SMS * 16) blocks = KM_NUM_SMS * 16;
+    if (blocks > km_num_sms() * 16) blocks = km_num_sms() * 16;
     nonfinite_kernel<T><<<(unsigned)blocks, 256, 0, km_stream(stream)>>>(X, n, d, ldx, bad);
     KM_LAUNCH_RET();
 }
@@ -234,7 +234,7 @@ static int blobs_impl(T *X, int64_t n, int d, int64_t ldx, const T *centers, int
                       int64_t row_offset, int32_t *y, void *stream) {
     KM_CHECK_ARG(X && centers && n > 0 && d > 0 && k_true > 0 && ldx >= d, B200KM_EINVAL);
     int64_t blocks = (n * (int64_t)((d + 3) / 4) + 255) / 256;
-    if (blocks > KM_NUM_SMS * 32) blocks = KM_NUM_SMS * 32;
+    if (blocks > km_num_sms() * 32) blocks = km_num_sms() * 32;
     blobs_kernel<T><<<(unsigned)blocks, 256, 0, km_stream(stream)>>>(X, n, d, ldx, centers, k_true, cluster_std,
                                                                      (uint32_t)seed, (uint32_t)(seed >> 32), row_offset, y);
     KM_LAUNCH_RET();

@@ -16,6 +16,8 @@
 //   update_atomic_kernel (any k*d): warp per row, lanes = features, fp64 RED into the global
 //       table (L2-resident), counts via one RED per row.
 #include "common.cuh"
+#include <cooperative_groups.h>
+namespace cg = cooperative_groups;
 
 int km_k2_variant();  // assign.cu (b200km_set_option)
 
@@ -311,7 +313,7 @@ static int update_impl(const T *X, int64_t n, int d, int64_t ldx, const int32_t 
         static bool attr_set[KM_MAX_DEVICES] = {};
         if (int rc = km_set_smem_once(kern, 96 * 1024, attr_set)) return rc;
         int64_t blocks = (n + 1023) / 1024;
-        const int64_t cap = (int64_t)KM_NUM_SMS * 2;
+        const int64_t cap = (int64_t)km_num_sms() * 2;
         if (blocks > cap) blocks = cap;
         kern<<<(unsigned)blocks, UP_THREADS, smem, st>>>(X, n, d, ldx, labels, mind2, k, acc, scale_sqrt);
     } else if (use_seg) {
@@ -325,7 +327,7 @@ static int update_impl(const T *X, int64_t n, int d, int64_t ldx, const int32_t 
         if (int rc = km_set_smem_once(update_seg_kernel<T, true>, 200 * 1024, attr_n)) return rc;
         if (int rc = km_set_smem_once(update_seg_kernel<T, false>, 200 * 1024, attr_w)) return rc;
         int64_t blocks = (n + SEG_R - 1) / SEG_R;
-        const int64_t cap = (int64_t)KM_NUM_SMS * 4;   // several CTAs per SM: one sorts while another gathers
+        const int64_t cap = (int64_t)km_num_sms() * 4;   // several CTAs per SM: one sorts while another gathers
         if (blocks > cap) blocks = cap;
         if (d <= 32)
             update_seg_kernel<T, true><<<(unsigned)blocks, SEG_THREADS, seg_smem, st>>>(X, n, d, ldx, labels, mind2, k, acc,
@@ -335,7 +337,7 @@ static int update_impl(const T *X, int64_t n, int d, int64_t ldx, const int32_t 
                                                                                        acc, scale_sqrt, SEG_R);
     } else {
         int64_t blocks = (n + 4 * UP_WARPS - 1) / (4 * UP_WARPS);
-        const int64_t cap = (int64_t)KM_NUM_SMS * 8;
+        const int64_t cap = (int64_t)km_num_sms() * 8;
         if (blocks > cap) blocks = cap;
         update_atomic_kernel<T><<<(unsigned)blocks, UP_THREADS, 0, st>>>(X, n, d, ldx, labels, mind2, k, acc, scale_sqrt);
     }
@@ -354,14 +356,26 @@ extern "C" int b200km_update_f64(const double *X, int64_t n, int d, int64_t ldx,
 // ---------------------------------------------------------------------------------------------
 // K3 finalize
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256)
+// One thread-block cluster of FIN_CTAS CTAs does the whole job, so the shift is summed in ONE FIXED ORDER (thread
+// partials over a fixed stride -> warp shuffles -> warps in index order -> CTAs in rank order through distributed
+// shared memory): every rank of a multi-GPU fit computes bit-identical centres AND a bit-identical shift from the
+// allreduced buffer, so all ranks take the same `shift < tol` / `shift > 1e-7` decisions (k_means.py:608, :612) and
+// no rank is left alone in a collective.  (The earlier multi-block kernel summed the shift with floating-point
+// atomics, whose order -- and so whose last bit -- could differ from rank to rank.)
+constexpr int FIN_CTAS = 8;
+constexpr int FIN_THREADS = 512;
+
+__global__ void __cluster_dims__(FIN_CTAS, 1, 1) __launch_bounds__(FIN_THREADS)
 finalize_kernel(const double *__restrict__ acc, int k, int d, const double *__restrict__ cold,
                 double *__restrict__ cnew, double *__restrict__ shift_out) {
-    __shared__ double red[32];
+    __shared__ double red[FIN_THREADS / 32];
+    __shared__ double cta_part[FIN_CTAS];   // used in CTA 0 only: one slot per CTA of the cluster
+    cg::cluster_group cluster = cg::this_cluster();
+    const unsigned rank = cluster.block_rank();
     const double *counts = acc + (size_t)k * d;
     double s = 0.0;
     const int64_t total = (int64_t)k * d;
-    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+    for (int64_t e = (int64_t)rank * FIN_THREADS + threadIdx.x; e < total; e += (int64_t)FIN_CTAS * FIN_THREADS) {
         const int j = (int)(e / d);
         const double c = fmax(counts[j], 1.0);  // k_means.py:600
         const double v = acc[e] / c;            // :601
@@ -369,18 +383,28 @@ finalize_kernel(const double *__restrict__ acc, int k, int d, const double *__re
         const double df = cold[e] - v;  // :605
         s = fma(df, df, s);
     }
-    km_block_atomic_add(s, shift_out, red);
+    s = km_warp_sum(s);
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    if (lane == 0) red[w] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int i = 0; i < FIN_THREADS / 32; ++i) t += red[i];
+        double *slot = cluster.map_shared_rank(cta_part, 0) + rank;
+        *slot = t;
+    }
+    cluster.sync();
+    if (rank == 0 && threadIdx.x == 0) {
+        double t = 0.0;
+        for (int i = 0; i < FIN_CTAS; ++i) t += cta_part[i];
+        *shift_out = t;
+    }
 }
 
 extern "C" int b200km_finalize(const double *acc, int k, int d, const double *centers_old, double *centers_new,
                                double *shift_out, void *stream) {
     KM_CHECK_ARG(acc && centers_old && centers_new && shift_out && k > 0 && d > 0, B200KM_EINVAL);
-    cudaStream_t st = km_stream(stream);
-    cudaError_t e = cudaMemsetAsync(shift_out, 0, sizeof(double), st);
-    if (e != cudaSuccess) return (int)e;
-    int64_t blocks = ((int64_t)k * d + 255) / 256;
-    if (blocks > KM_NUM_SMS * 4) blocks = KM_NUM_SMS * 4;
-    finalize_kernel<<<(unsigned)blocks, 256, 0, st>>>(acc, k, d, centers_old, centers_new, shift_out);
+    finalize_kernel<<<FIN_CTAS, FIN_THREADS, 0, km_stream(stream)>>>(acc, k, d, centers_old, centers_new, shift_out);
     KM_LAUNCH_RET();
 }
 
@@ -402,7 +426,7 @@ template <typename T>
 static int reduce_sum_impl(const T *v, int64_t n, int take_sqrt, double *out, void *stream) {
     KM_CHECK_ARG(v && out && n > 0, B200KM_EINVAL);
     int64_t blocks = (n + 255) / 256;
-    if (blocks > KM_NUM_SMS * 8) blocks = KM_NUM_SMS * 8;
+    if (blocks > km_num_sms() * 8) blocks = km_num_sms() * 8;
     reduce_sum_kernel<T><<<(unsigned)blocks, 256, 0, km_stream(stream)>>>(v, n, take_sqrt, out);
     KM_LAUNCH_RET();
 }
@@ -582,7 +606,7 @@ static int assign_update_impl(const TX *X, int64_t n, int d, int64_t ldx, const 
     KM_CHECK_ARG(n > 0 && d > 0 && k > 0 && ldx >= d, B200KM_EINVAL);
     KM_CHECK_ARG(k <= FU_MAXK && d <= FU_MAXD, B200KM_ETOOBIG);
     int64_t blocks = (n + FU_R - 1) / FU_R;
-    const int64_t cap = (int64_t)KM_NUM_SMS * (d <= 16 ? 2 : 4);   // resident CTAs per SM of the two variants
+    const int64_t cap = (int64_t)km_num_sms() * (d <= 16 ? 2 : 4);   // resident CTAs per SM of the two variants
     if (blocks > cap) blocks = cap;
     const size_t smem = sizeof(double) * ((size_t)FU_R * (d + 1) + 1 + (size_t)k * (d + 1));
     if (d <= 16) {

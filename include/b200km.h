@@ -63,8 +63,14 @@ const char *b200km_error_string(int code);
 /* ------------------------------------------------------------------------------------------
  * Centre pack.  The fp64 master copy of the centres (k x d, row-major) is expanded once per
  * Lloyd iteration into the layouts the assign kernels read:
- *   fp32 row-major copy, fp32 column-tiled copy ([tile][d+1][128], zero padded, last row = squared
- *   norms, +inf padded), fp32 and fp64 squared norms, max squared norm, fp64 copy.
+ *   mu = mean of the centres (fp32; the float32 kernels work on x - mu and c - mu) and a zero vector that
+ *   stands in for it when the rows are already centred; fp32 row-major copy of c - mu; fp32 column-tiled
+ *   copy ([tile of 128][d+1][128], zero padded, last row = squared norms, +inf padded); fp32 and fp64
+ *   squared norms, max squared norm; fp64 copy of the master; and, for d <= 2048, the tcgen05 operand
+ *   image: per tile of 256 centres one augmented K-step block (||c||^2 split in three TF32 terms) and one
+ *   block per 8 features holding the TF32 hi and lo parts of -2(c - mu), in the UMMA no-swizzle K-major
+ *   layout.  (With B200KM_OPT_K1_VARIANT = 3 the image is laid out for the CTA-pair kernel: set the option
+ *   BEFORE packing.)
  * Replaces: the `Y` ndarray argument that R/dask_ml/metrics/pairwise.py:31-33 embeds in every
  * per-block task, and the per-call `row_norms(Y)` inside sklearn's ArgKmin.
  * ---------------------------------------------------------------------------------------- */

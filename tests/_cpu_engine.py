@@ -43,7 +43,9 @@ class NumpyEngine:
         return _Pack(centers64)
 
     def assign(self, X, pack, labels=None, mind2=None, want_mind2=True, refine=True):
-        lab, d2 = orc.pairwise_distances_argmin_min(X.numpy(), pack.centers64.numpy(), metric_kwargs={"squared": True})
+        # (a CUDA kernel does not raise on a NaN, it computes garbage; scikit-learn would raise here -- on this rank only)
+        lab, d2 = orc.pairwise_distances_argmin_min(np.nan_to_num(X.numpy()), pack.centers64.numpy(),
+                                                    metric_kwargs={"squared": True})
         lt = torch.from_numpy(lab.astype(np.int32))
         dt = torch.from_numpy(d2).to(X.dtype)
         if labels is not None:
@@ -69,7 +71,7 @@ class NumpyEngine:
         acc[k * d : k * d + k] += torch.from_numpy(np.bincount(labels.numpy(), minlength=k).astype(np.float64))
         if mind2 is not None:
             v = mind2.double()
-            acc[-1] += (v.sqrt() if sqrt else v).sum()
+            acc[k * d + k] += (v.sqrt() if sqrt else v).sum()
         return acc
 
     def finalize(self, acc, k, d, centers_old, centers_new=None, shift=None):
@@ -114,5 +116,14 @@ class NumpyEngine:
     def row_norms(self, X, squared=False):
         return torch.from_numpy(orc.row_norms(X.numpy(), squared=squared))
 
+    def nonfinite_flag(self, X, bad=None):
+        if bad is None:
+            bad = torch.zeros(1, dtype=torch.int32)
+        if not bool(torch.isfinite(X).all()):
+            bad += 1
+        return bad
+
     def has_nonfinite(self, X):
-        return not bool(torch.isfinite(X).all())
+        from dask_ml_b200._engine import any_rank_flag
+
+        return any_rank_flag(self.nonfinite_flag(X))

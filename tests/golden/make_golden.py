@@ -114,7 +114,7 @@ if __name__ == "__main__":
     lloyd_case("lloyd_f32_n2000_d128_k1500_c4.npz", 2000, 128, 1500, np.float32, 6, 2, 0.0, (1000, 1000))
     lloyd_case("lloyd_f64_n2500_d64_k300.npz", 2500, 64, 300, np.float64, 7, 3, 0.0, (900, 900, 700))
     lloyd_case("lloyd_f32_n2000_d8_k6_empty.npz", 2000, 8, 6, np.float32, 8, 1, 0.0, (500,) * 4, "far")
-    lloyd_case("lloyd_f32_n2500_d20_k40_tolbreak.npz", 2500, 20, 40, np.float32, 9, 100, 5.0, (900, 900, 700), "near")
+    lloyd_case("lloyd_f32_n2500_d20_k40_tolbreak.npz", 2500, 20, 40, np.float32, 9, 100, 5.0, (900, 900, 700))   # exit 4 with 1e-7 < shift < tol
     # k-means||: the supplement branch (< k candidates) and the re-cluster branch (>= k)
     init_case("init_f32_n4000_d8_k64.npz", 4000, 8, 64, np.float32, 5, 2, (2000, 2000))
     init_case("init_f64_n3000_d4_k6.npz", 3000, 4, 6, np.float64, 6, 2, (3000,))

@@ -46,7 +46,7 @@ LLOYD_CASES = [
     ("one_block",      1500, 5,   3,    np.float64, 6,    300,      1e-9, 1,       "rows"),
     ("many_blocks",    2100, 7,   12,   np.float64, 7,    5,        0.0,  17,      "rows"),   # two levels of dask's sum tree
     ("empty_cluster",  2000, 8,   6,    np.float32, 8,    1,        0.0,  4,       "far"),
-    ("tol_break",      2500, 20,  40,   np.float32, 9,    100,      5.0,  3,       "near"),   # shift < tol with shift > 1e-7
+    ("tol_break",      2500, 20,  40,   np.float32, 9,    100,      5.0,  3,       "rows"),   # shift < tol with shift > 1e-7
 ]
 
 
