@@ -18,7 +18,7 @@ from typing import List, Optional, Tuple
 
 import torch
 
-__all__ = ["Comm", "NullComm", "TorchDistComm", "default_comm"]
+__all__ = ["Comm", "NullComm", "TorchDistComm", "default_comm", "local_only"]
 
 
 class Comm:
@@ -95,9 +95,30 @@ class TorchDistComm(Comm):
         return sum(counts[: self.rank]), sum(counts)
 
 
+_override: Optional[Comm] = None
+
+
+class local_only:
+    """``with local_only(): KMeans(...).fit(X)`` -- inside the block this process fits on its own even though a
+    process group is initialised (no collectives are issued; X is the WHOLE data, not a shard).  Used to check a
+    sharded fit against a one-rank fit of the same rows in the same job."""
+
+    def __enter__(self):
+        global _override
+        self._prev, _override = _override, NullComm()
+        return self
+
+    def __exit__(self, *exc):
+        global _override
+        _override = self._prev
+        return False
+
+
 def default_comm() -> Comm:
     """TorchDistComm when a process group is initialised with more than one rank (each rank then
-    passes ITS row shard to ``fit``), NullComm otherwise."""
+    passes ITS row shard to ``fit``), NullComm otherwise (or inside ``local_only()``)."""
+    if _override is not None:
+        return _override
     try:
         import torch.distributed as dist
 

@@ -63,6 +63,7 @@ class PhiloxRandomState:
             seed = int(np.random.SeedSequence().generate_state(1, dtype=np.uint64)[0])
         self.seed = int(seed) & (2**64 - 1)
         self.round = 0
+        self.picks = []   # sorted global row indices picked in each k-means|| round so far (a record, never read back)
 
     def _host(self, tag: int) -> np.random.Generator:
         return np.random.Generator(np.random.Philox(key=[self.seed, tag]))
@@ -435,7 +436,10 @@ def _pick(eng, comm, mind2, cost, oversampling_factor, random_state, row0, n_tot
         picked = eng.bernoulli(mind2, scale, 0, 0, row0, draws=eng.to_device(u))
     if comm.world > 1:
         picked = comm.allgather_varlen(picked)
-    return np.sort(picked.cpu().numpy())
+    out = np.sort(picked.cpu().numpy())
+    if isinstance(getattr(random_state, "picks", None), list):
+        random_state.picks.append(out)
+    return out
 
 
 def _sample_points(X, centers, oversampling_factor, random_state):
