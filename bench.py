@@ -311,11 +311,16 @@ def lloyd_bench(torch, dist, eng, comm, args, workload, steps, warmup, local_ran
     shift_t = torch.zeros(1, dtype=torch.float64, device=dev)
     state = {"pack": None}
     fused = eng.can_fuse(k, d)
+    split = not fused and eng.lloyd_split(X, k, d)
 
     def step(c_old, c_new):
         acc.zero_()
         if fused:   # HBM-bound regime: K1+K2 in one pass (same branch as _kmeans_single_lloyd)
             eng.assign_update(X, c_old, labels, mind2, acc)
+        elif split:  # small k, d: labels from K1, inertia summed by K2 (same branch as _kmeans_single_lloyd)
+            state["pack"] = eng.pack(c_old, state["pack"])
+            eng.assign(X, state["pack"], labels, mind2, lloyd=True)
+            eng.update_inertia(X, labels, c_old, k, acc)
         else:
             state["pack"] = eng.pack(c_old, state["pack"])
             eng.assign(X, state["pack"], labels, mind2)

@@ -170,13 +170,23 @@ class CudaEngine:
                    launches=3 if d <= 2048 else 2)
         return out
 
+    LLOYD_MAX_K, LLOYD_MAX_D = 256, 32
+
+    def lloyd_split(self, X: torch.Tensor, k: int, d: int) -> bool:
+        """True where the Lloyd iteration runs as ``assign(..., lloyd=True)`` + ``update_inertia``: K1 decides the labels
+        only and K2 sums the inertia from the rows it reads anyway (float32 X on the small-k tensor-core kernel)."""
+        return (X.dtype == torch.float32 and 16 < k <= self.LLOYD_MAX_K and d <= self.LLOYD_MAX_D
+                and self.lib.b200km_get_option(_lib.OPT_K1_VARIANT) == _lib.K1_AUTO)
+
     def assign(self, X: torch.Tensor, pack: CenterPack, labels: Optional[torch.Tensor] = None,
-               mind2: Optional[torch.Tensor] = None, want_mind2: bool = True, refine: bool = True
-               ) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
+               mind2: Optional[torch.Tensor] = None, want_mind2: bool = True, refine: bool = True,
+               lloyd: bool = False) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
         """labels (int32) and squared min distances (X dtype) of every row of X.
 
-        float32 X: FFMA kernel, then the fp64 re-decision of the flagged near-tie rows, so the
+        float32 X: tensor-core kernel, then the fp64 re-decision of the flagged near-tie rows, so the
         labels equal what float64 arithmetic gives (reference: sklearn ArgKmin is float64).
+        ``lloyd=True`` (float32 X, with ``mind2`` as scratch): labels only -- ``mind2`` comes back unspecified
+        (b200km_assign_lloyd_f32); the caller takes the inertia from ``update_inertia``.
         """
         n, d, ldx = self._check_matrix(X)
         if d != pack.d:
@@ -199,7 +209,8 @@ class CudaEngine:
                     if self.k1_events is not None:
                         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                         e0.record()
-                    self._call("b200km_assign_f32", xs.data_ptr(), nn, d, ldx, pack.buf.data_ptr(), pack.k,
+                    self._call("b200km_assign_lloyd_f32" if (lloyd and mp is not None) else "b200km_assign_f32",
+                               xs.data_ptr(), nn, d, ldx, pack.buf.data_ptr(), pack.k,
                                ls.data_ptr(), mp, flags.data_ptr(), fcnt.data_ptr(), 1, st, launches=1)
                     if self.k1_events is not None:
                         e1.record()
@@ -278,6 +289,19 @@ class CudaEngine:
             self._call(f"b200km_update_{sfx}", X[r0 : r0 + nn].data_ptr(), nn, d, ldx, labels[r0 : r0 + nn].data_ptr(),
                        (mind2[r0 : r0 + nn].data_ptr() if mind2 is not None else None), k, acc.data_ptr(),
                        1 if sqrt else 0, st)
+        return acc
+
+    def update_inertia(self, X: torch.Tensor, labels: torch.Tensor, centers64: torch.Tensor, k: int,
+                       acc: torch.Tensor) -> torch.Tensor:
+        """acc += [sums | counts | sum_i ||x_i - centers64[labels_i]||^2], the inertia summed in float64 from the rows."""
+        n, d, ldx = self._check_matrix(X)
+        assert centers64.dtype == torch.float64 and centers64.is_contiguous() and centers64.shape == (k, d)
+        sfx = _suffix(X)
+        st = self._stream()
+        for r0 in range(0, n, _MAX_ROWS_PER_CALL):
+            nn = min(_MAX_ROWS_PER_CALL, n - r0)
+            self._call(f"b200km_update_inertia_{sfx}", X[r0 : r0 + nn].data_ptr(), nn, d, ldx,
+                       labels[r0 : r0 + nn].data_ptr(), centers64.data_ptr(), k, acc.data_ptr(), st)
         return acc
 
     FUSED_MAX_K, FUSED_MAX_D = 16, 32

@@ -42,6 +42,7 @@ PROTOTYPES = {
     "b200km_pack_centers": (c_int, [_P, c_int, c_int, _P, _P]),
     "b200km_assign_f32": (c_int, [_P, c_int64, c_int, c_int64, _P, c_int, _P, _P, _P, _P, c_int, _P]),
     "b200km_assign_f64": (c_int, [_P, c_int64, c_int, c_int64, _P, c_int, _P, _P, _P]),
+    "b200km_assign_lloyd_f32": (c_int, [_P, c_int64, c_int, c_int64, _P, c_int, _P, _P, _P, _P, c_int, _P]),
     "b200km_refine_f64": (c_int, [_P, c_int64, c_int, c_int64, _P, c_int, _P, _P, _P, _P, _P]),
     "b200km_center_convert_f64": (c_int, [_P, c_int64, c_int, c_int64, _P, c_int, _P, _P]),
     "b200km_assign_centred_f32": (c_int, [_P, c_int64, c_int, c_int64, _P, c_int, _P, _P, _P, _P, c_int, _P]),
@@ -53,6 +54,8 @@ PROTOTYPES = {
     "b200km_acc_len": (c_size_t, [c_int, c_int]),
     "b200km_update_f32": (c_int, [_P, c_int64, c_int, c_int64, _P, _P, c_int, _P, c_int, _P]),
     "b200km_update_f64": (c_int, [_P, c_int64, c_int, c_int64, _P, _P, c_int, _P, c_int, _P]),
+    "b200km_update_inertia_f32": (c_int, [_P, c_int64, c_int, c_int64, _P, _P, c_int, _P, _P]),
+    "b200km_update_inertia_f64": (c_int, [_P, c_int64, c_int, c_int64, _P, _P, c_int, _P, _P]),
     "b200km_assign_update_f32": (c_int, [_P, c_int64, c_int, c_int64, _P, c_int, _P, _P, _P, _P]),
     "b200km_assign_update_f64": (c_int, [_P, c_int64, c_int, c_int64, _P, c_int, _P, _P, _P, _P]),
     "b200km_reduce_sum_f32": (c_int, [_P, c_int64, c_int, _P, _P]),

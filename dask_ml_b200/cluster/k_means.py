@@ -576,6 +576,7 @@ def _kmeans_single_lloyd(X, n_clusters, max_iter=300, init="k-means||", verbose=
         with _timer("Lloyd loop %2d." % i, _logger=logger):
             acc.zero_()
             fused = getattr(eng, "can_fuse", lambda *_: False)(k, P)
+            split = not fused and getattr(eng, "lloyd_split", lambda *_: False)(X, k, P)
             if not fused:
                 pack = eng.pack(centers64, pack)
             # iteration 0 of a streamed upload runs chunk by chunk behind the copy engine; a HostMatrix is streamed
@@ -595,6 +596,10 @@ def _kmeans_single_lloyd(X, n_clusters, max_iter=300, init="k-means||", verbose=
                 if fused:
                     # HBM-bound regime (tiny k, d): labels + sums + counts + inertia in ONE pass over X
                     eng.assign_update(Xs, centers64, ls, ms, acc)  # :576-598, :616
+                elif split:
+                    # small k, d: K1 decides the labels only; K2 sums ||x - c||^2 (float64) from the rows it reads anyway
+                    eng.assign(Xs, pack, ls, ms, lloyd=True)  # :576-579
+                    eng.update_inertia(Xs, ls, centers64, k, acc)  # :582-598, :616
                 else:
                     eng.assign(Xs, pack, ls, ms)  # :576-579
                     eng.update(Xs, ls, ms, k, acc)  # :582-598, :616

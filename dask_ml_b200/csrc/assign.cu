@@ -19,7 +19,8 @@
 
 int km_launch_pack_tc(int k, int d, void *pack, cudaStream_t st);  // assign_tc.cu
 int km_launch_assign_tc(const float *X, int64_t n, int d, int64_t ldx, const void *pack, int k, int32_t *labels,
-                        float *mind2, int32_t *flag_rows, int32_t *flag_count, cudaStream_t st, bool precentred);
+                        float *mind2, int32_t *flag_rows, int32_t *flag_count, cudaStream_t st, bool precentred,
+                        bool sparse_d2);
 
 // =============================================================================================
 // centre pack
@@ -614,7 +615,7 @@ static int check_pack_args(const void *X, int64_t n, int d, int64_t ldx, const v
 
 static int assign_f32_impl(const float *X, int64_t n, int d, int64_t ldx, const void *pack, int k,
                            int32_t *labels, float *mind2, int32_t *flag_rows, int32_t *flag_count,
-                           int reset_flags, void *stream, bool precentred) {
+                           int reset_flags, void *stream, bool precentred, bool sparse_d2 = false) {
     int rc = check_pack_args(X, n, d, ldx, pack, k, labels);
     if (rc) return rc;
     // rows already centred on the pack's mu: only the kernels that work on centred data can take them
@@ -636,7 +637,7 @@ static int assign_f32_impl(const float *X, int64_t n, int d, int64_t ldx, const 
         return launch_rb<float, 32, 8, 8, false>(X, n, d, ldx, c64, nullptr, k, nullptr, nullptr, labels, mind2, st);
     }
     if (use_tc_path(d, k))
-        return km_launch_assign_tc(X, n, d, ldx, pack, k, labels, mind2, flag_rows, flag_count, st, precentred);
+        return km_launch_assign_tc(X, n, d, ldx, pack, k, labels, mind2, flag_rows, flag_count, st, precentred, sparse_d2);
     const int ntiles = (k + KM_TILE_N - 1) / KM_TILE_N;
     const size_t smem = sizeof(float) * ((size_t)d * AT_XLD + 2 * (size_t)(d + 1) * KM_TILE_N);
     const bool vec = (d % 4 == 0) && (ldx % 4 == 0) && ((reinterpret_cast<uintptr_t>(X) & 15) == 0);
@@ -661,6 +662,12 @@ extern "C" int b200km_assign_f32(const float *X, int64_t n, int d, int64_t ldx, 
                                  int32_t *labels, float *mind2, int32_t *flag_rows, int32_t *flag_count,
                                  int reset_flags, void *stream) {
     return assign_f32_impl(X, n, d, ldx, pack, k, labels, mind2, flag_rows, flag_count, reset_flags, stream, false);
+}
+extern "C" int b200km_assign_lloyd_f32(const float *X, int64_t n, int d, int64_t ldx, const void *pack, int k,
+                                       int32_t *labels, float *score, int32_t *flag_rows, int32_t *flag_count,
+                                       int reset_flags, void *stream) {
+    KM_CHECK_ARG(score && flag_rows && flag_count, B200KM_EINVAL);
+    return assign_f32_impl(X, n, d, ldx, pack, k, labels, score, flag_rows, flag_count, reset_flags, stream, false, true);
 }
 extern "C" int b200km_assign_centred_f32(const float *Xc, int64_t n, int d, int64_t ldx, const void *pack, int k,
                                          int32_t *labels, float *mind2, int32_t *flag_rows, int32_t *flag_count,

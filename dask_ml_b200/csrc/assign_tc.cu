@@ -186,6 +186,26 @@ __device__ __forceinline__ void track(float v, int j, float &best, float &second
         : "f"(v), "r"(j));
 }
 
+// ---- threshold tracker (small-k kernel): what the (best, second, argmin) tracker above costs in ALU-pipe
+// instructions (FSETP / FMNMX / SEL: one warp instruction per 2 cycles) is moved to the FMA pipe.
+//   pass 1 over a 32-score chunk: its minimum with three-input min (FMNMX3: 0.5 ALU op per score);
+//   pass 2: u = sat((T - v) * BIG) is 1 for a score within the row's near-tie threshold T = min + bound, else 0;
+//           cnt += u;  idx += u * j   -- three FMA-pipe instructions per score, no compare, no select.
+// A row whose count is exactly 1 has ONE score within the threshold: it is the minimum and idx is its column.
+// Any other count sends the row to the float64 re-decision, exactly as `second - best <= bound` did (the threshold
+// is padded upward, so the test can only flag more rows, never fewer), and its provisional label comes from an
+// exact rescan (lowest column among equal minima) that a warp runs only when one of its rows needs it.
+__device__ __forceinline__ float min3f(float a, float b, float c) {
+    float r;
+    asm("min.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
+    return r;
+}
+__device__ __forceinline__ float fma_sat(float a, float b, float c) {
+    float r;
+    asm("fma.rn.sat.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
+    return r;
+}
+
 struct TcBars {
     uint64_t b_full[TC_BSTAGES_MAX];
     uint64_t b_empty[TC_BSTAGES_MAX];
@@ -758,7 +778,12 @@ assign_tc_small_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ld
                        const unsigned char *__restrict__ tc_img, const float *__restrict__ c32,
                        const float *__restrict__ mu, const unsigned int *__restrict__ cmax_bits, int k,
                        int32_t *__restrict__ labels, float *__restrict__ mind2,
-                       int32_t *__restrict__ flag_rows, int32_t *__restrict__ flag_count) {
+                       int32_t *__restrict__ flag_rows, int32_t *__restrict__ flag_count, int sparse_d2) {
+    // sparse_d2 != 0 (the Lloyd iteration, b200km_assign_lloyd_f32): the winner distance is NOT rebuilt here -- K2
+    // sums ||x - c||^2 in float64 from the rows it reads anyway -- and mind2 gets, for the flagged rows only, the
+    // expanded-form value ||x'||^2 + best score, which is all the pruned re-decision needs.  That takes the
+    // winner's centre-row gather and the re-read of the staged row (2/5 of the kernel's shared-memory traffic, the
+    // resource it was bound by) out of the step.
     extern __shared__ __align__(1024) unsigned char tc_smem[];
     constexpr int NCH = 8;                                 // 16-byte K chunks of a row at d = 32
     const int kpad = km_tc_kpad(d);
@@ -884,6 +909,13 @@ assign_tc_small_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ld
         const int r8 = lane & 7, cq = lane >> 3;
         const float cmax = __uint_as_float(*cmax_bits);
         const float bound_scale = 2.0f * (float)(d + 14) * 1.1920929e-07f;
+        // threshold tracker: BIG = 2^(30 - exponent of cmax) resolves 2^-30 of the data's scale (far below a score's
+        // own ulp), pad_abs = 2^-28 of that scale keeps every score within the true bound a FULL hit (u == 1)
+        int big_e = 284 - (int)((*cmax_bits >> 23) & 0xFFu);
+        big_e = big_e < 1 ? 1 : (big_e > 227 ? 227 : big_e);
+        const float big = __uint_as_float((uint32_t)big_e << 23);
+        const float nbig = -big;
+        const float pad_abs = cmax * 3.7252903e-09f;
         // the centring vector's two chunks this lane stages (mu is zero padded to kpad)
         const float4 mu0 = cq < nch ? __ldg(reinterpret_cast<const float4 *>(mu) + cq) : make_float4(0.f, 0.f, 0.f, 0.f);
         const float4 mu1 =
@@ -952,14 +984,17 @@ assign_tc_small_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ld
         };
         // labels / winner distance / near-tie flag of row rl of step j.  The winner's centre row comes from the
         // resident image: -(hi + lo) / 2 is the float32 centre exactly (lo is stored unrounded).
-        auto output = [&](int64_t j, float best, float second, int bi) {
+        auto output = [&](int64_t j, bool near_tie, int bi, float best_score) {
             const uint32_t bf = (uint32_t)(j & 1);
             const unsigned char *ph = xb + (size_t)(g * 2 + bf) * xbuf_bytes + (size_t)rl * 16;
             const unsigned char *pl = ph + xhi_bytes;
             const unsigned char *pc = bimg + KM_TC_AUG_BYTES + (size_t)bi * 16;
             float s = 0.f;
+            if (sparse_d2) {
+                s = fmaxf(bars->xn[g][bf][rl] + best_score, 0.f);
+            } else if (mind2) {
 #pragma unroll
-            for (int c = 0; c < NCH; ++c) {
+              for (int c = 0; c < NCH; ++c) {
                 if (c < nch) {
                     const float4 h = *reinterpret_cast<const float4 *>(ph + (size_t)c * 2048);
                     const float4 l = *reinterpret_cast<const float4 *>(pl + (size_t)c * 2048);
@@ -972,17 +1007,15 @@ assign_tc_small_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ld
                     df = fmaf(0.5f, ch.z + cl.z, h.z + l.z); s = fmaf(df, df, s);
                     df = fmaf(0.5f, ch.w + cl.w, h.w + l.w); s = fmaf(df, df, s);
                 }
+              }
             }
             const int64_t row = tile_row0(j) + rl;
             if (row < n) {
                 labels[row] = bi;
-                if (mind2) mind2[row] = s;
-                if (flag_rows) {
-                    const float thr = bound_scale * (bars->xn[g][bf][rl] + cmax);
-                    if (second - best <= thr) {
-                        const int pos = atomicAdd(flag_count, 1);
-                        flag_rows[pos] = (int32_t)row;
-                    }
+                if (mind2 && (!sparse_d2 || near_tie)) mind2[row] = s;
+                if (flag_rows && near_tie) {
+                    const int pos = atomicAdd(flag_count, 1);
+                    flag_rows[pos] = (int32_t)row;
                 }
             }
         };
@@ -999,12 +1032,14 @@ assign_tc_small_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ld
             if (j + 1 < nj) stage(ld, j + 1);       // its MMAs run under the tracking below
             if (j + 2 < nj) issue_x(ld, j + 2);
             if (q4 == 2) TC_TRACE(g, j, 3);
-            // ---- scores of step j: all 256 columns of this group's accumulator stage ----
-            float best2[2] = {INFINITY, INFINITY}, second2[2] = {INFINITY, INFINITY};
-            int bidx2[2] = {0, 0};
+            // ---- scores of step j: all 256 columns of this group's accumulator stage (threshold tracker) ----
+            const float thr = bound_scale * (bars->xn[g][j & 1][rl] + cmax);
+            const float thrp = fmaf(thr, 1.0001f, pad_abs);     // padded upward: can only flag more rows
+            float m = INFINITY, TB = 0.f;
+            float cnt0 = 0.f, cnt1 = 0.f, ix0 = 0.f, ix1 = 0.f;
             mbar_wait_bounded(&bars->a_full[g], (uint32_t)(j & 1));
             // The groups track strictly in turn (0, 1, 0, 1, ...).  Left alone they fall into lockstep -- both
-            // tracking at once on a shared ALU pipe, then both idle while their MMAs queue on the tensor core.
+            // tracking at once on shared pipes, then both idle while their MMAs queue on the tensor core.
             if (g == 1) mbar_wait_bounded(&bars->turn[1], (uint32_t)(j & 1));
             else if (j > 0) mbar_wait_bounded(&bars->turn[0], (uint32_t)((j - 1) & 1));
             tc_fence_after();
@@ -1019,27 +1054,68 @@ assign_tc_small_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ld
                 if (c + 1 < 8) tmem_ld32(tbase + (uint32_t)((c + 1) * 32), nxt);  // flies under this chunk
                 const int cb = c * 32;
                 if (cb < k) {               // chunks made of padding columns only cannot win (warp-uniform)
-                    const float before0 = best2[0], before1 = best2[1];
-                    int jloc0 = 0, jloc1 = 0;
+                    // pass 1: the chunk's minimum
+                    float cm0 = __uint_as_float(cur[0]), cm1 = __uint_as_float(cur[1]);
+#pragma unroll
+                    for (int jj = 2; jj < 32; jj += 4) {
+                        cm0 = min3f(cm0, __uint_as_float(cur[jj]), __uint_as_float(cur[jj + 1]));
+                        if (jj + 3 < 32) cm1 = min3f(cm1, __uint_as_float(cur[jj + 2]), __uint_as_float(cur[jj + 3]));
+                    }
+                    const float m_old = m;
+                    m = min3f(m, cm0, cm1);
+                    float T = m + thrp;
+                    T = fmaf(fabsf(T), 4.8e-7f, T);          // covers the rounding of the sum above
+                    // Earlier hits all lie at or above the old minimum.  If that is now outside the threshold they
+                    // are void; if it is inside, the row has two scores within the threshold and the stale count
+                    // (>= 2 with the new minimum's own hit) says so.
+                    const bool reset = m_old > T;
+                    TB = T * big;
+                    cnt0 = reset ? 0.f : cnt0;
+                    cnt1 = reset ? 0.f : cnt1;
+                    ix0 = reset ? 0.f : ix0;
+                    ix1 = reset ? 0.f : ix1;
+                    // pass 2: hits of this chunk (FMA pipe only)
 #pragma unroll
                     for (int jj = 0; jj < 32; jj += 2) {
-                        track(__uint_as_float(cur[jj]), jj, best2[0], second2[0], jloc0);
-                        track(__uint_as_float(cur[jj + 1]), jj + 1, best2[1], second2[1], jloc1);
+                        const float u0 = fma_sat(__uint_as_float(cur[jj]), nbig, TB);
+                        const float u1 = fma_sat(__uint_as_float(cur[jj + 1]), nbig, TB);
+                        cnt0 += u0;
+                        cnt1 += u1;
+                        ix0 = fmaf(u0, (float)(cb + jj), ix0);
+                        ix1 = fmaf(u1, (float)(cb + jj + 1), ix1);
                     }
-                    bidx2[0] = best2[0] < before0 ? cb + jloc0 : bidx2[0];
-                    bidx2[1] = best2[1] < before1 ? cb + jloc1 : bidx2[1];
                 }
                 if (c + 1 < 8) tmem_ld_wait();
+            }
+            const float cnt = cnt0 + cnt1;
+            const bool near_tie = !(cnt == 1.0f);        // also catches a NaN score
+            int bi = (int)(ix0 + ix1);
+            if (__any_sync(0xffffffffu, near_tie)) {
+                // exact provisional label for the rows that need one: lowest column whose score equals the minimum
+                // (ArgKmin's strict `<`); the accumulator stage is still ours, so it is simply read again
+                int bx = 0;
+                tmem_ld32(tbase + 7u * 32u, ra);
+                tmem_ld_wait();
+#pragma unroll
+                for (int c = 0; c < 8; ++c) {
+                    uint32_t (&cur)[32] = (c & 1) ? rb : ra;
+                    uint32_t (&nxt)[32] = (c & 1) ? ra : rb;
+                    if (c + 1 < 8) tmem_ld32(tbase + (uint32_t)((7 - (c + 1)) * 32), nxt);
+                    const int cb = (7 - c) * 32;            // chunks from the top down: the last match is the lowest column
+                    if (cb < k) {
+#pragma unroll
+                        for (int jj = 31; jj >= 0; --jj) bx = (__uint_as_float(cur[jj]) == m) ? cb + jj : bx;
+                    }
+                    if (c + 1 < 8) tmem_ld_wait();
+                }
+                if (near_tie) bi = bx;
             }
             tc_fence_before();
             mbar_arrive(&bars->a_empty[g]);
             mbar_arrive(&bars->turn[g ^ 1]);
             if (q4 == 2) TC_TRACE(g, j, 5);
-            // an exact tie keeps the lower column; it is flagged anyway
-            const bool takeb = best2[1] < best2[0] || (best2[1] == best2[0] && bidx2[1] < bidx2[0]);
-            const int bi = takeb ? bidx2[1] : bidx2[0];
-            output(j, takeb ? best2[1] : best2[0], fminf(fminf(second2[0], second2[1]), takeb ? best2[0] : best2[1]),
-                   bi >= k ? k - 1 : bi);
+            bi = bi < 0 ? 0 : bi;
+            output(j, near_tie, bi >= k ? k - 1 : bi, m);
         }
     }
 
@@ -1730,7 +1806,8 @@ int km_launch_cand_tc_wide(const float *X, int64_t n, int d, int64_t ldx, const 
 
 // host-side launcher, called from b200km_assign_f32
 int km_launch_assign_tc(const float *X, int64_t n, int d, int64_t ldx, const void *pack, int k, int32_t *labels,
-                        float *mind2, int32_t *flag_rows, int32_t *flag_count, cudaStream_t st, bool precentred) {
+                        float *mind2, int32_t *flag_rows, int32_t *flag_count, cudaStream_t st, bool precentred,
+                        bool sparse_d2) {
     const KmPackLayout L = km_pack_layout(k, d);
     const unsigned char *pk = static_cast<const unsigned char *>(pack);
     const int kpad = km_tc_kpad(d);
@@ -1770,10 +1847,10 @@ int km_launch_assign_tc(const float *X, int64_t n, int d, int64_t ldx, const voi
         if (int rc = km_set_smem_once(assign_tc_small_kernel<false>, 227 * 1024, attr_s)) return rc;
         if (vec)
             assign_tc_small_kernel<true><<<grid, TC_THREADS, smem_s, st>>>(X, n, d, ldx, img, c32, mu, cmax, k, labels, mind2,
-                                                                          flag_rows, flag_count);
+                                                                          flag_rows, flag_count, sparse_d2 ? 1 : 0);
         else
             assign_tc_small_kernel<false><<<grid, TC_THREADS, smem_s, st>>>(X, n, d, ldx, img, c32, mu, cmax, k, labels, mind2,
-                                                                           flag_rows, flag_count);
+                                                                           flag_rows, flag_count, sparse_d2 ? 1 : 0);
         return (int)cudaGetLastError();
     }
     const size_t stage_bytes = pair ? 8192 : 16384;

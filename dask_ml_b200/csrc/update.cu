@@ -94,10 +94,13 @@ update_owner_kernel(const T *__restrict__ X, int64_t n, int d, int64_t ldx, cons
     if (mind2) km_block_atomic_add(inert, acc + (size_t)k * d + k, red);
 }
 
+// `cen` != nullptr (b200km_update_inertia_*): the inertia is summed HERE, in float64, as sum_i ||x_i - cen[label_i]||^2
+// from the rows this kernel reads anyway, instead of from a per-row distance vector written by K1.
 template <typename T>
 __global__ void __launch_bounds__(UP_THREADS)
 update_atomic_kernel(const T *__restrict__ X, int64_t n, int d, int64_t ldx, const int32_t *__restrict__ labels,
-                     const T *__restrict__ mind2, int k, double *__restrict__ acc, int scale_sqrt) {
+                     const T *__restrict__ mind2, int k, double *__restrict__ acc, int scale_sqrt,
+                     const double *__restrict__ cen) {
     __shared__ double red[32];
     const int lane = threadIdx.x & 31;
     const int64_t warp_global = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -119,7 +122,13 @@ update_atomic_kernel(const T *__restrict__ X, int64_t n, int d, int64_t ldx, con
             }
 #pragma unroll
             for (int u = 0; u < RU; ++u)
-                if (lab[u] >= 0 && f < d) atomicAdd(acc + (size_t)lab[u] * d + f, (double)v[u]);
+                if (lab[u] >= 0 && f < d) {
+                    atomicAdd(acc + (size_t)lab[u] * d + f, (double)v[u]);
+                    if (cen) {
+                        const double df = (double)v[u] - __ldg(cen + (size_t)lab[u] * d + f);
+                        inert = fma(df, df, inert);
+                    }
+                }
         }
         if (lane < RU && r0 + lane < n) {
             const int l = __ldg(labels + r0 + lane);
@@ -130,7 +139,7 @@ update_atomic_kernel(const T *__restrict__ X, int64_t n, int d, int64_t ldx, con
             }
         }
     }
-    if (mind2) km_block_atomic_add(inert, acc + (size_t)k * d + k, red);
+    if (mind2 || cen) km_block_atomic_add(inert, acc + (size_t)k * d + k, red);
 }
 
 
@@ -149,10 +158,13 @@ constexpr int SEG_MAX_K = 8192;
 
 // NARROW (d <= 32): a row is one 32-lane load, so the second feature half (fb, w[]) is compiled out and the
 // registers it frees buy a third resident CTA (C2: 2.39 -> 2.64 TB/s); wider rows do better with two (C3).
-template <typename T, bool NARROW>
+// INERTIA: the run's centre row (float64, `cen`) is held by the lanes and every row adds (x - c)^2 to a float64
+// lane accumulator -- two more DFMA-pipe instructions per row per lane, hidden under the row gathers.
+template <typename T, bool NARROW, bool INERTIA>
 __global__ void __launch_bounds__(SEG_THREADS, NARROW ? 3 : 2)
 update_seg_kernel(const T *__restrict__ X, int64_t n, int d, int64_t ldx, const int32_t *__restrict__ labels,
-                  const T *__restrict__ mind2, int k, double *__restrict__ acc, int scale_sqrt, int SEG_R) {
+                  const T *__restrict__ mind2, int k, double *__restrict__ acc, int scale_sqrt, int SEG_R,
+                  const double *__restrict__ cen) {
     extern __shared__ __align__(16) unsigned char seg_smem[];
     int *start = reinterpret_cast<int *>(seg_smem);              // [k+1] histogram, then exclusive starts
     int *cursor = start + (k + 1);                               // [k]
@@ -223,6 +235,11 @@ update_seg_kernel(const T *__restrict__ X, int64_t n, int d, int64_t ldx, const 
             for (int f0 = 0; f0 < d; f0 += 64) {
                 const int fa = f0 + lane, fb = NARROW ? d : f0 + 32 + lane;   // NARROW: fb >= d, dead code
                 double a0 = 0.0, a1 = 0.0;
+                double ca = 0.0, cb = 0.0, qa = 0.0, qb = 0.0;
+                if (INERTIA) {
+                    if (fa < d) ca = __ldg(cen + (size_t)c * d + fa);
+                    if (!NARROW && fb < d) cb = __ldg(cen + (size_t)c * d + fb);
+                }
                 int p = s0;
                 for (; p + 8 <= s1; p += 8) {   // 8 rows (16 loads per lane) in flight
                     T v[8], w[8];
@@ -237,6 +254,22 @@ update_seg_kernel(const T *__restrict__ X, int64_t n, int d, int64_t ldx, const 
                     if (!NARROW)
                         a1 += (((double)w[0] + (double)w[1]) + ((double)w[2] + (double)w[3])) +
                               (((double)w[4] + (double)w[5]) + ((double)w[6] + (double)w[7]));
+                    if (INERTIA) {
+                        double q0 = 0.0, q1 = 0.0;   // two chains; a lane beyond d holds v = 0 and c = 0: adds 0
+#pragma unroll
+                        for (int u = 0; u < 8; u += 2) {
+                            const double d0 = (double)v[u] - ca, d1 = (double)v[u + 1] - ca;
+                            q0 = fma(d0, d0, q0);
+                            q1 = fma(d1, d1, q1);
+                            if (!NARROW) {
+                                const double e0 = (double)w[u] - cb, e1 = (double)w[u + 1] - cb;
+                                q0 = fma(e0, e0, q0);
+                                q1 = fma(e1, e1, q1);
+                            }
+                        }
+                        qa += q0;
+                        qb += q1;
+                    }
                 }
                 for (; p + 4 <= s1; p += 4) {
                     const int r0 = order[p], r1 = order[p + 1], r2 = order[p + 2], r3 = order[p + 3];
@@ -251,12 +284,29 @@ update_seg_kernel(const T *__restrict__ X, int64_t n, int d, int64_t ldx, const 
                     }
                     a0 += ((double)v0 + (double)v1) + ((double)v2 + (double)v3);
                     if (!NARROW) a1 += ((double)w0 + (double)w1) + ((double)w2 + (double)w3);
+                    if (INERTIA && fa < d) {
+                        const double d0 = (double)v0 - ca, d1 = (double)v1 - ca, d2 = (double)v2 - ca, d3 = (double)v3 - ca;
+                        qa = fma(d0, d0, qa); qb = fma(d1, d1, qb); qa = fma(d2, d2, qa); qb = fma(d3, d3, qb);
+                    }
+                    if (INERTIA && !NARROW && fb < d) {
+                        const double e0 = (double)w0 - cb, e1 = (double)w1 - cb, e2 = (double)w2 - cb, e3 = (double)w3 - cb;
+                        qa = fma(e0, e0, qa); qb = fma(e1, e1, qb); qa = fma(e2, e2, qa); qb = fma(e3, e3, qb);
+                    }
                 }
                 for (; p < s1; ++p) {
                     const int r0 = order[p];
-                    if (fa < d) a0 += (double)__ldg(Xb + (int64_t)r0 * ldx + fa);
-                    if (!NARROW && fb < d) a1 += (double)__ldg(Xb + (int64_t)r0 * ldx + fb);
+                    if (fa < d) {
+                        const double x0 = (double)__ldg(Xb + (int64_t)r0 * ldx + fa);
+                        a0 += x0;
+                        if (INERTIA) { const double d0 = x0 - ca; qa = fma(d0, d0, qa); }
+                    }
+                    if (!NARROW && fb < d) {
+                        const double x1 = (double)__ldg(Xb + (int64_t)r0 * ldx + fb);
+                        a1 += x1;
+                        if (INERTIA) { const double e0 = x1 - cb; qb = fma(e0, e0, qb); }
+                    }
                 }
+                if (INERTIA) inert += qa + qb;
                 if (fa < d) atomicAdd(acc + (size_t)c * d + fa, a0);
                 if (!NARROW && fb < d) atomicAdd(acc + (size_t)c * d + fb, a1);
             }
@@ -282,7 +332,7 @@ update_seg_kernel(const T *__restrict__ X, int64_t n, int d, int64_t ldx, const 
         __syncthreads();
         if (tid == 0) nlong = 0;
     }
-    if (mind2) km_block_atomic_add(inert, acc + (size_t)k * d + k, red);
+    if (mind2 || INERTIA) km_block_atomic_add(inert, acc + (size_t)k * d + k, red);
 }
 
 extern "C" size_t b200km_acc_len(int k, int d) {
@@ -292,8 +342,9 @@ extern "C" size_t b200km_acc_len(int k, int d) {
 
 template <typename T>
 static int update_impl(const T *X, int64_t n, int d, int64_t ldx, const int32_t *labels, const T *mind2, int k,
-                       double *acc, int scale_sqrt, void *stream) {
+                       double *acc, int scale_sqrt, void *stream, const double *cen = nullptr) {
     KM_CHECK_ARG(X && labels && acc, B200KM_EINVAL);
+    KM_CHECK_ARG(!(cen && mind2), B200KM_EINVAL);
     KM_CHECK_ARG(n > 0 && d > 0 && k > 0 && ldx >= d, B200KM_EINVAL);
     KM_CHECK_ARG(k <= B200KM_MAX_K && d <= B200KM_MAX_D, B200KM_ETOOBIG);
     cudaStream_t st = km_stream(stream);
@@ -306,7 +357,7 @@ static int update_impl(const T *X, int64_t n, int d, int64_t ldx, const int32_t 
     // the sort)
     // (the shared-memory owner table, once the choice for tiny tables, loses 3-6x to the chunk-sort kernel on every
     //  shape measured -- and 14x with one dominant cluster -- so auto takes it only when the chunk sort cannot run)
-    const bool use_owner = variant == 1 ? owner_ok : (variant == 0 && owner_ok && !seg_ok && (size_t)k * d <= 2048);
+    const bool use_owner = !cen && (variant == 1 ? owner_ok : (variant == 0 && owner_ok && !seg_ok && (size_t)k * d <= 2048));
     const bool use_seg = !use_owner && seg_ok && (variant == 2 || (variant == 0 && k <= 2048));
     if (use_owner) {
         auto kern = update_owner_kernel<T>;
@@ -323,23 +374,34 @@ static int update_impl(const T *X, int64_t n, int d, int64_t ldx, const int32_t 
         if (SEG_R > SEG_R_MAX) SEG_R = SEG_R_MAX;
         while (SEG_R > 4096 && sizeof(int) * (size_t)(2 * k + 1) + sizeof(unsigned short) * (size_t)SEG_R + 16 > 200 * 1024) SEG_R /= 2;
         const size_t seg_smem = sizeof(int) * (size_t)(2 * k + 1) + sizeof(unsigned short) * (size_t)SEG_R + 16;
-        static bool attr_n[KM_MAX_DEVICES] = {}, attr_w[KM_MAX_DEVICES] = {};
-        if (int rc = km_set_smem_once(update_seg_kernel<T, true>, 200 * 1024, attr_n)) return rc;
-        if (int rc = km_set_smem_once(update_seg_kernel<T, false>, 200 * 1024, attr_w)) return rc;
+        static bool attr_n[KM_MAX_DEVICES] = {}, attr_w[KM_MAX_DEVICES] = {}, attr_ni[KM_MAX_DEVICES] = {},
+                    attr_wi[KM_MAX_DEVICES] = {};
+        if (int rc = km_set_smem_once(update_seg_kernel<T, true, false>, 200 * 1024, attr_n)) return rc;
+        if (int rc = km_set_smem_once(update_seg_kernel<T, false, false>, 200 * 1024, attr_w)) return rc;
+        if (int rc = km_set_smem_once(update_seg_kernel<T, true, true>, 200 * 1024, attr_ni)) return rc;
+        if (int rc = km_set_smem_once(update_seg_kernel<T, false, true>, 200 * 1024, attr_wi)) return rc;
         int64_t blocks = (n + SEG_R - 1) / SEG_R;
         const int64_t cap = (int64_t)km_num_sms() * 4;   // several CTAs per SM: one sorts while another gathers
         if (blocks > cap) blocks = cap;
-        if (d <= 32)
-            update_seg_kernel<T, true><<<(unsigned)blocks, SEG_THREADS, seg_smem, st>>>(X, n, d, ldx, labels, mind2, k, acc,
-                                                                                      scale_sqrt, SEG_R);
+        const unsigned gb = (unsigned)blocks;
+        if (d <= 32 && cen)
+            update_seg_kernel<T, true, true><<<gb, SEG_THREADS, seg_smem, st>>>(X, n, d, ldx, labels, mind2, k, acc,
+                                                                              scale_sqrt, SEG_R, cen);
+        else if (d <= 32)
+            update_seg_kernel<T, true, false><<<gb, SEG_THREADS, seg_smem, st>>>(X, n, d, ldx, labels, mind2, k, acc,
+                                                                               scale_sqrt, SEG_R, cen);
+        else if (cen)
+            update_seg_kernel<T, false, true><<<gb, SEG_THREADS, seg_smem, st>>>(X, n, d, ldx, labels, mind2, k, acc,
+                                                                               scale_sqrt, SEG_R, cen);
         else
-            update_seg_kernel<T, false><<<(unsigned)blocks, SEG_THREADS, seg_smem, st>>>(X, n, d, ldx, labels, mind2, k,
-                                                                                       acc, scale_sqrt, SEG_R);
+            update_seg_kernel<T, false, false><<<gb, SEG_THREADS, seg_smem, st>>>(X, n, d, ldx, labels, mind2, k, acc,
+                                                                                scale_sqrt, SEG_R, cen);
     } else {
         int64_t blocks = (n + 4 * UP_WARPS - 1) / (4 * UP_WARPS);
         const int64_t cap = (int64_t)km_num_sms() * 8;
         if (blocks > cap) blocks = cap;
-        update_atomic_kernel<T><<<(unsigned)blocks, UP_THREADS, 0, st>>>(X, n, d, ldx, labels, mind2, k, acc, scale_sqrt);
+        update_atomic_kernel<T><<<(unsigned)blocks, UP_THREADS, 0, st>>>(X, n, d, ldx, labels, mind2, k, acc, scale_sqrt,
+                                                                          cen);
     }
     KM_LAUNCH_RET();
 }
@@ -351,6 +413,16 @@ extern "C" int b200km_update_f32(const float *X, int64_t n, int d, int64_t ldx, 
 extern "C" int b200km_update_f64(const double *X, int64_t n, int d, int64_t ldx, const int32_t *labels,
                                  const double *mind2, int k, double *acc, int scale_sqrt, void *stream) {
     return update_impl<double>(X, n, d, ldx, labels, mind2, k, acc, scale_sqrt, stream);
+}
+extern "C" int b200km_update_inertia_f32(const float *X, int64_t n, int d, int64_t ldx, const int32_t *labels,
+                                         const double *centers_f64, int k, double *acc, void *stream) {
+    KM_CHECK_ARG(centers_f64, B200KM_EINVAL);
+    return update_impl<float>(X, n, d, ldx, labels, nullptr, k, acc, 0, stream, centers_f64);
+}
+extern "C" int b200km_update_inertia_f64(const double *X, int64_t n, int d, int64_t ldx, const int32_t *labels,
+                                         const double *centers_f64, int k, double *acc, void *stream) {
+    KM_CHECK_ARG(centers_f64, B200KM_EINVAL);
+    return update_impl<double>(X, n, d, ldx, labels, nullptr, k, acc, 0, stream, centers_f64);
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -97,6 +97,17 @@ int b200km_assign_f32(const float *X, int64_t n, int d, int64_t ldx, const void 
                       int reset_flags, void *stream);
 int b200km_assign_f64(const double *X, int64_t n, int d, int64_t ldx, const void *pack, int k,
                       int32_t *labels, double *mind2, void *stream);
+/* K1 for the Lloyd ITERATION (float32 X): labels and near-tie flags like b200km_assign_f32, but the per-row winner
+ * distance is not required of it.  `score` (n floats, caller-owned) is written AT LEAST for the flagged rows, with
+ * a value good enough for b200km_refine_pruned_f64's threshold (||x - mu||^2 + best score, expanded form); every
+ * other entry is unspecified (kernels that rebuild the exact distance anyway write it for all rows).  The inertia of
+ * the iteration then comes from b200km_update_inertia_* below, which sums ||x - c||^2 in float64 from the rows K2
+ * reads anyway.  For k <= 256, d <= 32 this removes the winner's centre-row gather and the re-read of the staged
+ * row from K1 -- 2/5 of the shared-memory traffic the small-k kernel was bound by.
+ * Replaces: the same call as b200km_assign_f32 inside the loop, R/dask_ml/cluster/k_means.py:576-579. */
+int b200km_assign_lloyd_f32(const float *X, int64_t n, int d, int64_t ldx, const void *pack, int k,
+                            int32_t *labels, float *score, int32_t *flag_rows, int32_t *flag_count,
+                            int reset_flags, void *stream);
 /* float64 X on the tensor cores (k > 16).  The reference's arithmetic is float64 for float64 input too, but the labels
  * only need it where the float32 decision is inside its own rounding bound:
  *   b200km_center_convert_f64   out[i] = fl32(x_i - mu)  (mu = the pack's centring vector; n x d floats, ld = d)
@@ -173,10 +184,17 @@ int b200km_assign_static_f32(const float *X, int64_t n, int d, int64_t ldx, cons
  * `scale_sqrt` != 0 adds sqrt(mind2) instead (the reference's non-squared inertia, :612-616).
  * ---------------------------------------------------------------------------------------- */
 size_t b200km_acc_len(int k, int d); /* number of doubles in acc */
+/* b200km_update_inertia_*: the same sums and counts, and acc's inertia slot += sum_i ||x_i - centers[labels[i]]||^2
+ * computed HERE in float64 from the rows and `centers_f64` (k x d, the centres the labels were decided against) --
+ * the squared-distance inertia of R/dask_ml/cluster/k_means.py:616 without a per-row distance vector. */
 int b200km_update_f32(const float *X, int64_t n, int d, int64_t ldx, const int32_t *labels,
                       const float *mind2, int k, double *acc, int scale_sqrt, void *stream);
 int b200km_update_f64(const double *X, int64_t n, int d, int64_t ldx, const int32_t *labels,
                       const double *mind2, int k, double *acc, int scale_sqrt, void *stream);
+int b200km_update_inertia_f32(const float *X, int64_t n, int d, int64_t ldx, const int32_t *labels,
+                              const double *centers_f64, int k, double *acc, void *stream);
+int b200km_update_inertia_f64(const double *X, int64_t n, int d, int64_t ldx, const int32_t *labels,
+                              const double *centers_f64, int k, double *acc, void *stream);
 
 /* K1+K2 fused into ONE pass over X for the HBM-bound regime: k <= 16 and d <= 32 (else B200KM_ETOOBIG).
  * labels / mind2 as K1 (float64 arithmetic, so no re-decision is needed), acc += as K2 (squared inertia).

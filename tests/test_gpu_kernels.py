@@ -173,6 +173,58 @@ def test_update_and_finalize(eng, n, d, k, dtype):
     npt.assert_allclose(shift.item(), ((C - ref_new) ** 2).sum(), rtol=1e-6)
 
 
+@pytest.mark.parametrize("n,d,k,dtype", [(6000, 32, 256, np.float32), (50000, 32, 200, np.float32),
+                                         (3000, 64, 1024, np.float32), (2047, 5, 3, np.float64),
+                                         (40000, 24, 40, np.float64), (33000, 130, 8192, np.float32),
+                                         (20000, 16, 64, np.float32), (300, 8, 100, np.float32)])
+def test_update_inertia(eng, n, d, k, dtype):
+    """b200km_update_inertia_*: the sums and counts of b200km_update_* and, in the inertia slot, the float64 sum of
+    ||x - c_label||^2 taken from the rows themselves (reference dask_ml/cluster/k_means.py:616 on the squared pass)."""
+    import torch
+
+    X, C = blobs(n, d, k, seed=k + 1, dtype=dtype)
+    labels = np.random.RandomState(0).randint(0, k, size=n).astype(np.int32)
+    if k > 100:
+        labels[: n // 2] = 7          # one dominant cluster: the long-run path of the chunk-sort kernel
+    C64 = (C + 1000.0).astype(np.float64) if d == 24 else C.astype(np.float64)   # data far from the centres too
+    Xd, ld, cd = eng.to_device(X), eng.to_device(labels), eng.to_device(C64, torch.float64)
+    acc = torch.zeros(eng.acc_len(k, d), dtype=torch.float64, device=eng.device)
+    eng.update_inertia(Xd, ld, cd, k, acc)
+    a = acc.cpu().numpy()
+    ref = eng.update(Xd, ld, None, k).cpu().numpy()
+    npt.assert_allclose(a[: k * d], ref[: k * d], rtol=1e-12, atol=1e-9 * np.abs(ref[: k * d]).max())
+    npt.assert_array_equal(a[k * d : k * d + k], np.bincount(labels, minlength=k))
+    want = ((X.astype(np.float64) - C64[labels]) ** 2).sum()
+    npt.assert_allclose(a[k * d + k], want, rtol=1e-12)
+
+
+@pytest.mark.parametrize("n,d,k", [(20000, 32, 256), (5001, 32, 200), (30000, 16, 64), (7000, 7, 33), (4000, 32, 17)])
+def test_assign_lloyd_labels_match_full_assign(eng, n, d, k):
+    """b200km_assign_lloyd_f32 (labels + near-tie flags only) gives the labels of b200km_assign_f32 after the
+    float64 re-decision -- with both the pruned and the full re-decision -- on separated blobs and on one
+    Gaussian cloud split between many centres (lots of near ties)."""
+    import torch
+
+    for seed, k_true in ((1, k), (2, 1)):
+        X, _ = blobs(n, d, k_true, seed=seed, dtype=np.float32)
+        C = X[:k].astype(np.float64) if k_true > 1 else np.random.RandomState(5).standard_normal((k, d))
+        Xd = eng.to_device(X)
+        pack = eng.pack(eng.to_device(C, torch.float64))
+        want, d2 = eng.assign(Xd, pack)
+        for pruned in (True, False):
+            eng.pruned_refine = pruned
+            try:
+                scratch = torch.full((n,), float("nan"), dtype=torch.float32, device=eng.device)
+                got, _ = eng.assign(Xd, pack, mind2=scratch, lloyd=True)
+            finally:
+                eng.pruned_refine = True
+            assert int((got != want).sum().item()) == 0
+        # and against the float64 oracle outside float64's own near ties
+        lab_o, d2_o = orc.pairwise_distances_argmin_min(X.astype(np.float64), C, metric_kwargs={"squared": True})
+        bad = want.cpu().numpy() != lab_o
+        assert bad.sum() <= _near_tie_mask(X, C).sum() and not (bad & ~_near_tie_mask(X, C)).any()
+
+
 @pytest.mark.parametrize("dtype", [np.float32, np.float64])
 @pytest.mark.parametrize("n,d", [(5000, 64), (3001, 3), (1000, 100), (64, 16), (2000, 33)])
 def test_mindist_and_cost(eng, n, d, dtype):
