@@ -760,6 +760,9 @@ extern "C" int b200km_debug_read_trace(long long *host, int max_events) {
 #define TC_TRACE(role, step, ev) do { } while (0)
 #endif
 
+#ifndef TC_SMALL_TOKEN_AT
+#define TC_SMALL_TOKEN_AT 6
+#endif
 struct TcSmallBars {
     uint64_t b_ready;
     uint64_t a_full[2];
@@ -1038,6 +1041,7 @@ assign_tc_small_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ld
             float m = INFINITY, TB = 0.f;
             float cnt0 = 0.f, cnt1 = 0.f, ix0 = 0.f, ix1 = 0.f;
             mbar_wait_bounded(&bars->a_full[g], (uint32_t)(j & 1));
+            if (q4 == 2) TC_TRACE(g, j, 2);
             // The groups track strictly in turn (0, 1, 0, 1, ...).  Left alone they fall into lockstep -- both
             // tracking at once on shared pipes, then both idle while their MMAs queue on the tensor core.
             if (g == 1) mbar_wait_bounded(&bars->turn[1], (uint32_t)(j & 1));
@@ -1052,6 +1056,10 @@ assign_tc_small_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ld
                 uint32_t (&cur)[32] = (c & 1) ? rb : ra;
                 uint32_t (&nxt)[32] = (c & 1) ? ra : rb;
                 if (c + 1 < 8) tmem_ld32(tbase + (uint32_t)((c + 1) * 32), nxt);  // flies under this chunk
+                // The step is paced by the TMEM reads (a warp's 32 x 32 floats take ~256 cycles), so the token goes
+                // to the other group as soon as this group's LAST read is queued: its first read then queues right
+                // behind instead of waiting for this group's arithmetic on the last chunks.
+                if (c == TC_SMALL_TOKEN_AT) mbar_arrive(&bars->turn[g ^ 1]);
                 const int cb = c * 32;
                 if (cb < k) {               // chunks made of padding columns only cannot win (warp-uniform)
                     // pass 1: the chunk's minimum
@@ -1090,7 +1098,8 @@ assign_tc_small_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ld
             const float cnt = cnt0 + cnt1;
             const bool near_tie = !(cnt == 1.0f);        // also catches a NaN score
             int bi = (int)(ix0 + ix1);
-            if (__any_sync(0xffffffffu, near_tie)) {
+            // (sparse_d2: the re-decision that follows looks at scores only, never at a flagged row's provisional label)
+            if (!sparse_d2 && __any_sync(0xffffffffu, near_tie)) {
                 // exact provisional label for the rows that need one: lowest column whose score equals the minimum
                 // (ArgKmin's strict `<`); the accumulator stage is still ours, so it is simply read again
                 int bx = 0;
@@ -1112,10 +1121,10 @@ assign_tc_small_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ld
             }
             tc_fence_before();
             mbar_arrive(&bars->a_empty[g]);
-            mbar_arrive(&bars->turn[g ^ 1]);
             if (q4 == 2) TC_TRACE(g, j, 5);
             bi = bi < 0 ? 0 : bi;
             output(j, near_tie, bi >= k ? k - 1 : bi, m);
+            if (q4 == 2) TC_TRACE(g, j, 6);
         }
     }
 

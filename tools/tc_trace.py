@@ -10,13 +10,15 @@ C = (torch.rand(k, d, generator=g, dtype=torch.float64) * 20 - 10)
 X = eng.make_blobs(n, d, C.float(), 1.0, seed=1)
 pack = eng.pack(X[:k].double().contiguous())
 lab, m2 = eng.assign(X, pack)
+kw = {"lloyd": True} if (len(sys.argv) > 5 and sys.argv[5] == "1") else {}
 for _ in range(3):
-    eng.assign(X, pack, lab, m2)
+    eng.assign(X, pack, lab, m2, **kw)
 torch.cuda.synchronize()
 buf = (ctypes.c_longlong * (4 * 256 * 8))()
 raw = ctypes.CDLL(lib._name)
 raw.b200km_debug_read_trace(buf, 0)
-names = {0: "mma issue", 1: "iter start", 3: "stage+issue done", 4: "a_full+turn seen", 5: "track done"}
+names = {0: "mma issue", 1: "iter start", 3: "stage+issue done", 2: "a_full seen", 4: "turn seen", 5: "track done",
+         6: "output done"}
 ev = []
 for role in range(4):
     for step in range(256):
