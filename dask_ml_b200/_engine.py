@@ -96,6 +96,7 @@ class CudaEngine:
             t = t.to(dtype)
         return t.to(self.device, non_blocking=True).contiguous()
 
+    FLAG_SCRATCH = 4              # flag buffer = this many int32 per row: room for long candidate lists (pruned re-decision)
     F64_BLOCK_BYTES = 1 << 30     # float32 scratch of the float64-on-tensor-cores path (rows per block = this / 4d)
     STREAM_MIN_BYTES = 64 << 20   # host inputs at least this big are uploaded in overlapped row chunks
     STREAM_CHUNKS = 8
@@ -204,7 +205,8 @@ class CudaEngine:
             mp = (mind2[r0 : r0 + nn].data_ptr() if mptr is not None else None)
             if sfx == "f32":
                 if refine:
-                    flags = self._buf("flag_rows", (nn,), torch.int32)
+                    flen = nn * self.FLAG_SCRATCH if (mptr is not None and self.pruned_refine) else nn
+                    flags = self._buf("flag_rows", (flen,), torch.int32)
                     fcnt = self._buf("flag_count", (1,), torch.int32)
                     if self.k1_events is not None:
                         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -217,10 +219,12 @@ class CudaEngine:
                         self.k1_events.append((e0, e1))
                     # float64 re-decision of the flagged rows; with the winner distances at hand the tensor cores
                     # first list each row's possible winners (4 launches, 2 of them gated off on the device)
-                    fn = "b200km_refine_pruned_f64" if (mp is not None and self.pruned_refine) else "b200km_refine_f64"
-                    self._call(fn, xs.data_ptr(), nn, d, ldx, pack.buf.data_ptr(), pack.k,
-                               flags.data_ptr(), fcnt.data_ptr(), ls.data_ptr(), mp, st,
-                               launches=4 if fn.endswith("pruned_f64") else 1)
+                    if mp is not None and self.pruned_refine:
+                        self._call("b200km_refine_pruned_len_f64", xs.data_ptr(), nn, d, ldx, pack.buf.data_ptr(), pack.k,
+                                   flags.data_ptr(), flen, fcnt.data_ptr(), ls.data_ptr(), mp, st, launches=4)
+                    else:
+                        self._call("b200km_refine_f64", xs.data_ptr(), nn, d, ldx, pack.buf.data_ptr(), pack.k,
+                                   flags.data_ptr(), fcnt.data_ptr(), ls.data_ptr(), mp, st, launches=1)
                 else:
                     self._call("b200km_assign_f32", xs.data_ptr(), nn, d, ldx, pack.buf.data_ptr(), pack.k,
                                ls.data_ptr(), mp, None, None, 0, st, launches=1)
@@ -232,7 +236,8 @@ class CudaEngine:
                     e0.record()
                 blk = max(1, min(nn, self.F64_BLOCK_BYTES // (4 * d)))
                 xc = self._buf("x_centred", (blk, d), torch.float32)
-                flags = self._buf("flag_rows", (blk,), torch.int32)
+                flen = blk * self.FLAG_SCRATCH if (refine and self.pruned_refine) else blk
+                flags = self._buf("flag_rows", (flen,), torch.int32)
                 fcnt = self._buf("flag_count", (1,), torch.int32)
                 for b0 in range(0, nn, blk):
                     bn = min(blk, nn - b0)
@@ -244,8 +249,8 @@ class CudaEngine:
                                lb.data_ptr(), d32.data_ptr() if d32 is not None else None, flags.data_ptr(),
                                fcnt.data_ptr(), 1, st, launches=1)
                     if refine and d32 is not None:
-                        self._call("b200km_refine_pruned_x64_f64", xb.data_ptr(), bn, d, ldx, xc.data_ptr(),
-                                   d32.data_ptr(), pack.buf.data_ptr(), pack.k, flags.data_ptr(), fcnt.data_ptr(),
+                        self._call("b200km_refine_pruned_x64_len_f64", xb.data_ptr(), bn, d, ldx, xc.data_ptr(),
+                                   d32.data_ptr(), pack.buf.data_ptr(), pack.k, flags.data_ptr(), flen, fcnt.data_ptr(),
                                    lb.data_ptr(), None, st, launches=4)
                     elif refine:
                         self._call("b200km_refine_x64_f64", xb.data_ptr(), bn, d, ldx, pack.buf.data_ptr(), pack.k,
@@ -303,6 +308,14 @@ class CudaEngine:
             self._call(f"b200km_update_inertia_{sfx}", X[r0 : r0 + nn].data_ptr(), nn, d, ldx,
                        labels[r0 : r0 + nn].data_ptr(), centers64.data_ptr(), k, acc.data_ptr(), st)
         return acc
+
+    def label_counts(self, labels: torch.Tensor, k: int, counts: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """counts (float64, k) += histogram of ``labels`` (b200km_label_counts)."""
+        if counts is None:
+            counts = torch.zeros(k, dtype=torch.float64, device=self.device)
+        if labels.numel():
+            self._call("b200km_label_counts", labels.data_ptr(), labels.numel(), k, counts.data_ptr(), self._stream())
+        return counts
 
     FUSED_MAX_K, FUSED_MAX_D = 16, 32
 

@@ -50,7 +50,10 @@ PROTOTYPES = {
     "b200km_rowdist_f64": (c_int, [_P, c_int64, c_int, c_int64, _P, c_int, _P, _P, _P]),
     "b200km_refine_pruned_x64_f64": (c_int, [_P, c_int64, c_int, c_int64, _P, _P, _P, c_int, _P, _P, _P, _P, _P]),
     "b200km_refine_pruned_f64": (c_int, [_P, c_int64, c_int, c_int64, _P, c_int, _P, _P, _P, _P, _P]),
+    "b200km_refine_pruned_len_f64": (c_int, [_P, c_int64, c_int, c_int64, _P, c_int, _P, c_int64, _P, _P, _P, _P]),
+    "b200km_refine_pruned_x64_len_f64": (c_int, [_P, c_int64, c_int, c_int64, _P, _P, _P, c_int, _P, c_int64, _P, _P, _P, _P]),
     "b200km_assign_static_f32": (c_int, [_P, c_int64, c_int, c_int64, _P, c_int, _P, _P, _P]),
+    "b200km_label_counts": (c_int, [_P, c_int64, c_int, _P, _P]),
     "b200km_acc_len": (c_size_t, [c_int, c_int]),
     "b200km_update_f32": (c_int, [_P, c_int64, c_int, c_int64, _P, _P, c_int, _P, c_int, _P]),
     "b200km_update_f64": (c_int, [_P, c_int64, c_int, c_int64, _P, _P, c_int, _P, c_int, _P]),

@@ -814,33 +814,34 @@ extern "C" int b200km_refine_x64_f64(const double *X, int64_t n, int d, int64_t 
 // =============================================================================================
 // pruned float64 re-decision: only the centres the candidate kernel listed
 // =============================================================================================
-constexpr int KM_CAND_CAP = 6;   // == TC_CAND_CAP (assign_tc.cu)
 int km_launch_cand_tc(const float *X, int64_t n, int d, int64_t ldx, const void *pack, int k, int32_t *flag_rows,
-                      const int32_t *flag_count, const float *mind2, cudaStream_t st, bool precentred);
+                      int64_t flen, const int32_t *flag_count, const float *mind2, cudaStream_t st, bool precentred);
 int km_launch_cand_tc_wide(const float *X, int64_t n, int d, int64_t ldx, const void *pack, int k,
-                           int32_t *flag_rows, const int32_t *flag_count, float *mind2, cudaStream_t st, bool precentred);
+                           int32_t *flag_rows, int64_t flen, const int32_t *flag_count, float *mind2, cudaStream_t st,
+                           bool precentred);
 
 // One thread per flagged row: the listed columns are scored exactly as assign_rb_kernel<INDIRECT> scores them
 // (cn64 - 2 * sum_f x_f c_f, one DFMA per term in feature order, strict < then lowest index), so the two paths
-// give the same labels bit for bit.  A row with more than KM_CAND_CAP listed columns (duplicate centres, e.g.
+// give the same labels bit for bit.  A row with more listed columns than its list holds (km_cand_cap; duplicate centres, e.g.
 // several empty clusters parked at the origin) goes to the overflow list and gets the full scan.
 template <typename TX>
 __global__ void __launch_bounds__(128)
 refine_cand_kernel(const TX *__restrict__ X, int64_t n, int d, int64_t ldx, const double *__restrict__ c64,
-                   const double *__restrict__ cn64, int32_t *__restrict__ F, const int32_t *__restrict__ flag_count,
-                   int32_t *__restrict__ labels, TX *__restrict__ mind2) {
-    const int64_t M = (n - 1) / (KM_CAND_CAP + 3);
+                   const double *__restrict__ cn64, int32_t *__restrict__ F, int64_t flen,
+                   const int32_t *__restrict__ flag_count, int32_t *__restrict__ labels, TX *__restrict__ mind2) {
+    const int64_t M = km_cand_rows_max(flen);
     const int64_t cnt = (int64_t)(*flag_count);
     if (cnt > M) return;
+    const int cap = km_cand_cap(flen, cnt);
     const int32_t *cand = F + M;
-    int32_t *ovf = F + M * (KM_CAND_CAP + 2);
+    int32_t *ovf = F + (flen - 1 - M);
     for (int64_t pos = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; pos < cnt;
          pos += (int64_t)gridDim.x * blockDim.x) {
         const int64_t row = (int64_t)F[pos];
-        const int32_t *cl = cand + pos * (KM_CAND_CAP + 1);
+        const int32_t *cl = cand + pos * (cap + 1);
         const int nc = cl[0];
-        if (nc > KM_CAND_CAP || nc <= 0) {   // (0 cannot happen: the winner itself is always within the threshold)
-            const int q = atomicAdd(F + (n - 1), 1);
+        if (nc > cap || nc <= 0) {   // (0 cannot happen: the winner itself is always within the threshold)
+            const int q = atomicAdd(F + (flen - 1), 1);
             ovf[q] = (int32_t)row;
             continue;
         }
@@ -872,53 +873,66 @@ refine_cand_kernel(const TX *__restrict__ X, int64_t n, int d, int64_t ldx, cons
 // for float32 input the same rows and K1's mind2, for float64 input the centred float32 block and its distances.
 template <typename TX>
 static int refine_pruned_impl(const TX *X, int64_t n, int d, int64_t ldx, const float *Xc, int64_t ldxc, bool precentred,
-                              float *dist32, const void *pack, int k, int32_t *flag_rows, const int32_t *flag_count,
-                              int32_t *labels, TX *mind2, cudaStream_t st) {
+                              float *dist32, const void *pack, int k, int32_t *flag_rows, int64_t flen,
+                              const int32_t *flag_count, int32_t *labels, TX *mind2, cudaStream_t st) {
     const KmPackLayout L = km_pack_layout(k, d);
     const double *c64 = reinterpret_cast<const double *>(static_cast<const unsigned char *>(pack) + L.off_c64);
     const double *cn64 = reinterpret_cast<const double *>(static_cast<const unsigned char *>(pack) + L.off_cn64);
-    const int64_t M = (n - 1) / (KM_CAND_CAP + 3);
+    const int64_t M = km_cand_rows_max(flen);
     // more flagged rows than the scratch layout holds: the full scan, gated on the device-side count
     int rc = launch_rb<TX, 32, 8, 8, true>(X, n, d, ldx, c64, cn64, k, flag_rows, flag_count, labels, mind2, st,
                                            flag_count, M, 0);
     if (rc) return rc;
     rc = d <= KM_TC_MAX_D
-             ? km_launch_cand_tc(Xc, n, d, ldxc, pack, k, flag_rows, flag_count, dist32, st, precentred)
-             : km_launch_cand_tc_wide(Xc, n, d, ldxc, pack, k, flag_rows, flag_count, dist32, st, precentred);
+             ? km_launch_cand_tc(Xc, n, d, ldxc, pack, k, flag_rows, flen, flag_count, dist32, st, precentred)
+             : km_launch_cand_tc_wide(Xc, n, d, ldxc, pack, k, flag_rows, flen, flag_count, dist32, st, precentred);
     if (rc) return rc;
-    refine_cand_kernel<TX><<<km_num_sms() * 4, 128, 0, st>>>(X, n, d, ldx, c64, cn64, flag_rows, flag_count, labels, mind2);
+    refine_cand_kernel<TX><<<km_num_sms() * 4, 128, 0, st>>>(X, n, d, ldx, c64, cn64, flag_rows, flen, flag_count, labels,
+                                                             mind2);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return (int)e;
     // rows with too many candidates: the full scan over the overflow list (its size is flag_rows[n-1])
-    return launch_rb<TX, 32, 8, 8, true>(X, n, d, ldx, c64, cn64, k, flag_rows + M * (KM_CAND_CAP + 2),
-                                         flag_rows + (n - 1), labels, mind2, st, flag_count, M, 1);
+    return launch_rb<TX, 32, 8, 8, true>(X, n, d, ldx, c64, cn64, k, flag_rows + (flen - 1 - M),
+                                         flag_rows + (flen - 1), labels, mind2, st, flag_count, M, 1);
 }
 
-extern "C" int b200km_refine_pruned_f64(const float *X, int64_t n, int d, int64_t ldx, const void *pack, int k,
-                                        int32_t *flag_rows, const int32_t *flag_count, int32_t *labels,
-                                        float *mind2, void *stream) {
+extern "C" int b200km_refine_pruned_len_f64(const float *X, int64_t n, int d, int64_t ldx, const void *pack, int k,
+                                            int32_t *flag_rows, int64_t flag_len, const int32_t *flag_count,
+                                            int32_t *labels, float *mind2, void *stream) {
     int rc = check_pack_args(X, n, d, ldx, pack, k, labels);
     if (rc) return rc;
-    KM_CHECK_ARG(flag_rows && flag_count, B200KM_EINVAL);
+    KM_CHECK_ARG(flag_rows && flag_count && flag_len >= n, B200KM_EINVAL);
     // the candidate pass needs the tensor-core image (one-CTA layout) and the winner distances
     if (d > KM_TC_WIDE_MAX_D || km_tc_pair_mode() || !mind2 || n < 4096)
         return b200km_refine_f64(X, n, d, ldx, pack, k, flag_rows, flag_count, labels, mind2, stream);
-    return refine_pruned_impl<float>(X, n, d, ldx, X, ldx, false, mind2, pack, k, flag_rows, flag_count, labels, mind2,
-                                     km_stream(stream));
+    return refine_pruned_impl<float>(X, n, d, ldx, X, ldx, false, mind2, pack, k, flag_rows, flag_len, flag_count, labels,
+                                     mind2, km_stream(stream));
+}
+extern "C" int b200km_refine_pruned_f64(const float *X, int64_t n, int d, int64_t ldx, const void *pack, int k,
+                                        int32_t *flag_rows, const int32_t *flag_count, int32_t *labels,
+                                        float *mind2, void *stream) {
+    return b200km_refine_pruned_len_f64(X, n, d, ldx, pack, k, flag_rows, n, flag_count, labels, mind2, stream);
 }
 
 // the same for float64 rows: Xc = the centred float32 block b200km_center_convert_f64 wrote (ld = d), dist32 = the
 // distances b200km_assign_centred_f32 wrote for it; mind2 (float64, nullable) is updated for the re-decided rows
+extern "C" int b200km_refine_pruned_x64_len_f64(const double *X, int64_t n, int d, int64_t ldx, const float *Xc,
+                                                float *dist32, const void *pack, int k, int32_t *flag_rows,
+                                                int64_t flag_len, const int32_t *flag_count, int32_t *labels,
+                                                double *mind2, void *stream) {
+    int rc = check_pack_args(X, n, d, ldx, pack, k, labels);
+    if (rc) return rc;
+    KM_CHECK_ARG(flag_rows && flag_count && flag_len >= n, B200KM_EINVAL);
+    if (d > KM_TC_WIDE_MAX_D || km_tc_pair_mode() || !Xc || !dist32 || n < 4096)
+        return b200km_refine_x64_f64(X, n, d, ldx, pack, k, flag_rows, flag_count, labels, mind2, stream);
+    return refine_pruned_impl<double>(X, n, d, ldx, Xc, d, true, dist32, pack, k, flag_rows, flag_len, flag_count, labels,
+                                      mind2, km_stream(stream));
+}
 extern "C" int b200km_refine_pruned_x64_f64(const double *X, int64_t n, int d, int64_t ldx, const float *Xc,
                                             float *dist32, const void *pack, int k, int32_t *flag_rows,
                                             const int32_t *flag_count, int32_t *labels, double *mind2, void *stream) {
-    int rc = check_pack_args(X, n, d, ldx, pack, k, labels);
-    if (rc) return rc;
-    KM_CHECK_ARG(flag_rows && flag_count, B200KM_EINVAL);
-    if (d > KM_TC_WIDE_MAX_D || km_tc_pair_mode() || !Xc || !dist32 || n < 4096)
-        return b200km_refine_x64_f64(X, n, d, ldx, pack, k, flag_rows, flag_count, labels, mind2, stream);
-    return refine_pruned_impl<double>(X, n, d, ldx, Xc, d, true, dist32, pack, k, flag_rows, flag_count, labels, mind2,
-                                      km_stream(stream));
+    return b200km_refine_pruned_x64_len_f64(X, n, d, ldx, Xc, dist32, pack, k, flag_rows, n, flag_count, labels, mind2,
+                                            stream);
 }
 
 // =============================================================================================

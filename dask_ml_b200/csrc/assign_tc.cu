@@ -1148,7 +1148,7 @@ assign_tc_small_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ld
 // Scratch: the unused tail of flag_rows (n entries, *flag_count used), laid out by capacity M = (n-1) / (CAP + 3):
 //   [0, M) row indices | [M, M + M*(CAP+1)) per flagged row: count, CAP columns | then the overflow list | [n-1] its size
 // Runs only when *flag_count <= M; otherwise the full re-decision kernel does the work.
-constexpr int TC_CAND_CAP = 6;
+// (capacity of a row's list: km_cand_cap in common.cuh)
 
 struct TcCandBars {
     uint64_t b_full[5];
@@ -1163,20 +1163,21 @@ struct TcCandBars {
     alignas(16) float mu[KM_TC_MAX_D];
     float xn_part[2][128];
     int ccnt[128];
-    int clist[128][TC_CAND_CAP];
 };
 
 template <bool VEC>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 cand_tc_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx, const unsigned char *__restrict__ tc_img,
                const float *__restrict__ mu, const unsigned int *__restrict__ cmax_bits, int k,
-               int32_t *__restrict__ F, const int32_t *__restrict__ flag_count, const float *__restrict__ mind2) {
+               int32_t *__restrict__ F, int64_t flen, const int32_t *__restrict__ flag_count,
+               const float *__restrict__ mind2) {
     extern __shared__ __align__(1024) unsigned char tc_smem[];
-    const int64_t M = (n - 1) / (TC_CAND_CAP + 3);
+    const int64_t M = km_cand_rows_max(flen);
     const int64_t cnt = (int64_t)(*flag_count);
     if (cnt > M) return;                                   // uniform: the full re-decision handles this call
-    if (blockIdx.x == 0 && threadIdx.x == 0) F[n - 1] = 0; // size of the overflow list
+    if (blockIdx.x == 0 && threadIdx.x == 0) F[flen - 1] = 0; // size of the overflow list
     if (cnt <= 0) return;
+    const int cap = km_cand_cap(flen, cnt);
     const int kpad = km_tc_kpad(d);
     const int nch = kpad / 4;
     const int nks = kpad / 8;
@@ -1342,9 +1343,9 @@ cand_tc_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx, const
                     const int cb = t * KM_TC_BN + g * 128 + c * 32;
 #pragma unroll
                     for (int j = 0; j < 32; ++j) {
-                        if (__uint_as_float(r[j]) <= T && cb + j < k) {
+                        if (__uint_as_float(r[j]) <= T && cb + j < k) {     // (T = -inf for a row that is not live)
                             const int q = atomicAdd(&bars->ccnt[rl], 1);
-                            if (q < TC_CAND_CAP) bars->clist[rl][q] = cb + j;
+                            if (q < cap) cand[pos * (cap + 1) + 1 + q] = cb + j;
                         }
                     }
                 }
@@ -1353,12 +1354,7 @@ cand_tc_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx, const
             }
             mbar_arrive(&bars->l_done);
             mbar_wait_bounded(&bars->l_done, li & 1);
-            if (g == 0 && live) {
-                int32_t *out = cand + pos * (TC_CAND_CAP + 1);
-                const int c = bars->ccnt[rl];
-                out[0] = c;
-                for (int q = 0; q < TC_CAND_CAP; ++q) out[1 + q] = q < c ? bars->clist[rl][q] : 0;
-            }
+            if (g == 0 && live) cand[pos * (cap + 1)] = bars->ccnt[rl];
         }
     }
 
@@ -1371,7 +1367,7 @@ cand_tc_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx, const
 }
 
 int km_launch_cand_tc(const float *X, int64_t n, int d, int64_t ldx, const void *pack, int k, int32_t *flag_rows,
-                      const int32_t *flag_count, const float *mind2, cudaStream_t st, bool precentred) {
+                      int64_t flen, const int32_t *flag_count, const float *mind2, cudaStream_t st, bool precentred) {
     const KmPackLayout L = km_pack_layout(k, d);
     const unsigned char *pk = static_cast<const unsigned char *>(pack);
     const int nch = km_tc_kpad(d) / 4;
@@ -1385,9 +1381,9 @@ int km_launch_cand_tc(const float *X, int64_t n, int d, int64_t ldx, const void 
     if (int rc = km_set_smem_once(cand_tc_kernel<true>, 227 * 1024, attr_v)) return rc;
     if (int rc = km_set_smem_once(cand_tc_kernel<false>, 227 * 1024, attr_s)) return rc;
     if (vec)
-        cand_tc_kernel<true><<<km_num_sms(), TC_THREADS, smem, st>>>(X, n, d, ldx, img, mu, cmax, k, flag_rows, flag_count, mind2);
+        cand_tc_kernel<true><<<km_num_sms(), TC_THREADS, smem, st>>>(X, n, d, ldx, img, mu, cmax, k, flag_rows, flen, flag_count, mind2);
     else
-        cand_tc_kernel<false><<<km_num_sms(), TC_THREADS, smem, st>>>(X, n, d, ldx, img, mu, cmax, k, flag_rows, flag_count, mind2);
+        cand_tc_kernel<false><<<km_num_sms(), TC_THREADS, smem, st>>>(X, n, d, ldx, img, mu, cmax, k, flag_rows, flen, flag_count, mind2);
     return (int)cudaGetLastError();
 }
 
@@ -1413,17 +1409,19 @@ assign_tc_wide_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx
                       const unsigned char *__restrict__ tc_img, const float *__restrict__ c32,
                       const float *__restrict__ mu, const unsigned int *__restrict__ cmax_bits, int k,
                       int32_t *__restrict__ labels, float *__restrict__ mind2,
-                      int32_t *__restrict__ flag_rows, int32_t *__restrict__ flag_count) {
+                      int32_t *__restrict__ flag_rows, int32_t *__restrict__ flag_count, int64_t flen) {
     extern __shared__ __align__(1024) unsigned char tc_smem[];
     int64_t nrows = n;                                          // rows (or flagged rows) to process
     int64_t cand_M = 0;
+    int cand_cap = 0;
     if (CAND) {
-        cand_M = (n - 1) / (TC_CAND_CAP + 3);
+        cand_M = km_cand_rows_max(flen);
         const int64_t cnt = (int64_t)(*flag_count);
         if (cnt > cand_M) return;                               // uniform: the full re-decision handles this call
-        if (blockIdx.x == 0 && threadIdx.x == 0) flag_rows[n - 1] = 0;   // size of the overflow list
+        if (blockIdx.x == 0 && threadIdx.x == 0) flag_rows[flen - 1] = 0;   // size of the overflow list
         if (cnt <= 0) return;
         nrows = cnt;
+        cand_cap = km_cand_cap(flen, cnt);
     }
     const int kpad = km_tc_kpad(d);
     const int nks = kpad / 8;                                   // K-steps of a whole row
@@ -1565,8 +1563,7 @@ assign_tc_wide_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx
                 row4[q] = pos < nrows ? (CAND ? (int64_t)__ldg(flag_rows + pos) : pos) : -1;
             }
             float cand_T = -INFINITY;
-            int *ccnt = reinterpret_cast<int *>(&bars->m_best[0][0][0]);      // CAND: per-row list length ...
-            int *clist = reinterpret_cast<int *>(&bars->m_second[0][0][0]);   // ... and columns (over m_second, m_idx)
+            int *ccnt = reinterpret_cast<int *>(&bars->m_best[0][0][0]);      // CAND: per-row list length
             float best2[2] = {INFINITY, INFINITY}, second2[2] = {INFINITY, INFINITY};
             int bidx2[2] = {0, 0};
             float xn4[4] = {0.f, 0.f, 0.f, 0.f};
@@ -1587,9 +1584,9 @@ assign_tc_wide_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx
                     if (CAND) {
 #pragma unroll
                         for (int j = 0; j < 32; ++j) {
-                            if (__uint_as_float(cur[j]) <= cand_T && cb + j < k) {
+                            if (__uint_as_float(cur[j]) <= cand_T && cb + j < k) {   // (cand_T = -inf: row not live)
                                 const int q = atomicAdd(&ccnt[rl], 1);
-                                if (q < TC_CAND_CAP) clist[rl * TC_CAND_CAP + q] = cb + j;
+                                if (q < cand_cap) flag_rows[cand_M + pos_t * (cand_cap + 1) + 1 + q] = cb + j;
                             }
                         }
                     } else if (cb < k) {
@@ -1692,12 +1689,7 @@ assign_tc_wide_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx
             if (CAND) {
                 mbar_arrive(&bars->m_ready[0]);                 // both column halves have finished listing
                 mbar_wait_bounded(&bars->m_ready[0], li & 1);
-                if (g == 0 && live_t) {
-                    int32_t *out = flag_rows + cand_M + pos_t * (TC_CAND_CAP + 1);
-                    const int c = ccnt[rl];
-                    out[0] = c;
-                    for (int q = 0; q < TC_CAND_CAP; ++q) out[1 + q] = q < c ? clist[rl * TC_CAND_CAP + q] : 0;
-                }
+                if (g == 0 && live_t) flag_rows[cand_M + pos_t * (cand_cap + 1)] = ccnt[rl];
             } else {
             // ---- merge the two column halves; every thread ends up with its row's winner -------------------
             float xn_half;
@@ -1791,7 +1783,8 @@ assign_tc_wide_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx
 }
 
 int km_launch_cand_tc_wide(const float *X, int64_t n, int d, int64_t ldx, const void *pack, int k,
-                           int32_t *flag_rows, const int32_t *flag_count, float *mind2, cudaStream_t st, bool precentred) {
+                           int32_t *flag_rows, int64_t flen, const int32_t *flag_count, float *mind2, cudaStream_t st,
+                           bool precentred) {
     const KmPackLayout L = km_pack_layout(k, d);
     const unsigned char *pk = static_cast<const unsigned char *>(pack);
     const size_t xbuf_w = (size_t)(TCW_PCH + 2) * 128 * 16 + (size_t)TCW_PCH * 128 * 16;
@@ -1806,10 +1799,10 @@ int km_launch_cand_tc_wide(const float *X, int64_t n, int d, int64_t ldx, const 
     if (int rc = km_set_smem_once(assign_tc_wide_kernel<false, true>, 227 * 1024, attr_s)) return rc;
     if (vec)
         assign_tc_wide_kernel<true, true><<<km_num_sms(), TC_THREADS, smem_w, st>>>(
-            X, n, d, ldx, img, c32, mu, cmax, k, nullptr, mind2, flag_rows, const_cast<int32_t *>(flag_count));
+            X, n, d, ldx, img, c32, mu, cmax, k, nullptr, mind2, flag_rows, const_cast<int32_t *>(flag_count), flen);
     else
         assign_tc_wide_kernel<false, true><<<km_num_sms(), TC_THREADS, smem_w, st>>>(
-            X, n, d, ldx, img, c32, mu, cmax, k, nullptr, mind2, flag_rows, const_cast<int32_t *>(flag_count));
+            X, n, d, ldx, img, c32, mu, cmax, k, nullptr, mind2, flag_rows, const_cast<int32_t *>(flag_count), flen);
     return (int)cudaGetLastError();
 }
 
@@ -1839,10 +1832,10 @@ int km_launch_assign_tc(const float *X, int64_t n, int d, int64_t ldx, const voi
         if (int rc = km_set_smem_once(assign_tc_wide_kernel<false, false>, 227 * 1024, attr_s)) return rc;
         if (vec)
             assign_tc_wide_kernel<true, false><<<grid, TC_THREADS, smem_w, st>>>(X, n, d, ldx, img, c32, mu, cmax, k, labels, mind2,
-                                                                         flag_rows, flag_count);
+                                                                         flag_rows, flag_count, 0);
         else
             assign_tc_wide_kernel<false, false><<<grid, TC_THREADS, smem_w, st>>>(X, n, d, ldx, img, c32, mu, cmax, k, labels, mind2,
-                                                                          flag_rows, flag_count);
+                                                                          flag_rows, flag_count, 0);
         return (int)cudaGetLastError();
     }
     if (!pair && k <= KM_TC_BN && d <= 32 && km_tc_small_enabled()) {

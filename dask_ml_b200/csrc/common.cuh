@@ -72,6 +72,24 @@ __host__ __device__ inline size_t km_tc_tile_bytes(int d) {
     return (size_t)KM_TC_AUG_BYTES + (size_t)(km_tc_kpad(d) / 8) * KM_TC_KS_BYTES;
 }
 
+// ---------------------------------------------------------------------------------------------
+// Scratch layout of the pruned float64 re-decision inside the flag buffer F (L int32 entries, L >= n):
+//   [0, M)               rows K1 flagged (cnt of them), M = (L - 1) / 9 = the most the pruned path takes
+//   [M, L - 1 - M)       per flagged row: number of listed columns, then `cap` columns
+//   [L - 1 - M, L - 1)   rows with more than `cap` listed columns (they get the full scan)
+//   [L - 1]              size of that overflow list
+// `cap` is decided on the device from cnt: whatever the list area allows, up to KM_CAND_CAP_MAX -- at least
+// KM_CAND_CAP_MIN (cnt = M), all 32 when few rows are flagged or the caller hands over a buffer longer than n.
+// ---------------------------------------------------------------------------------------------
+constexpr int KM_CAND_CAP_MIN = 6;
+constexpr int KM_CAND_CAP_MAX = 32;
+__host__ __device__ inline int64_t km_cand_rows_max(int64_t L) { return (L - 1) / (KM_CAND_CAP_MIN + 3); }
+__host__ __device__ inline int km_cand_cap(int64_t L, int64_t cnt) {
+    if (cnt <= 0) return KM_CAND_CAP_MAX;
+    const int64_t cap = (L - 1 - 2 * km_cand_rows_max(L)) / cnt - 1;
+    return (int)(cap > KM_CAND_CAP_MAX ? KM_CAND_CAP_MAX : cap);
+}
+
 struct KmPackLayout {
     size_t off_hdr;   // int32[4]: k, d, ntiles, magic
     size_t off_cmax;  // uint32: bits of max_j ||c32_j||^2 (fp32, non-negative)

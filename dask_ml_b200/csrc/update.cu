@@ -426,6 +426,66 @@ extern "C" int b200km_update_inertia_f64(const double *X, int64_t n, int d, int6
 }
 
 // ---------------------------------------------------------------------------------------------
+// candidate weighting (k-means|| steps 7-8 of Bahmani et al.: w_c = number of rows closest to candidate c).
+// The labels come from K1 against the candidate set; this is the count half of K2 on its own -- a histogram of
+// the labels (4 bytes per row, HBM-bound) without the second read of X that the sums would cost.
+// ---------------------------------------------------------------------------------------------
+constexpr int LC_THREADS = 512;
+__global__ void __launch_bounds__(LC_THREADS)
+label_counts_kernel(const int32_t *__restrict__ labels, int64_t n, int k, double *__restrict__ counts) {
+    extern __shared__ int lc_hist[];   // [k]
+    for (int j = threadIdx.x; j < k; j += LC_THREADS) lc_hist[j] = 0;
+    __syncthreads();
+    const int64_t n4 = n >> 2;
+    const int4 *l4 = reinterpret_cast<const int4 *>(labels);   // cudaMalloc'ed / row-sliced label vectors: see the launcher
+    for (int64_t i = (int64_t)blockIdx.x * LC_THREADS + threadIdx.x; i < n4; i += (int64_t)gridDim.x * LC_THREADS) {
+        const int4 v = __ldg(l4 + i);
+        if ((unsigned)v.x < (unsigned)k) atomicAdd(&lc_hist[v.x], 1);
+        if ((unsigned)v.y < (unsigned)k) atomicAdd(&lc_hist[v.y], 1);
+        if ((unsigned)v.z < (unsigned)k) atomicAdd(&lc_hist[v.z], 1);
+        if ((unsigned)v.w < (unsigned)k) atomicAdd(&lc_hist[v.w], 1);
+    }
+    if (blockIdx.x == 0)
+        for (int64_t i = (n4 << 2) + threadIdx.x; i < n; i += LC_THREADS) {
+            const int l = __ldg(labels + i);
+            if ((unsigned)l < (unsigned)k) atomicAdd(&lc_hist[l], 1);
+        }
+    __syncthreads();
+    for (int j = threadIdx.x; j < k; j += LC_THREADS) {
+        const int c = lc_hist[j];
+        if (c) atomicAdd(counts + j, (double)c);     // integers below 2^53: exact in any order
+    }
+}
+__global__ void __launch_bounds__(256)
+label_counts_scalar_kernel(const int32_t *__restrict__ labels, int64_t n, int k, double *__restrict__ counts) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const int l = __ldg(labels + i);
+        if ((unsigned)l < (unsigned)k) atomicAdd(counts + l, 1.0);
+    }
+}
+
+extern "C" int b200km_label_counts(const int32_t *labels, int64_t n, int k, double *counts, void *stream) {
+    KM_CHECK_ARG(labels && counts && n > 0 && k > 0, B200KM_EINVAL);
+    cudaStream_t st = km_stream(stream);
+    const bool aligned = (reinterpret_cast<uintptr_t>(labels) & 15) == 0;
+    if (aligned && (size_t)k * sizeof(int) <= 200 * 1024) {
+        static bool attr_set[KM_MAX_DEVICES] = {};
+        if (int rc = km_set_smem_once(label_counts_kernel, 200 * 1024, attr_set)) return rc;
+        int64_t blocks = (n / 4 + LC_THREADS * 8 - 1) / (LC_THREADS * 8);
+        if (blocks < 1) blocks = 1;
+        const int64_t cap = (int64_t)km_num_sms() * 2;
+        if (blocks > cap) blocks = cap;
+        label_counts_kernel<<<(unsigned)blocks, LC_THREADS, (size_t)k * sizeof(int), st>>>(labels, n, k, counts);
+    } else {
+        int64_t blocks = (n + 255) / 256;
+        const int64_t cap = (int64_t)km_num_sms() * 8;
+        if (blocks > cap) blocks = cap;
+        label_counts_scalar_kernel<<<(unsigned)blocks, 256, 0, st>>>(labels, n, k, counts);
+    }
+    KM_LAUNCH_RET();
+}
+
+// ---------------------------------------------------------------------------------------------
 // K3 finalize
 // ---------------------------------------------------------------------------------------------
 // One thread-block cluster of FIN_CTAS CTAs does the whole job, so the shift is summed in ONE FIXED ORDER (thread

@@ -134,6 +134,9 @@ int b200km_rowdist_f64(const double *X, int64_t n, int d, int64_t ldx, const voi
 int b200km_refine_pruned_x64_f64(const double *X, int64_t n, int d, int64_t ldx, const float *Xc, float *dist32,
                                  const void *pack, int k, int32_t *flag_rows, const int32_t *flag_count,
                                  int32_t *labels, double *mind2, void *stream);
+int b200km_refine_pruned_x64_len_f64(const double *X, int64_t n, int d, int64_t ldx, const float *Xc, float *dist32,
+                                     const void *pack, int k, int32_t *flag_rows, int64_t flag_len,
+                                     const int32_t *flag_count, int32_t *labels, double *mind2, void *stream);
 /* fp64 re-decision of the flagged rows of a float32 X (labels / mind2 updated in place).
  * `flag_count` is read on the device: no host synchronisation is needed between the two calls.
  * Replaces: nothing separate -- it is what makes K1's float32 labels equal the reference's
@@ -144,16 +147,23 @@ int b200km_refine_f64(const float *X, int64_t n, int d, int64_t ldx, const void 
 /* The same re-decision, pruned: a flagged row's float64 winner has a float32 score within the rounding bound of
  * the row's best, so a second, small tensor-core pass over the flagged rows (gathered through flag_rows) lists
  * the columns with score <= (mind2 - ||x||^2) + 2 * bound -- typically 2-3 of k -- and only those are scored in
- * float64 (same arithmetic and tie rule as b200km_refine_f64: identical labels).  Rows with more than 6 listed
- * columns (duplicate centres) get the full scan.
- *   flag_rows: the n-entry buffer b200km_assign_f32 filled; entries from *flag_count on are used as scratch
- *   (hence not const).  mind2 must hold b200km_assign_f32's output for these rows.
+ * float64 (same arithmetic and tie rule as b200km_refine_f64: identical labels).  A row's list holds as many
+ * columns as the scratch allows for the number of rows flagged (decided on the device): at least 6, up to 32;
+ * rows with more listed columns (duplicate centres, heavily overlapping clusters) get the full scan.
+ *   flag_rows: the buffer b200km_assign_f32 filled; entries from *flag_count on are used as scratch (hence not
+ *   const).  It has n entries -- or, in the _len form, flag_len >= n entries: a longer buffer (the Python engine
+ *   hands over 4 n) keeps the lists long when many rows are flagged (overlapping clusters: 11 % of the rows of the
+ *   C4 shape, where 6-column lists sent most of them to the full scan).  mind2 must hold b200km_assign_f32's
+ *   output for these rows (or b200km_assign_lloyd_f32's score).
  *   Falls back to b200km_refine_f64 when mind2 == NULL, n < 4096 or K1 variant 3 is selected, and -- decided
- *   on the device, no host synchronisation -- when more than (n-1)/9 rows are flagged.
+ *   on the device, no host synchronisation -- when more than (flag_len - 1) / 9 rows are flagged.
  * Replaces: nothing in the reference (see b200km_refine_f64). */
 int b200km_refine_pruned_f64(const float *X, int64_t n, int d, int64_t ldx, const void *pack, int k,
                              int32_t *flag_rows, const int32_t *flag_count, int32_t *labels,
                              float *mind2, void *stream);
+int b200km_refine_pruned_len_f64(const float *X, int64_t n, int d, int64_t ldx, const void *pack, int k,
+                                 int32_t *flag_rows, int64_t flag_len, const int32_t *flag_count, int32_t *labels,
+                                 float *mind2, void *stream);
 
 /* K1 without caller-provided scratch.  No counterpart in the reference (it has no device memory to
  * manage); it exists for callers that cannot allocate on the device: plugins confined to the buffers
@@ -173,6 +183,15 @@ int b200km_refine_pruned_f64(const float *X, int64_t n, int d, int64_t ldx, cons
 #define B200KM_STATIC_MAX_PACK_BYTES (2 << 20)
 int b200km_assign_static_f32(const float *X, int64_t n, int d, int64_t ldx, const double *centers_f64,
                              int k, int32_t *labels, float *mind2, void *stream);
+
+/* Candidate weighting of k-means|| (Bahmani et al., steps 7-8: w_c = number of rows whose closest candidate is c):
+ * counts[label] += 1 for every row, float64, accumulated INTO counts (the caller zeroes it; one allreduce over the
+ * ranks gives the global weights).  The labels come from b200km_assign_* against the candidate set.  Labels outside
+ * [0, k) are ignored.
+ * The reference leaves this step out ("scikit-learn doesn't have weighted k-means", R/dask_ml/cluster/k_means.py:
+ * 481-487) and re-clusters the candidates unweighted (:503-513); here it is opt-in
+ * (dask_ml_b200.cluster.k_means.init_scalable(..., weighted=True)), default off, so reference parity is untouched. */
+int b200km_label_counts(const int32_t *labels, int64_t n, int k, double *counts, void *stream);
 
 /* ------------------------------------------------------------------------------------------
  * K2  per-cluster sum and count (+ inertia = sum of mind2).

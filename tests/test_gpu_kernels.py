@@ -498,6 +498,30 @@ def test_refine_pruned_duplicate_centres_overflow(eng):
     assert (lp == 5).sum() > 100
 
 
+@pytest.mark.parametrize("scratch", [1, 4])
+def test_refine_pruned_long_candidate_lists(eng, scratch):
+    """Heavily overlapping clusters: every blob is shared out between 16 centres that differ by 1e-3 sigma, so a flagged
+    row lists ~16 columns.  With the n-entry flag buffer of the C ABI's base form (scratch = 1) the lists hold what the
+    buffer allows for the number of rows flagged and longer ones overflow to the full scan; with the engine's 4 n
+    entries they hold up to 32.  Either way: the labels and distances of the full float64 scan, bit for bit."""
+    rs = np.random.RandomState(11)
+    n, d, k = 40000, 64, 512
+    blobs_c = rs.uniform(-10, 10, size=(k // 16, d))
+    X = (blobs_c[rs.randint(0, k // 16, n)] + rs.standard_normal((n, d))).astype(np.float32)
+    C = np.repeat(blobs_c, 16, axis=0) + 1e-3 * rs.standard_normal((k, d))
+    old = eng.FLAG_SCRATCH
+    eng.FLAG_SCRATCH = scratch
+    try:
+        (lp, mp, fp), (lf, mf, ff) = _assign_both_refines(eng, X, C)
+    finally:
+        eng.FLAG_SCRATCH = old
+    assert fp == ff and fp > 0.5 * n
+    npt.assert_array_equal(lp, lf)
+    npt.assert_array_equal(mp, mf)
+    lab_ref, _ = orc.pairwise_distances_argmin_min(X, C, metric_kwargs={"squared": True})
+    assert not ((lp != lab_ref) & ~_near_tie_mask(X, C)).any()
+
+
 def test_refine_pruned_falls_back_when_most_rows_are_flagged(eng):
     """All centres equal: every row is flagged, more than the scratch layout holds, so the device-side gate runs the
     full scan instead (and the pruned kernels return at once)."""
@@ -586,7 +610,19 @@ def test_assign_f64_on_tensor_cores_equals_float64_kernels(eng, n, d, k, offset)
         assert (gap[diff] <= 1e-9 * D[r, out[False][0]][diff] + 1e-13 * ((X ** 2).sum(1)[diff] + (C ** 2).sum(1).max())).all()
     same = ~diff
     npt.assert_allclose(out[True][1][same], out[False][1][same], rtol=1e-12, atol=1e-300)
+    # against the oracle (scikit-learn's float64 ArgKmin, expanded form ||x||^2 - 2 x.c + ||c||^2): its squared
+    # distances carry a cancellation error |e_i| <= 2 (d + 2) 2^-52 (||x_i||^2 + ||c||^2), so a label may differ
+    # only where the two best float64 distances are closer than that noise (or than north_star's 1e-6-relative tie),
+    # and a distance by 1e-10 relative plus that noise
     lab_ref, d_ref = orc.pairwise_distances_argmin_min(X, C, metric_kwargs={"squared": True})
-    agree = out[True][0] == lab_ref
-    assert agree.mean() > 0.999
-    npt.assert_allclose(out[True][1][agree], d_ref[agree], rtol=1e-8, atol=1e-9 * ((X ** 2).sum(1).max() + 1))
+    e = 2.0 * (d + 2) * 2.0**-52 * ((X ** 2).sum(1) + (C ** 2).sum(1).max())
+    got_lab, got_d2 = out[True]
+    bad = got_lab != lab_ref
+    if bad.any():
+        rows = np.where(bad)[0]
+        Db = sklearn.metrics.pairwise_distances(X[rows], C, metric="sqeuclidean")
+        part = np.partition(Db, 1, axis=1)
+        gap = part[:, 1] - part[:, 0]
+        assert (gap <= np.maximum(4 * e[rows], 1e-6 * part[:, 1])).all(), f"{bad.sum()} labels differ from the oracle"
+    ok = ~bad
+    assert (np.abs(got_d2[ok] - d_ref[ok]) <= 1e-10 * d_ref[ok] + e[ok]).all()
