@@ -341,6 +341,21 @@ class CudaEngine:
                 e1.record()
                 self.k1_events.append((e0, e1))
 
+    def lloyd_small(self, X: torch.Tensor, centers64: torch.Tensor, labels: torch.Tensor, mind2: torch.Tensor,
+                    acc: torch.Tensor, ticket: torch.Tensor, centers_new: torch.Tensor, shift_inertia: torch.Tensor) -> None:
+        """b200km_lloyd_small_*: one whole iteration (assign + sums + counts + inertia + divide + shift) in one launch.
+        ``acc`` / ``ticket`` (int32[1]) must be zero on entry and come back zero; single GPU, X resident (n < 2^30)."""
+        n, d, ldx = self._check_matrix(X)
+        if self.k1_events is not None:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+        self._call(f"b200km_lloyd_small_{_suffix(X)}", X.data_ptr(), n, d, ldx, centers64.data_ptr(), centers64.shape[0],
+                   labels.data_ptr(), mind2.data_ptr(), acc.data_ptr(), ticket.data_ptr(), centers_new.data_ptr(),
+                   shift_inertia.data_ptr(), self._stream())
+        if self.k1_events is not None:
+            e1.record()
+            self.k1_events.append((e0, e1))
+
     def finalize(self, acc: torch.Tensor, k: int, d: int, centers_old: torch.Tensor,
                  centers_new: Optional[torch.Tensor] = None, shift: Optional[torch.Tensor] = None):
         if centers_new is None:

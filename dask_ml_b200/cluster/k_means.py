@@ -41,7 +41,7 @@ from ..utils import DeviceArray, _timed, _timer, check_array
 logger = logging.getLogger(__name__)
 
 __all__ = ["KMeans", "k_means", "k_init", "init_scalable", "init_random", "init_pp", "evaluate_cost",
-           "_sample_points", "_kmeans_single_lloyd", "PhiloxRandomState"]
+           "_sample_points", "_kmeans_single_lloyd", "PhiloxRandomState", "candidate_weights"]
 
 
 # ---------------------------------------------------------------------------------------------
@@ -459,14 +459,44 @@ def _sample_points(X, centers, oversampling_factor, random_state):
     return _pick(eng, comm, mind2, float(cost.item()), oversampling_factor, random_state, row0, n_total)
 
 
+def candidate_weights(X, candidates):
+    """Step 7 of k-means|| (Bahmani et al., algorithm 2): ``w_c`` = number of rows of X whose closest candidate is
+    ``c`` -- one K1 pass against the candidate set (float64-exact labels, lowest index on ties, as
+    ``pairwise_distances_argmin_min``) and a histogram of the labels (``b200km_label_counts``), summed over the ranks.
+    The reference leaves this step out (``k_means.py:481-487``: "scikit-learn doesn't have weighted k-means");
+    scikit-learn has had ``sample_weight`` since 0.20, so ``init_scalable(..., weighted=True)`` can use it.
+
+    Returns an ndarray (len(candidates),) float64 of integer counts; their sum is the total number of rows."""
+    X = _as_device_matrix(X)
+    eng = get_engine(X.device)
+    comm = _comm.default_comm()
+    C = np.ascontiguousarray(candidates.detach().cpu().numpy() if isinstance(candidates, torch.Tensor) else candidates,
+                             dtype=np.float64)
+    m = C.shape[0]
+    counts = torch.zeros(m, dtype=torch.float64, device=eng.device)
+    pack = eng.pack(eng.to_device(C, torch.float64))
+    labels = eng._buf("cand_labels", (max(1, min(X.shape[0], getattr(X, "chunk_rows", X.shape[0]))),), torch.int32)
+    for r0, r1, Xs in row_chunks(X):
+        if r1 > r0:
+            ls = labels[: r1 - r0]
+            eng.assign(Xs, pack, ls, None, want_mind2=True)
+            eng.label_counts(ls, m, counts)
+    comm.allreduce_sum_(counts)
+    return counts.cpu().numpy()
+
+
 @_timed(_logger=logger)
-def init_scalable(X, n_clusters, random_state=None, max_iter=None, oversampling_factor=2, n_init="auto"):
+def init_scalable(X, n_clusters, random_state=None, max_iter=None, oversampling_factor=2, n_init="auto", weighted=False):
     """K-Means initialization using k-means|| (reference :435-513; algorithm 2 of Bahmani et al.
     as the reference modifies it).
 
     A running per-row minimum is kept on the device, so each round costs one pass of K4 over the
     rows for the NEW candidates only plus one pass of K5 over the minima; the reference
     recomputes the full n x |C| block matrices every round (:533).
+
+    ``weighted`` (an extension, default off so that the reference's behaviour is untouched): when at least
+    ``n_clusters`` candidates were found, re-cluster them WEIGHTED by the number of rows closest to each
+    (``candidate_weights``; the paper's steps 7-8) instead of unweighted (:503-513).
     """
     logger.info("Initializing with k-means||")
     X = _as_device_matrix(X)
@@ -523,7 +553,10 @@ def init_scalable(X, n_clusters, random_state=None, max_iter=None, oversampling_
         # host, exactly as the reference does
         rng2 = random_state.randint(0, np.iinfo("i4").max - 1)
         km = sklearn.cluster.KMeans(n_clusters, random_state=rng2, n_init=n_init)
-        km.fit(centers)
+        if weighted:
+            km.fit(centers, sample_weight=candidate_weights(X, centers))
+        else:
+            km.fit(centers)
     return km.cluster_centers_
 
 
@@ -572,8 +605,31 @@ def _kmeans_single_lloyd(X, n_clusters, max_iter=300, init="k-means||", verbose=
         # every small host->device copy of the set-up is queued by now: start the big one behind them
         eng.start_upload(X)
         pending = X._b200_pending
+    # k <= 16, d <= 32 on one GPU with X resident: the WHOLE iteration is one launch (b200km_lloyd_small_*: the CTA
+    # that finishes last divides, measures the shift and hands acc back zeroed)
+    one_launch = (comm.world == 1 and hasattr(eng, "lloyd_small") and not isinstance(X, HostMatrix)
+                  and getattr(eng, "can_fuse", lambda *_: False)(k, P) and 0 < n_local < (1 << 30))
+    if one_launch:
+        ticket = torch.zeros(1, dtype=torch.int32, device=eng.device)
+        out2 = torch.zeros(2, dtype=torch.float64, device=eng.device)
+    acc_dirty = False
+    last_one = False
     for i in range(max_iter):
         with _timer("Lloyd loop %2d." % i, _logger=logger):
+            if one_launch and not pending:
+                if acc_dirty:
+                    acc.zero_()
+                    acc_dirty = False
+                eng.lloyd_small(X, centers64, labels, mind2, acc, ticket, new64, out2)  # :576-605
+                shift = float(out2[0].item())  # :602 -- the one round trip per iteration
+                last_one = True
+                logger.info("Shift: %0.4f", shift)
+                if shift < tol:
+                    break
+                centers64, new64 = new64, centers64  # :610
+                continue
+            last_one = False
+            acc_dirty = True
             acc.zero_()
             fused = getattr(eng, "can_fuse", lambda *_: False)(k, P)
             split = not fused and getattr(eng, "lloyd_split", lambda *_: False)(X, k, P)
@@ -627,6 +683,8 @@ def _kmeans_single_lloyd(X, n_clusters, max_iter=300, init="k-means||", verbose=
                 eng.assign(Xs, pack, labels[r0:r1], mind2[r0:r1])
         inertia_t = eng.reduce_sum(mind2, sqrt=True)
         comm.allreduce_sum_(inertia_t)
+    elif last_one:
+        inertia_t = out2[1:2].clone()
     else:
         inertia_t = acc[acc_n - 1 : acc_n].clone()
     inertia = DeviceArray(inertia_t.reshape(()))  # :616

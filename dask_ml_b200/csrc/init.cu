@@ -70,6 +70,26 @@ mindist_kernel(const T *__restrict__ X, int64_t n, int d, int64_t ldx, const T *
     km_block_atomic_add(cost, cost_out, red);
 }
 
+// Sum NV per-lane values over the O*2 lanes of a group with a TRANSPOSING reduction: at every step a lane passes on
+// half of what it holds and adds what it receives to the other half, so the group needs NV - NV/LPR shuffles in
+// all instead of NV * log2(LPR) (32 values over 16 lanes: 30 instead of 128 -- the butterfly made K4 shuffle-bound
+// once a round brought more than two new candidates).  Afterwards lane l of the group holds, in v[0 .. NV/LPR),
+// the full sums of the original entries l * NV/LPR ... .
+template <typename T, int NV, int CNT, int O>
+struct KmTrReduce {
+    static __device__ __forceinline__ void run(T (&v)[NV], int l) {
+        constexpr int H = CNT / 2;
+        const bool up = (l & O) != 0;
+#pragma unroll
+        for (int i = 0; i < H; ++i) {
+            const T send = up ? v[i] : v[i + H];
+            const T keep = up ? v[i + H] : v[i];
+            v[i] = keep + __shfl_xor_sync(0xffffffffu, send, O);
+        }
+        if constexpr (O > 1) KmTrReduce<T, NV, H, O / 2>::run(v, l);
+    }
+};
+
 // Vector path (rows 16-byte aligned, d % VEC == 0): LPR lanes cooperate on one row, each lane loads whole
 // 16-byte vectors, and U row groups are in flight per warp so enough bytes are outstanding to cover the
 // HBM latency (the scalar kernel above kept ~32 KB per SM in flight and reached 25 % of the HBM peak).
@@ -93,10 +113,14 @@ mindist_vec_kernel(const T *__restrict__ X, int64_t n, int d, int64_t ldx, const
     const int64_t nwarps = ((int64_t)gridDim.x * MD_THREADS) >> 5;
     double cost = 0.0;
     for (int64_t r0 = warp_global * (RPW * U); r0 < n; r0 += nwarps * (RPW * U)) {
-        // lane (sub, l) with l < U owns the running minimum of row r0 + l*RPW + sub: loaded up front (not on
-        // the critical path after the reduction) and written back coalesced
-        const int64_t myrow = r0 + (int64_t)l * RPW + sub;
-        const bool mine = l < U && myrow < n;
+        // One lane per row owns its running minimum: loaded up front (not on the critical path after the
+        // reduction) and written back coalesced.  TR: the transposing reduction leaves row u's sums with the G lanes
+        // u*G .. u*G+G-1 and lane u*G owns the row; otherwise (more lanes than values) lane u does.
+        constexpr bool TR = (U * MM >= LPR) && (LPR > 1);
+        constexpr int G = TR ? LPR / U : 1;
+        const int own_u = TR ? l / G : l;
+        const int64_t myrow = r0 + (int64_t)own_u * RPW + sub;
+        const bool mine = (TR ? (l % G) == 0 : l < U) && myrow < n;
         T oldv = (T)INFINITY;
         if (mine && !init) oldv = mind2[myrow];
         T mybest = (T)INFINITY;
@@ -136,21 +160,40 @@ mindist_vec_kernel(const T *__restrict__ X, int64_t n, int d, int64_t ldx, const
                 }
             }
         }
+        if constexpr (TR) {
+            constexpr int NV = U * MM, R = NV / LPR;
+            T v[NV];
 #pragma unroll
-        for (int u = 0; u < U; ++u) {
-            const int64_t row = r0 + u * RPW + sub;
+            for (int u = 0; u < U; ++u)
+#pragma unroll
+                for (int j = 0; j < MM; ++j) v[u * MM + j] = acc[u][j];
+            KmTrReduce<T, NV, NV, LPR / 2>::run(v, l);
+            // this lane now holds candidates j = (l % G) * R + i, i < R, of row l / G
+            const int j0 = (l % G) * R;
             T best = (T)INFINITY;
 #pragma unroll
-            for (int j = 0; j < MM; ++j) {
-                if (j < m) {
-                    T v = acc[u][j];
+            for (int i = 0; i < R; ++i) best = (j0 + i < m && v[i] < best) ? v[i] : best;
 #pragma unroll
-                    for (int o = LPR / 2; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-                    best = v < best ? v : best;
-                }
+            for (int o = 1; o < G; o <<= 1) {
+                const T other = __shfl_xor_sync(0xffffffffu, best, o);
+                best = other < best ? other : best;
             }
-            (void)row;
-            if (l == u) mybest = best;
+            mybest = best;
+        } else {
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                T best = (T)INFINITY;
+#pragma unroll
+                for (int j = 0; j < MM; ++j) {
+                    if (j < m) {
+                        T v = acc[u][j];
+#pragma unroll
+                        for (int o = LPR / 2; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+                        best = v < best ? v : best;
+                    }
+                }
+                if (l == u) mybest = best;
+            }
         }
         if (mine) {
             const T r = oldv < mybest ? oldv : mybest;

@@ -586,7 +586,8 @@ constexpr int FU_MAXD = 32;
 template <typename TX, int DMAX>
 __global__ void __launch_bounds__(FU_R, DMAX <= 16 ? 2 : 3)   // the prefetching variant trades a resident CTA for registers
 assign_update_small_kernel(const TX *__restrict__ X, int64_t n, int d, int64_t ldx, const double *__restrict__ c64,
-                           int k, int32_t *__restrict__ labels, TX *__restrict__ mind2, double *__restrict__ acc) {
+                           int k, int32_t *__restrict__ labels, TX *__restrict__ mind2, double *__restrict__ acc,
+                           unsigned int *__restrict__ done, double *__restrict__ cnew, double *__restrict__ out2) {
     extern __shared__ __align__(16) double fu_smem[];
     const int xld = d + 1;
     double *xs = fu_smem;                            // [FU_R][d+1]
@@ -729,11 +730,43 @@ assign_update_small_kernel(const TX *__restrict__ X, int64_t n, int d, int64_t l
     if (tid + FU_R < ncell && cell1 != 0.0) atomicAdd(acc + tid + FU_R, cell1);
     if (tid < k && mycount != 0.0) atomicAdd(acc + ncell + tid, mycount);
     km_block_atomic_add(inert, acc + ncell + k, red);
+    if (done == nullptr) return;
+    // ---- whole iteration in ONE launch (b200km_lloyd_small_*; single GPU): the CTA that finishes last divides the
+    // sums by the counts (K3, k_means.py:600-605), leaves [shift, inertia] in out2 and hands acc and the ticket back
+    // zeroed for the next iteration -- no memset, no finalize launch between two iterations.
+    __shared__ unsigned int ticket;
+    __threadfence();                                   // this CTA's REDs are visible before its ticket
+    __syncthreads();
+    if (tid == 0) ticket = atomicAdd(done, 1u);
+    __syncthreads();
+    if (ticket != gridDim.x - 1) return;
+    __threadfence();
+    double sh = 0.0;
+    for (int e = tid; e < ncell; e += FU_R) {
+        const double cnt = fmax(__ldcg(acc + ncell + e / d), 1.0);     // :600 (L2: other CTAs wrote these)
+        const double v = __ldcg(acc + e) / cnt;                         // :601
+        cnew[e] = v;
+        const double df = c64[e] - v;                                   // :605
+        sh = fma(df, df, sh);
+    }
+    sh = km_warp_sum(sh);
+    if (lane == 0) red[warp] = sh;
+    __syncthreads();                                   // (also: every thread has read its acc entries)
+    if (tid == 0) {
+        double t = 0.0;
+        for (int w = 0; w < FU_R / 32; ++w) t += red[w];
+        out2[0] = t;
+        out2[1] = __ldcg(acc + ncell + k);
+        *done = 0u;
+    }
+    __syncthreads();
+    for (int e = tid; e < ncell + k + 1; e += FU_R) acc[e] = 0.0;
 }
 
 template <typename TX>
 static int assign_update_impl(const TX *X, int64_t n, int d, int64_t ldx, const double *centers_f64, int k,
-                              int32_t *labels, TX *mind2, double *acc, void *stream) {
+                              int32_t *labels, TX *mind2, double *acc, void *stream, unsigned int *done = nullptr,
+                              double *cnew = nullptr, double *out2 = nullptr) {
     KM_CHECK_ARG(X && centers_f64 && labels && acc, B200KM_EINVAL);
     KM_CHECK_ARG(n > 0 && d > 0 && k > 0 && ldx >= d, B200KM_EINVAL);
     KM_CHECK_ARG(k <= FU_MAXK && d <= FU_MAXD, B200KM_ETOOBIG);
@@ -745,14 +778,30 @@ static int assign_update_impl(const TX *X, int64_t n, int d, int64_t ldx, const 
         auto kern = assign_update_small_kernel<TX, 16>;
         static bool attr_set[KM_MAX_DEVICES] = {};
         if (int rc = km_set_smem_once(kern, 80 * 1024, attr_set)) return rc;
-        kern<<<(unsigned)blocks, FU_R, smem, km_stream(stream)>>>(X, n, d, ldx, centers_f64, k, labels, mind2, acc);
+        kern<<<(unsigned)blocks, FU_R, smem, km_stream(stream)>>>(X, n, d, ldx, centers_f64, k, labels, mind2, acc, done, cnew,
+                                                                  out2);
     } else {
         auto kern = assign_update_small_kernel<TX, FU_MAXD>;
         static bool attr_set[KM_MAX_DEVICES] = {};
         if (int rc = km_set_smem_once(kern, 80 * 1024, attr_set)) return rc;
-        kern<<<(unsigned)blocks, FU_R, smem, km_stream(stream)>>>(X, n, d, ldx, centers_f64, k, labels, mind2, acc);
+        kern<<<(unsigned)blocks, FU_R, smem, km_stream(stream)>>>(X, n, d, ldx, centers_f64, k, labels, mind2, acc, done, cnew,
+                                                                  out2);
     }
     KM_LAUNCH_RET();
+}
+extern "C" int b200km_lloyd_small_f32(const float *X, int64_t n, int d, int64_t ldx, const double *centers_f64, int k,
+                                      int32_t *labels, float *mind2, double *acc, unsigned int *ticket,
+                                      double *centers_new, double *shift_inertia, void *stream) {
+    KM_CHECK_ARG(ticket && centers_new && shift_inertia, B200KM_EINVAL);
+    return assign_update_impl<float>(X, n, d, ldx, centers_f64, k, labels, mind2, acc, stream, ticket, centers_new,
+                                     shift_inertia);
+}
+extern "C" int b200km_lloyd_small_f64(const double *X, int64_t n, int d, int64_t ldx, const double *centers_f64, int k,
+                                      int32_t *labels, double *mind2, double *acc, unsigned int *ticket,
+                                      double *centers_new, double *shift_inertia, void *stream) {
+    KM_CHECK_ARG(ticket && centers_new && shift_inertia, B200KM_EINVAL);
+    return assign_update_impl<double>(X, n, d, ldx, centers_f64, k, labels, mind2, acc, stream, ticket, centers_new,
+                                      shift_inertia);
 }
 extern "C" int b200km_assign_update_f32(const float *X, int64_t n, int d, int64_t ldx, const double *centers_f64,
                                         int k, int32_t *labels, float *mind2, double *acc, void *stream) {

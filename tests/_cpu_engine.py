@@ -59,6 +59,12 @@ class NumpyEngine:
     def flagged_count(self):
         return 0
 
+    def label_counts(self, labels, k, counts=None):
+        if counts is None:
+            counts = torch.zeros(k, dtype=torch.float64)
+        counts += torch.from_numpy(np.bincount(labels.numpy(), minlength=k).astype(np.float64))
+        return counts
+
     def acc_len(self, k, d):
         return k * d + k + 1
 

@@ -65,6 +65,7 @@ def _run(rank, world, port, out):
     res["none"] = km3.cluster_centers_
     res["cost"] = kmod.evaluate_cost(Xl, X[[0, 5, 9]])
     res["picks"] = kmod._sample_points(Xl, X[[0, 5, 9]], 40, kmod.PhiloxRandomState(11))
+    res["weights"] = kmod.candidate_weights(Xl, X[[0, 5, 9, 100, 2000]])
     # a NaN in the LAST rank's shard only: every rank must raise the reference's ValueError (reference :195-201) --
     # a rank raising alone would leave the others in the next collective
     Xbad = Xl.clone()
@@ -102,6 +103,8 @@ def test_two_ranks_match_one(tmp_path):
         np.testing.assert_allclose(r[i]["par"][1], one["par"][1], rtol=1e-9)
         np.testing.assert_allclose(r[i]["cost"], one["cost"], rtol=1e-9)
         np.testing.assert_array_equal(r[i]["picks"], one["picks"])
+        np.testing.assert_array_equal(r[i]["weights"], one["weights"])    # candidate weights: one allreduce of the counts
+        assert r[i]["weights"].sum() == 3001
         assert r[i]["nan_fixed"].startswith("Input contains NaN") and r[i]["nan_par"].startswith("Input contains NaN")
     np.testing.assert_array_equal(r[0]["none"], r[1]["none"])           # same seed on both ranks
     np.testing.assert_allclose(r[0]["lloyd"][0], r[1]["lloyd"][0], rtol=0, atol=0)  # bit-identical centres

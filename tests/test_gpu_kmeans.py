@@ -309,6 +309,51 @@ def test_golden_init_scalable(path):
         npt.assert_allclose(C, g["centers"], rtol=1e-6, atol=1e-6)
 
 
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+def test_candidate_weights_and_weighted_recluster(dtype):
+    """Steps 7-8 of k-means|| (not in the reference, opt-in): the weight of a candidate is the number of rows it is
+    the closest candidate of -- ``np.bincount`` of the oracle's argmin -- and ``init_scalable(weighted=True)`` hands
+    those weights to scikit-learn's re-cluster of the candidates."""
+    import importlib
+
+    import sklearn.cluster
+
+    kmod = importlib.import_module("dask_ml_b200.cluster.k_means")
+    X, _ = blobs(40000, 10, 12, seed=21, dtype=dtype)
+    cand = X[np.random.RandomState(0).choice(len(X), 300, replace=False)]
+    w = kmod.candidate_weights(X, cand)
+    lab, _ = orc.pairwise_distances_argmin_min(X, cand.astype(np.float64))
+    npt.assert_array_equal(w, np.bincount(lab, minlength=len(cand)))
+    assert w.sum() == len(X) and w.dtype == np.float64
+    # weighted=True changes only the re-cluster branch: same candidates, same rng2, sample_weight = the counts
+    seen = {}
+
+    class RS(kmod.PhiloxRandomState):
+        pass
+
+    real_fit = sklearn.cluster.KMeans.fit
+
+    def spy(self, Xc, y=None, sample_weight=None):
+        seen["cand"], seen["w"] = np.array(Xc), None if sample_weight is None else np.array(sample_weight)
+        return real_fit(self, Xc, y, sample_weight=sample_weight)
+
+    sklearn.cluster.KMeans.fit = spy
+    try:
+        C_w = kmod.init_scalable(X, 4, RS(3), None, 6, "auto", weighted=True)
+        cand_w, w_w = seen["cand"], seen["w"]
+        C_u = kmod.init_scalable(X, 4, RS(3), None, 6, "auto")
+        assert seen["w"] is None
+    finally:
+        sklearn.cluster.KMeans.fit = real_fit
+    npt.assert_array_equal(cand_w, seen["cand"])
+    lab2, _ = orc.pairwise_distances_argmin_min(X, cand_w.astype(np.float64))
+    npt.assert_array_equal(w_w, np.bincount(lab2, minlength=len(cand_w)))
+    assert C_w.shape == C_u.shape == (4, 10) and not np.allclose(C_w, C_u)
+    rng2 = RS(3).randint(0, np.iinfo("i4").max - 1)
+    want = sklearn.cluster.KMeans(4, random_state=rng2, n_init="auto").fit(cand_w, sample_weight=w_w).cluster_centers_
+    npt.assert_allclose(C_w, want, rtol=1e-12)
+
+
 def test_evaluate_cost_and_sample_points_match_oracle():
     from dask_ml_b200.cluster.k_means import _sample_points, evaluate_cost
 
