@@ -55,6 +55,7 @@ class CudaEngine:
         self.k1_events = None  # bench.py: set to a list to collect (start, end) CUDA events around K1
         self.pruned_refine = True   # tests flip this to compare with the full float64 scan
         self.f64_on_tensor_cores = True   # float64 X, k > 16: centre + round, tcgen05 decision, float64 re-decision
+        self.cdist_on_tensor_cores = True   # float32 X, d <= 64: distance / rbf matrices on the tcgen05 kernel
 
         self.trace = None      # tools/: set to a list to collect (entry point, event) per launch
         self._scratch = {}
@@ -443,10 +444,45 @@ class CudaEngine:
         return out
 
     # ---- K7 + helpers ---------------------------------------------------------------------
+    CDIST_TC_MAX_D = 64
+    CDIST_TC_MAX_K = 1 << 16     # centres of one tensor-core call (the pack holds five copies of them)
+
+    def _cdist_tc(self, X: torch.Tensor, Y: torch.Tensor, mode: int, gamma: float = 0.0) -> Optional[torch.Tensor]:
+        """K7 on the tensor cores (b200km_cdist_pack_f32) where it applies -- float32, <= 64 features, the one-CTA
+        pack layout -- else None (the caller takes the FFMA tile kernel).  The kernel writes (rows x centres) with
+        the centres as the packed side; when Y has more rows than X (SpectralClustering's B block: 100 kept rows
+        against millions) the roles are swapped -- distances and the rbf kernel are symmetric -- and the result is
+        the transposed view of what was written."""
+        n, d, _ = self._check_matrix(X)
+        k = Y.shape[0]
+        if (X.dtype != torch.float32 or Y.dtype != torch.float32 or d > self.CDIST_TC_MAX_D
+                or not self.cdist_on_tensor_cores or n == 0 or k == 0
+                or self.lib.b200km_get_option(_lib.OPT_K1_VARIANT) == _lib.K1_TCGEN05_PAIR):
+            return None
+        swap = k > n
+        if swap:
+            X, Y, n, k = Y, X, k, n
+            if X.stride(1) != 1:
+                X = X.contiguous()
+        if k > self.CDIST_TC_MAX_K:
+            return None
+        ldx = X.stride(0) if n > 1 else d
+        pack = self.pack(Y.to(torch.float64).contiguous())
+        out = torch.empty(n, k, dtype=torch.float32, device=self.device)
+        for r0 in range(0, n, _MAX_ROWS_PER_CALL):
+            nn = min(_MAX_ROWS_PER_CALL, n - r0)
+            self._call("b200km_cdist_pack_f32", X[r0 : r0 + nn].data_ptr(), nn, d, ldx, pack.buf.data_ptr(), pack.k,
+                       out[r0 : r0 + nn].data_ptr(), out.stride(0), mode, float(gamma), self._stream())
+        return out.t() if swap else out
+
     def cdist(self, X: torch.Tensor, Y: torch.Tensor, squared: bool = False, xnorm2=None, ynorm2=None) -> torch.Tensor:
         n, d, ldx = self._check_matrix(X)
         Y = Y.contiguous()
         k = Y.shape[0]
+        if xnorm2 is None and ynorm2 is None:    # (caller-supplied norms are honoured as given: the FFMA kernel below)
+            res = self._cdist_tc(X, Y, _lib.CDIST_SQUARED if squared else _lib.CDIST_DIST)
+            if res is not None:
+                return res
         out = torch.empty(n, k, dtype=X.dtype, device=self.device)
         if n and k:
             self._call(f"b200km_cdist_{_suffix(X)}", X.data_ptr(), n, d, ldx, Y.data_ptr(), k,
@@ -463,6 +499,10 @@ class CudaEngine:
         n, d, ldx = self._check_matrix(X)
         Y = Y.contiguous()
         k = Y.shape[0]
+        if kind == "rbf":
+            res = self._cdist_tc(X, Y, _lib.CDIST_RBF, gamma)
+            if res is not None:
+                return res
         out = torch.empty(n, k, dtype=X.dtype, device=self.device)
         if n and k:
             self._call(f"b200km_pairwise_kernel_{_suffix(X)}", X.data_ptr(), n, d, ldx, Y.data_ptr(), k, out.data_ptr(),

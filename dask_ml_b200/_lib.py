@@ -28,6 +28,7 @@ class B200KernelError(RuntimeError):
 OPT_K1_VARIANT = 1      # B200KM_OPT_K1_VARIANT
 OPT_K2_VARIANT = 2      # B200KM_OPT_K2_VARIANT
 K1_AUTO, K1_FFMA, K1_TCGEN05, K1_TCGEN05_PAIR = 0, 1, 2, 3
+CDIST_SQUARED, CDIST_DIST, CDIST_RBF = 0, 1, 2   # b200km_cdist_pack_f32 modes
 
 _P = c_void_p  # device pointers and the stream are passed as plain addresses
 
@@ -76,6 +77,7 @@ PROTOTYPES = {
     "b200km_gather_rows_f64": (c_int, [_P, c_int64, c_int, c_int64, _P, c_int, _P, _P]),
     "b200km_cdist_f32": (c_int, [_P, c_int64, c_int, c_int64, _P, c_int, _P, _P, _P, c_int, _P]),
     "b200km_cdist_f64": (c_int, [_P, c_int64, c_int, c_int64, _P, c_int, _P, _P, _P, c_int, _P]),
+    "b200km_cdist_pack_f32": (c_int, [_P, c_int64, c_int, c_int64, _P, c_int, _P, c_int64, c_int, c_double, _P]),
     "b200km_pairwise_kernel_f32": (c_int, [_P, c_int64, c_int, c_int64, _P, c_int, _P, c_int, c_double, c_double, c_int, _P]),
     "b200km_pairwise_kernel_f64": (c_int, [_P, c_int64, c_int, c_int64, _P, c_int, _P, c_int, c_double, c_double, c_int, _P]),
     "b200km_row_norms_f32": (c_int, [_P, c_int64, c_int, c_int64, _P, c_int, _P]),

@@ -116,6 +116,18 @@ extern "C" int b200km_cdist_f64(const double *X, int64_t n, int d, int64_t ldx, 
     return cdist_impl<double>(X, n, d, ldx, Y, k, xnorm2, ynorm2, out, squared ? CD_SQDIST : CD_DIST, 0.0, 0.0, 0, stream);
 }
 
+// K7 on the tensor cores (cdist_tc.cu): float32 rows of up to 64 features against a centre pack
+int km_launch_cdist_tc(const float *X, int64_t n, int d, int64_t ldx, const void *pack, int k, float *out, int64_t ldo,
+                       int mode, float gamma, cudaStream_t st);
+extern "C" int b200km_cdist_pack_f32(const float *X, int64_t n, int d, int64_t ldx, const void *pack, int k, float *out,
+                                     int64_t ldo, int mode, double gamma, void *stream) {
+    KM_CHECK_ARG(X && pack && out && n > 0 && d > 0 && k > 0 && ldx >= d && ldo >= k, B200KM_EINVAL);
+    KM_CHECK_ARG(mode >= B200KM_CDIST_SQUARED && mode <= B200KM_CDIST_RBF, B200KM_EINVAL);
+    KM_CHECK_ARG(k <= B200KM_MAX_K, B200KM_ETOOBIG);
+    KM_CHECK_ARG((reinterpret_cast<uintptr_t>(pack) & 255) == 0, B200KM_EALIGN);
+    return km_launch_cdist_tc(X, n, d, ldx, pack, k, out, ldo, mode, (float)gamma, km_stream(stream));
+}
+
 // pairwise kernels on the same tile kernel (the SpectralClustering tail)
 extern "C" int b200km_pairwise_kernel_f32(const float *X, int64_t n, int d, int64_t ldx, const float *Y, int k,
                                           float *out, int kind, double gamma, double coef0, int degree, void *stream) {

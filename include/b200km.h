@@ -307,6 +307,22 @@ int b200km_cdist_f32(const float *X, int64_t n, int d, int64_t ldx, const float 
 int b200km_cdist_f64(const double *X, int64_t n, int d, int64_t ldx, const double *Y, int k,
                      const double *xnorm2, const double *ynorm2, double *out, int squared, void *stream);
 
+/* K7 on the tensor cores, for float32 rows of at most 64 features (else B200KM_ETOOBIG: use the entry points
+ * above): out[i * ldo + j] = f(||x_i - c_j||^2), c_j the centres of a pack built by b200km_pack_centers (one-CTA
+ * layout, i.e. not under B200KM_OPT_K1_VARIANT = 3), f by `mode`.  The op is bound by its output -- k floats per
+ * row -- so the centres are the M side of the 3xTF32 tcgen05 MMA and 256 rows the N side: a warp of the epilogue
+ * holds 32 neighbouring centres of one row per register and every store writes 128 contiguous bytes.  Both squared
+ * norms ride in an augmented K-step; rows and centres are centred on the pack's mu, so the cancellation error
+ * scales with the spread of the data, not its distance from the origin (more accurate than the float32 expanded
+ * form the reference evaluates, R/dask_ml/metrics/pairwise.py:101-105).
+ * Replaces: euclidean_distances (R/dask_ml/metrics/pairwise.py:70-105) = KMeans.transform
+ *           (R/dask_ml/cluster/k_means.py:225-228), pairwise_distances (:50-67), rbf_kernel (:141-151). */
+#define B200KM_CDIST_SQUARED 0 /* ||x - c||^2                 */
+#define B200KM_CDIST_DIST 1    /* ||x - c||                   */
+#define B200KM_CDIST_RBF 2     /* exp(-gamma * ||x - c||^2)   */
+int b200km_cdist_pack_f32(const float *X, int64_t n, int d, int64_t ldx, const void *pack, int k, float *out,
+                          int64_t ldo, int mode, double gamma, void *stream);
+
 /* Kernel matrices on the same tile kernel: out[i,j] = kernel(x_i, y_j) in the input precision.
  * Replaces: dask_ml.metrics.pairwise.{rbf,linear,polynomial,sigmoid}_kernel / pairwise_kernels
  *           (R/dask_ml/metrics/pairwise.py:135-226), the affinity blocks of SpectralClustering's Nystrom

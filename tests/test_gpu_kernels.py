@@ -225,6 +225,59 @@ def test_assign_lloyd_labels_match_full_assign(eng, n, d, k):
         assert bad.sum() <= _near_tie_mask(X, C).sum() and not (bad & ~_near_tie_mask(X, C)).any()
 
 
+@pytest.mark.parametrize("n,d,k,offset", [(5000, 64, 1024, 0.0), (3001, 32, 256, 0.0), (777, 7, 5, 0.0), (260, 64, 129, 0.0),
+                                           (4096, 48, 300, 100.0), (10000, 16, 40, -1000.0), (300, 1, 3, 0.0),
+                                           (2000, 61, 1000, 5.0)])
+def test_cdist_on_tensor_cores(eng, n, d, k, offset):
+    """K7's tcgen05 kernel (float32, d <= 64: b200km_cdist_pack_f32) against float64 numpy: squared distances,
+    distances and the rbf kernel, incl. ragged n / k / d, strided rows and data far from the origin (rows and centres
+    are centred on the mean of the centres, so the error scales with the spread of the data); and against the FFMA
+    tile kernel it replaces for these shapes (the reference evaluates the float32 expanded form, atol 1e-4 in its
+    own tests: reference tests/metrics/test_metrics.py:15-19, 42-71)."""
+    import torch
+
+    rs = np.random.RandomState(n + d + k)
+    cen = rs.uniform(-10, 10, size=(max(2, k // 8), d))
+    X = (cen[rs.randint(0, len(cen), n)] + rs.standard_normal((n, d)) + offset).astype(np.float32)
+    Y = (cen[rs.randint(0, len(cen), k)] + 0.5 * rs.standard_normal((k, d)) + offset).astype(np.float32)
+    D2 = sklearn.metrics.pairwise_distances(X.astype(np.float64), Y.astype(np.float64), metric="sqeuclidean")
+    big = torch.zeros(n, d + 3, dtype=torch.float32, device=eng.device)    # ldx > d
+    big[:, :d] = eng.to_device(X)
+    Xd, Yd = big[:, :d], eng.to_device(Y)
+    launches0 = eng.launches
+    got2 = eng.cdist(Xd, Yd, squared=True).cpu().numpy()
+    assert eng.launches - launches0 == 4          # three pack kernels + the tensor-core kernel: not the FFMA tile kernel
+    # error model: fp32 accumulation of 3xTF32 products on CENTRED data -- a few 1e-7 of (||x'||^2 + ||c'||^2)
+    mu = Y.astype(np.float64).mean(0)
+    scale = ((X - mu) ** 2).sum(1)[:, None] + ((Y - mu) ** 2).sum(1)[None, :]
+    assert (np.abs(got2 - D2) <= 4e-6 * scale + 1e-30).all()
+    got = eng.cdist(Xd, Yd).cpu().numpy()
+    # (the square root of a squared distance that is mostly rounding noise -- a row on top of a centre -- is off by
+    #  up to the root of that noise, for the reference's float32 expanded form just the same)
+    assert (np.abs(got - np.sqrt(D2)) <= 1e-4 * np.sqrt(D2) + np.sqrt(4e-6 * scale) + 1e-6).all()
+    gamma = 1.0 / max(D2.mean(), 1e-9)
+    npt.assert_allclose(eng.pairwise_kernel(Xd, Yd, "rbf", gamma=gamma).cpu().numpy(), np.exp(-gamma * D2), atol=2e-5)
+    eng.cdist_on_tensor_cores = False
+    try:
+        ffma = eng.cdist(Xd, Yd, squared=True).cpu().numpy()
+    finally:
+        eng.cdist_on_tensor_cores = True
+    npt.assert_allclose(got2, ffma, rtol=1e-3, atol=1e-4 * max(1.0, (offset * offset * d)))
+
+
+def test_cdist_on_tensor_cores_long_second_operand(eng):
+    """SpectralClustering's B block: 100 kept rows against many rows.  The long side becomes the streamed operand
+    (roles swapped, the result handed back as the transposed view of what was written): same values."""
+    rs = np.random.RandomState(0)
+    A = rs.standard_normal((100, 20)).astype(np.float32)
+    B = rs.standard_normal((70001, 20)).astype(np.float32)
+    D2 = sklearn.metrics.pairwise_distances(A.astype(np.float64), B.astype(np.float64), metric="sqeuclidean")
+    got = eng.pairwise_kernel(eng.to_device(A), eng.to_device(B), "rbf", gamma=0.05)
+    assert tuple(got.shape) == (100, 70001)
+    npt.assert_allclose(got.cpu().numpy(), np.exp(-0.05 * D2), atol=2e-5)
+    npt.assert_allclose(eng.cdist(eng.to_device(A), eng.to_device(B), squared=True).cpu().numpy(), D2, rtol=1e-4, atol=1e-3)
+
+
 @pytest.mark.parametrize("dtype", [np.float32, np.float64])
 @pytest.mark.parametrize("n,d", [(5000, 64), (3001, 3), (1000, 100), (64, 16), (2000, 33)])
 def test_mindist_and_cost(eng, n, d, dtype):
