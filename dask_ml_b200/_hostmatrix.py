@@ -24,7 +24,7 @@ __all__ = ["HostMatrix", "row_chunks"]
 class HostMatrix:
     CHUNK_BYTES = 256 << 20          # per device buffer (two of them); tests shrink it
 
-    def __init__(self, host, eng, nonfinite_msg: Optional[str] = None):
+    def __init__(self, host, eng, nonfinite_msg: Optional[str] = None, share_verdict: bool = False):
         t = host if isinstance(host, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(host))
         if t.is_cuda or t.dim() != 2 or t.dtype not in (torch.float32, torch.float64):
             raise ValueError("HostMatrix wraps a 2-D float32/float64 HOST array")
@@ -35,6 +35,7 @@ class HostMatrix:
         self.device = torch.device(eng.device)
         self.ndim = 2
         self.nonfinite_msg = nonfinite_msg
+        self.share_verdict = share_verdict   # fit(): all ranks learn of a NaN / inf on any rank (a collective)
         self._scanned = nonfinite_msg is None
         self._bufs = None
         self._registered = False
@@ -129,7 +130,9 @@ class HostMatrix:
             self._scanned = True
             from ._engine import any_rank_flag
 
-            if any_rank_flag(bad):      # every rank finishes its first pass here: the verdict is shared
+            # fit(): every rank finishes its first pass here and the verdict is shared; predict / transform are not
+            # collective calls, there the rank decides alone
+            if any_rank_flag(bad) if self.share_verdict else bool(int(bad.item())):
                 raise ValueError(self.nonfinite_msg)
 
 

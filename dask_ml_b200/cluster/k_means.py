@@ -164,7 +164,7 @@ class KMeans(TransformerMixin, BaseEstimator):
                 and _out_of_core(eng, X):
             # larger than the device can hold: X stays in (page-locked) host memory and every pass streams it;
             # the NaN/inf scan (:195-201) rides on the first pass
-            return HostMatrix(X, eng, nonfinite_msg=self._NONFINITE_MSG)
+            return HostMatrix(X, eng, nonfinite_msg=self._NONFINITE_MSG, share_verdict=defer)
         if (defer and host and hasattr(eng, "to_device_streamed") and X.ndim == 2
                 and str(X.dtype).replace("torch.", "") in ("float32", "float64")
                 and X.shape[0] * X.shape[1] * (4 if "32" in str(X.dtype) else 8) >= eng.STREAM_MIN_BYTES):

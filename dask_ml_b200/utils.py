@@ -7,6 +7,7 @@ check_array :123-214, _timer/_timed :515-559); nothing else from that module is 
 from __future__ import annotations
 
 import contextlib
+import os
 import functools
 import logging
 from timeit import default_timer as tic
@@ -185,13 +186,29 @@ def _format(seconds: float) -> str:
     return "%.2f s" % seconds if seconds >= 1 else "%.2f ms" % (seconds * 1e3)
 
 
+_NVTX = os.environ.get("B200KM_NVTX", "") not in ("", "0")
+
+
 @contextlib.contextmanager
 def _timer(name, _logger=None, level="info"):
-    """reference dask_ml/utils.py:515-536 -- log start / finish + wall time."""
+    """reference dask_ml/utils.py:515-536 -- log start / finish + wall time.  With ``B200KM_NVTX=1`` every timed
+    section (a Lloyd iteration, a k-means|| round, an initialiser) is also an NVTX range, so the kernels of one
+    iteration group together on a profiler's timeline."""
     start = tic()
     _logger = _logger or logger
     _logger.info("Starting %s", name)
-    yield
+    pushed = False
+    if _NVTX:
+        try:
+            torch.cuda.nvtx.range_push(str(name))
+            pushed = True
+        except Exception:  # pragma: no cover - NVTX is optional
+            pushed = False
+    try:
+        yield
+    finally:
+        if pushed:
+            torch.cuda.nvtx.range_pop()
     getattr(_logger, level)("Finished %s in %s", name, _format(tic() - start))
 
 
