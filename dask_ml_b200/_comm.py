@@ -36,6 +36,10 @@ class Comm:
     def broadcast_(self, t: torch.Tensor, src: int = 0) -> torch.Tensor:
         raise NotImplementedError
 
+    def allgather_fixed(self, t: torch.Tensor) -> torch.Tensor:
+        """(world, *t.shape): the same-shaped tensors of all ranks, in rank order -- ONE collective, no size exchange."""
+        raise NotImplementedError
+
     def row_range(self, n_local: int) -> Tuple[int, int]:
         """(global offset of this rank's first row, total rows)."""
         raise NotImplementedError
@@ -50,6 +54,9 @@ class NullComm(Comm):
 
     def broadcast_(self, t, src=0):
         return t
+
+    def allgather_fixed(self, t):
+        return t[None]
 
     def row_range(self, n_local):
         return 0, int(n_local)
@@ -71,6 +78,11 @@ class TorchDistComm(Comm):
     def broadcast_(self, t, src=0):
         self.dist.broadcast(t, src=src, group=self.group)
         return t
+
+    def allgather_fixed(self, t):
+        bufs = [torch.empty_like(t) for _ in range(self.world)]
+        self.dist.all_gather(bufs, t.contiguous(), group=self.group)
+        return torch.stack(bufs)
 
     def _counts(self, n: int, device) -> List[int]:
         mine = torch.tensor([n], dtype=torch.int64, device=device)

@@ -433,6 +433,20 @@ class CudaEngine:
                 return picked[:c].clone()
             capacity = c  # rare: more picks than room -- redo with the exact size (same draws)
 
+    def bernoulli_buf(self, mind2: torch.Tensor, scale: float, seed: int, round_: int, row_offset: int,
+                      draws: Optional[torch.Tensor] = None, capacity: int = 1024) -> torch.Tensor:
+        """The same pick WITHOUT a host synchronisation: a device int64 vector ``[count, pick_0, ..., pick_{cap-1}]``
+        (``count`` may exceed ``capacity``: the caller then asks again with more room -- same draws)."""
+        n = mind2.numel()
+        buf = self._buf("picked_buf", (capacity + 1,), torch.int64)
+        buf[:1].zero_()
+        self._call(f"b200km_bernoulli_pick_{_suffix(mind2)}", mind2.data_ptr(), n, float(scale),
+                   int(seed) & (2**64 - 1), int(round_) & 0xFFFFFFFF, int(row_offset),
+                   (draws.data_ptr() if draws is not None else None), buf[1:].data_ptr(),
+                   buf.data_ptr(),          # the int32 counter = the low half of buf[0] (little endian)
+                   capacity, self._stream())
+        return buf
+
     def gather(self, X: torch.Tensor, idx_local: torch.Tensor) -> torch.Tensor:
         n, d, ldx = self._check_matrix(X)
         m = idx_local.numel()

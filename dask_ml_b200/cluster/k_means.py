@@ -321,9 +321,13 @@ def _gather_global_rows(X: torch.Tensor, gidx, comm, row0: int) -> torch.Tensor:
     loc = torch.from_numpy(g[mine] - row0)
     rows = X.rows(loc) if isinstance(X, HostMatrix) else eng.gather(X, loc)
     if comm.world > 1:
-        # ranks own increasing, disjoint row ranges and gidx is sorted, so rank-order
-        # concatenation IS index order
-        rows = comm.allgather_varlen(rows)
+        # every rank knows which positions of the (sorted) index list it owns: each fills in its rows, zeros elsewhere,
+        # and ONE allreduce puts the (m, d) matrix on every rank -- exact (x + 0 + ... + 0), no exchange of sizes
+        full = torch.zeros(len(g), rows.shape[1], dtype=rows.dtype, device=rows.device)
+        if mine.any():
+            full[torch.from_numpy(np.flatnonzero(mine)).to(rows.device)] = rows
+        comm.allreduce_sum_(full)
+        rows = full
     return rows
 
 
@@ -423,8 +427,9 @@ def evaluate_cost(X, centers):
 def _pick(eng, comm, mind2, cost, oversampling_factor, random_state, row0, n_total) -> np.ndarray:
     """Second half of _sample_points (reference :535-541): p = l * d2 / cost ; picked = p > draws."""
     scale = float(oversampling_factor) / cost
+    draws_t = None
     if isinstance(random_state, PhiloxRandomState):
-        picked = eng.bernoulli(mind2, scale, random_state.seed, random_state.round, row0)
+        seed, rnd = random_state.seed, random_state.round
         random_state.round += 1
     else:
         # injected host draws (np RandomState, or an object restating dask's RandomState)
@@ -433,7 +438,23 @@ def _pick(eng, comm, mind2, cost, oversampling_factor, random_state, row0, n_tot
         except TypeError:
             u = random_state.uniform(size=n_total)
         u = np.asarray(u, dtype=np.float64)[row0 : row0 + mind2.numel()]
-        picked = eng.bernoulli(mind2, scale, 0, 0, row0, draws=eng.to_device(u))
+        seed, rnd, draws_t = 0, 0, eng.to_device(u)
+    if hasattr(eng, "bernoulli_buf"):
+        # one collective and ONE device->host read per round: every rank hands over [count, picks...] in a
+        # fixed-size buffer (no exchange of sizes first); more picks than room -> once more with room (same draws)
+        cap = 1024
+        while True:
+            buf = eng.bernoulli_buf(mind2, scale, seed, rnd, row0, draws=draws_t, capacity=cap)
+            h = comm.allgather_fixed(buf).cpu().numpy()
+            if int(h[:, 0].max()) <= cap:
+                break
+            cap = int(h[:, 0].max())
+        picked_h = np.concatenate([h[r, 1 : 1 + int(h[r, 0])] for r in range(h.shape[0])])
+        out = np.sort(picked_h.astype(np.int64))
+        if isinstance(getattr(random_state, "picks", None), list):
+            random_state.picks.append(out)
+        return out
+    picked = eng.bernoulli(mind2, scale, seed, rnd, row0, draws=draws_t)
     if comm.world > 1:
         picked = comm.allgather_varlen(picked)
     out = np.sort(picked.cpu().numpy())
