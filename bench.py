@@ -55,6 +55,7 @@ WORKLOADS = {
 # bench launch to fill roofline.traffic.  Source files under profiles/.
 NCU_TRAFFIC_BYTES_PER_ROW = {
     # filled only from captures of the CURRENT build (profiles/r2_*); absent -> roofline.traffic is null
+    ("c3", "tc"): ((1.025004e9 + 33.045504e6) / 4_000_000, "profiles/r2_k1_tcgen05_c3_ncu_full_raw.csv"),
 }
 C5_ROWS_TOTAL = 500_000_000   # BASELINE config 5: k-means|| init only, N = 5e8, d = 64, k = 4096, l = 2
 METRIC = "lloyd_points_per_sec"
