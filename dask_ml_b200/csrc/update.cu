@@ -584,7 +584,16 @@ constexpr int FU_MAXK = 16;
 constexpr int FU_MAXD = 32;
 
 template <typename TX, int DMAX>
-__global__ void __launch_bounds__(FU_R, DMAX <= 16 ? 2 : 3)   // the prefetching variant trades a resident CTA for registers
+// d <= 16: four resident CTAs per SM and no register prefetch of the next tile (measured at C1, 1e6 x 16 float64,
+// k = 8: 2 CTAs + prefetch 0.092 ms, 3 + prefetch 0.108 (spills), 3 without 0.084, 4 without 0.080 -- the kernel is
+// latency-bound, more warps hide more than the prefetch did)
+#ifndef FU_OCC16
+#define FU_OCC16 4
+#endif
+#ifndef FU_PREF
+#define FU_PREF 0
+#endif
+__global__ void __launch_bounds__(FU_R, DMAX <= 16 ? FU_OCC16 : 3)
 assign_update_small_kernel(const TX *__restrict__ X, int64_t n, int d, int64_t ldx, const double *__restrict__ c64,
                            int k, int32_t *__restrict__ labels, TX *__restrict__ mind2, double *__restrict__ acc,
                            unsigned int *__restrict__ done, double *__restrict__ cnew, double *__restrict__ out2) {
@@ -617,7 +626,7 @@ assign_update_small_kernel(const TX *__restrict__ X, int64_t n, int d, int64_t l
     // divisions), 32/dp rows per warp instruction, dp loads per thread and tile.  For d <= 16 the NEXT tile's loads
     // are issued into registers before the current tile is worked on (they land under phases A-C), so a tile no
     // longer costs a full memory latency on top of its compute; wider rows keep the batched in-place staging.
-    constexpr bool PREFETCH = DMAX <= 16;
+    constexpr bool PREFETCH = DMAX <= 16 && FU_PREF;
     const int sub = lane >> lg_dp, fl = lane & (dp - 1);
     const int rpi = 32 >> lg_dp;                       // rows per warp instruction
     const int r_first = warp * rpi + sub;
@@ -771,7 +780,7 @@ static int assign_update_impl(const TX *X, int64_t n, int d, int64_t ldx, const 
     KM_CHECK_ARG(n > 0 && d > 0 && k > 0 && ldx >= d, B200KM_EINVAL);
     KM_CHECK_ARG(k <= FU_MAXK && d <= FU_MAXD, B200KM_ETOOBIG);
     int64_t blocks = (n + FU_R - 1) / FU_R;
-    const int64_t cap = (int64_t)km_num_sms() * (d <= 16 ? 2 : 4);   // resident CTAs per SM of the two variants
+    const int64_t cap = (int64_t)km_num_sms() * (d <= 16 ? FU_OCC16 : 4);   // resident CTAs per SM of the two variants
     if (blocks > cap) blocks = cap;
     const size_t smem = sizeof(double) * ((size_t)FU_R * (d + 1) + 1 + (size_t)k * (d + 1));
     if (d <= 16) {
