@@ -1,6 +1,8 @@
 """One-off stress run: many random (n, d, k, variant, offset, scale, stride) cases through K1 + re-decision against
 float64 numpy.  Labels must match outside the float64 expanded form's own rounding; winner distances within the float32
-accuracy model written at the check.  argv: trials seed"""
+accuracy model written at the check.  Where the Lloyd iteration would take the labels-only form (k <= 256, d <= 32:
+b200km_assign_lloyd_f32) that form must give the same labels.  argv: trials seed [small]
+("small": only shapes of the small-k tensor-core kernel)"""
 import os, sys
 import numpy as np
 import torch
@@ -10,9 +12,12 @@ eng = get_engine(); lib = eng.lib
 trials = int(sys.argv[1]) if len(sys.argv) > 1 else 200
 rs = np.random.RandomState(int(sys.argv[2]) if len(sys.argv) > 2 else 0)
 bad = 0
+small = len(sys.argv) > 3 and sys.argv[3] == "small"
 for t in range(trials):
-    d = int(rs.choice([1, 2, 3, 4, 7, 8, 13, 16, 24, 31, 32, 33, 48, 64, 65, 100, 128, 129, 160]))
-    k = int(rs.choice([1, 2, 5, 16, 17, 31, 64, 100, 255, 256, 257, 300, 512, 513, 1024, 1500]))
+    d = int(rs.choice([1, 2, 3, 4, 7, 8, 13, 16, 24, 31, 32] if small else
+                      [1, 2, 3, 4, 7, 8, 13, 16, 24, 31, 32, 33, 48, 64, 65, 100, 128, 129, 160]))
+    k = int(rs.choice([17, 31, 32, 33, 64, 100, 129, 200, 255, 256] if small else
+                      [1, 2, 5, 16, 17, 31, 64, 100, 255, 256, 257, 300, 512, 513, 1024, 1500]))
     n = int(rs.choice([1, 2, 31, 127, 128, 129, 1000, 4095, 4096, 4097, 10007, 40000, 150001]))
     variant = int(rs.choice([0, 0, 0, 1, 2, 3]))
     offset = float(rs.choice([0.0, 0.0, 5.0, 300.0, -2000.0]))
@@ -43,6 +48,10 @@ for t in range(trials):
     try:
         pack = eng.pack(eng.to_device(C, torch.float64))
         lab, m2 = eng.assign(Xd, pack)
+        lab_l = None
+        if eng.lloyd_split(Xd, k, d):
+            scratch = torch.full((n,), float("nan"), dtype=torch.float32, device=eng.device)
+            lab_l, _ = eng.assign(Xd, pack, mind2=scratch, lloyd=True)
         torch.cuda.synchronize()
     finally:
         lib.b200km_set_option(1, 0)
@@ -60,9 +69,11 @@ for t in range(trials):
     xc = np.sqrt(((X64 - mu) ** 2).sum(1)); cc = np.sqrt(((C - mu) ** 2).sum(1))[lab]
     allowed = 3e-6 * m_at + 8 * 2.0 ** -24 * np.sqrt(m_at) * (xc + cc) + 1e-37
     err = np.abs(m2 - m_at) / allowed
-    ok = (not hard.any()) and err.max() < 1.0
+    same = lab_l is None or bool((lab_l == torch.as_tensor(lab, device=lab_l.device)).all().item())
+    ok = (not hard.any()) and err.max() < 1.0 and same
     if not ok:
         bad += 1
         print(f"FAIL trial {t}: n={n} d={d} k={k} variant={variant} offset={offset} scale={scale} pad={pad} dup={dup}: "
-              f"{int(hard.sum())} hard label mismatches, mind2 error / allowed {err.max():.2e}", flush=True)
+              f"{int(hard.sum())} hard label mismatches, mind2 error / allowed {err.max():.2e}, "
+              f"labels-only form equal: {same}", flush=True)
 print(f"{trials} trials, {bad} failures")
