@@ -55,7 +55,7 @@ class CudaEngine:
         self.k1_events = None  # bench.py: set to a list to collect (start, end) CUDA events around K1
         self.pruned_refine = True   # tests flip this to compare with the full float64 scan
         self.f64_on_tensor_cores = True   # float64 X, k > 16: centre + round, tcgen05 decision, float64 re-decision
-        self.cdist_on_tensor_cores = True   # float32 X, d <= 64: distance / rbf matrices on the tcgen05 kernel
+        self.cdist_on_tensor_cores = True   # float32 X, d <= 128: distance / rbf matrices on the tcgen05 kernel
 
         self.trace = None      # tools/: set to a list to collect (entry point, event) per launch
         self._scratch = {}
@@ -458,11 +458,11 @@ class CudaEngine:
         return out
 
     # ---- K7 + helpers ---------------------------------------------------------------------
-    CDIST_TC_MAX_D = 64
+    CDIST_TC_MAX_D = 128
     CDIST_TC_MAX_K = 1 << 16     # centres of one tensor-core call (the pack holds five copies of them)
 
     def _cdist_tc(self, X: torch.Tensor, Y: torch.Tensor, mode: int, gamma: float = 0.0) -> Optional[torch.Tensor]:
-        """K7 on the tensor cores (b200km_cdist_pack_f32) where it applies -- float32, <= 64 features, the one-CTA
+        """K7 on the tensor cores (b200km_cdist_pack_f32) where it applies -- float32, <= 128 features, the one-CTA
         pack layout -- else None (the caller takes the FFMA tile kernel).  The kernel writes (rows x centres) with
         the centres as the packed side; when Y has more rows than X (SpectralClustering's B block: 100 kept rows
         against millions) the roles are swapped -- distances and the rbf kernel are symmetric -- and the result is

@@ -2,7 +2,7 @@
 //
 // Replaces dask_ml.metrics.euclidean_distances (reference dask_ml/metrics/pairwise.py:70-105, the body of
 // KMeans.transform, dask_ml/cluster/k_means.py:225-228), pairwise_distances (:50-67) and rbf_kernel (:141-151) for
-// float32 rows of up to 64 features; everything else stays on the FFMA / DFMA tile kernel in misc.cu.
+// float32 rows of up to 128 features; everything else stays on the FFMA / DFMA tile kernel in misc.cu.
 //
 // The op is bound by its OUTPUT (k floats written per row against 2*k*d flops), so the kernel is built around the
 // store: the roles of the operands are SWAPPED with respect to K1 -- the centres are the M side of the MMA (128 per
@@ -16,7 +16,7 @@
 // Rows and centres are centred on the pack's mu (distances are translation invariant; the norms that the
 // cancellation error scales with become those of the centred data).
 //
-// CTA = 320 threads, persistent, one per SM, 256 rows per block:
+// CTA = 320 threads, persistent, one per SM, 256 rows per block (128 for 64 < d <= 128):
 //   warp 0     : producer -- the 256-centre tiles of the pack's tcgen05 image, K-step block by K-step block (1-D bulk
 //                async copies through a 5-stage ring), once per 128-centre half
 //   warp 1     : tcgen05.mma M = 128 (centres), N = 256 (rows), K = 8, kind::tf32; two accumulator stages of 256 columns
@@ -26,9 +26,10 @@
 
 namespace {
 
-constexpr int CD_ROWS = 256;      // rows of X per block (N of the MMA)
+// rows of X per block (N of the MMA): 256 while a 256-row block (hi + lo parts) fits next to the ring (d <= 64),
+// 128 beyond that (d <= 128; two staging threads per row then)
 constexpr int CD_NST = 5;         // ring stages of 16 KB
-constexpr int CD_MAX_D = 64;      // a 256-row block (hi + lo parts) fits next to the ring up to here
+constexpr int CD_MAX_D = 128;
 
 __device__ __forceinline__ float sqrt_approx(float x) {
     float r;
@@ -46,10 +47,11 @@ struct CdBars {
     uint32_t tmem_base;
     uint32_t pad;
     alignas(16) float mu[CD_MAX_D];
+    float xn_part[128];            // CD_ROWS = 128: the second staging thread's half of ||x||^2
 };
 
 // MODE 0: squared distance, 1: distance, 2: exp(-gamma * squared distance)
-template <bool VEC, int MODE>
+template <bool VEC, int MODE, int CD_ROWS>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 cdist_tc_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx, const unsigned char *__restrict__ tc_img,
                 const float *__restrict__ mu, int k, float *__restrict__ out, int64_t ldo, float gamma) {
@@ -113,11 +115,12 @@ cdist_tc_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx, cons
         const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(CD_ROWS >> 3) << 17) |
                                ((uint32_t)(128 >> 4) << 24);
         const uint32_t desc_hi = (128u >> 4) | (1u << 14);           // SBO = 128 B, version = 1
-        const uint32_t lbo = ((256u * 16u) >> 4) << 16;              // both operands: 256 rows x 16 B per K chunk
+        const uint32_t lbo = ((256u * 16u) >> 4) << 16;              // centres: the image's 256 rows x 16 B per K chunk
+        const uint32_t xlbo = (((uint32_t)CD_ROWS * 16u) >> 4) << 16;   // rows: CD_ROWS x 16 B per K chunk
         const uint32_t xb_a = km_smem_u32(xb), bst_a = km_smem_u32(bst);
         const bool leader = elect_one();
         uint32_t it = 0, ita = 0, li = 0;
-        const uint32_t xh = ((xb_a & 0x3FFFFu) >> 4) | lbo;          // X (the B operand), hi parts
+        const uint32_t xh = ((xb_a & 0x3FFFFu) >> 4) | xlbo;         // X (the B operand), hi parts
         const uint32_t xl = xh + (xhi_bytes >> 4);
         for (int64_t blk = blockIdx.x; blk < nblocks; blk += gridDim.x, ++li) {
             mbar_wait_bounded(&bars->x_ready, li & 1);
@@ -154,17 +157,22 @@ cdist_tc_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx, cons
         }
     } else {
         // ================= row staging + epilogue (warps 2..9) =================
-        const int et = tid - 64;                 // 0..255: the row of the block this thread stages
+        // staging: CD_ROWS = 256 -> thread et stages row et; CD_ROWS = 128 -> two threads per row, alternate chunks
+        const int et = tid - 64;                 // 0..255
+        constexpr int TPR = 256 / CD_ROWS;       // staging threads per row
+        const int srow = et % CD_ROWS, shalf = et / CD_ROWS;
         const float ngamma = -gamma;
-        const int g = (warp - 2) >> 2;           // epilogue: column half (rows 0..127 / 128..255 of the block)
+        const int g = (warp - 2) >> 2;           // epilogue: column half of the accumulator (rows of the block)
         const int q4 = warp & 3;                 // epilogue: TMEM lane quarter (32 centres)
-        constexpr int NCHM = CD_MAX_D / 4;
+        constexpr int NCHM = 16;                 // chunks per staging thread: 64 features (x 2 threads at CD_ROWS = 128)
+        constexpr int EC = CD_ROWS / 64;         // 32-column chunks per epilogue warp
         float4 ld[NCHM];
         auto issue_loads = [&](int64_t blk) {
-            const int64_t row = blk * CD_ROWS + et;
+            const int64_t row = blk * CD_ROWS + srow;
             const float *src = X + row * ldx;
 #pragma unroll
-            for (int c = 0; c < NCHM; ++c) {
+            for (int i = 0; i < NCHM; ++i) {
+                const int c = i * TPR + shalf;
                 float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
                 if (c < nch && row < n) {
                     if (VEC) {
@@ -177,7 +185,7 @@ cdist_tc_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx, cons
                         v.w = f + 3 < d ? __ldg(src + f + 3) : 0.f;
                     }
                 }
-                ld[c] = v;
+                ld[i] = v;
             }
         };
         if ((int64_t)blockIdx.x < nblocks) issue_loads(blockIdx.x);
@@ -186,14 +194,15 @@ cdist_tc_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx, cons
             // ---- stage this block's rows: x - mu split into TF32 hi / exact lo parts, norms into the augmented chunks
             if (li > 0) mbar_wait_bounded(&bars->x_free, (li - 1) & 1);
             {
-                const bool live = blk * CD_ROWS + et < n;
-                unsigned char *ph = xb + (size_t)et * 16;
+                const bool live = blk * CD_ROWS + srow < n;
+                unsigned char *ph = xb + (size_t)srow * 16;
                 unsigned char *pl = ph + xhi_bytes;
                 float s = 0.f;
 #pragma unroll
-                for (int c = 0; c < NCHM; ++c) {
+                for (int i = 0; i < NCHM; ++i) {
+                    const int c = i * TPR + shalf;
                     if (c < nch) {
-                        float4 v = ld[c];
+                        float4 v = ld[i];
                         const float4 mq = *reinterpret_cast<const float4 *>(&bars->mu[c * 4]);
                         if (live) { v.x -= mq.x; v.y -= mq.y; v.z -= mq.z; v.w -= mq.w; }
                         // (features beyond d: the loads gave 0 and mu is zero padded, so they stay 0)
@@ -205,34 +214,41 @@ cdist_tc_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx, cons
                         *reinterpret_cast<float4 *>(pl + (size_t)c * (CD_ROWS * 16)) = l;
                     }
                 }
-                // augmented chunks: [1, 1, 1, xn_h] [xn_m, xn_l, 0, 0] against the image's [cn_h, cn_m, cn_l, 1] [1, 1, 0, 0]
-                const float sh = tf32_rna(s);
-                const float sm = tf32_rna(s - sh);
-                const float sl = (s - sh) - sm;
-                *reinterpret_cast<float4 *>(ph + (size_t)nch * (CD_ROWS * 16)) = make_float4(1.f, 1.f, 1.f, sh);
-                *reinterpret_cast<float4 *>(ph + (size_t)(nch + 1) * (CD_ROWS * 16)) = make_float4(sm, sl, 0.f, 0.f);
+                if (TPR == 2) {      // the row's two halves meet: the second thread publishes, the first adds
+                    if (shalf == 1) bars->xn_part[srow] = s;
+                    asm volatile("bar.sync 1, 256;" ::: "memory");
+                    if (shalf == 0) s += bars->xn_part[srow];
+                }
+                if (shalf == 0) {
+                    // augmented chunks: [1, 1, 1, xn_h] [xn_m, xn_l, 0, 0] against the image's [cn_h, cn_m, cn_l, 1] [1, 1, 0, 0]
+                    const float sh = tf32_rna(s);
+                    const float sm = tf32_rna(s - sh);
+                    const float sl = (s - sh) - sm;
+                    *reinterpret_cast<float4 *>(ph + (size_t)nch * (CD_ROWS * 16)) = make_float4(1.f, 1.f, 1.f, sh);
+                    *reinterpret_cast<float4 *>(ph + (size_t)(nch + 1) * (CD_ROWS * 16)) = make_float4(sm, sl, 0.f, 0.f);
+                }
                 km_fence_proxy_async();
                 mbar_arrive(&bars->x_ready);
             }
             const int64_t nblk = blk + gridDim.x;
             if (nblk < nblocks) issue_loads(nblk);       // lands while this block's stages are computed and stored
-            // ---- epilogue: one accumulator stage = 128 centres x 256 rows
-            const int64_t row0 = blk * CD_ROWS + g * 128;
+            // ---- epilogue: one accumulator stage = 128 centres x CD_ROWS rows
+            const int64_t row0 = blk * CD_ROWS + g * (CD_ROWS / 2);
             for (int s = 0; s < nst; ++s, ++ita) {
                 const int a = ita % TC_ASTAGES;
                 mbar_wait_bounded(&bars->a_full[a], (ita / TC_ASTAGES) & 1);
                 tc_fence_after();
                 const int j = s * 128 + q4 * 32 + lane;                 // this lane's centre
                 const bool jok = j < k;
-                const uint32_t tbase = tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(a * CD_ROWS + g * 128);
+                const uint32_t tbase = tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(a * CD_ROWS + g * (CD_ROWS / 2));
                 uint32_t ra[32], rb[32];
                 tmem_ld32(tbase, ra);
                 tmem_ld_wait();
 #pragma unroll
-                for (int c = 0; c < 4; ++c) {
+                for (int c = 0; c < EC; ++c) {
                     uint32_t (&cur)[32] = (c & 1) ? rb : ra;
                     uint32_t (&nxt)[32] = (c & 1) ? ra : rb;
-                    if (c + 1 < 4) tmem_ld32(tbase + (uint32_t)((c + 1) * 32), nxt);   // flies under this chunk's stores
+                    if (c + 1 < EC) tmem_ld32(tbase + (uint32_t)((c + 1) * 32), nxt);   // flies under this chunk's stores
                     const int64_t r0 = row0 + c * 32;
                     if (r0 < n) {                                        // warp-uniform
                         float *po = out + r0 * ldo + j;
@@ -257,7 +273,7 @@ cdist_tc_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx, cons
                                 if (jok && i < lim) po[(int64_t)i * ldo] = v[i];
                         }
                     }
-                    if (c + 1 < 4) tmem_ld_wait();
+                    if (c + 1 < EC) tmem_ld_wait();
                 }
                 tc_fence_before();
                 mbar_arrive(&bars->a_empty[a]);
@@ -284,24 +300,28 @@ int km_launch_cdist_tc(const float *X, int64_t n, int d, int64_t ldx, const void
     const KmPackLayout L = km_pack_layout(k, d);
     const unsigned char *pk = static_cast<const unsigned char *>(pack);
     const int nch = km_tc_kpad(d) / 4;
-    const size_t smem = (size_t)(nch + 2) * CD_ROWS * 16 + (size_t)nch * CD_ROWS * 16 + (size_t)CD_NST * KM_TC_KS_BYTES +
+    const int rows = d <= 64 ? 256 : 128;
+    const size_t smem = (size_t)(nch + 2) * rows * 16 + (size_t)nch * rows * 16 + (size_t)CD_NST * KM_TC_KS_BYTES +
                         sizeof(CdBars) + 64;
     const bool vec = (d % 4 == 0) && (ldx % 4 == 0) && ((reinterpret_cast<uintptr_t>(X) & 15) == 0);
     const unsigned char *img = pk + L.off_tc;
     const float *mu = reinterpret_cast<const float *>(pk + L.off_mu);
-    const int64_t nblocks = (n + CD_ROWS - 1) / CD_ROWS;
+    const int64_t nblocks = (n + rows - 1) / rows;
     const unsigned grid = (unsigned)(nblocks < km_num_sms() ? nblocks : km_num_sms());
-#define CD_LAUNCH(VEC_, MODE_)                                                                                     \
+#define CD_LAUNCH(VEC_, MODE_, ROWS_)                                                                              \
     {                                                                                                              \
         static bool attr[KM_MAX_DEVICES] = {};                                                                     \
-        if (int rc = km_set_smem_once(cdist_tc_kernel<VEC_, MODE_>, 227 * 1024, attr)) return rc;                  \
-        cdist_tc_kernel<VEC_, MODE_><<<grid, TC_THREADS, smem, st>>>(X, n, d, ldx, img, mu, k, out, ldo, gamma);    \
+        if (int rc = km_set_smem_once(cdist_tc_kernel<VEC_, MODE_, ROWS_>, 227 * 1024, attr)) return rc;           \
+        cdist_tc_kernel<VEC_, MODE_, ROWS_><<<grid, TC_THREADS, smem, st>>>(X, n, d, ldx, img, mu, k, out, ldo, gamma); \
     }
-    if (vec) {
-        if (mode == 0) CD_LAUNCH(true, 0) else if (mode == 1) CD_LAUNCH(true, 1) else CD_LAUNCH(true, 2)
+#define CD_LAUNCH_M(VEC_, ROWS_)                                                                                   \
+    if (mode == 0) CD_LAUNCH(VEC_, 0, ROWS_) else if (mode == 1) CD_LAUNCH(VEC_, 1, ROWS_) else CD_LAUNCH(VEC_, 2, ROWS_)
+    if (rows == 256) {
+        if (vec) { CD_LAUNCH_M(true, 256) } else { CD_LAUNCH_M(false, 256) }
     } else {
-        if (mode == 0) CD_LAUNCH(false, 0) else if (mode == 1) CD_LAUNCH(false, 1) else CD_LAUNCH(false, 2)
+        if (vec) { CD_LAUNCH_M(true, 128) } else { CD_LAUNCH_M(false, 128) }
     }
+#undef CD_LAUNCH_M
 #undef CD_LAUNCH
     return (int)cudaGetLastError();
 }

@@ -307,10 +307,10 @@ int b200km_cdist_f32(const float *X, int64_t n, int d, int64_t ldx, const float 
 int b200km_cdist_f64(const double *X, int64_t n, int d, int64_t ldx, const double *Y, int k,
                      const double *xnorm2, const double *ynorm2, double *out, int squared, void *stream);
 
-/* K7 on the tensor cores, for float32 rows of at most 64 features (else B200KM_ETOOBIG: use the entry points
+/* K7 on the tensor cores, for float32 rows of at most 128 features (else B200KM_ETOOBIG: use the entry points
  * above): out[i * ldo + j] = f(||x_i - c_j||^2), c_j the centres of a pack built by b200km_pack_centers (one-CTA
  * layout, i.e. not under B200KM_OPT_K1_VARIANT = 3), f by `mode`.  The op is bound by its output -- k floats per
- * row -- so the centres are the M side of the 3xTF32 tcgen05 MMA and 256 rows the N side: a warp of the epilogue
+ * row -- so the centres are the M side of the 3xTF32 tcgen05 MMA and 256 rows (128 beyond 64 features) the N side: a warp of the epilogue
  * holds 32 neighbouring centres of one row per register and every store writes 128 contiguous bytes.  Both squared
  * norms ride in an augmented K-step; rows and centres are centred on the pack's mu, so the cancellation error
  * scales with the spread of the data, not its distance from the origin (more accurate than the float32 expanded

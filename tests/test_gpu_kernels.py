@@ -227,9 +227,10 @@ def test_assign_lloyd_labels_match_full_assign(eng, n, d, k):
 
 @pytest.mark.parametrize("n,d,k,offset", [(5000, 64, 1024, 0.0), (3001, 32, 256, 0.0), (777, 7, 5, 0.0), (260, 64, 129, 0.0),
                                            (4096, 48, 300, 100.0), (10000, 16, 40, -1000.0), (300, 1, 3, 0.0),
-                                           (2000, 61, 1000, 5.0)])
+                                           (2000, 61, 1000, 5.0), (3000, 128, 700, 0.0), (1001, 100, 130, 20.0),
+                                           (500, 65, 64, 0.0)])
 def test_cdist_on_tensor_cores(eng, n, d, k, offset):
-    """K7's tcgen05 kernel (float32, d <= 64: b200km_cdist_pack_f32) against float64 numpy: squared distances,
+    """K7's tcgen05 kernel (float32, d <= 128: b200km_cdist_pack_f32) against float64 numpy: squared distances,
     distances and the rbf kernel, incl. ragged n / k / d, strided rows and data far from the origin (rows and centres
     are centred on the mean of the centres, so the error scales with the spread of the data); and against the FFMA
     tile kernel it replaces for these shapes (the reference evaluates the float32 expanded form, atol 1e-4 in its
