@@ -159,9 +159,11 @@ constexpr int SEG_MAX_K = 8192;
 // NARROW (d <= 32): a row is one 32-lane load, so the second feature half (fb, w[]) is compiled out and the
 // registers it frees buy a third resident CTA (C2: 2.39 -> 2.64 TB/s); wider rows do better with two (C3).
 // INERTIA: the run's centre row (float64, `cen`) is held by the lanes and every row adds (x - c)^2 to a float64
-// lane accumulator -- two more DFMA-pipe instructions per row per lane, hidden under the row gathers.
+// lane accumulator -- two more DFMA-pipe instructions per row per lane, hidden under the row gathers.  It needs more
+// registers than three resident CTAs leave (40: it spilled), so it runs two per SM -- which is also faster
+// (5e7 x 32 rows, k = 256: 2.16 -> 1.75 ms, 3.8 TB/s; tools/upd_inertia_bench.py).
 template <typename T, bool NARROW, bool INERTIA>
-__global__ void __launch_bounds__(SEG_THREADS, NARROW ? 3 : 2)
+__global__ void __launch_bounds__(SEG_THREADS, (NARROW && !INERTIA) ? 3 : 2)
 update_seg_kernel(const T *__restrict__ X, int64_t n, int d, int64_t ldx, const int32_t *__restrict__ labels,
                   const T *__restrict__ mind2, int k, double *__restrict__ acc, int scale_sqrt, int SEG_R,
                   const double *__restrict__ cen) {
