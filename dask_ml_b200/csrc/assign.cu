@@ -16,6 +16,7 @@
 //                        float64 X, for tiny k (HBM-bound regime), as the generic fallback and
 //                        (with row indirection) as the refine kernel.
 #include "common.cuh"
+#include <atomic>
 
 int km_launch_pack_tc(int k, int d, void *pack, cudaStream_t st);  // assign_tc.cu
 int km_launch_assign_tc(const float *X, int64_t n, int d, int64_t ldx, const void *pack, int k, int32_t *labels,
@@ -575,10 +576,12 @@ static int launch_tiled_f64(const TX *X, int64_t n, int d, int64_t ldx, const do
 // entry points
 // =============================================================================================
 
-static int g_k1_variant = 0;  // B200KM_OPT_K1_VARIANT: 0 auto, 1 FFMA, 2 tcgen05 (one CTA), 3 tcgen05 (CTA pair)
+// (atomics: the options are process-wide and may be set from one thread while another launches; a reader sees the old
+//  or the new value, never a torn one.  The pack layout follows variant 3, so set it BEFORE packing -- see the header.)
+static std::atomic<int> g_k1_variant{0};  // B200KM_OPT_K1_VARIANT: 0 auto, 1 FFMA, 2 tcgen05 (one CTA), 3 tcgen05 (CTA pair)
 bool km_tc_pair_mode() { return g_k1_variant == 3; }
 bool km_tc_small_enabled() { return g_k1_variant == 0; }   // auto only: variant 2 keeps the general tcgen05 kernel
-static int g_k2_variant = 0;  // B200KM_OPT_K2_VARIANT: 0 auto, 1 owner table, 2 chunk sort, 3 global atomics
+static std::atomic<int> g_k2_variant{0};  // B200KM_OPT_K2_VARIANT: 0 auto, 1 owner table, 2 chunk sort, 3 global atomics
 int km_k2_variant() { return g_k2_variant; }
 
 extern "C" int b200km_set_option(int key, int value) {
