@@ -578,12 +578,12 @@ def run_ours(args):
     cpu = None
     if world == 1 and not args.no_cpu:
         cores = os.cpu_count() or 1
-        n_s = args.cpu_rows or {"c3": 1_000_000, "c2": 2_000_000, "c1": 1_000_000, "c4": 100_000}[args.workload]
+        n_s = args.cpu_rows or {"c3": 4_000_000, "c2": 8_000_000, "c1": 1_000_000, "c4": 400_000}[args.workload]
         n_s = min(n_s, n_local)
         Xs = X[:n_s].cpu().numpy()
-        rate, sec = cpu_lloyd_step_rate(Xs, k, 2, cores)
+        rate, sec = cpu_lloyd_step_rate(Xs, k, 3, cores)
         cpu = {"value": rate, "unit": UNIT, "cores": cores, "kind": "port",
-               "sample": f"first {n_s} rows of the same device-generated blobs; 1 warm-up + 2 timed Lloyd iterations "
+               "sample": f"first {n_s} rows of the same device-generated blobs; 1 warm-up + 3 timed Lloyd iterations "
                          f"of oracle/kmeans_oracle.py (sklearn ArgKmin float64 + numba scatter, one row block per "
                          f"core, {cores} threads; the oracle is pinned to the unmodified reference modules by "
                          f"tests/test_reference_pin.py); {sec * 1e3:.1f} ms per iteration",
