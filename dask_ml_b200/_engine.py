@@ -172,13 +172,13 @@ class CudaEngine:
                    launches=3 if d <= 2048 else 2)
         return out
 
-    LLOYD_MAX_K, LLOYD_MAX_D = 256, 32
+    LLOYD_MAX_D = 128
 
     def lloyd_split(self, X: torch.Tensor, k: int, d: int) -> bool:
         """True where the Lloyd iteration runs as ``assign(..., lloyd=True)`` + ``update_inertia``: K1 decides the labels
-        only and K2 sums the inertia from the rows it reads anyway (float32 X on the small-k tensor-core kernel)."""
-        return (X.dtype == torch.float32 and 16 < k <= self.LLOYD_MAX_K and d <= self.LLOYD_MAX_D
-                and self.lib.b200km_get_option(_lib.OPT_K1_VARIANT) == _lib.K1_AUTO)
+        only and K2 sums the inertia from the rows it reads anyway (float32 X on the tensor-core kernels, d <= 128)."""
+        return (X.dtype == torch.float32 and k > 16 and d <= self.LLOYD_MAX_D
+                and self.lib.b200km_get_option(_lib.OPT_K1_VARIANT) in (_lib.K1_AUTO, _lib.K1_TCGEN05))
 
     def assign(self, X: torch.Tensor, pack: CenterPack, labels: Optional[torch.Tensor] = None,
                mind2: Optional[torch.Tensor] = None, want_mind2: bool = True, refine: bool = True,

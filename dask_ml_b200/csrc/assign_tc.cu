@@ -120,7 +120,10 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
                      const unsigned char *__restrict__ tc_img, const float *__restrict__ c32,
                      const float *__restrict__ mu, const unsigned int *__restrict__ cmax_bits, int k,
                      int32_t *__restrict__ labels, float *__restrict__ mind2,
-                     int32_t *__restrict__ flag_rows, int32_t *__restrict__ flag_count) {
+                     int32_t *__restrict__ flag_rows, int32_t *__restrict__ flag_count, int sparse_d2) {
+    // sparse_d2 != 0 (b200km_assign_lloyd_f32): the winner distance is not rebuilt here (K2 sums ||x - c||^2 itself);
+    // a flagged row gets ||x'||^2 + best score, which is what the pruned re-decision needs.  That drops the gather of
+    // the winner's centre row (256 B per row through L2) and the re-read of the staged row from every step.
     extern __shared__ __align__(1024) unsigned char tc_smem[];
     const int kpad = km_tc_kpad(d);
     const int nch = kpad / 4;                 // 16-byte K chunks of the real features
@@ -370,8 +373,9 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
             const unsigned char *ph = xb + (size_t)p_buf * xbuf_bytes + (size_t)rl * 16;
             const unsigned char *pl = ph + xhi_bytes;
             float s = 0.f;
+            if (!sparse_d2) {
 #pragma unroll
-            for (int c = 0; c < NCH_H; ++c) {
+              for (int c = 0; c < NCH_H; ++c) {
                 if (c < nch_h) {
                     const float4 h = *reinterpret_cast<const float4 *>(ph + (size_t)(c_lo + c) * 2048);
                     const float4 l = *reinterpret_cast<const float4 *>(pl + (size_t)(c_lo + c) * 2048);
@@ -382,6 +386,7 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
                     df = (h.z + l.z) - cc.z; s = fmaf(df, df, s);
                     df = (h.w + l.w) - cc.w; s = fmaf(df, df, s);
                 }
+              }
             }
             if (g == 1) {
                 bars->s_part[p_buf][rl] = s;
@@ -392,14 +397,16 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
                 s += bars->s_part[p_buf][rl];
                 if (p_row < n) {
                     labels[p_row] = p_bi;
-                    if (mind2) mind2[p_row] = s;
-                    if (flag_rows) {
-                        const float xn = bars->xn_part[p_buf][0][rl] + bars->xn_pub[p_buf][rl];
-                        const float thr = bound_scale * (xn + cmax);
-                        if (p_second - p_best <= thr) {
-                            const int pos = atomicAdd(flag_count, 1);
-                            flag_rows[pos] = (int32_t)p_row;
-                        }
+                    const float xn = bars->xn_part[p_buf][0][rl] + bars->xn_pub[p_buf][rl];
+                    const bool near_tie = flag_rows && (p_second - p_best <= bound_scale * (xn + cmax));
+                    if (sparse_d2) {
+                        if (mind2 && near_tie) mind2[p_row] = fmaxf(xn + p_best, 0.f);
+                    } else if (mind2) {
+                        mind2[p_row] = s;
+                    }
+                    if (near_tie) {
+                        const int pos = atomicAdd(flag_count, 1);
+                        flag_rows[pos] = (int32_t)p_row;
                     }
                 }
             }
@@ -489,7 +496,7 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
                 track_tile(0, it);
                 publish(xbuf, step * step_rows + crank * TC_ROWS + rl, li >> 1);
                 merge_pending();
-                issue_row_loads(ldc, c32 + (size_t)p_bi * d, true);
+                if (!sparse_d2) issue_row_loads(ldc, c32 + (size_t)p_bi * d, true);
             }
             if (pend) output_pending(ldc);
         } else {
@@ -506,7 +513,7 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
                     // loads issued here land while this tile's scores are being tracked
                     if (t == 0 && pend) {
                         merge_pending();
-                        issue_row_loads(ld, c32 + (size_t)p_bi * d, true);
+                        if (!sparse_d2) issue_row_loads(ld, c32 + (size_t)p_bi * d, true);
                     }
                     if (t == t_stage && have_next && !(t == 0 && pend))
                         issue_row_loads(ld, X + (nrow < n ? nrow : 0) * ldx, nrow < n);
@@ -524,7 +531,7 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
                 if (!DBUF) {
                     // one X buffer: write this step out now, then restage once the tensor core has let go of it
                     merge_pending();
-                    issue_row_loads(ld, c32 + (size_t)p_bi * d, true);
+                    if (!sparse_d2) issue_row_loads(ld, c32 + (size_t)p_bi * d, true);
                     output_pending(ld);
                     pend = false;
                     if (have_next) {
@@ -535,7 +542,7 @@ assign_tc_f32_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx,
             }
             if (pend) {
                 merge_pending();
-                issue_row_loads(ld, c32 + (size_t)p_bi * d, true);
+                if (!sparse_d2) issue_row_loads(ld, c32 + (size_t)p_bi * d, true);
                 output_pending(ld);
             }
         }
@@ -1695,13 +1702,14 @@ int km_launch_assign_tc(const float *X, int64_t n, int d, int64_t ldx, const voi
     attr1[0].val.clusterDim.z = 1;
     cfg.attrs = attr1;
     cfg.numAttrs = pair ? 1 : 0;
+    const int sparse_i = (sparse_d2 && flag_rows) ? 1 : 0;
 #define TC_LAUNCH(VEC_, DBUF_, PAIR_)                                                                      \
     {                                                                                                       \
         auto kern = assign_tc_f32_kernel<VEC_, DBUF_, PAIR_>;                                               \
         static bool attr[KM_MAX_DEVICES] = {};                                                              \
         if (int rc = km_set_smem_once(kern, 227 * 1024, attr)) return rc;                                   \
         cudaError_t le = cudaLaunchKernelEx(&cfg, kern, X, n, d, ldx, img, c32, mu, cmax, k, labels, mind2,     \
-                                            flag_rows, flag_count);                                         \
+                                            flag_rows, flag_count, sparse_i);                               \
         if (le != cudaSuccess) return (int)le;                                                              \
     }
 #define TC_LAUNCH_VD(PAIR_)                     \

@@ -198,7 +198,8 @@ def test_update_inertia(eng, n, d, k, dtype):
     npt.assert_allclose(a[k * d + k], want, rtol=1e-12)
 
 
-@pytest.mark.parametrize("n,d,k", [(20000, 32, 256), (5001, 32, 200), (30000, 16, 64), (7000, 7, 33), (4000, 32, 17)])
+@pytest.mark.parametrize("n,d,k", [(20000, 32, 256), (5001, 32, 200), (30000, 16, 64), (7000, 7, 33), (4000, 32, 17),
+                                    (20000, 64, 1024), (6000, 128, 1500), (9000, 48, 300), (5000, 100, 257)])
 def test_assign_lloyd_labels_match_full_assign(eng, n, d, k):
     """b200km_assign_lloyd_f32 (labels + near-tie flags only) gives the labels of b200km_assign_f32 after the
     float64 re-decision -- with both the pruned and the full re-decision -- on separated blobs and on one
