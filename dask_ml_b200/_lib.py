@@ -8,7 +8,7 @@ from __future__ import annotations
 
 import ctypes
 import os
-from ctypes import c_char_p, c_double, c_float, c_int, c_int32, c_int64, c_size_t, c_uint32, c_uint64, c_void_p
+from ctypes import c_char_p, c_double, c_float, c_int, c_int64, c_size_t, c_uint32, c_uint64, c_void_p
 
 __all__ = ["load", "check", "B200LibraryError", "B200KernelError", "LIB_PATH", "PROTOTYPES", "OPT_K1_VARIANT",
            "OPT_K2_VARIANT", "K1_AUTO", "K1_FFMA", "K1_TCGEN05", "K1_TCGEN05_PAIR"]

@@ -24,7 +24,6 @@ from __future__ import annotations
 
 import logging
 from numbers import Integral
-from typing import Optional
 
 import numpy as np
 import sklearn.cluster
