@@ -377,16 +377,29 @@ class CudaEngine:
 
     # ---- K4 .. K6 -------------------------------------------------------------------------
     MINDIST_MAX_M = 8
+    MINDIST_K1_MIN_M = 48        # from this many new candidates on, one K1 pass beats m / 8 passes of K4
 
     def mindist_update(self, X: torch.Tensor, cand: torch.Tensor, mind2: torch.Tensor, init: bool) -> torch.Tensor:
         """Running min of squared distances to ``cand`` rows; returns the (1,) float64 local cost."""
         n, d, ldx = self._check_matrix(X)
         sfx = _suffix(X)
-        cand = cand.to(X.dtype).contiguous()
         m = cand.shape[0]
-        per = max(1, min(self.MINDIST_MAX_M, (96 * 1024) // (d * X.element_size())))
         cost = torch.zeros(1, dtype=torch.float64, device=self.device)
         st = self._stream()
+        if m >= self.MINDIST_K1_MIN_M and n:
+            # many new candidates (a large oversampling factor): ONE K1 pass against all of them instead of m / 8
+            # passes of K4, then the merge into the running minimum
+            pack = self.pack(cand.to(torch.float64).contiguous())
+            lab = self._buf("mindist_labels", (n,), torch.int32)
+            other = self._buf("mindist_other", (n,), X.dtype)
+            self.assign(X, pack, lab, other)
+            for r0 in range(0, n, _MAX_ROWS_PER_CALL):
+                nn = min(_MAX_ROWS_PER_CALL, n - r0)
+                self._call(f"b200km_mindist_merge_{sfx}", other[r0 : r0 + nn].data_ptr(), nn,
+                           mind2[r0 : r0 + nn].data_ptr(), 1 if init else 0, cost.data_ptr(), st)
+            return cost
+        cand = cand.to(X.dtype).contiguous()
+        per = max(1, min(self.MINDIST_MAX_M, (96 * 1024) // (d * X.element_size())))
         first = init
         for j0 in range(0, m, per):
             cj = cand[j0 : j0 + per]

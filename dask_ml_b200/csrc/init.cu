@@ -274,6 +274,43 @@ extern "C" int b200km_mindist_update_f64(const double *X, int64_t n, int d, int6
     return mindist_impl<double>(X, n, d, ldx, cand, m, mind2, init, cost_out, stream);
 }
 
+// Many new candidates at once (a large oversampling factor: the paper's l = 2k brings ~2k picks per round): one K4
+// launch handles 8, so a round would cost m / 8 passes over X.  The host then takes K1 against the m candidates (one
+// tensor-core pass, the distance matrix never exists) and this kernel merges its winner distances into the running
+// minimum and sums the cost: mind2[i] = min(mind2[i], other[i]).
+template <typename T>
+__global__ void __launch_bounds__(256)
+mindist_merge_kernel(const T *__restrict__ other, int64_t n, T *__restrict__ mind2, int init, double *__restrict__ cost) {
+    __shared__ double red[32];
+    double c = 0.0;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        T v = __ldg(other + i);
+        if (!init) {
+            const T o = mind2[i];
+            v = o < v ? o : v;
+        }
+        mind2[i] = v;
+        c += (double)v;
+    }
+    km_block_atomic_add(c, cost, red);
+}
+template <typename T>
+static int mindist_merge_impl(const T *other, int64_t n, T *mind2, int init, double *cost, void *stream) {
+    KM_CHECK_ARG(other && mind2 && cost && n > 0, B200KM_EINVAL);
+    int64_t blocks = (n + 255) / 256;
+    if (blocks > km_num_sms() * 16) blocks = km_num_sms() * 16;
+    mindist_merge_kernel<T><<<(unsigned)blocks, 256, 0, km_stream(stream)>>>(other, n, mind2, init, cost);
+    KM_LAUNCH_RET();
+}
+extern "C" int b200km_mindist_merge_f32(const float *other, int64_t n, float *mind2, int init, double *cost_out,
+                                        void *stream) {
+    return mindist_merge_impl<float>(other, n, mind2, init, cost_out, stream);
+}
+extern "C" int b200km_mindist_merge_f64(const double *other, int64_t n, double *mind2, int init, double *cost_out,
+                                        void *stream) {
+    return mindist_merge_impl<double>(other, n, mind2, init, cost_out, stream);
+}
+
 // ---------------------------------------------------------------------------------------------
 // k-means++ trial potentials: pots[j] = sum_i min(mind2[i], ||x_i - cand_j||^2), mind2 left untouched.
 // Replaces, per k-means++ step, scikit-learn's `distance_to_candidates = euclidean_distances(X[candidate_ids], X)`

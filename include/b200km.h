@@ -262,6 +262,11 @@ int b200km_mindist_update_f32(const float *X, int64_t n, int d, int64_t ldx, con
                               int m, float *mind2, int init, double *cost_out, void *stream);
 int b200km_mindist_update_f64(const double *X, int64_t n, int d, int64_t ldx, const double *cand,
                               int m, double *mind2, int init, double *cost_out, void *stream);
+/* The same update when the distances to the new candidates come from somewhere else (K1 against MANY candidates at
+ * once -- an oversampling factor in the thousands -- instead of m / 8 passes of the kernel above):
+ * mind2[i] = min(mind2[i], other[i]) (init != 0: mind2[i] = other[i]); cost_out += sum_i mind2[i]. */
+int b200km_mindist_merge_f32(const float *other, int64_t n, float *mind2, int init, double *cost_out, void *stream);
+int b200km_mindist_merge_f64(const double *other, int64_t n, double *mind2, int init, double *cost_out, void *stream);
 /* k-means++ trial potentials: pots[j] += sum_i min(mind2[i], ||x_i - cand_j||^2) for m <= B200KM_MINDIST_MAX_M
  * candidates, mind2 untouched (pots must be zeroed by the caller).  Replaces, per k-means++ step, the
  * (trials x n) distance matrix + np.minimum + potential sums of scikit-learn's _kmeans_plusplus, which the

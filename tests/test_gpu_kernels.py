@@ -267,6 +267,31 @@ def test_cdist_on_tensor_cores(eng, n, d, k, offset):
     npt.assert_allclose(got2, ffma, rtol=1e-3, atol=1e-4 * max(1.0, (offset * offset * d)))
 
 
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+def test_mindist_many_candidates_goes_through_k1(eng, dtype):
+    """From 48 new candidates on (a large oversampling factor) the running minimum is updated by ONE K1 pass against all
+    of them + b200km_mindist_merge_* instead of m / 8 passes of K4: same minima, same cost."""
+    import torch
+
+    X, _ = blobs(30000, 20, 9, seed=5, dtype=dtype)
+    Xd = eng.to_device(X)
+    tol = 3e-5 if dtype == np.float32 else 1e-10
+    mind2 = torch.empty(len(X), dtype=Xd.dtype, device=eng.device)
+    eng.mindist_update(Xd, Xd[:1], mind2, init=True)
+    cand = X[np.random.RandomState(1).choice(len(X), 300, replace=False)]
+    launches0 = eng.launches
+    cost = eng.mindist_update(Xd, eng.to_device(cand), mind2, init=False).item()
+    assert eng.launches - launches0 < 20                       # not 300 / 8 passes of K4
+    allc = np.vstack([X[:1], cand])
+    d2 = sklearn.metrics.pairwise_distances(X.astype(np.float64), allc.astype(np.float64), metric="sqeuclidean").min(1)
+    npt.assert_allclose(mind2.cpu().numpy(), d2, rtol=tol * 3, atol=tol * d2.max())
+    npt.assert_allclose(cost, d2.sum(), rtol=tol)
+    # init form (no old minima)
+    cost0 = eng.mindist_update(Xd, eng.to_device(cand), mind2, init=True).item()
+    d20 = sklearn.metrics.pairwise_distances(X.astype(np.float64), cand.astype(np.float64), metric="sqeuclidean").min(1)
+    npt.assert_allclose(cost0, d20.sum(), rtol=tol)
+
+
 def test_cdist_on_tensor_cores_long_second_operand(eng):
     """SpectralClustering's B block: 100 kept rows against many rows.  The long side becomes the streamed operand
     (roles swapped, the result handed back as the transposed view of what was written): same values."""

@@ -354,6 +354,26 @@ def test_candidate_weights_and_weighted_recluster(dtype):
     npt.assert_allclose(C_w, want, rtol=1e-12)
 
 
+def test_init_scalable_large_oversampling_matches_oracle():
+    """The paper's setting, l = 2k: hundreds of picks per round (K1 + merge for the running minimum, the pick buffer
+    grown on demand).  Same Philox draws -> the oracle's candidates and, after scikit-learn's re-cluster of them with
+    the same seed, its centres."""
+    import importlib
+
+    kmod = importlib.import_module("dask_ml_b200.cluster.k_means")
+    X, _ = blobs(20000, 8, 30, seed=12, dtype=np.float64)
+    k, l = 60, 120
+    rs = kmod.PhiloxRandomState(9)
+    C = kmod.init_scalable(X, k, rs, 3, l)
+    trace = []
+    Co = orc.init_scalable(X, k, orc.PhiloxDraws(9), 3, l, "auto", (len(X),), trace=trace)
+    want = [np.array(t["picked"], dtype=np.int64) for t in trace if "picked" in t]
+    assert len(rs.picks) == len(want) == 3 and max(len(w) for w in want) > 48
+    for got, w in zip(rs.picks, want):
+        npt.assert_array_equal(got, w)
+    npt.assert_allclose(C, Co, rtol=1e-9)
+
+
 def test_evaluate_cost_and_sample_points_match_oracle():
     from dask_ml_b200.cluster.k_means import _sample_points, evaluate_cost
 
