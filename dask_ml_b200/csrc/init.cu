@@ -218,7 +218,9 @@ static int mindist_impl(const T *X, int64_t n, int d, int64_t ldx, const T *cand
         const int dv = d / VECW;
         int64_t cap = (int64_t)km_num_sms() * 8;
 #define MDV_LAUNCH(LPR_, U_)  /* U_ <= LPR_: every row of a warp step needs an owner lane */                   \
-    if (m <= 2) MDV_LAUNCH2(LPR_, (2 * U_ <= LPR_ ? 2 * U_ : U_), 2) else MDV_LAUNCH2(LPR_, U_, MD_MAXM)
+    if (m <= 2) MDV_LAUNCH2(LPR_, (2 * U_ <= LPR_ ? 2 * U_ : U_), 2)                                             \
+    else if (m <= 4) MDV_LAUNCH2(LPR_, (2 * U_ <= LPR_ ? 2 * U_ : U_), 4)                                       \
+    else MDV_LAUNCH2(LPR_, U_, MD_MAXM)
 #define MDV_LAUNCH2(LPR_, U_, MM_)                                                                               \
     {                                                                                                            \
         auto kern = mindist_vec_kernel<T, LPR_, U_, MM_>;                                                        \

@@ -17,12 +17,17 @@ mind2 = torch.empty(n, device=eng.device)
 for _ in range(2):
     cost = eng.mindist_update(X, X[:1], mind2, init=True)
     cost = eng.mindist_update(X, X[7:9], mind2, init=False)
+    cost = eng.mindist_update(X, X[20:26], mind2, init=False)     # six new candidates in one launch
+    cost = eng.mindist_update(X, X[30:33], mind2, init=False)     # three
     eng.bernoulli(mind2, 2.0 / float(cost.item()), 1, 0, 0)
 # C2 shape: K2
 n2, d2, k2 = 20_000_000, 32, 256
 X2 = torch.randn(n2, d2, device=eng.device); l2 = torch.randint(0, k2, (n2,), device=eng.device, dtype=torch.int32)
+C2c = torch.randn(k2, d2, device=eng.device, dtype=torch.float64)
+acc2 = torch.zeros(eng.acc_len(k2, d2), dtype=torch.float64, device=eng.device)
 for _ in range(2):
     eng.update(X2, l2, None, k2)
+    eng.update_inertia(X2, l2, C2c, k2, acc2)     # the form the Lloyd iteration uses since round 2
 # C1 shape: fused K1+K2
 n1, d1, k1 = 1_000_000, 16, 8
 X1 = torch.randn(n1, d1, device=eng.device, dtype=torch.float64)
