@@ -316,12 +316,11 @@ def lloyd_bench(torch, dist, eng, comm, args, workload, steps, warmup, local_ran
 
     one_launch = fused and world == 1
     ticket = torch.zeros(1, dtype=torch.int32, device=dev)
-    out2 = torch.zeros(2, dtype=torch.float64, device=dev)
 
     def step(c_old, c_new):
         if one_launch:   # single GPU, tiny k and d: the whole iteration is one launch (same branch as _kmeans_single_lloyd)
-            eng.lloyd_small(X, c_old, labels, mind2, acc, ticket, c_new, out2)
-            return float(out2[0].item())
+            shift, state["inertia"] = eng.lloyd_small(X, c_old, labels, mind2, acc, ticket, c_new)
+            return shift
         acc.zero_()
         if fused:   # HBM-bound regime: K1+K2 in one pass (same branch as _kmeans_single_lloyd)
             eng.assign_update(X, c_old, labels, mind2, acc)
@@ -371,7 +370,7 @@ def lloyd_bench(torch, dist, eng, comm, args, workload, steps, warmup, local_ran
     eng.k1_events = None
     flagged = eng.flagged_count() if not fused and dtype_s == "float32" else 0
     if one_launch:   # acc comes back zeroed: the counts are checked through one separate pass
-        inertia = float(out2[1].item())
+        inertia = float(state["inertia"])
         chk = torch.zeros_like(acc)
         eng.assign_update(X, c_b, labels, mind2, chk)
         counts_ok = int(round(float(chk[k * d : k * d + k].sum().item()))) == n_local * world

@@ -343,19 +343,43 @@ class CudaEngine:
                 self.k1_events.append((e0, e1))
 
     def lloyd_small(self, X: torch.Tensor, centers64: torch.Tensor, labels: torch.Tensor, mind2: torch.Tensor,
-                    acc: torch.Tensor, ticket: torch.Tensor, centers_new: torch.Tensor, shift_inertia: torch.Tensor) -> None:
+                    acc: torch.Tensor, ticket: torch.Tensor, centers_new: torch.Tensor) -> Tuple[float, float]:
         """b200km_lloyd_small_*: one whole iteration (assign + sums + counts + inertia + divide + shift) in one launch.
-        ``acc`` / ``ticket`` (int32[1]) must be zero on entry and come back zero; single GPU, X resident (n < 2^30)."""
+        ``acc`` / ``ticket`` (int32[1]) must be zero on entry and come back zero; single GPU, X resident (n < 2^30).
+        Returns (shift, inertia): the kernel writes them into page-locked host memory followed by this call's tag, and
+        the host polls for the tag instead of synchronising the stream (falls back to a synchronisation after 2 s)."""
         n, d, ldx = self._check_matrix(X)
+        if not hasattr(self, "_ls_host"):
+            self._ls_host = torch.zeros(3, dtype=torch.float64).pin_memory()
+            self._ls_view = self._ls_host.numpy()
+            self._ls_tag = 0.0
+        self._ls_tag += 1.0
+        tag = self._ls_tag
         if self.k1_events is not None:
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
         self._call(f"b200km_lloyd_small_{_suffix(X)}", X.data_ptr(), n, d, ldx, centers64.data_ptr(), centers64.shape[0],
                    labels.data_ptr(), mind2.data_ptr(), acc.data_ptr(), ticket.data_ptr(), centers_new.data_ptr(),
-                   shift_inertia.data_ptr(), self._stream())
+                   self._ls_host.data_ptr(), tag, self._stream())
         if self.k1_events is not None:
             e1.record()
             self.k1_events.append((e0, e1))
+        view = self._ls_view
+        deadline = None
+        spins = 0
+        while view[2] != tag:
+            spins += 1
+            if (spins & 0xFFFF) == 0:
+                import time
+
+                now = time.perf_counter()
+                if deadline is None:
+                    deadline = now + 2.0
+                elif now > deadline:      # a failed launch never writes the tag: let the synchronisation report it
+                    torch.cuda.current_stream(self.device).synchronize()
+                    if view[2] != tag:
+                        raise _lib.B200KernelError("b200km_lloyd_small: the iteration's result never arrived")
+        return float(view[0]), float(view[1])
 
     def finalize(self, acc: torch.Tensor, k: int, d: int, centers_old: torch.Tensor,
                  centers_new: Optional[torch.Tensor] = None, shift: Optional[torch.Tensor] = None):

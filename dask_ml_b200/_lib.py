@@ -62,8 +62,8 @@ PROTOTYPES = {
     "b200km_update_inertia_f64": (c_int, [_P, c_int64, c_int, c_int64, _P, _P, c_int, _P, _P]),
     "b200km_assign_update_f32": (c_int, [_P, c_int64, c_int, c_int64, _P, c_int, _P, _P, _P, _P]),
     "b200km_assign_update_f64": (c_int, [_P, c_int64, c_int, c_int64, _P, c_int, _P, _P, _P, _P]),
-    "b200km_lloyd_small_f32": (c_int, [_P, c_int64, c_int, c_int64, _P, c_int, _P, _P, _P, _P, _P, _P, _P]),
-    "b200km_lloyd_small_f64": (c_int, [_P, c_int64, c_int, c_int64, _P, c_int, _P, _P, _P, _P, _P, _P, _P]),
+    "b200km_lloyd_small_f32": (c_int, [_P, c_int64, c_int, c_int64, _P, c_int, _P, _P, _P, _P, _P, _P, c_double, _P]),
+    "b200km_lloyd_small_f64": (c_int, [_P, c_int64, c_int, c_int64, _P, c_int, _P, _P, _P, _P, _P, _P, c_double, _P]),
     "b200km_reduce_sum_f32": (c_int, [_P, c_int64, c_int, _P, _P]),
     "b200km_reduce_sum_f64": (c_int, [_P, c_int64, c_int, _P, _P]),
     "b200km_finalize": (c_int, [_P, c_int, c_int, _P, _P, _P, _P]),

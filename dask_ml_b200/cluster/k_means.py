@@ -631,7 +631,7 @@ def _kmeans_single_lloyd(X, n_clusters, max_iter=300, init="k-means||", verbose=
                   and getattr(eng, "can_fuse", lambda *_: False)(k, P) and 0 < n_local < (1 << 30))
     if one_launch:
         ticket = torch.zeros(1, dtype=torch.int32, device=eng.device)
-        out2 = torch.zeros(2, dtype=torch.float64, device=eng.device)
+        inertia_one = 0.0
     acc_dirty = False
     last_one = False
     for i in range(max_iter):
@@ -640,8 +640,8 @@ def _kmeans_single_lloyd(X, n_clusters, max_iter=300, init="k-means||", verbose=
                 if acc_dirty:
                     acc.zero_()
                     acc_dirty = False
-                eng.lloyd_small(X, centers64, labels, mind2, acc, ticket, new64, out2)  # :576-605
-                shift = float(out2[0].item())  # :602 -- the one round trip per iteration
+                # :576-605; the shift comes back through page-locked memory the kernel writes (:602 -- the one round trip)
+                shift, inertia_one = eng.lloyd_small(X, centers64, labels, mind2, acc, ticket, new64)
                 last_one = True
                 logger.info("Shift: %0.4f", shift)
                 if shift < tol:
@@ -704,7 +704,7 @@ def _kmeans_single_lloyd(X, n_clusters, max_iter=300, init="k-means||", verbose=
         inertia_t = eng.reduce_sum(mind2, sqrt=True)
         comm.allreduce_sum_(inertia_t)
     elif last_one:
-        inertia_t = out2[1:2].clone()
+        inertia_t = torch.tensor([inertia_one], dtype=torch.float64, device=eng.device)
     else:
         inertia_t = acc[acc_n - 1 : acc_n].clone()
     inertia = DeviceArray(inertia_t.reshape(()))  # :616

@@ -598,7 +598,8 @@ template <typename TX, int DMAX>
 __global__ void __launch_bounds__(FU_R, DMAX <= 16 ? FU_OCC16 : 3)
 assign_update_small_kernel(const TX *__restrict__ X, int64_t n, int d, int64_t ldx, const double *__restrict__ c64,
                            int k, int32_t *__restrict__ labels, TX *__restrict__ mind2, double *__restrict__ acc,
-                           unsigned int *__restrict__ done, double *__restrict__ cnew, double *__restrict__ out2) {
+                           unsigned int *__restrict__ done, double *__restrict__ cnew, double *__restrict__ out2,
+                           double tag) {
     extern __shared__ __align__(16) double fu_smem[];
     const int xld = d + 1;
     double *xs = fu_smem;                            // [FU_R][d+1]
@@ -766,8 +767,14 @@ assign_update_small_kernel(const TX *__restrict__ X, int64_t n, int d, int64_t l
     if (tid == 0) {
         double t = 0.0;
         for (int w = 0; w < FU_R / 32; ++w) t += red[w];
-        out2[0] = t;
-        out2[1] = __ldcg(acc + ncell + k);
+        // out2 may be page-locked HOST memory the GPU writes directly: [shift, inertia] first, then -- after a
+        // system-scope fence -- the caller's tag, so a host that polls out2[2] sees complete values without
+        // synchronising the stream (the 8-byte read back is the only per-iteration round trip left)
+        volatile double *o = out2;
+        o[0] = t;
+        o[1] = __ldcg(acc + ncell + k);
+        __threadfence_system();
+        o[2] = tag;
         *done = 0u;
     }
     __syncthreads();
@@ -777,7 +784,7 @@ assign_update_small_kernel(const TX *__restrict__ X, int64_t n, int d, int64_t l
 template <typename TX>
 static int assign_update_impl(const TX *X, int64_t n, int d, int64_t ldx, const double *centers_f64, int k,
                               int32_t *labels, TX *mind2, double *acc, void *stream, unsigned int *done = nullptr,
-                              double *cnew = nullptr, double *out2 = nullptr) {
+                              double *cnew = nullptr, double *out2 = nullptr, double tag = 0.0) {
     KM_CHECK_ARG(X && centers_f64 && labels && acc, B200KM_EINVAL);
     KM_CHECK_ARG(n > 0 && d > 0 && k > 0 && ldx >= d, B200KM_EINVAL);
     KM_CHECK_ARG(k <= FU_MAXK && d <= FU_MAXD, B200KM_ETOOBIG);
@@ -790,29 +797,29 @@ static int assign_update_impl(const TX *X, int64_t n, int d, int64_t ldx, const 
         static bool attr_set[KM_MAX_DEVICES] = {};
         if (int rc = km_set_smem_once(kern, 80 * 1024, attr_set)) return rc;
         kern<<<(unsigned)blocks, FU_R, smem, km_stream(stream)>>>(X, n, d, ldx, centers_f64, k, labels, mind2, acc, done, cnew,
-                                                                  out2);
+                                                                  out2, tag);
     } else {
         auto kern = assign_update_small_kernel<TX, FU_MAXD>;
         static bool attr_set[KM_MAX_DEVICES] = {};
         if (int rc = km_set_smem_once(kern, 80 * 1024, attr_set)) return rc;
         kern<<<(unsigned)blocks, FU_R, smem, km_stream(stream)>>>(X, n, d, ldx, centers_f64, k, labels, mind2, acc, done, cnew,
-                                                                  out2);
+                                                                  out2, tag);
     }
     KM_LAUNCH_RET();
 }
 extern "C" int b200km_lloyd_small_f32(const float *X, int64_t n, int d, int64_t ldx, const double *centers_f64, int k,
                                       int32_t *labels, float *mind2, double *acc, unsigned int *ticket,
-                                      double *centers_new, double *shift_inertia, void *stream) {
+                                      double *centers_new, double *shift_inertia, double tag, void *stream) {
     KM_CHECK_ARG(ticket && centers_new && shift_inertia, B200KM_EINVAL);
     return assign_update_impl<float>(X, n, d, ldx, centers_f64, k, labels, mind2, acc, stream, ticket, centers_new,
-                                     shift_inertia);
+                                   shift_inertia, tag);
 }
 extern "C" int b200km_lloyd_small_f64(const double *X, int64_t n, int d, int64_t ldx, const double *centers_f64, int k,
                                       int32_t *labels, double *mind2, double *acc, unsigned int *ticket,
-                                      double *centers_new, double *shift_inertia, void *stream) {
+                                      double *centers_new, double *shift_inertia, double tag, void *stream) {
     KM_CHECK_ARG(ticket && centers_new && shift_inertia, B200KM_EINVAL);
     return assign_update_impl<double>(X, n, d, ldx, centers_f64, k, labels, mind2, acc, stream, ticket, centers_new,
-                                      shift_inertia);
+                                   shift_inertia, tag);
 }
 extern "C" int b200km_assign_update_f32(const float *X, int64_t n, int d, int64_t ldx, const double *centers_f64,
                                         int k, int32_t *labels, float *mind2, double *acc, void *stream) {

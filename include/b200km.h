@@ -228,16 +228,18 @@ int b200km_assign_update_f64(const double *X, int64_t n, int d, int64_t ldx, con
                              int32_t *labels, double *mind2, double *acc, void *stream);
 /* The whole Lloyd iteration of that regime in ONE launch, for a single GPU (no allreduce between the sums and the
  * division): b200km_assign_update_* and, by the CTA that finishes last, K3 -- centers_new = sums / max(count, 1),
- * shift_inertia[0] = ||centers_f64 - centers_new||_F^2, shift_inertia[1] = the iteration's inertia.  `acc`
- * (b200km_acc_len doubles) and `ticket` (one uint32) are scratch that must be ZERO on entry and are zero again on
- * return, so consecutive iterations need no memset between them.
+ * shift_inertia[0] = ||centers_f64 - centers_new||_F^2, shift_inertia[1] = the iteration's inertia, and then, after
+ * a system-scope fence, shift_inertia[2] = tag.  shift_inertia (3 doubles) may be page-locked host memory (UVA: the
+ * GPU writes it directly); a host that passes a fresh tag per call can poll shift_inertia[2] for it and read the
+ * shift without synchronising the stream.  `acc` (b200km_acc_len doubles) and `ticket` (one uint32) are scratch
+ * that must be ZERO on entry and are zero again on return, so consecutive iterations need no memset between them.
  * Replaces: one trip round the loop body R/dask_ml/cluster/k_means.py:576-605. */
 int b200km_lloyd_small_f32(const float *X, int64_t n, int d, int64_t ldx, const double *centers_f64, int k,
                            int32_t *labels, float *mind2, double *acc, unsigned int *ticket, double *centers_new,
-                           double *shift_inertia, void *stream);
+                           double *shift_inertia, double tag, void *stream);
 int b200km_lloyd_small_f64(const double *X, int64_t n, int d, int64_t ldx, const double *centers_f64, int k,
                            int32_t *labels, double *mind2, double *acc, unsigned int *ticket, double *centers_new,
-                           double *shift_inertia, void *stream);
+                           double *shift_inertia, double tag, void *stream);
 
 /* out[0] += sum_i v[i]  (or sum_i sqrt(v[i]) when take_sqrt != 0), float64; caller zeroes out.
  * Replaces: distances.sum() (R/dask_ml/cluster/k_means.py:616) on the non-squared final pass. */
