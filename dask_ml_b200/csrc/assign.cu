@@ -583,6 +583,8 @@ bool km_tc_pair_mode() { return g_k1_variant == 3; }
 bool km_tc_small_enabled() { return g_k1_variant == 0; }   // auto only: variant 2 keeps the general tcgen05 kernel
 static std::atomic<int> g_k2_variant{0};  // B200KM_OPT_K2_VARIANT: 0 auto, 1 owner table, 2 chunk sort, 3 global atomics
 int km_k2_variant() { return g_k2_variant; }
+static std::atomic<int> g_fused_variant{0};  // B200KM_OPT_FUSED_VARIANT: 0 auto, 1 sorted-tile kernel, 2 cp.async kernel where it fits
+int km_fused_variant() { return g_fused_variant; }
 
 extern "C" int b200km_set_option(int key, int value) {
     if (key == B200KM_OPT_K1_VARIANT && value >= 0 && value <= 3) {
@@ -593,11 +595,16 @@ extern "C" int b200km_set_option(int key, int value) {
         g_k2_variant = value;
         return 0;
     }
+    if (key == B200KM_OPT_FUSED_VARIANT && value >= 0 && value <= 2) {
+        g_fused_variant = value;
+        return 0;
+    }
     return B200KM_EINVAL;
 }
 extern "C" int b200km_get_option(int key) {
     if (key == B200KM_OPT_K1_VARIANT) return g_k1_variant;
     if (key == B200KM_OPT_K2_VARIANT) return g_k2_variant;
+    if (key == B200KM_OPT_FUSED_VARIANT) return g_fused_variant;
     return B200KM_EINVAL;
 }
 

@@ -585,6 +585,51 @@ constexpr int FU_R = 256;        // rows per tile == threads per CTA
 constexpr int FU_MAXK = 16;
 constexpr int FU_MAXD = 32;
 
+// Tail of the fused kernels when the whole iteration is ONE launch (b200km_lloyd_small_*; single GPU; done != nullptr):
+// the CTA that finishes last divides the sums by the counts (K3, k_means.py:600-605), leaves [shift, inertia] in out2
+// and hands acc and the ticket back zeroed for the next iteration -- no memset, no finalize launch between two
+// iterations.  Called by every thread of the CTA after its REDs into acc; `red` = 32 doubles of shared memory.
+__device__ __forceinline__ void fu_last_cta_finalize(double *__restrict__ acc, int ncell, int k, int d,
+                                                     const double *__restrict__ c64, unsigned int *__restrict__ done,
+                                                     double *__restrict__ cnew, double *__restrict__ out2, double tag,
+                                                     double *red) {
+    if (done == nullptr) return;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nthr = blockDim.x;
+    __shared__ unsigned int ticket;
+    __threadfence();                                   // this CTA's REDs are visible before its ticket
+    __syncthreads();
+    if (tid == 0) ticket = atomicAdd(done, 1u);
+    __syncthreads();
+    if (ticket != gridDim.x - 1) return;
+    __threadfence();
+    double sh = 0.0;
+    for (int e = tid; e < ncell; e += nthr) {
+        const double cnt = fmax(__ldcg(acc + ncell + e / d), 1.0);     // :600 (L2: other CTAs wrote these)
+        const double v = __ldcg(acc + e) / cnt;                         // :601
+        cnew[e] = v;
+        const double df = c64[e] - v;                                   // :605
+        sh = fma(df, df, sh);
+    }
+    sh = km_warp_sum(sh);
+    if (lane == 0) red[warp] = sh;
+    __syncthreads();                                   // (also: every thread has read its acc entries)
+    if (tid == 0) {
+        double t = 0.0;
+        for (int w = 0; w < nthr / 32; ++w) t += red[w];
+        // out2 may be page-locked HOST memory the GPU writes directly: [shift, inertia] first, then -- after a
+        // system-scope fence -- the caller's tag, so a host that polls out2[2] sees complete values without
+        // synchronising the stream (the 8-byte read back is the only per-iteration round trip left)
+        volatile double *o = out2;
+        o[0] = t;
+        o[1] = __ldcg(acc + ncell + k);
+        __threadfence_system();
+        o[2] = tag;
+        *done = 0u;
+    }
+    __syncthreads();
+    for (int e = tid; e < ncell + k + 1; e += nthr) acc[e] = 0.0;
+}
+
 template <typename TX, int DMAX>
 // d <= 16: four resident CTAs per SM and no register prefetch of the next tile (measured at C1, 1e6 x 16 float64,
 // k = 8: 2 CTAs + prefetch 0.092 ms, 3 + prefetch 0.108 (spills), 3 without 0.084, 4 without 0.080 -- the kernel is
@@ -742,43 +787,195 @@ assign_update_small_kernel(const TX *__restrict__ X, int64_t n, int d, int64_t l
     if (tid + FU_R < ncell && cell1 != 0.0) atomicAdd(acc + tid + FU_R, cell1);
     if (tid < k && mycount != 0.0) atomicAdd(acc + ncell + tid, mycount);
     km_block_atomic_add(inert, acc + ncell + k, red);
-    if (done == nullptr) return;
-    // ---- whole iteration in ONE launch (b200km_lloyd_small_*; single GPU): the CTA that finishes last divides the
-    // sums by the counts (K3, k_means.py:600-605), leaves [shift, inertia] in out2 and hands acc and the ticket back
-    // zeroed for the next iteration -- no memset, no finalize launch between two iterations.
-    __shared__ unsigned int ticket;
-    __threadfence();                                   // this CTA's REDs are visible before its ticket
+    fu_last_cta_finalize(acc, ncell, k, d, c64, done, cnew, out2, tag, red);
+}
+
+// ---------------------------------------------------------------------------------------------
+// The same pass for rows of exactly 64 or 128 bytes (d = 16 / 32 float32, d = 8 / 16 float64 -- C1), 16-byte aligned.
+//   staging : cp.async (LDGSTS, 16 bytes per thread and instruction) into one of two shared-memory buffers: the next
+//             tile lands while this one is worked on and no register holds it on the way.  The 16-byte chunks of a
+//             row are XOR-swizzled by the row number, so the thread-per-row reads of phase A (128-bit loads, 8 lanes
+//             per shared-memory phase, rows 64 / 128 bytes apart) hit eight different bank groups.
+//   phase A : thread per row, float64 direct-form distances -- the arithmetic, in the order, of the kernel above.
+//   phase B : sums = onehot(labels)^T . X on the FP64 tensor cores (mma.sync m8n8k4, DMMA): every warp multiplies the
+//             one-hot matrix of ITS 32 rows' labels (clusters x rows, built from the labels by one shuffle + select per
+//             four rows) with those rows (read back from shared memory in fragment order) and keeps the
+//             clusters x features accumulator fragments in registers for the CTA's whole life -- 16 DMMAs per warp
+//             and tile at C1 instead of a sort and 32-row dependent chains; warp-local, so one block barrier per tile
+//             instead of five.  Counts: one shared-memory integer RED per row.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void fu_cp_async16(void *smem_dst, const void *gmem_src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(km_smem_u32(smem_dst)), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void fu_cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void fu_cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
+// D (8x8, float64) += A (8x4, row major) . B (4x8, column major); lane l holds A[l >> 2][l & 3], B[l & 3][l >> 2] and
+// D[l >> 2][2 * (l & 3) + {0, 1}]
+__device__ __forceinline__ void fu_dmma884(double &d0, double &d1, double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0, %1}, {%2}, {%3}, {%0, %1};"
+                 : "+d"(d0), "+d"(d1)
+                 : "d"(a), "d"(b));
+}
+
+template <typename TX, int D, int KMAX>
+__global__ void __launch_bounds__(FU_R, (KMAX <= 8 && D * sizeof(TX) <= 128 && D <= 16) ? 3 : 2)
+assign_update_bulk_kernel(const TX *__restrict__ X, int64_t n, int64_t ldx, const double *__restrict__ c64, int k,
+                          int32_t *__restrict__ labels, TX *__restrict__ mind2, double *__restrict__ acc,
+                          unsigned int *__restrict__ done, double *__restrict__ cnew, double *__restrict__ out2,
+                          double tag) {
+    constexpr int RB = D * (int)sizeof(TX);     // row bytes: 64 or 128
+    constexpr int CPR = RB / 16;                // 16-byte chunks per row: 4 or 8
+    constexpr int EPC = 16 / (int)sizeof(TX);   // elements per chunk
+    static_assert(CPR == 4 || CPR == 8, "rows of 64 or 128 bytes");
+    extern __shared__ __align__(128) unsigned char fb_smem[];
+    unsigned char *xs = fb_smem;                                              // [2][FU_R][RB], chunks swizzled
+    double *cs = reinterpret_cast<double *>(fb_smem + 2 * FU_R * RB);         // [KMAX][D]
+    int *cnt_s = reinterpret_cast<int *>(cs + KMAX * D);                      // [KMAX]
+    __shared__ double red[32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (int e = tid; e < KMAX * D; e += FU_R) cs[e] = e < k * D ? c64[e] : 0.0;
+    if (tid < KMAX) cnt_s[tid] = 0;
+    // swizzle of row r: chunk c is stored at position c ^ sw(r); sw(r) = r & 7 (128-byte rows), (r >> 1) & 3 (64-byte)
+    auto sw = [](int r) { return CPR == 8 ? (r & 7) : ((r >> 1) & 3); };
+
+    // staging: chunk e = tid + FU_R * i of the tile (consecutive threads -> consecutive 16-byte pieces of X)
+    const int st_c = tid % CPR, st_r0 = tid / CPR;
+    auto issue = [&](int64_t base, int b) {
+        const int64_t left = n - base;
+        unsigned char *dstb = xs + (size_t)b * FU_R * RB;
+#pragma unroll
+        for (int i = 0; i < CPR; ++i) {
+            const int r = st_r0 + (FU_R / CPR) * i;
+            if (r < left) fu_cp_async16(dstb + r * RB + ((st_c ^ sw(r)) << 4), X + (base + r) * ldx + st_c * EPC);
+        }
+        fu_cp_async_commit();
+    };
+
+    constexpr int MB = KMAX / 8, NB = D / 8;                // 8-cluster and 8-feature blocks of the sums
+    double cell[MB][NB][2];                                 // clusters 8 mb + (lane >> 2), features 8 nb + 2 (lane & 3) + {0, 1}
+#pragma unroll
+    for (int mb = 0; mb < MB; ++mb)
+#pragma unroll
+        for (int nb = 0; nb < NB; ++nb) cell[mb][nb][0] = cell[mb][nb][1] = 0.0;
+    double inert = 0.0;
+    const int pa_sw = sw(tid);
+    const int l4 = lane & 3, l8 = lane >> 2;
+
+    const int64_t stride = (int64_t)gridDim.x * FU_R;
+    int64_t base = (int64_t)blockIdx.x * FU_R;
+    if (base < n) issue(base, 0);
+    for (int it = 0; base < n; base += stride, ++it) {
+        const int b = it & 1;
+        const int rows = (int)((n - base) < FU_R ? (n - base) : FU_R);
+        fu_cp_async_wait_all();
+        __syncthreads();          // the tile has landed for every thread; phase B of the previous tile is over
+        if (base + stride < n) issue(base + stride, b ^ 1);
+        const unsigned char *xb = xs + (size_t)b * FU_R * RB;
+        // ---- phase A: argmin (lowest index on ties) -------------------------------------------
+        int lab = -1;
+        if (tid < rows) {
+            const unsigned char *xrow = xb + tid * RB;
+            double xr[D];
+#pragma unroll
+            for (int j = 0; j < CPR; ++j) {
+                const unsigned char *p = xrow + ((j ^ pa_sw) << 4);
+                if constexpr (sizeof(TX) == 8) {
+                    const double2 v = *reinterpret_cast<const double2 *>(p);
+                    xr[j * 2] = v.x; xr[j * 2 + 1] = v.y;
+                } else {
+                    const float4 v = *reinterpret_cast<const float4 *>(p);
+                    xr[j * 4] = (double)v.x; xr[j * 4 + 1] = (double)v.y;
+                    xr[j * 4 + 2] = (double)v.z; xr[j * 4 + 3] = (double)v.w;
+                }
+            }
+            double best = INFINITY;
+            for (int c = 0; c < k; ++c) {
+                const double *cr = cs + c * D;
+                double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+                for (int f = 0; f < D; f += 2) {
+                    const double2 cv = *reinterpret_cast<const double2 *>(cr + f);
+                    const double d0 = xr[f] - cv.x, d1 = xr[f + 1] - cv.y;
+                    s0 = fma(d0, d0, s0);
+                    s1 = fma(d1, d1, s1);
+                }
+                const double s = s0 + s1;
+                if (s < best) { best = s; lab = c; }
+            }
+            labels[base + tid] = lab;
+            if (mind2) mind2[base + tid] = (TX)best;
+            inert += best;
+            if (lab >= 0) atomicAdd(&cnt_s[lab], 1);   // (lab < 0: a row of NaNs, as in the kernel above)
+        }
+        // ---- phase B: sums += onehot(labels)^T . X for this warp's 32 rows (lane l holds the label of row 32 warp + l)
+        {
+            // a row without a label (beyond the tile's end: stale shared memory; or all-NaN distances) must add
+            // nothing, and 0 * NaN would not: such warps zero those rows' values on the way in
+            const bool sanitize = __any_sync(0xffffffffu, lab < 0);
+            const unsigned char *xw = xb + (size_t)warp * 32 * RB;
+#pragma unroll
+            for (int ks = 0; ks < 8; ++ks) {                 // rows 4 ks .. 4 ks + 3 of the warp
+                const int rr = 4 * ks + l4;                 // this lane's row of the B fragment
+                const int lr = __shfl_sync(0xffffffffu, lab, rr);
+                const unsigned char *xrow = xw + rr * RB;
+                const int rsw = sw(warp * 32 + rr);
+                double a[MB];
+#pragma unroll
+                for (int mb = 0; mb < MB; ++mb) a[mb] = lr == 8 * mb + l8 ? 1.0 : 0.0;
+#pragma unroll
+                for (int nb = 0; nb < NB; ++nb) {
+                    const int f = 8 * nb + l8;
+                    double x = (double)*reinterpret_cast<const TX *>(xrow + (((f / EPC) ^ rsw) << 4) +
+                                                                     (f % EPC) * (int)sizeof(TX));
+                    if (sanitize && lr < 0) x = 0.0;
+#pragma unroll
+                    for (int mb = 0; mb < MB; ++mb) fu_dmma884(cell[mb][nb][0], cell[mb][nb][1], a[mb], x);
+                }
+            }
+        }
+    }
+    // ---- flush: the warps' accumulator fragments through shared memory, then one RED per cell and CTA -------
+    __syncthreads();                                        // every thread is done with xs
+    double *wtab = reinterpret_cast<double *>(xs);          // [FU_R / 32][KMAX][D]
+#pragma unroll
+    for (int mb = 0; mb < MB; ++mb)
+#pragma unroll
+        for (int nb = 0; nb < NB; ++nb) {
+            double *w = wtab + ((size_t)warp * KMAX + 8 * mb + l8) * D + 8 * nb + 2 * l4;
+            w[0] = cell[mb][nb][0];
+            w[1] = cell[mb][nb][1];
+        }
     __syncthreads();
-    if (tid == 0) ticket = atomicAdd(done, 1u);
-    __syncthreads();
-    if (ticket != gridDim.x - 1) return;
-    __threadfence();
-    double sh = 0.0;
+    const int ncell = k * D;
     for (int e = tid; e < ncell; e += FU_R) {
-        const double cnt = fmax(__ldcg(acc + ncell + e / d), 1.0);     // :600 (L2: other CTAs wrote these)
-        const double v = __ldcg(acc + e) / cnt;                         // :601
-        cnew[e] = v;
-        const double df = c64[e] - v;                                   // :605
-        sh = fma(df, df, sh);
-    }
-    sh = km_warp_sum(sh);
-    if (lane == 0) red[warp] = sh;
-    __syncthreads();                                   // (also: every thread has read its acc entries)
-    if (tid == 0) {
+        const int c = e / D, f = e % D;
         double t = 0.0;
-        for (int w = 0; w < FU_R / 32; ++w) t += red[w];
-        // out2 may be page-locked HOST memory the GPU writes directly: [shift, inertia] first, then -- after a
-        // system-scope fence -- the caller's tag, so a host that polls out2[2] sees complete values without
-        // synchronising the stream (the 8-byte read back is the only per-iteration round trip left)
-        volatile double *o = out2;
-        o[0] = t;
-        o[1] = __ldcg(acc + ncell + k);
-        __threadfence_system();
-        o[2] = tag;
-        *done = 0u;
+#pragma unroll
+        for (int w = 0; w < FU_R / 32; ++w) t += wtab[(w * KMAX + c) * D + f];
+        if (t != 0.0) atomicAdd(acc + e, t);
     }
-    __syncthreads();
-    for (int e = tid; e < ncell + k + 1; e += FU_R) acc[e] = 0.0;
+    if (tid < k && cnt_s[tid] != 0) atomicAdd(acc + ncell + tid, (double)cnt_s[tid]);
+    km_block_atomic_add(inert, acc + ncell + k, red);
+    fu_last_cta_finalize(acc, ncell, k, D, c64, done, cnew, out2, tag, red);
+}
+
+int km_fused_variant();  // assign.cu (b200km_set_option)
+
+template <typename TX, int D, int KMAX>
+static int launch_bulk(const TX *X, int64_t n, int64_t ldx, const double *c64, int k, int32_t *labels, TX *mind2,
+                       double *acc, cudaStream_t st, unsigned int *done, double *cnew, double *out2, double tag) {
+    auto kern = assign_update_bulk_kernel<TX, D, KMAX>;
+    constexpr int RB = D * (int)sizeof(TX);
+    constexpr int OCC = (KMAX <= 8 && RB <= 128 && D <= 16) ? 3 : 2;
+    const size_t smem = (size_t)2 * FU_R * RB + sizeof(double) * KMAX * D + sizeof(int) * (FU_R + KMAX);
+    static bool attr_set[KM_MAX_DEVICES] = {};
+    if (int rc = km_set_smem_once(kern, 80 * 1024, attr_set)) return rc;
+    int64_t blocks = (n + FU_R - 1) / FU_R;
+    const int64_t cap = (int64_t)km_num_sms() * OCC;
+    if (blocks > cap) blocks = cap;
+    kern<<<(unsigned)blocks, FU_R, smem, st>>>(X, n, ldx, c64, k, labels, mind2, acc, done, cnew, out2, tag);
+    KM_LAUNCH_RET();
 }
 
 template <typename TX>
@@ -788,6 +985,18 @@ static int assign_update_impl(const TX *X, int64_t n, int d, int64_t ldx, const 
     KM_CHECK_ARG(X && centers_f64 && labels && acc, B200KM_EINVAL);
     KM_CHECK_ARG(n > 0 && d > 0 && k > 0 && ldx >= d, B200KM_EINVAL);
     KM_CHECK_ARG(k <= FU_MAXK && d <= FU_MAXD, B200KM_ETOOBIG);
+    // rows of 64 / 128 bytes, 16-byte aligned: the cp.async kernel (B200KM_OPT_FUSED_VARIANT 1 keeps the sorted-tile one)
+    const int rb = d * (int)sizeof(TX);
+    if (km_fused_variant() != 1 && (rb == 64 || rb == 128) && (reinterpret_cast<uintptr_t>(X) & 15) == 0 &&
+        (ldx * sizeof(TX)) % 16 == 0) {
+        cudaStream_t st = km_stream(stream);
+        constexpr int DS = sizeof(TX) == 8 ? 8 : 16, DL = 2 * DS;   // the two row widths of this element type
+        if (d == DS)
+            return k <= 8 ? launch_bulk<TX, DS, 8>(X, n, ldx, centers_f64, k, labels, mind2, acc, st, done, cnew, out2, tag)
+                          : launch_bulk<TX, DS, 16>(X, n, ldx, centers_f64, k, labels, mind2, acc, st, done, cnew, out2, tag);
+        return k <= 8 ? launch_bulk<TX, DL, 8>(X, n, ldx, centers_f64, k, labels, mind2, acc, st, done, cnew, out2, tag)
+                      : launch_bulk<TX, DL, 16>(X, n, ldx, centers_f64, k, labels, mind2, acc, st, done, cnew, out2, tag);
+    }
     int64_t blocks = (n + FU_R - 1) / FU_R;
     const int64_t cap = (int64_t)km_num_sms() * (d <= 16 ? FU_OCC16 : 4);   // resident CTAs per SM of the two variants
     if (blocks > cap) blocks = cap;

@@ -53,6 +53,8 @@ extern "C" {
                                   * 3 = the general tcgen05 kernel on CTA pairs (cta_group::2).
                                   * Set it BEFORE b200km_pack_centers: the tensor-core image differs for 3. */
 #define B200KM_OPT_K2_VARIANT 2 /* 0 = auto, 1 = shared-memory owner table, 2 = chunk sort + run sums, 3 = global atomics */
+#define B200KM_OPT_FUSED_VARIANT 3 /* fused K1+K2 (k <= 16, d <= 32): 0 = auto, 1 = the sorted-tile kernel always,
+                                     * 2 = same as auto (the cp.async kernel for 16-byte aligned rows of 64 / 128 bytes) */
 int b200km_set_option(int key, int value);
 int b200km_get_option(int key);
 

@@ -418,6 +418,77 @@ def test_assign_update_fused(eng, n, d, k, dtype):
                           labels[:4], mind2[:4], acc)
 
 
+@pytest.mark.parametrize("n,d,k,dtype,pad", [(100001, 16, 8, np.float64, 0), (5000, 16, 16, np.float64, 0),
+                                             (70001, 8, 5, np.float64, 0), (33333, 8, 13, np.float64, 2),
+                                             (90000, 16, 3, np.float32, 0), (1234, 16, 16, np.float32, 4),
+                                             (300001, 32, 8, np.float32, 0), (65537, 32, 16, np.float32, 8),
+                                             (255, 16, 8, np.float64, 0), (1, 16, 1, np.float64, 0)])
+def test_fused_kernels_agree(eng, n, d, k, dtype, pad):
+    """The cp.async fused kernel (rows of 64 / 128 bytes, 16-byte aligned) against the sorted-tile one
+    (B200KM_OPT_FUSED_VARIANT = 1): same arithmetic in phase A, so labels and distances are bit-equal; the float64
+    sums differ only in the order of the additions.  ``pad`` > 0: rows with a leading dimension of d + pad."""
+    import torch
+
+    from dask_ml_b200 import _lib
+
+    X, C = blobs(n, d, k, seed=3 * n + k, dtype=dtype)
+    C = C + 0.1
+    full = eng.to_device(np.concatenate([X, np.zeros((n, pad), dtype)], axis=1)) if pad else eng.to_device(X)
+    Xd = full[:, :d]
+    assert Xd.stride(0) == d + pad
+    Cd = eng.to_device(C, torch.float64)
+    out = {}
+    try:
+        for variant in (1, 0):
+            assert eng.lib.b200km_set_option(_lib.OPT_FUSED_VARIANT, variant) == 0
+            labels = torch.full((n,), -1, dtype=torch.int32, device=eng.device)
+            mind2 = torch.zeros(n, dtype=Xd.dtype, device=eng.device)
+            acc = torch.zeros(eng.acc_len(k, d), dtype=torch.float64, device=eng.device)
+            eng.assign_update(Xd, Cd, labels, mind2, acc)
+            out[variant] = (labels.cpu().numpy(), mind2.cpu().numpy(), acc.cpu().numpy())
+    finally:
+        eng.lib.b200km_set_option(_lib.OPT_FUSED_VARIANT, 0)
+    npt.assert_array_equal(out[0][0], out[1][0])
+    npt.assert_array_equal(out[0][1], out[1][1])
+    a0, a1 = out[0][2], out[1][2]
+    npt.assert_array_equal(a0[k * d : k * d + k], a1[k * d : k * d + k])
+    npt.assert_allclose(a0[: k * d], a1[: k * d], rtol=1e-13, atol=1e-11 * max(np.abs(a1[: k * d]).max(), 1.0))
+    npt.assert_allclose(a0[-1], a1[-1], rtol=1e-13)
+    lab_ref, _ = orc.pairwise_distances_argmin_min(X, C, metric_kwargs={"squared": True})
+    assert not ((out[0][0] != lab_ref) & ~_near_tie_mask(X, C, 1e-12)).any()
+    sums = orc.centers_dense(X, out[0][0].astype(np.int32), k)
+    npt.assert_allclose(a0[: k * d].reshape(k, d), sums, rtol=1e-12, atol=1e-9 * max(np.abs(sums).max(), 1.0))
+
+
+@pytest.mark.parametrize("dtype,d,k", [(np.float64, 16, 8), (np.float32, 32, 16), (np.float64, 5, 3)])
+def test_lloyd_small_one_launch_matches_separate_steps(eng, dtype, d, k):
+    """b200km_lloyd_small_* (one launch: assign + sums + divide + shift, result through page-locked memory) against
+    assign_update + finalize, on the shapes of both fused kernels; acc and the ticket come back zeroed."""
+    import torch
+
+    n = 50001
+    X, C = blobs(n, d, k, seed=11 + d, dtype=dtype)
+    Xd = eng.to_device(X)
+    Cd = eng.to_device(C + 0.3, torch.float64)
+    labels = torch.empty(n, dtype=torch.int32, device=eng.device)
+    mind2 = torch.empty(n, dtype=Xd.dtype, device=eng.device)
+    acc = torch.zeros(eng.acc_len(k, d) + 1, dtype=torch.float64, device=eng.device)
+    ticket = torch.zeros(1, dtype=torch.int32, device=eng.device)
+    new = torch.empty_like(Cd)
+    shift, inertia = eng.lloyd_small(Xd, Cd, labels, mind2, acc, ticket, new)
+    assert int(ticket.item()) == 0 and float(acc.abs().max().item()) == 0.0
+    l2 = torch.empty_like(labels)
+    m2 = torch.empty_like(mind2)
+    acc2 = torch.zeros(eng.acc_len(k, d), dtype=torch.float64, device=eng.device)
+    eng.assign_update(Xd, Cd, l2, m2, acc2)
+    inertia2 = float(acc2[-1].item())
+    new2, shift2 = eng.finalize(acc2, k, d, Cd)
+    assert torch.equal(labels, l2) and torch.equal(mind2, m2)
+    npt.assert_allclose(new.cpu().numpy(), new2.cpu().numpy(), rtol=1e-13, atol=1e-13)
+    npt.assert_allclose(shift, float(shift2.item()), rtol=1e-10)
+    npt.assert_allclose(inertia, inertia2, rtol=1e-13)
+
+
 def test_datasets_make_blobs_api(eng):
     """dask_ml_b200.datasets.make_blobs: reference signature (dask_ml/datasets.py:78-205), device output."""
     from dask_ml_b200.datasets import make_blobs
