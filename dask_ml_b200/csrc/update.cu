@@ -17,6 +17,7 @@
 //       table (L2-resident), counts via one RED per row.
 #include "common.cuh"
 #include <cooperative_groups.h>
+#include <type_traits>
 namespace cg = cooperative_groups;
 
 int km_k2_variant();  // assign.cu (b200km_set_option)
@@ -796,13 +797,18 @@ assign_update_small_kernel(const TX *__restrict__ X, int64_t n, int d, int64_t l
 //             tile lands while this one is worked on and no register holds it on the way.  The 16-byte chunks of a
 //             row are XOR-swizzled by the row number, so the thread-per-row reads of phase A (128-bit loads, 8 lanes
 //             per shared-memory phase, rows 64 / 128 bytes apart) hit eight different bank groups.
-//   phase A : thread per row, float64 direct-form distances -- the arithmetic, in the order, of the kernel above.
+//   phase A : scores = (||c'||^2 + 2 mu . c') - 2 x . c' on the FP64 tensor cores (DMMA m8n8k4: 8 rows x 8 clusters x 4
+//             features; c' = c - mu, mu the mean of the centres -- |x - c|^2 minus a per-row constant; the -2 c' fragments
+//             and the cluster constants live in registers for the whole kernel); the four lanes that share a row
+//             reduce (score, index) by two butterfly steps -- lowest index on ties, as above -- and then rebuild the
+//             winner's distance in the DIRECT form sum (x - c)^2 from the raw values they already hold, so the
+//             distances keep the accuracy of the kernel above.
 //   phase B : sums = onehot(labels)^T . X on the FP64 tensor cores (mma.sync m8n8k4, DMMA): every warp multiplies the
 //             one-hot matrix of ITS 32 rows' labels (clusters x rows, built from the labels by one shuffle + select per
 //             four rows) with those rows (read back from shared memory in fragment order) and keeps the
 //             clusters x features accumulator fragments in registers for the CTA's whole life -- 16 DMMAs per warp
 //             and tile at C1 instead of a sort and 32-row dependent chains; warp-local, so one block barrier per tile
-//             instead of five.  Counts: one shared-memory integer RED per row.
+//             instead of five.  Counts: the one-hot predicates, counted in integer registers.
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ void fu_cp_async16(void *smem_dst, const void *gmem_src) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(km_smem_u32(smem_dst)), "l"(gmem_src) : "memory");
@@ -827,40 +833,102 @@ assign_update_bulk_kernel(const TX *__restrict__ X, int64_t n, int64_t ldx, cons
     constexpr int RB = D * (int)sizeof(TX);     // row bytes: 64 or 128
     constexpr int CPR = RB / 16;                // 16-byte chunks per row: 4 or 8
     constexpr int EPC = 16 / (int)sizeof(TX);   // elements per chunk
+    constexpr int ES = (int)sizeof(TX);
     static_assert(CPR == 4 || CPR == 8, "rows of 64 or 128 bytes");
     extern __shared__ __align__(128) unsigned char fb_smem[];
     unsigned char *xs = fb_smem;                                              // [2][FU_R][RB], chunks swizzled
-    double *cs = reinterpret_cast<double *>(fb_smem + 2 * FU_R * RB);         // [KMAX][D]
-    int *cnt_s = reinterpret_cast<int *>(cs + KMAX * D);                      // [KMAX]
+    // centre rows padded by 4 doubles: the eight row groups of a warp gather 32-byte pieces of (mostly) different
+    // centres in the distance rebuild, and rows a multiple of 128 bytes apart would all sit on the same banks
+    constexpr int CLD = D + 4;
+    double *cs = reinterpret_cast<double *>(fb_smem + 2 * FU_R * RB);         // [KMAX][CLD]
     __shared__ double red[32];
+    __shared__ double mu_s[32], cn_s[FU_MAXK];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    for (int e = tid; e < KMAX * D; e += FU_R) cs[e] = e < k * D ? c64[e] : 0.0;
-    if (tid < KMAX) cnt_s[tid] = 0;
-    // swizzle of row r: chunk c is stored at position c ^ sw(r); sw(r) = r & 7 (128-byte rows), (r >> 1) & 3 (64-byte)
+    const int l4 = lane & 3, l8 = lane >> 2;
+    for (int e = tid; e < KMAX * D; e += FU_R) cs[(e / D) * CLD + e % D] = e < k * D ? c64[e] : 0.0;
+    // swizzle of row r: chunk c is stored at position c ^ sw(r); sw(r) = r & 7 (128-byte rows), (r >> 1) & 3 (64-byte).
+    // Every row set used below is a fixed row plus a multiple of 8, so each thread's swizzles are loop constants.
     auto sw = [](int r) { return CPR == 8 ? (r & 7) : ((r >> 1) & 3); };
+    auto xoff = [&](int r, int f) { return r * RB + (((f / EPC) ^ sw(r)) << 4) + (f % EPC) * ES; };
 
+    // ---- constants of the score MMAs: centring vector (mean of the centres), c' = c - mu, and per cluster
+    //      ||c'||^2 + 2 mu . c'  (so that the A operand is the RAW row: |x - c|^2 = [row constant] + this - 2 x . c')
+    __syncthreads();
+    if (tid < D) {
+        double m = 0.0;
+        for (int c = 0; c < k; ++c) m += cs[c * CLD + tid];
+        mu_s[tid] = m / (double)k;
+    }
+    __syncthreads();
+    if (tid < KMAX) {
+        double q = INFINITY;                                // a padded cluster never wins
+        if (tid < k) {
+            q = 0.0;
+            for (int f = 0; f < D; ++f) { const double t = cs[tid * CLD + f] - mu_s[f]; q = fma(t, t + 2.0 * mu_s[f], q); }
+        }
+        cn_s[tid] = q;
+    }
+    __syncthreads();
+    constexpr int MB = KMAX / 8, NB = D / 8;                // 8-cluster and 8-feature blocks
+    constexpr int KS = D / 4;                               // K-steps of the score MMAs (4 features each)
+    double bq[MB][KS], cnq[MB][2];
+#pragma unroll
+    for (int ks = 0; ks < KS; ++ks)
+#pragma unroll
+        for (int mb = 0; mb < MB; ++mb)                      // B[feature 4 ks + l4][cluster 8 mb + l8] = -2 c'
+            bq[mb][ks] = 8 * mb + l8 < k ? -2.0 * (cs[(8 * mb + l8) * CLD + 4 * ks + l4] - mu_s[4 * ks + l4]) : 0.0;
+#pragma unroll
+    for (int mb = 0; mb < MB; ++mb) {
+        cnq[mb][0] = cn_s[8 * mb + 2 * l4];
+        cnq[mb][1] = cn_s[8 * mb + 2 * l4 + 1];
+    }
+    double cell[MB][NB][2];                                 // sums: clusters 8 mb + l8, features 8 nb + 2 l4 + {0, 1}
+    int icnt[MB];                                           // rows of cluster 8 mb + l8 among this lane's B-fragment rows
+#pragma unroll
+    for (int mb = 0; mb < MB; ++mb) {
+        icnt[mb] = 0;
+#pragma unroll
+        for (int nb = 0; nb < NB; ++nb) cell[mb][nb][0] = cell[mb][nb][1] = 0.0;
+    }
+    double inert = 0.0;
+
+    // ---- per-thread byte offsets (shared-memory window of the warp's 32 rows) ---------------------------------
+    // phase A: lane (l8, l4) holds row 8 mbr + l8, features 4 ks + l4
+    uint32_t offA[KS];
+#pragma unroll
+    for (int ks = 0; ks < KS; ++ks) offA[ks] = (uint32_t)xoff(l8, 4 * ks + l4);
+    // phase B: the four rows of a K-step are picked so that, under the swizzle, the fragment load spreads over all
+    // the banks: rows 8 (ks >> 1) + {0, 2, 4, 6} + (ks & 1) for 128-byte rows, {0, 1, 4, 5} + 2 (ks & 1) for 64-byte
+    // rows (consecutive rows would fold onto half of them); lane (l8, l4) holds row 8 (ks >> 1) + r7[ks & 1], feature 8 nb + l8
+    int r7[2];
+    uint32_t offB[2][NB];
+#pragma unroll
+    for (int pp = 0; pp < 2; ++pp) {
+        r7[pp] = CPR == 8 ? 2 * l4 + pp : (l4 & 1) + 4 * (l4 >> 1) + 2 * pp;
+#pragma unroll
+        for (int nb = 0; nb < NB; ++nb) offB[pp][nb] = (uint32_t)xoff(r7[pp], 8 * nb + l8);
+    }
     // staging: chunk e = tid + FU_R * i of the tile (consecutive threads -> consecutive 16-byte pieces of X)
+    constexpr int SROWS = FU_R / CPR;                       // rows between two chunks of one thread
     const int st_c = tid % CPR, st_r0 = tid / CPR;
+    const uint32_t sdst = km_smem_u32(xs) + (uint32_t)xoff(st_r0, st_c * EPC);
+    const int64_t gstep = (int64_t)SROWS * ldx;
     auto issue = [&](int64_t base, int b) {
         const int64_t left = n - base;
-        unsigned char *dstb = xs + (size_t)b * FU_R * RB;
+        const TX *src = X + (base + st_r0) * ldx + st_c * EPC;
+        const uint32_t dst = sdst + (uint32_t)b * (FU_R * RB);
+        if (left >= FU_R) {
 #pragma unroll
-        for (int i = 0; i < CPR; ++i) {
-            const int r = st_r0 + (FU_R / CPR) * i;
-            if (r < left) fu_cp_async16(dstb + r * RB + ((st_c ^ sw(r)) << 4), X + (base + r) * ldx + st_c * EPC);
+            for (int i = 0; i < CPR; ++i)
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + i * SROWS * RB), "l"(src + i * gstep) : "memory");
+        } else {
+#pragma unroll
+            for (int i = 0; i < CPR; ++i)
+                if (st_r0 + SROWS * i < left)
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + i * SROWS * RB), "l"(src + i * gstep) : "memory");
         }
         fu_cp_async_commit();
     };
-
-    constexpr int MB = KMAX / 8, NB = D / 8;                // 8-cluster and 8-feature blocks of the sums
-    double cell[MB][NB][2];                                 // clusters 8 mb + (lane >> 2), features 8 nb + 2 (lane & 3) + {0, 1}
-#pragma unroll
-    for (int mb = 0; mb < MB; ++mb)
-#pragma unroll
-        for (int nb = 0; nb < NB; ++nb) cell[mb][nb][0] = cell[mb][nb][1] = 0.0;
-    double inert = 0.0;
-    const int pa_sw = sw(tid);
-    const int l4 = lane & 3, l8 = lane >> 2;
 
     const int64_t stride = (int64_t)gridDim.x * FU_R;
     int64_t base = (int64_t)blockIdx.x * FU_R;
@@ -871,69 +939,79 @@ assign_update_bulk_kernel(const TX *__restrict__ X, int64_t n, int64_t ldx, cons
         fu_cp_async_wait_all();
         __syncthreads();          // the tile has landed for every thread; phase B of the previous tile is over
         if (base + stride < n) issue(base + stride, b ^ 1);
-        const unsigned char *xb = xs + (size_t)b * FU_R * RB;
-        // ---- phase A: argmin (lowest index on ties) -------------------------------------------
-        int lab = -1;
-        if (tid < rows) {
-            const unsigned char *xrow = xb + tid * RB;
-            double xr[D];
+        const unsigned char *xw = xs + (size_t)b * FU_R * RB + (size_t)warp * 32 * RB;   // this warp's 32 rows
+        // ---- phase A: four blocks of 8 rows ------------------------------------------------------------------
+        int lab4[4];                                        // label of row 8 mbr + l8 (the same in the row's 4 lanes)
+        bool unlabelled = false;
 #pragma unroll
-            for (int j = 0; j < CPR; ++j) {
-                const unsigned char *p = xrow + ((j ^ pa_sw) << 4);
-                if constexpr (sizeof(TX) == 8) {
-                    const double2 v = *reinterpret_cast<const double2 *>(p);
-                    xr[j * 2] = v.x; xr[j * 2 + 1] = v.y;
-                } else {
-                    const float4 v = *reinterpret_cast<const float4 *>(p);
-                    xr[j * 4] = (double)v.x; xr[j * 4 + 1] = (double)v.y;
-                    xr[j * 4 + 2] = (double)v.z; xr[j * 4 + 3] = (double)v.w;
-                }
-            }
+        for (int mbr = 0; mbr < 4; ++mbr) {
+            const int rt = warp * 32 + 8 * mbr + l8;        // row within the tile
+            double xa[KS], sc[MB][2];
+#pragma unroll
+            for (int ks = 0; ks < KS; ++ks) xa[ks] = (double)*reinterpret_cast<const TX *>(xw + mbr * 8 * RB + offA[ks]);
+#pragma unroll
+            for (int mb = 0; mb < MB; ++mb) { sc[mb][0] = cnq[mb][0]; sc[mb][1] = cnq[mb][1]; }
+#pragma unroll
+            for (int ks = 0; ks < KS; ++ks)
+#pragma unroll
+                for (int mb = 0; mb < MB; ++mb) fu_dmma884(sc[mb][0], sc[mb][1], xa[ks], bq[mb][ks]);
             double best = INFINITY;
-            for (int c = 0; c < k; ++c) {
-                const double *cr = cs + c * D;
-                double s0 = 0.0, s1 = 0.0;
+            int bi = -1;
 #pragma unroll
-                for (int f = 0; f < D; f += 2) {
-                    const double2 cv = *reinterpret_cast<const double2 *>(cr + f);
-                    const double d0 = xr[f] - cv.x, d1 = xr[f + 1] - cv.y;
-                    s0 = fma(d0, d0, s0);
-                    s1 = fma(d1, d1, s1);
-                }
-                const double s = s0 + s1;
-                if (s < best) { best = s; lab = c; }
+            for (int mb = 0; mb < MB; ++mb)
+#pragma unroll
+                for (int e = 0; e < 2; ++e)
+                    if (sc[mb][e] < best) { best = sc[mb][e]; bi = 8 * mb + 2 * l4 + e; }
+#pragma unroll
+            for (int o = 1; o <= 2; o <<= 1) {
+                const double ob = __shfl_xor_sync(0xffffffffu, best, o);
+                const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+                if (ob < best || (ob == best && oi < bi)) { best = ob; bi = oi; }
             }
-            labels[base + tid] = lab;
-            if (mind2) mind2[base + tid] = (TX)best;
-            inert += best;
-            if (lab >= 0) atomicAdd(&cnt_s[lab], 1);   // (lab < 0: a row of NaNs, as in the kernel above)
-        }
-        // ---- phase B: sums += onehot(labels)^T . X for this warp's 32 rows (lane l holds the label of row 32 warp + l)
-        {
-            // a row without a label (beyond the tile's end: stale shared memory; or all-NaN distances) must add
-            // nothing, and 0 * NaN would not: such warps zero those rows' values on the way in
-            const bool sanitize = __any_sync(0xffffffffu, lab < 0);
-            const unsigned char *xw = xb + (size_t)warp * 32 * RB;
+            if (rt >= rows) bi = -1;                        // beyond the end of X
+            // the winner's distance, direct form, from the raw values
+            const double *cr = cs + (bi < 0 ? 0 : bi) * CLD + l4;
+            double dd = 0.0;
 #pragma unroll
-            for (int ks = 0; ks < 8; ++ks) {                 // rows 4 ks .. 4 ks + 3 of the warp
-                const int rr = 4 * ks + l4;                 // this lane's row of the B fragment
-                const int lr = __shfl_sync(0xffffffffu, lab, rr);
-                const unsigned char *xrow = xw + rr * RB;
-                const int rsw = sw(warp * 32 + rr);
+            for (int ks = 0; ks < KS; ++ks) {
+                const double t = xa[ks] - cr[4 * ks];
+                dd = fma(t, t, dd);
+            }
+            dd += __shfl_xor_sync(0xffffffffu, dd, 1);
+            dd += __shfl_xor_sync(0xffffffffu, dd, 2);
+            if (l4 == 0 && rt < rows) {
+                labels[base + rt] = bi;
+                if (mind2) mind2[base + rt] = (TX)dd;
+                inert += dd;
+            }
+            lab4[mbr] = bi;
+            unlabelled |= bi < 0;
+        }
+        // ---- phase B: sums += onehot(labels)^T . X for this warp's 32 rows -------------------------------------
+        // a row without a label (beyond the tile's end: stale shared memory; or all-NaN distances) must add nothing,
+        // and 0 * NaN would not: a warp that has one zeroes those rows' values on the way in (warp-uniform branch)
+        auto phase_b = [&](auto SAN) {
+            constexpr bool sanitize = decltype(SAN)::value;
+#pragma unroll
+            for (int ks = 0; ks < 8; ++ks) {
+                const int lr = __shfl_sync(0xffffffffu, lab4[ks >> 1], 4 * r7[ks & 1]);   // label of this lane's row
                 double a[MB];
 #pragma unroll
-                for (int mb = 0; mb < MB; ++mb) a[mb] = lr == 8 * mb + l8 ? 1.0 : 0.0;
+                for (int mb = 0; mb < MB; ++mb) {
+                    const bool hit = lr == 8 * mb + l8;
+                    a[mb] = hit ? 1.0 : 0.0;
+                    icnt[mb] += hit ? 1 : 0;
+                }
 #pragma unroll
                 for (int nb = 0; nb < NB; ++nb) {
-                    const int f = 8 * nb + l8;
-                    double x = (double)*reinterpret_cast<const TX *>(xrow + (((f / EPC) ^ rsw) << 4) +
-                                                                     (f % EPC) * (int)sizeof(TX));
+                    double x = (double)*reinterpret_cast<const TX *>(xw + (ks >> 1) * 8 * RB + offB[ks & 1][nb]);
                     if (sanitize && lr < 0) x = 0.0;
 #pragma unroll
                     for (int mb = 0; mb < MB; ++mb) fu_dmma884(cell[mb][nb][0], cell[mb][nb][1], a[mb], x);
                 }
             }
-        }
+        };
+        if (__any_sync(0xffffffffu, unlabelled)) phase_b(std::true_type{}); else phase_b(std::false_type{});
     }
     // ---- flush: the warps' accumulator fragments through shared memory, then one RED per cell and CTA -------
     __syncthreads();                                        // every thread is done with xs
@@ -946,6 +1024,14 @@ assign_update_bulk_kernel(const TX *__restrict__ X, int64_t n, int64_t ldx, cons
             w[0] = cell[mb][nb][0];
             w[1] = cell[mb][nb][1];
         }
+    __shared__ int wcnt[FU_R / 32][FU_MAXK];
+#pragma unroll
+    for (int mb = 0; mb < MB; ++mb) {
+        int c = icnt[mb];                                   // the four lanes of a cluster counted disjoint rows
+        c += __shfl_xor_sync(0xffffffffu, c, 1);
+        c += __shfl_xor_sync(0xffffffffu, c, 2);
+        if (l4 == 0) wcnt[warp][8 * mb + l8] = c;
+    }
     __syncthreads();
     const int ncell = k * D;
     for (int e = tid; e < ncell; e += FU_R) {
@@ -955,7 +1041,12 @@ assign_update_bulk_kernel(const TX *__restrict__ X, int64_t n, int64_t ldx, cons
         for (int w = 0; w < FU_R / 32; ++w) t += wtab[(w * KMAX + c) * D + f];
         if (t != 0.0) atomicAdd(acc + e, t);
     }
-    if (tid < k && cnt_s[tid] != 0) atomicAdd(acc + ncell + tid, (double)cnt_s[tid]);
+    if (tid < k) {
+        int t = 0;
+#pragma unroll
+        for (int w = 0; w < FU_R / 32; ++w) t += wcnt[w][tid];
+        if (t != 0) atomicAdd(acc + ncell + tid, (double)t);
+    }
     km_block_atomic_add(inert, acc + ncell + k, red);
     fu_last_cta_finalize(acc, ncell, k, D, c64, done, cnew, out2, tag, red);
 }
@@ -968,7 +1059,7 @@ static int launch_bulk(const TX *X, int64_t n, int64_t ldx, const double *c64, i
     auto kern = assign_update_bulk_kernel<TX, D, KMAX>;
     constexpr int RB = D * (int)sizeof(TX);
     constexpr int OCC = (KMAX <= 8 && RB <= 128 && D <= 16) ? 3 : 2;
-    const size_t smem = (size_t)2 * FU_R * RB + sizeof(double) * KMAX * D + sizeof(int) * (FU_R + KMAX);
+    const size_t smem = (size_t)2 * FU_R * RB + sizeof(double) * KMAX * (D + 4);
     static bool attr_set[KM_MAX_DEVICES] = {};
     if (int rc = km_set_smem_once(kern, 80 * 1024, attr_set)) return rc;
     int64_t blocks = (n + FU_R - 1) / FU_R;

@@ -425,8 +425,8 @@ def test_assign_update_fused(eng, n, d, k, dtype):
                                              (255, 16, 8, np.float64, 0), (1, 16, 1, np.float64, 0)])
 def test_fused_kernels_agree(eng, n, d, k, dtype, pad):
     """The cp.async fused kernel (rows of 64 / 128 bytes, 16-byte aligned) against the sorted-tile one
-    (B200KM_OPT_FUSED_VARIANT = 1): same arithmetic in phase A, so labels and distances are bit-equal; the float64
-    sums differ only in the order of the additions.  ``pad`` > 0: rows with a leading dimension of d + pad."""
+    (B200KM_OPT_FUSED_VARIANT = 1): same labels (up to exact near-ties), distances to the last bits, same counts;
+    the float64 sums differ only in the order of the additions.  ``pad`` > 0: rows with a leading dimension of d + pad."""
     import torch
 
     from dask_ml_b200 import _lib
@@ -448,12 +448,17 @@ def test_fused_kernels_agree(eng, n, d, k, dtype, pad):
             out[variant] = (labels.cpu().numpy(), mind2.cpu().numpy(), acc.cpu().numpy())
     finally:
         eng.lib.b200km_set_option(_lib.OPT_FUSED_VARIANT, 0)
-    npt.assert_array_equal(out[0][0], out[1][0])
-    npt.assert_array_equal(out[0][1], out[1][1])
+    # (the cp.async kernel decides on centred expanded-form float64 scores from the FP64 tensor cores and rebuilds the
+    #  winner's distance in direct form; the sorted-tile kernel is direct form throughout: exact near-ties may differ)
+    same = out[0][0] == out[1][0]
+    assert not (~same & ~_near_tie_mask(X, C, 1e-12)).any()
+    npt.assert_allclose(out[0][1][same], out[1][1][same], rtol=1e-13 if dtype == np.float64 else 2e-7)
     a0, a1 = out[0][2], out[1][2]
-    npt.assert_array_equal(a0[k * d : k * d + k], a1[k * d : k * d + k])
-    npt.assert_allclose(a0[: k * d], a1[: k * d], rtol=1e-13, atol=1e-11 * max(np.abs(a1[: k * d]).max(), 1.0))
-    npt.assert_allclose(a0[-1], a1[-1], rtol=1e-13)
+    if same.all():
+        npt.assert_array_equal(a0[k * d : k * d + k], a1[k * d : k * d + k])
+        npt.assert_allclose(a0[: k * d], a1[: k * d], rtol=1e-13, atol=1e-11 * max(np.abs(a1[: k * d]).max(), 1.0))
+        npt.assert_allclose(a0[-1], a1[-1], rtol=1e-13)
+    npt.assert_array_equal(a0[k * d : k * d + k], np.bincount(out[0][0], minlength=k))
     lab_ref, _ = orc.pairwise_distances_argmin_min(X, C, metric_kwargs={"squared": True})
     assert not ((out[0][0] != lab_ref) & ~_near_tie_mask(X, C, 1e-12)).any()
     sums = orc.centers_dense(X, out[0][0].astype(np.int32), k)
