@@ -908,24 +908,30 @@ assign_update_bulk_kernel(const TX *__restrict__ X, int64_t n, int64_t ldx, cons
 #pragma unroll
         for (int nb = 0; nb < NB; ++nb) offB[pp][nb] = (uint32_t)xoff(r7[pp], 8 * nb + l8);
     }
-    // staging: chunk e = tid + FU_R * i of the tile (consecutive threads -> consecutive 16-byte pieces of X)
-    constexpr int SROWS = FU_R / CPR;                       // rows between two chunks of one thread
-    const int st_c = tid % CPR, st_r0 = tid / CPR;
-    const uint32_t sdst = km_smem_u32(xs) + (uint32_t)xoff(st_r0, st_c * EPC);
+    // staging: every warp loads ITS 32 rows of the tile (32 * RB contiguous bytes when ldx == d) and nobody else
+    // touches them, so the warps run independent two-buffer pipelines: cp.async.wait_group + __syncwarp, no block
+    // barrier in the loop.  Lane l moves chunk l % CPR of rows l / CPR + (32 / CPR) * i.
+    constexpr int SROWS = 32 / CPR;                         // rows between two chunks of one lane
+    const int st_c = lane % CPR, st_r0 = lane / CPR;
+    const uint32_t sdst = km_smem_u32(xs) + (uint32_t)(warp * 32 * RB) + (uint32_t)xoff(st_r0, st_c * EPC);
     const int64_t gstep = (int64_t)SROWS * ldx;
+    // (row st_r0 + SROWS * i: SROWS = 4 resp. 8 keeps the swizzle of st_r0 only for 128-byte rows -- recompute per i)
+    uint32_t sofs[CPR];
+#pragma unroll
+    for (int i = 0; i < CPR; ++i) sofs[i] = (uint32_t)xoff(st_r0 + SROWS * i, st_c * EPC) - (uint32_t)xoff(st_r0, st_c * EPC);
     auto issue = [&](int64_t base, int b) {
-        const int64_t left = n - base;
-        const TX *src = X + (base + st_r0) * ldx + st_c * EPC;
+        const int64_t left = n - base - warp * 32;          // rows of this warp's slice that exist
+        const TX *src = X + (base + warp * 32 + st_r0) * ldx + st_c * EPC;
         const uint32_t dst = sdst + (uint32_t)b * (FU_R * RB);
-        if (left >= FU_R) {
+        if (left >= 32) {
 #pragma unroll
             for (int i = 0; i < CPR; ++i)
-                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + i * SROWS * RB), "l"(src + i * gstep) : "memory");
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + sofs[i]), "l"(src + i * gstep) : "memory");
         } else {
 #pragma unroll
             for (int i = 0; i < CPR; ++i)
                 if (st_r0 + SROWS * i < left)
-                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + i * SROWS * RB), "l"(src + i * gstep) : "memory");
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + sofs[i]), "l"(src + i * gstep) : "memory");
         }
         fu_cp_async_commit();
     };
@@ -937,7 +943,7 @@ assign_update_bulk_kernel(const TX *__restrict__ X, int64_t n, int64_t ldx, cons
         const int b = it & 1;
         const int rows = (int)((n - base) < FU_R ? (n - base) : FU_R);
         fu_cp_async_wait_all();
-        __syncthreads();          // the tile has landed for every thread; phase B of the previous tile is over
+        __syncwarp();             // the slice has landed for every lane; the warp is done with the other buffer
         if (base + stride < n) issue(base + stride, b ^ 1);
         const unsigned char *xw = xs + (size_t)b * FU_R * RB + (size_t)warp * 32 * RB;   // this warp's 32 rows
         // ---- phase A: four blocks of 8 rows ------------------------------------------------------------------
