@@ -837,15 +837,17 @@ assign_update_bulk_kernel(const TX *__restrict__ X, int64_t n, int64_t ldx, cons
     static_assert(CPR == 4 || CPR == 8, "rows of 64 or 128 bytes");
     extern __shared__ __align__(128) unsigned char fb_smem[];
     unsigned char *xs = fb_smem;                                              // [2][FU_R][RB], chunks swizzled
-    // centre rows padded by 4 doubles: the eight row groups of a warp gather 32-byte pieces of (mostly) different
-    // centres in the distance rebuild, and rows a multiple of 128 bytes apart would all sit on the same banks
-    constexpr int CLD = D + 4;
-    double *cs = reinterpret_cast<double *>(fb_smem + 2 * FU_R * RB);         // [KMAX][CLD]
+    // the centres feature-major, [D][CLD] with CLD = KMAX (+ 2 for 16 clusters): in the distance rebuild the lanes of a
+    // warp read (feature 4 ks + l4, cluster = their row's label) -- four neighbouring table rows, any labels: with the
+    // clusters of a feature side by side that is 256 contiguous bytes for k <= 8, two shared-memory wavefronts whatever
+    // the labels are (centre-major rows of 128 bytes put the same feature of every centre on the same banks)
+    constexpr int CLD = KMAX <= 8 ? KMAX : KMAX + 2;
+    double *cs = reinterpret_cast<double *>(fb_smem + 2 * FU_R * RB);         // [D][CLD]
     __shared__ double red[32];
     __shared__ double mu_s[32], cn_s[FU_MAXK];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int l4 = lane & 3, l8 = lane >> 2;
-    for (int e = tid; e < KMAX * D; e += FU_R) cs[(e / D) * CLD + e % D] = e < k * D ? c64[e] : 0.0;
+    for (int e = tid; e < KMAX * D; e += FU_R) cs[(e % D) * CLD + e / D] = e < k * D ? c64[e] : 0.0;
     // swizzle of row r: chunk c is stored at position c ^ sw(r); sw(r) = r & 7 (128-byte rows), (r >> 1) & 3 (64-byte).
     // Every row set used below is a fixed row plus a multiple of 8, so each thread's swizzles are loop constants.
     auto sw = [](int r) { return CPR == 8 ? (r & 7) : ((r >> 1) & 3); };
@@ -856,7 +858,7 @@ assign_update_bulk_kernel(const TX *__restrict__ X, int64_t n, int64_t ldx, cons
     __syncthreads();
     if (tid < D) {
         double m = 0.0;
-        for (int c = 0; c < k; ++c) m += cs[c * CLD + tid];
+        for (int c = 0; c < k; ++c) m += cs[tid * CLD + c];
         mu_s[tid] = m / (double)k;
     }
     __syncthreads();
@@ -864,7 +866,7 @@ assign_update_bulk_kernel(const TX *__restrict__ X, int64_t n, int64_t ldx, cons
         double q = INFINITY;                                // a padded cluster never wins
         if (tid < k) {
             q = 0.0;
-            for (int f = 0; f < D; ++f) { const double t = cs[tid * CLD + f] - mu_s[f]; q = fma(t, t + 2.0 * mu_s[f], q); }
+            for (int f = 0; f < D; ++f) { const double t = cs[f * CLD + tid] - mu_s[f]; q = fma(t, t + 2.0 * mu_s[f], q); }
         }
         cn_s[tid] = q;
     }
@@ -876,7 +878,7 @@ assign_update_bulk_kernel(const TX *__restrict__ X, int64_t n, int64_t ldx, cons
     for (int ks = 0; ks < KS; ++ks)
 #pragma unroll
         for (int mb = 0; mb < MB; ++mb)                      // B[feature 4 ks + l4][cluster 8 mb + l8] = -2 c'
-            bq[mb][ks] = 8 * mb + l8 < k ? -2.0 * (cs[(8 * mb + l8) * CLD + 4 * ks + l4] - mu_s[4 * ks + l4]) : 0.0;
+            bq[mb][ks] = 8 * mb + l8 < k ? -2.0 * (cs[(4 * ks + l4) * CLD + 8 * mb + l8] - mu_s[4 * ks + l4]) : 0.0;
 #pragma unroll
     for (int mb = 0; mb < MB; ++mb) {
         cnq[mb][0] = cn_s[8 * mb + 2 * l4];
@@ -948,6 +950,7 @@ assign_update_bulk_kernel(const TX *__restrict__ X, int64_t n, int64_t ldx, cons
         const unsigned char *xw = xs + (size_t)b * FU_R * RB + (size_t)warp * 32 * RB;   // this warp's 32 rows
         // ---- phase A: four blocks of 8 rows ------------------------------------------------------------------
         int lab4[4];                                        // label of row 8 mbr + l8 (the same in the row's 4 lanes)
+        double ddp[4];
         bool unlabelled = false;
 #pragma unroll
         for (int mbr = 0; mbr < 4; ++mbr) {
@@ -976,22 +979,34 @@ assign_update_bulk_kernel(const TX *__restrict__ X, int64_t n, int64_t ldx, cons
             }
             if (rt >= rows) bi = -1;                        // beyond the end of X
             // the winner's distance, direct form, from the raw values
-            const double *cr = cs + (bi < 0 ? 0 : bi) * CLD + l4;
+            const double *cr = cs + l4 * CLD + (bi < 0 ? 0 : bi);
             double dd = 0.0;
 #pragma unroll
             for (int ks = 0; ks < KS; ++ks) {
-                const double t = xa[ks] - cr[4 * ks];
+                const double t = xa[ks] - cr[4 * ks * CLD];
                 dd = fma(t, t, dd);
             }
-            dd += __shfl_xor_sync(0xffffffffu, dd, 1);
-            dd += __shfl_xor_sync(0xffffffffu, dd, 2);
-            if (l4 == 0 && rt < rows) {
+            ddp[mbr] = dd;                                  // this lane's features only
+            lab4[mbr] = bi;
+            unlabelled |= bi < 0;
+        }
+        {
+            // the four partial distances of the four row blocks, summed over the row's four lanes by a transposing
+            // reduction (3 exchanges instead of 8): lane (l8, l4) ends up with the distance of row 8 l4 + l8 and writes
+            // that row's outputs
+            const bool b0 = l4 & 1, b1 = l4 & 2;
+            double k0 = b0 ? ddp[1] : ddp[0], k1 = b0 ? ddp[3] : ddp[2];
+            k0 += __shfl_xor_sync(0xffffffffu, b0 ? ddp[0] : ddp[1], 1);
+            k1 += __shfl_xor_sync(0xffffffffu, b0 ? ddp[2] : ddp[3], 1);
+            double dd = b1 ? k1 : k0;
+            dd += __shfl_xor_sync(0xffffffffu, b1 ? k0 : k1, 2);
+            const int rt = warp * 32 + 8 * l4 + l8;
+            if (rt < rows) {
+                const int bi = b1 ? (b0 ? lab4[3] : lab4[2]) : (b0 ? lab4[1] : lab4[0]);
                 labels[base + rt] = bi;
                 if (mind2) mind2[base + rt] = (TX)dd;
                 inert += dd;
             }
-            lab4[mbr] = bi;
-            unlabelled |= bi < 0;
         }
         // ---- phase B: sums += onehot(labels)^T . X for this warp's 32 rows -------------------------------------
         // a row without a label (beyond the tile's end: stale shared memory; or all-NaN distances) must add nothing,
@@ -1065,7 +1080,7 @@ static int launch_bulk(const TX *X, int64_t n, int64_t ldx, const double *c64, i
     auto kern = assign_update_bulk_kernel<TX, D, KMAX>;
     constexpr int RB = D * (int)sizeof(TX);
     constexpr int OCC = (KMAX <= 8 && RB <= 128 && D <= 16) ? 3 : 2;
-    const size_t smem = (size_t)2 * FU_R * RB + sizeof(double) * KMAX * (D + 4);
+    const size_t smem = (size_t)2 * FU_R * RB + sizeof(double) * D * (KMAX + 2);
     static bool attr_set[KM_MAX_DEVICES] = {};
     if (int rc = km_set_smem_once(kern, 80 * 1024, attr_set)) return rc;
     int64_t blocks = (n + FU_R - 1) / FU_R;
