@@ -240,7 +240,9 @@ def _roofline(torch, eng, args, workload, n_local, d, k, dtype_s, k1_avg_ms, ms_
     esize = 4 if dtype_s == "float32" else 8
     flops = 2.0 * n_local * k * d
     bytes_alg = n_local * (d * esize + 4)
-    roof = {"kernel": "assign_update_small_kernel (K1+K2 fused)" if fused else "assign (K1)", "traffic": None}
+    fused_name = ("assign_update_bulk_kernel (K1+K2 fused: cp.async staging, scores and per-cluster sums on the FP64 "
+                  "tensor cores)" if d * esize in (64, 128) else "assign_update_small_kernel (K1+K2 fused)")
+    roof = {"kernel": fused_name if fused else "assign (K1)", "traffic": None}
     variant = eng.lib.b200km_get_option(_lib.OPT_K1_VARIANT)
     k1_is_tc = dtype_s == "float32" and k > 16 and d <= 128 and variant != _lib.K1_FFMA
     k1_is_ffma = dtype_s == "float32" and k > 16 and d <= 128 and not k1_is_tc
@@ -336,9 +338,35 @@ def lloyd_bench(torch, dist, eng, comm, args, workload, steps, warmup, local_ran
         eng.finalize(acc, k, d, c_old, c_new, shift_t)
         return float(shift_t.item())
 
-    for _ in range(warmup):
-        step(c_a, c_b)
-        c_a, c_b = c_b, c_a
+    if one_launch:
+        # as _kmeans_single_lloyd runs it: iteration j + 1 is queued behind iteration j before j's shift is read (three
+        # centre buffers, two label / distance buffers in rotation), every iteration's result is read on the host
+        cbuf = [c_a, c_b, torch.empty_like(c_a)]
+        lbuf = [labels, torch.empty_like(labels)]
+        mbuf = [mind2, torch.empty_like(mind2)]
+        state["q"] = 0
+
+        def run(nsteps):
+            q0 = state["q"]
+
+            def launch(q):
+                return eng.lloyd_small_launch(X, cbuf[q % 3], lbuf[q & 1], mbuf[q & 1], acc, ticket, cbuf[(q + 1) % 3],
+                                              slot=q & 1)
+
+            tag = launch(q0)
+            for q in range(q0, q0 + nsteps):
+                nxt = launch(q + 1) if q + 1 < q0 + nsteps else None
+                _shift, state["inertia"] = eng.lloyd_small_wait(tag, slot=q & 1)
+                tag = nxt
+            state["q"] = q0 + nsteps
+    else:
+        def run(nsteps):
+            nonlocal c_a, c_b
+            for _ in range(nsteps):
+                step(c_a, c_b)
+                c_a, c_b = c_b, c_a
+
+    run(warmup)
 
     # ---- timed region -----------------------------------------------------------------------
     sampler = ClockSampler(local_rank)
@@ -352,9 +380,7 @@ def lloyd_bench(torch, dist, eng, comm, args, workload, steps, warmup, local_ran
     torch.cuda.synchronize()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record()
-    for _ in range(steps):
-        step(c_a, c_b)
-        c_a, c_b = c_b, c_a
+    run(steps)
     ev1.record()
     torch.cuda.synchronize()
     if world > 1:
@@ -372,7 +398,7 @@ def lloyd_bench(torch, dist, eng, comm, args, workload, steps, warmup, local_ran
     if one_launch:   # acc comes back zeroed: the counts are checked through one separate pass
         inertia = float(state["inertia"])
         chk = torch.zeros_like(acc)
-        eng.assign_update(X, c_b, labels, mind2, chk)
+        eng.assign_update(X, cbuf[state["q"] % 3], labels, mind2, chk)
         counts_ok = int(round(float(chk[k * d : k * d + k].sum().item()))) == n_local * world
     else:
         inertia = float(acc[k * d + k].item())

@@ -342,15 +342,18 @@ class CudaEngine:
                 e1.record()
                 self.k1_events.append((e0, e1))
 
-    def lloyd_small(self, X: torch.Tensor, centers64: torch.Tensor, labels: torch.Tensor, mind2: torch.Tensor,
-                    acc: torch.Tensor, ticket: torch.Tensor, centers_new: torch.Tensor) -> Tuple[float, float]:
+    _LS_SLOTS = 2                 # results in flight (the Lloyd driver keeps the next iteration queued behind this one)
+
+    def lloyd_small_launch(self, X: torch.Tensor, centers64: torch.Tensor, labels: torch.Tensor, mind2: torch.Tensor,
+                           acc: torch.Tensor, ticket: torch.Tensor, centers_new: torch.Tensor, slot: int = 0) -> float:
         """b200km_lloyd_small_*: one whole iteration (assign + sums + counts + inertia + divide + shift) in one launch.
-        ``acc`` / ``ticket`` (int32[1]) must be zero on entry and come back zero; single GPU, X resident (n < 2^30).
-        Returns (shift, inertia): the kernel writes them into page-locked host memory followed by this call's tag, and
-        the host polls for the tag instead of synchronising the stream (falls back to a synchronisation after 2 s)."""
+        ``acc`` / ``ticket`` (int32[1]) must be zero when the kernel STARTS and come back zero (so launches may be
+        queued back to back); single GPU, X resident (n < 2^30).  The kernel writes [shift, inertia] into page-locked
+        host memory (one 64-byte slot per ``slot``) followed by this launch's tag; returns the tag for
+        ``lloyd_small_wait``."""
         n, d, ldx = self._check_matrix(X)
         if not hasattr(self, "_ls_host"):
-            self._ls_host = torch.zeros(3, dtype=torch.float64).pin_memory()
+            self._ls_host = torch.zeros(8 * self._LS_SLOTS, dtype=torch.float64).pin_memory()
             self._ls_view = self._ls_host.numpy()
             self._ls_tag = 0.0
         self._ls_tag += 1.0
@@ -360,14 +363,20 @@ class CudaEngine:
             e0.record()
         self._call(f"b200km_lloyd_small_{_suffix(X)}", X.data_ptr(), n, d, ldx, centers64.data_ptr(), centers64.shape[0],
                    labels.data_ptr(), mind2.data_ptr(), acc.data_ptr(), ticket.data_ptr(), centers_new.data_ptr(),
-                   self._ls_host.data_ptr(), tag, self._stream())
+                   self._ls_host.data_ptr() + 64 * slot, tag, self._stream())
         if self.k1_events is not None:
             e1.record()
             self.k1_events.append((e0, e1))
+        return tag
+
+    def lloyd_small_wait(self, tag: float, slot: int = 0) -> Tuple[float, float]:
+        """(shift, inertia) of the launch that carries ``tag``: the host polls the slot's tag word instead of
+        synchronising the stream (falls back to a synchronisation after 2 s)."""
         view = self._ls_view
+        o = 8 * slot
         deadline = None
         spins = 0
-        while view[2] != tag:
+        while view[o + 2] != tag:
             spins += 1
             if (spins & 0xFFFF) == 0:
                 import time
@@ -377,9 +386,14 @@ class CudaEngine:
                     deadline = now + 2.0
                 elif now > deadline:      # a failed launch never writes the tag: let the synchronisation report it
                     torch.cuda.current_stream(self.device).synchronize()
-                    if view[2] != tag:
+                    if view[o + 2] != tag:
                         raise _lib.B200KernelError("b200km_lloyd_small: the iteration's result never arrived")
-        return float(view[0]), float(view[1])
+        return float(view[o]), float(view[o + 1])
+
+    def lloyd_small(self, X: torch.Tensor, centers64: torch.Tensor, labels: torch.Tensor, mind2: torch.Tensor,
+                    acc: torch.Tensor, ticket: torch.Tensor, centers_new: torch.Tensor) -> Tuple[float, float]:
+        """One iteration, launched and awaited: (shift, inertia)."""
+        return self.lloyd_small_wait(self.lloyd_small_launch(X, centers64, labels, mind2, acc, ticket, centers_new))
 
     def finalize(self, acc: torch.Tensor, k: int, d: int, centers_old: torch.Tensor,
                  centers_new: Optional[torch.Tensor] = None, shift: Optional[torch.Tensor] = None):

@@ -640,14 +640,35 @@ def _kmeans_single_lloyd(X, n_clusters, max_iter=300, init="k-means||", verbose=
                 if acc_dirty:
                     acc.zero_()
                     acc_dirty = False
-                # :576-605; the shift comes back through page-locked memory the kernel writes (:602 -- the one round trip)
-                shift, inertia_one = eng.lloyd_small(X, centers64, labels, mind2, acc, ticket, new64)
+                # :576-605, every remaining iteration: iteration j + 1 is queued behind iteration j BEFORE j's shift is
+                # read (the kernels hand centres, acc and the ticket to one another on the device), so the host's round
+                # trip (:602) and the launch latency sit under the next kernel.  A break at j leaves j's centres,
+                # labels and distances untouched: three centre buffers and two label / distance buffers rotate; the
+                # one queued iteration that is not needed then only costs its time.
+                cbuf = [centers64, new64, torch.empty_like(centers64)]
+                lbuf = [labels, torch.empty_like(labels)]
+                mbuf = [mind2, torch.empty_like(mind2)]
+
+                def _launch(j, i0=i):
+                    q = j - i0
+                    return eng.lloyd_small_launch(X, cbuf[q % 3], lbuf[q & 1], mbuf[q & 1], acc, ticket,
+                                                  cbuf[(q + 1) % 3], slot=q & 1)
+
+                i0, tag = i, _launch(i)
+                for i in range(i0, max_iter):
+                    nxt = _launch(i + 1) if i + 1 < max_iter else None
+                    shift, inertia_one = eng.lloyd_small_wait(tag, slot=(i - i0) & 1)
+                    logger.info("Shift: %0.4f", shift)
+                    tag = nxt
+                    if shift < tol:
+                        break
+                q = i - i0
+                labels, mind2 = lbuf[q & 1], mbuf[q & 1]
+                # :606-610 -- a break keeps the centres the last pass was made with, a full run ends on the update
+                centers64 = cbuf[q % 3] if shift < tol else cbuf[(q + 1) % 3]
+                new64 = cbuf[(q + 2) % 3]
                 last_one = True
-                logger.info("Shift: %0.4f", shift)
-                if shift < tol:
-                    break
-                centers64, new64 = new64, centers64  # :610
-                continue
+                break
             last_one = False
             acc_dirty = True
             acc.zero_()
