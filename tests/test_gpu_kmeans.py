@@ -233,6 +233,24 @@ def test_lloyd_fixed_init_matches_oracle(n, d, k, dtype, max_iter, tol):
     _lloyd_vs_oracle(X, k, X[:k].copy(), max_iter, tol, 1e-5 if dtype == np.float32 else 1e-10)
 
 
+@pytest.mark.parametrize("n,d,k,dtype,max_iter,tol", [
+    (20000, 16, 8, np.float64, 300, 1e-12),   # runs until the shift is ~0: labels / inertia of the LAST pass are kept
+    (20000, 16, 8, np.float64, 300, 0.5),     # breaks with 1e-7 < shift < tol: final labelling pass on the kept centres
+    (20000, 16, 8, np.float64, 1, 0.0),       # max_iter 1: nothing is queued ahead
+    (20000, 16, 8, np.float64, 2, 0.0),
+    (15000, 32, 16, np.float32, 300, 1e-6),   # float32 rows of 128 bytes
+    (15000, 16, 5, np.float32, 300, 1.0),
+    (9000, 8, 16, np.float64, 300, 1e-9),     # float64 rows of 64 bytes
+    (9000, 7, 6, np.float64, 300, 1e-9),      # the sorted-tile kernel behind the same loop
+])
+def test_lloyd_small_k_pipelined_loop_matches_oracle(n, d, k, dtype, max_iter, tol):
+    """k <= 16, d <= 32 on one GPU: one launch per iteration, iteration j + 1 queued before j's shift is read.  Every way
+    out of the loop (max_iter, break above / below 1e-7) must leave the centres, labels and inertia of the reference's
+    loop (k_means.py:576-616)."""
+    X, true = blobs(n, d, k, seed=n + k + d, dtype=dtype)
+    _lloyd_vs_oracle(X, k, (true + 0.3).astype(dtype), max_iter, tol, 1e-5 if dtype == np.float32 else 1e-10)
+
+
 @pytest.mark.parametrize("dtype", [np.float32, np.float64])
 def test_lloyd_far_from_origin_matches_oracle(dtype):
     """The same blobs 1000 sigma away from the origin (raw sensor values, timestamps): the kernels centre rows and
