@@ -220,6 +220,10 @@ int b200km_update_inertia_f64(const double *X, int64_t n, int d, int64_t ldx, co
 
 /* K1+K2 fused into ONE pass over X for the HBM-bound regime: k <= 16 and d <= 32 (else B200KM_ETOOBIG).
  * labels / mind2 as K1 (float64 arithmetic, so no re-decision is needed), acc += as K2 (squared inertia).
+ * 16-byte aligned rows of exactly 64 or 128 bytes (d = 16 / 32 float32, d = 8 / 16 float64; ldx * sizeof a multiple
+ * of 16) take the cp.async / FP64-tensor-core kernel, every other shape the sorted-tile kernel
+ * (B200KM_OPT_FUSED_VARIANT = 1 keeps the latter for all); same labels up to exact float64 near-ties, same
+ * distances to the last bits.  A row whose distances are all NaN gets label -1 and adds to no sum or count.
  * Replaces: the two passes R/dask_ml/cluster/k_means.py:576-598 makes over X per iteration
  *           (pairwise_distances_argmin_min, then _centers_dense + bincount). */
 #define B200KM_FUSED_MAX_K 16
