@@ -11,7 +11,7 @@ lib = sys.argv[1] if len(sys.argv) > 1 else os.path.join(os.path.dirname(os.path
                                                          "dask_ml_b200", "libb200km.so")
 out = subprocess.run(["cuobjdump", "-sass", lib], capture_output=True, text=True).stdout
 WATCH = ["UTCHMMA", "UTCBAR", "LDTM", "UTCATOMSWS", "UBLKCP", "UTMALDG", "SYNCS", "FMNMX3", "FFMA.SAT", "DFMA", "DADD", "FFMA",
-         "HMMA", "ATOMG", "RED", "BAR.SYNC", "UCGABAR"]
+         "HMMA", "DMMA", "LDGSTS", "ATOMG", "RED", "BAR.SYNC", "UCGABAR"]
 kern = None
 counts = collections.OrderedDict()
 for line in out.splitlines():
