@@ -465,6 +465,49 @@ def test_fused_kernels_agree(eng, n, d, k, dtype, pad):
     npt.assert_allclose(a0[: k * d].reshape(k, d), sums, rtol=1e-12, atol=1e-9 * max(np.abs(sums).max(), 1.0))
 
 
+def test_fused_kernel_random_shapes_fuzz(eng):
+    """The cp.async / FP64-tensor-core fused kernel on random shapes of its domain: every row width it takes, k from 1
+    to 16, sizes around the tile and warp boundaries, data far from the origin, duplicated centres (lowest index must win
+    an exact tie) -- labels against float64 direct-form distances, sums / counts / inertia against numpy."""
+    import torch
+
+    rs = np.random.RandomState(1234)
+    for trial in range(40):
+        dtype = [np.float32, np.float64][trial & 1]
+        d = int(rs.choice([16, 32] if dtype == np.float32 else [8, 16]))
+        k = int(rs.randint(1, 17))
+        n = int(rs.choice([1, 31, 32, 33, 255, 256, 257, 511, 1000, 4097, 20001, 66000]))
+        offset = float(rs.choice([0.0, 0.0, 100.0, -3e4]))
+        scale = float(rs.choice([1.0, 1e-3, 50.0]))
+        C = rs.uniform(-10, 10, size=(k, d)) * scale + offset
+        if k >= 4:
+            C[k - 1] = C[1]                       # an exact duplicate: index 1 must win every tie with index k - 1
+        X = (C[rs.randint(0, k, size=n)] + rs.standard_normal((n, d)) * scale).astype(dtype)
+        Xd, Cd = eng.to_device(X), eng.to_device(C, torch.float64)
+        labels = torch.full((n,), -7, dtype=torch.int32, device=eng.device)
+        mind2 = torch.zeros(n, dtype=Xd.dtype, device=eng.device)
+        acc = torch.zeros(eng.acc_len(k, d), dtype=torch.float64, device=eng.device)
+        eng.assign_update(Xd, Cd, labels, mind2, acc)
+        got = labels.cpu().numpy()
+        D = ((X.astype(np.float64)[:, None, :] - C[None, :, :]) ** 2).sum(-1)
+        ref = D.argmin(1)
+        best = D[np.arange(n), ref]
+        mine = D[np.arange(n), got]
+        # a different label only where the two distances agree to rounding (relative to the centred magnitudes)
+        tol = 1e-11 * (np.abs(X.astype(np.float64) - C.mean(0)).max() ** 2 * d + 1e-300)
+        assert (np.abs(mine - best) <= tol).all(), (trial, dtype, n, d, k, offset, scale)
+        if k >= 4:
+            assert not (got == k - 1).any(), (trial, "duplicate centre won a tie")
+        npt.assert_allclose(mind2.cpu().numpy().astype(np.float64), mine, rtol=1e-12 if dtype == np.float64 else 2e-7,
+                            atol=1e-300)
+        a = acc.cpu().numpy()
+        sums = np.zeros((k, d))
+        np.add.at(sums, got, X.astype(np.float64))
+        npt.assert_allclose(a[: k * d].reshape(k, d), sums, rtol=1e-12, atol=1e-12 * max(np.abs(sums).max(), 1e-300))
+        npt.assert_array_equal(a[k * d : k * d + k], np.bincount(got, minlength=k))
+        npt.assert_allclose(a[-1], mind2.double().sum().item(), rtol=1e-6 if dtype == np.float32 else 1e-12)
+
+
 @pytest.mark.parametrize("dtype,d,k", [(np.float64, 16, 8), (np.float32, 32, 16), (np.float64, 5, 3)])
 def test_lloyd_small_one_launch_matches_separate_steps(eng, dtype, d, k):
     """b200km_lloyd_small_* (one launch: assign + sums + divide + shift, result through page-locked memory) against
