@@ -238,7 +238,10 @@ int b200km_assign_update_f64(const double *X, int64_t n, int d, int64_t ldx, con
  * a system-scope fence, shift_inertia[2] = tag.  shift_inertia (3 doubles) may be page-locked host memory (UVA: the
  * GPU writes it directly); a host that passes a fresh tag per call can poll shift_inertia[2] for it and read the
  * shift without synchronising the stream.  `acc` (b200km_acc_len doubles) and `ticket` (one uint32) are scratch
- * that must be ZERO on entry and are zero again on return, so consecutive iterations need no memset between them.
+ * that must be ZERO on entry and are zero again on return, so consecutive iterations need no memset between them --
+ * and iteration j + 1 (centers_f64 := iteration j's centers_new, its own labels / mind2 / centers_new / shift_inertia
+ * buffers) may be queued on the same stream BEFORE the host has read iteration j's result: the host's round trip and
+ * the launch latency then sit under a running kernel (what dask_ml_b200/cluster/k_means.py does).
  * Replaces: one trip round the loop body R/dask_ml/cluster/k_means.py:576-605. */
 int b200km_lloyd_small_f32(const float *X, int64_t n, int d, int64_t ldx, const double *centers_f64, int k,
                            int32_t *labels, float *mind2, double *acc, unsigned int *ticket, double *centers_new,
