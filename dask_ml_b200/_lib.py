@@ -28,6 +28,7 @@ class B200KernelError(RuntimeError):
 OPT_K1_VARIANT = 1      # B200KM_OPT_K1_VARIANT
 OPT_K2_VARIANT = 2      # B200KM_OPT_K2_VARIANT
 OPT_FUSED_VARIANT = 3   # B200KM_OPT_FUSED_VARIANT (1 = the sorted-tile fused kernel always)
+OPT_K4_VARIANT = 4      # B200KM_OPT_K4_VARIANT (1 = the register-path K4 kernel always)
 K1_AUTO, K1_FFMA, K1_TCGEN05, K1_TCGEN05_PAIR = 0, 1, 2, 3
 CDIST_SQUARED, CDIST_DIST, CDIST_RBF = 0, 1, 2   # b200km_cdist_pack_f32 modes
 

@@ -585,6 +585,8 @@ static std::atomic<int> g_k2_variant{0};  // B200KM_OPT_K2_VARIANT: 0 auto, 1 ow
 int km_k2_variant() { return g_k2_variant; }
 static std::atomic<int> g_fused_variant{0};  // B200KM_OPT_FUSED_VARIANT: 0 auto, 1 sorted-tile kernel, 2 cp.async kernel where it fits
 int km_fused_variant() { return g_fused_variant; }
+static std::atomic<int> g_k4_variant{0};  // B200KM_OPT_K4_VARIANT: 0 auto (TMA ring where it pays), 1 register path always, 2 TMA ring wherever it fits
+int km_k4_variant() { return g_k4_variant; }
 
 extern "C" int b200km_set_option(int key, int value) {
     if (key == B200KM_OPT_K1_VARIANT && value >= 0 && value <= 3) {
@@ -599,12 +601,17 @@ extern "C" int b200km_set_option(int key, int value) {
         g_fused_variant = value;
         return 0;
     }
+    if (key == B200KM_OPT_K4_VARIANT && value >= 0 && value <= 2) {
+        g_k4_variant = value;
+        return 0;
+    }
     return B200KM_EINVAL;
 }
 extern "C" int b200km_get_option(int key) {
     if (key == B200KM_OPT_K1_VARIANT) return g_k1_variant;
     if (key == B200KM_OPT_K2_VARIANT) return g_k2_variant;
     if (key == B200KM_OPT_FUSED_VARIANT) return g_fused_variant;
+    if (key == B200KM_OPT_K4_VARIANT) return g_k4_variant;
     return B200KM_EINVAL;
 }
 

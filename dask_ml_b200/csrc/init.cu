@@ -9,6 +9,8 @@
 #include "common.cuh"
 #include <type_traits>
 
+int km_k4_variant();  // assign.cu (b200km_set_option)
+
 constexpr int MD_THREADS = 256;
 constexpr int MD_MAXM = B200KM_MINDIST_MAX_M;
 
@@ -204,6 +206,173 @@ mindist_vec_kernel(const T *__restrict__ X, int64_t n, int d, int64_t ldx, const
     km_block_atomic_add(cost, cost_out, red);
 }
 
+// ---------------------------------------------------------------------------------------------
+// K4 on a TMA ring (float32, contiguous 16-byte aligned rows): mindist_vec_kernel's arithmetic, fed from shared memory.
+// The register path above keeps U row groups of loads in flight per warp and reaches 0.99 of the HBM peak with one new
+// candidate but 0.87 / 0.76 with two / four -- more accumulators per row leave fewer registers for loads in flight.
+// Here the loads are not the threads' business: one persistent CTA per SM, warp 0 streams 256-row pieces of X into a
+// ring of MT_NST shared-memory stages with 1-D bulk async copies (mbarrier full / empty per stage; a copy stream of this
+// kind alone reads 7.4 TB/s), and the eight compute warps take 32 rows of a stage each -- same per-lane accumulation
+// order and same cross-lane reduction tree as above, so every row's result is bit-identical to the register path's.
+// A warp's 32 running minima are one coalesced load issued before the wait for the stage, and one coalesced store.
+// ---------------------------------------------------------------------------------------------
+#ifndef MT_NW_DEF
+#define MT_NW_DEF 16
+#endif
+constexpr int MT_NW = MT_NW_DEF;               // compute warps
+constexpr int MT_THREADS = 32 * (MT_NW + 1);   // + the producer warp
+constexpr int MT_NST = 3;
+constexpr int MT_STAGE_BYTES = 64 * 1024;
+
+struct MtShared {
+    uint64_t full[MT_NST];
+    uint64_t empty[MT_NST];
+    float rowmin[MT_NW][32];
+    double red[32];
+};
+
+template <int LPR, int U, int MM>
+__global__ void __launch_bounds__(MT_THREADS, 1)
+mindist_tma_kernel(const float *__restrict__ X, int64_t n, int d, const float *__restrict__ cand, int m,
+                   float *__restrict__ mind2, int init, double *__restrict__ cost_out, int RW) {
+    extern __shared__ __align__(128) unsigned char mt_smem[];
+    unsigned char *ring = mt_smem;                                              // [MT_NST][MT_STAGE_BYTES]
+    float *cs = reinterpret_cast<float *>(mt_smem + (size_t)MT_NST * MT_STAGE_BYTES);   // [m][d]
+    __shared__ MtShared sh;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    for (int e = tid; e < m * d; e += MT_THREADS) cs[e] = cand[e];
+    if (tid == 0) {
+        for (int i = 0; i < MT_NST; ++i) { km_mbar_init(&sh.full[i], 1); km_mbar_init(&sh.empty[i], MT_NW); }
+        km_fence_mbar_init();
+    }
+    __syncthreads();
+    const int R = MT_NW * RW;                                                    // rows per stage
+    const int64_t nsub = (n + R - 1) / R;
+    const uint32_t rb = (uint32_t)d * 4u;
+    double cost = 0.0;
+
+    if (warp == 0) {
+        // ================= producer =================
+        if (lane == 0) {
+            uint32_t i = 0;
+            for (int64_t sub = blockIdx.x; sub < nsub; sub += gridDim.x, ++i) {
+                const uint32_t st = i % MT_NST;
+                const int64_t base = sub * R;
+                const uint32_t rows = (uint32_t)((n - base) < R ? (n - base) : R);
+                if (i >= MT_NST) km_mbar_wait(&sh.empty[st], ((i / MT_NST) - 1) & 1);
+                km_mbar_expect_tx(&sh.full[st], rows * rb);
+                km_bulk_g2s(ring + (size_t)st * MT_STAGE_BYTES, X + base * d, rows * rb, &sh.full[st]);
+            }
+        }
+    } else {
+        // ================= compute warps: warp w takes rows [w RW, (w + 1) RW) of every stage =================
+        constexpr int RPW = 32 / LPR;
+        constexpr bool TR = (U * MM >= LPR) && (LPR > 1);
+        constexpr int G = TR ? LPR / U : 1;
+        const int w = warp - 1;
+        const int sub_l = lane / LPR, l = lane % LPR;
+        const int dv = d / 4;
+        const int own_u = TR ? l / G : l;
+        const bool owner = TR ? (l % G) == 0 : l < U;
+        uint32_t i = 0;
+        for (int64_t sub = blockIdx.x; sub < nsub; sub += gridDim.x, ++i) {
+            const uint32_t st = i % MT_NST;
+            const int64_t base = sub * R + (int64_t)w * RW;              // this warp's first row
+            const int64_t left = n - base;                                // rows of the warp's slice that exist
+            float oldv = INFINITY;
+            if (!init && lane < RW && lane < left) oldv = mind2[base + lane];
+            km_mbar_wait(&sh.full[st], (i / MT_NST) & 1);
+            const float *xs = reinterpret_cast<const float *>(ring + (size_t)st * MT_STAGE_BYTES) + (size_t)w * RW * d;
+            for (int g0 = 0; g0 < RW; g0 += RPW * U) {
+                float acc[U][MM];
+#pragma unroll
+                for (int u = 0; u < U; ++u)
+#pragma unroll
+                    for (int j = 0; j < MM; ++j) acc[u][j] = 0.f;
+                for (int q0 = 0; q0 < dv; q0 += LPR) {
+                    const int q = q0 + l;
+                    float4 xv[U];
+#pragma unroll
+                    for (int u = 0; u < U; ++u) {
+                        const int r = g0 + u * RPW + sub_l;
+                        xv[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+                        if (r < left && q < dv) xv[u] = *reinterpret_cast<const float4 *>(xs + (size_t)r * d + q * 4);
+                    }
+                    if (q < dv) {
+#pragma unroll
+                        for (int j = 0; j < MM; ++j) {
+                            if (j < m) {
+                                const float4 cv = *reinterpret_cast<const float4 *>(cs + (size_t)j * d + (size_t)q * 4);
+                                const float *cp = reinterpret_cast<const float *>(&cv);
+#pragma unroll
+                                for (int u = 0; u < U; ++u) {
+                                    const float *xp = reinterpret_cast<const float *>(&xv[u]);
+#pragma unroll
+                                    for (int e = 0; e < 4; ++e) {
+                                        const float df = xp[e] - cp[e];
+                                        acc[u][j] = fmaf(df, df, acc[u][j]);
+                                    }
+                                }
+                            }
+                        }
+                    }
+                }
+                float mybest = INFINITY;
+                if constexpr (TR) {
+                    constexpr int NV = U * MM, RR = NV / LPR;
+                    float v[NV];
+#pragma unroll
+                    for (int u = 0; u < U; ++u)
+#pragma unroll
+                        for (int j = 0; j < MM; ++j) v[u * MM + j] = acc[u][j];
+                    KmTrReduce<float, NV, NV, LPR / 2>::run(v, l);
+                    const int j0 = (l % G) * RR;
+                    float best = INFINITY;
+#pragma unroll
+                    for (int ii = 0; ii < RR; ++ii) best = (j0 + ii < m && v[ii] < best) ? v[ii] : best;
+#pragma unroll
+                    for (int o = 1; o < G; o <<= 1) {
+                        const float other = __shfl_xor_sync(0xffffffffu, best, o);
+                        best = other < best ? other : best;
+                    }
+                    mybest = best;
+                } else {
+#pragma unroll
+                    for (int u = 0; u < U; ++u) {
+                        float best = INFINITY;
+#pragma unroll
+                        for (int j = 0; j < MM; ++j) {
+                            if (j < m) {
+                                float v = acc[u][j];
+#pragma unroll
+                                for (int o = LPR / 2; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+                                best = v < best ? v : best;
+                            }
+                        }
+                        if (l == u) mybest = best;
+                    }
+                }
+                if (owner) {
+                    const int r = g0 + own_u * RPW + sub_l;
+                    if (r < RW) sh.rowmin[w][r] = mybest;
+                }
+            }
+            __syncwarp();                                     // rowmin complete; every lane is done with the stage
+            if (lane == 0)
+                asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(km_smem_u32(&sh.empty[st])) : "memory");
+            if (lane < RW && lane < left) {
+                const float nb = sh.rowmin[w][lane];
+                const float r = oldv < nb ? oldv : nb;
+                mind2[base + lane] = r;
+                cost += (double)r;
+            }
+            __syncwarp();                                     // rowmin is rewritten by the next stage's groups
+        }
+    }
+    __syncthreads();
+    km_block_atomic_add(cost, cost_out, sh.red);
+}
+
 template <typename T>
 static int mindist_impl(const T *X, int64_t n, int d, int64_t ldx, const T *cand, int m, T *mind2, int init,
                         double *cost_out, void *stream) {
@@ -217,6 +386,48 @@ static int mindist_impl(const T *X, int64_t n, int d, int64_t ldx, const T *cand
     if (d % VECW == 0 && ldx % VECW == 0 && (reinterpret_cast<uintptr_t>(X) & 15) == 0) {
         const int dv = d / VECW;
         int64_t cap = (int64_t)km_num_sms() * 8;
+        if constexpr (sizeof(T) == 4) {
+            // the TMA ring (B200KM_OPT_K4_VARIANT = 1 keeps the register path): contiguous rows, a row group size that
+            // divides a warp's slice of a stage, and enough rows to fill the ring on every SM
+            // (measured, tools/k4_bench.py: the ring wins whenever the pass is HBM-bound -- one or two new candidates, any
+            //  row width -- and for 132..256-byte rows with any number; with 3+ candidates on narrow or wide rows the
+            //  pass is bound by its arithmetic and the register path's 8 resident CTAs per SM do as well or better)
+            const bool ring_pays = m <= 2 || (dv > 8 && dv <= 16) || (dv > 16 && m > 4);
+            if (km_k4_variant() != 1 && (ring_pays || km_k4_variant() == 2) && ldx == d && n >= (int64_t)km_num_sms() * 1024) {
+                int rc_done = -1;
+#define MTV_TRY(LPR_, U_, MM_)                                                                                   \
+    {                                                                                                            \
+        constexpr int GR = (32 / LPR_) * U_;              /* rows of one accumulation group */                   \
+        int RW = 32;                                                                                             \
+        while (RW >= GR && (size_t)MT_NW * RW * d * 4 > (size_t)MT_STAGE_BYTES) RW /= 2;                         \
+        if (GR <= 32 && RW >= GR && RW % GR == 0) {                                                              \
+            auto kern = mindist_tma_kernel<LPR_, U_, MM_>;                                                       \
+            static bool attr_set[KM_MAX_DEVICES] = {};                                                           \
+            if (int rc = km_set_smem_once(kern, 216 * 1024, attr_set)) return rc;                                \
+            const size_t tsm = (size_t)MT_NST * MT_STAGE_BYTES + smem;                                           \
+            int64_t blocks = (n + (int64_t)MT_NW * RW - 1) / ((int64_t)MT_NW * RW);                              \
+            if (blocks > km_num_sms()) blocks = km_num_sms();                                                    \
+            kern<<<(unsigned)blocks, MT_THREADS, tsm, st>>>(reinterpret_cast<const float *>(X), n, d,            \
+                                                            reinterpret_cast<const float *>(cand), m,            \
+                                                            reinterpret_cast<float *>(mind2), init, cost_out, RW); \
+            rc_done = (int)cudaGetLastError();                                                                   \
+        }                                                                                                        \
+    }
+                /* rows in flight per lane group: U * MM == LPR values per lane (one transposing reduction, one value
+                   per lane afterwards), at most 8 -- the loads come from shared memory, not from HBM */
+#define MTV_LAUNCH(LPR_)                                                                                         \
+    if (m <= 2) MTV_TRY(LPR_, (LPR_ / 2 < 8 ? LPR_ / 2 : 8), 2)                                                  \
+    else if (m <= 4) MTV_TRY(LPR_, (LPR_ / 4 < 8 ? LPR_ / 4 : 8), 4)                                             \
+    else MTV_TRY(LPR_, (LPR_ / 8 < 8 ? LPR_ / 8 : 8), MD_MAXM)
+                if (dv <= 4) { }                      /* rows of <= 64 bytes: copies too small to pay */
+                else if (dv <= 8) MTV_LAUNCH(8)
+                else if (dv <= 16) MTV_LAUNCH(16)
+                else if (dv <= 128) MTV_LAUNCH(32)
+#undef MTV_LAUNCH
+#undef MTV_TRY
+                if (rc_done >= 0) return rc_done;
+            }
+        }
 #define MDV_LAUNCH(LPR_, U_)  /* U_ <= LPR_: every row of a warp step needs an owner lane */                   \
     if (m <= 2) MDV_LAUNCH2(LPR_, (2 * U_ <= LPR_ ? 2 * U_ : U_), 2)                                             \
     else if (m <= 4) MDV_LAUNCH2(LPR_, (2 * U_ <= LPR_ ? 2 * U_ : U_), 4)                                       \

@@ -55,6 +55,9 @@ extern "C" {
 #define B200KM_OPT_K2_VARIANT 2 /* 0 = auto, 1 = shared-memory owner table, 2 = chunk sort + run sums, 3 = global atomics */
 #define B200KM_OPT_FUSED_VARIANT 3 /* fused K1+K2 (k <= 16, d <= 32): 0 = auto, 1 = the sorted-tile kernel always,
                                      * 2 = same as auto (the cp.async kernel for 16-byte aligned rows of 64 / 128 bytes) */
+#define B200KM_OPT_K4_VARIANT 4 /* K4 (b200km_mindist_update_f32): 0 = auto (rows streamed through a TMA ring when they are contiguous,
+                                  * 128 .. 2048 bytes long, there are enough of them and the pass is HBM-bound), 1 = the register-path kernel
+                                  * always, 2 = the ring wherever it fits.  Same results bit for bit. */
 int b200km_set_option(int key, int value);
 int b200km_get_option(int key);
 

@@ -325,6 +325,41 @@ def test_mindist_and_cost(eng, n, d, dtype):
     npt.assert_allclose(mind2.cpu().numpy(), d2, rtol=tol * 3, atol=tol * d2.max())
 
 
+@pytest.mark.parametrize("n,d", [(200001, 64), (160000, 32), (180017, 128), (155000, 256), (170000, 48), (160000, 512)])
+def test_mindist_tma_ring_equals_register_path(eng, n, d):
+    """K4 fed by the TMA ring (B200KM_OPT_K4_VARIANT = 2: wherever it fits, from 1024 rows per SM on) against the
+    register-path kernel (= 1): the same per-row arithmetic, so the running minima are equal bit for bit; the
+    float64 cost differs only in the order of the additions.  1 .. 8 new candidates, first pass and update."""
+    import torch
+
+    from dask_ml_b200 import _lib
+
+    rs = np.random.RandomState(n + d)
+    X = (rs.standard_normal((n, d)) * 3 + rs.uniform(-10, 10, size=(1, d))).astype(np.float32)
+    Xd = eng.to_device(X)
+    out = {}
+    try:
+        for variant in (1, 2):
+            assert eng.lib.b200km_set_option(_lib.OPT_K4_VARIANT, variant) == 0
+            mind2 = torch.empty(n, dtype=torch.float32, device=eng.device)
+            costs = [eng.mindist_update(Xd, Xd[:1], mind2, init=True).item()]
+            first = 1
+            for m in (2, 3, 1, 5, 8, 4):
+                cand = Xd[first * 37 : first * 37 + m].contiguous()
+                costs.append(eng.mindist_update(Xd, cand, mind2, init=False).item())
+                first += m
+            out[variant] = (mind2.cpu().numpy(), np.array(costs))
+    finally:
+        eng.lib.b200km_set_option(_lib.OPT_K4_VARIANT, 0)
+    npt.assert_array_equal(out[2][0], out[1][0])
+    npt.assert_allclose(out[2][1], out[1][1], rtol=1e-13)
+    picked = np.concatenate([[0]] + [np.arange(f * 37, f * 37 + m) for f, m in
+                                     zip(np.cumsum([1, 2, 3, 1, 5, 8]), (2, 3, 1, 5, 8, 4))])
+    d2 = sklearn.metrics.pairwise_distances(X[:20000].astype(np.float64), X[picked].astype(np.float64),
+                                            metric="sqeuclidean").min(1)
+    npt.assert_allclose(out[2][0][:20000], d2, rtol=1e-4, atol=3e-5 * d2.max())
+
+
 def test_bernoulli_matches_oracle_philox(eng):
     import torch
 
