@@ -416,6 +416,9 @@ class CudaEngine:
     # ---- K4 .. K6 -------------------------------------------------------------------------
     MINDIST_MAX_M = 8
     MINDIST_K1_MIN_M = 48        # from this many new candidates on, one K1 pass beats m / 8 passes of K4
+    # b200km_mindist_tc_f32 (float32, d <= 128): one pass for up to 128 candidates; it pays from nine on (two launches of
+    # the 8-candidate kernel: 12.4 ms against 11.0 ms per 6e7 x 64 rows; 40 candidates 31 -> 11.3 ms)
+    MINDIST_TC_MIN_M, MINDIST_TC_MAX_M = 9, 128
 
     def mindist_update(self, X: torch.Tensor, cand: torch.Tensor, mind2: torch.Tensor, init: bool) -> torch.Tensor:
         """Running min of squared distances to ``cand`` rows; returns the (1,) float64 local cost."""
@@ -424,6 +427,18 @@ class CudaEngine:
         m = cand.shape[0]
         cost = torch.zeros(1, dtype=torch.float64, device=self.device)
         st = self._stream()
+        if (self.MINDIST_TC_MIN_M <= m <= self.MINDIST_TC_MAX_M and n and X.dtype == torch.float32
+                and d <= self.CDIST_TC_MAX_D and hasattr(self.lib, "b200km_mindist_tc_f32")
+                and self.lib.b200km_get_option(_lib.OPT_K1_VARIANT) in (_lib.K1_AUTO, _lib.K1_TCGEN05)
+                and self.lib.b200km_get_option(_lib.OPT_K4_VARIANT) != 1):
+            # 9 .. 128 new candidates: ONE pass on the tensor cores (K7's kernel with a min-merge epilogue) instead of
+            # m / 8 passes of an FFMA kernel that is bound by its arithmetic from three candidates on
+            pack = self.pack(cand.to(torch.float64).contiguous())
+            for r0 in range(0, n, _MAX_ROWS_PER_CALL):
+                nn = min(_MAX_ROWS_PER_CALL, n - r0)
+                self._call("b200km_mindist_tc_f32", X[r0 : r0 + nn].data_ptr(), nn, d, ldx, pack.buf.data_ptr(), m,
+                           mind2[r0 : r0 + nn].data_ptr(), 1 if init else 0, cost.data_ptr(), st)
+            return cost
         if m >= self.MINDIST_K1_MIN_M and n:
             # many new candidates (a large oversampling factor): ONE K1 pass against all of them instead of m / 8
             # passes of K4, then the merge into the running minimum

@@ -71,6 +71,7 @@ PROTOTYPES = {
     "b200km_finalize": (c_int, [_P, c_int, c_int, _P, _P, _P, _P]),
     "b200km_mindist_update_f32": (c_int, [_P, c_int64, c_int, c_int64, _P, c_int, _P, c_int, _P, _P]),
     "b200km_mindist_update_f64": (c_int, [_P, c_int64, c_int, c_int64, _P, c_int, _P, c_int, _P, _P]),
+    "b200km_mindist_tc_f32": (c_int, [_P, c_int64, c_int, c_int64, _P, c_int, _P, c_int, _P, _P]),
     "b200km_mindist_merge_f32": (c_int, [_P, c_int64, _P, c_int, _P, _P]),
     "b200km_mindist_merge_f64": (c_int, [_P, c_int64, _P, c_int, _P, _P]),
     "b200km_mindist_pots_f32": (c_int, [_P, c_int64, c_int, c_int64, _P, c_int, _P, _P, _P]),

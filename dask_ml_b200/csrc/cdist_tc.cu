@@ -48,13 +48,20 @@ struct CdBars {
     uint32_t pad;
     alignas(16) float mu[CD_MAX_D];
     float xn_part[128];            // CD_ROWS = 128: the second staging thread's half of ||x||^2
+    float mins[2][4][4][32];       // MODE 3: [row half][32-row chunk][lane quarter][row]: the quarters' minima
 };
 
 // MODE 0: squared distance, 1: distance, 2: exp(-gamma * squared distance)
+// MODE 3 (K4 against many new candidates, b200km_mindist_tc_f32): nothing of the matrix is stored -- `out` is the
+//   running per-row minimum: out[i] = min(out[i], min_j ||x_i - c_j||^2) (init != 0: the old value is ignored) and
+//   *cost += sum_i out[i].  The k <= 128 candidates are the 128 TMEM lanes of ONE accumulator stage; the warps that
+//   own lanes with real candidates read their 32 x 32 pieces and a transposing min-reduction over the 32 lanes leaves
+//   row i's minimum in lane i -- coalesced access to the minima, one exchange per value instead of five.
 template <bool VEC, int MODE, int CD_ROWS>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 cdist_tc_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx, const unsigned char *__restrict__ tc_img,
-                const float *__restrict__ mu, int k, float *__restrict__ out, int64_t ldo, float gamma) {
+                const float *__restrict__ mu, int k, float *__restrict__ out, int64_t ldo, float gamma,
+                double *__restrict__ cost, int init) {
     extern __shared__ __align__(1024) unsigned char tc_smem[];
     const int kpad = km_tc_kpad(d);
     const int nch = kpad / 4;                 // 16-byte K chunks of the real features
@@ -167,6 +174,7 @@ cdist_tc_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx, cons
         constexpr int NCHM = 16;                 // chunks per staging thread: 64 features (x 2 threads at CD_ROWS = 128)
         constexpr int EC = CD_ROWS / 64;         // 32-column chunks per epilogue warp
         float4 ld[NCHM];
+        double cost_acc = 0.0;                   // MODE 3
         auto issue_loads = [&](int64_t blk) {
             const int64_t row = blk * CD_ROWS + srow;
             const float *src = X + row * ldx;
@@ -241,6 +249,59 @@ cdist_tc_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx, cons
                 const int j = s * 128 + q4 * 32 + lane;                 // this lane's centre
                 const bool jok = j < k;
                 const uint32_t tbase = tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(a * CD_ROWS + g * (CD_ROWS / 2));
+                if (MODE == 3) {
+                    // lane quarters 1..3 have work only when k > 32 * q4; padded candidates carry ||c||^2 = 1e30 and
+                    // never win.  mmin[c]: after the reduction, lane i holds the minimum of row r0 + i over this
+                    // warp's 32 candidates; the quarters are merged through shared memory (mins[g][c][q4][lane]).
+                    const bool busy = 32 * q4 < k;
+#pragma unroll
+                    for (int c = 0; c < EC; ++c) {
+                        float v[32];
+                        if (busy) {
+                            uint32_t r[32];
+                            tmem_ld32(tbase + (uint32_t)(c * 32), r);
+                            tmem_ld_wait();
+#pragma unroll
+                            for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+                            // transposing min-reduction: at every step a lane hands on half of what it holds
+#pragma unroll
+                            for (int O = 16, H = 16; O >= 1; O >>= 1, H >>= 1) {
+                                const bool up = (lane & O) != 0;
+#pragma unroll
+                                for (int i = 0; i < 16; ++i) {
+                                    if (i < H) {
+                                        const float send = up ? v[i] : v[i + H];
+                                        const float keep = up ? v[i + H] : v[i];
+                                        v[i] = fminf(keep, __shfl_xor_sync(0xffffffffu, send, O));
+                                    }
+                                }
+                            }
+                        } else {
+                            v[0] = INFINITY;
+                        }
+                        bars->mins[g][c][q4][lane] = v[0];
+                    }
+                    tc_fence_before();
+                    mbar_arrive(&bars->a_empty[a]);
+                    // the four quarters of this row half meet (named barrier per half: 128 threads), quarter 0 finishes
+                    asm volatile("bar.sync %0, 128;" ::"r"(2 + g) : "memory");
+                    if (q4 == 0) {
+#pragma unroll
+                        for (int c = 0; c < EC; ++c) {
+                            const int64_t r = row0 + c * 32 + lane;
+                            if (r < n) {
+                                float mn = fminf(fminf(bars->mins[g][c][0][lane], bars->mins[g][c][1][lane]),
+                                                 fminf(bars->mins[g][c][2][lane], bars->mins[g][c][3][lane]));
+                                mn = fmaxf(mn, 0.f);
+                                if (!init) mn = fminf(mn, out[r]);
+                                out[r] = mn;
+                                cost_acc += (double)mn;
+                            }
+                        }
+                    }
+                    asm volatile("bar.sync %0, 128;" ::"r"(2 + g) : "memory");   // mins is rewritten by the next block
+                    continue;
+                }
                 uint32_t ra[32], rb[32];
                 tmem_ld32(tbase, ra);
                 tmem_ld_wait();
@@ -279,6 +340,10 @@ cdist_tc_kernel(const float *__restrict__ X, int64_t n, int d, int64_t ldx, cons
                 mbar_arrive(&bars->a_empty[a]);
             }
         }
+        if (MODE == 3) {
+            cost_acc = km_warp_sum(cost_acc);
+            if (lane == 0 && cost_acc != 0.0) atomicAdd(cost, cost_acc);
+        }
     }
 
     tc_fence_before();
@@ -295,8 +360,9 @@ bool km_tc_pair_mode();   // assign.cu
 
 // host-side launcher, called from b200km_cdist_pack_f32 (misc.cu)
 int km_launch_cdist_tc(const float *X, int64_t n, int d, int64_t ldx, const void *pack, int k, float *out, int64_t ldo,
-                       int mode, float gamma, cudaStream_t st) {
+                       int mode, float gamma, cudaStream_t st, double *cost, int init) {
     if (d > CD_MAX_D || km_tc_pair_mode()) return B200KM_ETOOBIG;
+    if (mode == 3 && k > 128) return B200KM_ETOOBIG;
     const KmPackLayout L = km_pack_layout(k, d);
     const unsigned char *pk = static_cast<const unsigned char *>(pack);
     const int nch = km_tc_kpad(d) / 4;
@@ -312,10 +378,12 @@ int km_launch_cdist_tc(const float *X, int64_t n, int d, int64_t ldx, const void
     {                                                                                                              \
         static bool attr[KM_MAX_DEVICES] = {};                                                                     \
         if (int rc = km_set_smem_once(cdist_tc_kernel<VEC_, MODE_, ROWS_>, 227 * 1024, attr)) return rc;           \
-        cdist_tc_kernel<VEC_, MODE_, ROWS_><<<grid, TC_THREADS, smem, st>>>(X, n, d, ldx, img, mu, k, out, ldo, gamma); \
+        cdist_tc_kernel<VEC_, MODE_, ROWS_><<<grid, TC_THREADS, smem, st>>>(X, n, d, ldx, img, mu, k, out, ldo, gamma,  \
+                                                                      cost, init);                             \
     }
 #define CD_LAUNCH_M(VEC_, ROWS_)                                                                                   \
-    if (mode == 0) CD_LAUNCH(VEC_, 0, ROWS_) else if (mode == 1) CD_LAUNCH(VEC_, 1, ROWS_) else CD_LAUNCH(VEC_, 2, ROWS_)
+    if (mode == 0) CD_LAUNCH(VEC_, 0, ROWS_) else if (mode == 1) CD_LAUNCH(VEC_, 1, ROWS_)                          \
+    else if (mode == 2) CD_LAUNCH(VEC_, 2, ROWS_) else CD_LAUNCH(VEC_, 3, ROWS_)
     if (rows == 256) {
         if (vec) { CD_LAUNCH_M(true, 256) } else { CD_LAUNCH_M(false, 256) }
     } else {

@@ -118,14 +118,24 @@ extern "C" int b200km_cdist_f64(const double *X, int64_t n, int d, int64_t ldx, 
 
 // K7 on the tensor cores (cdist_tc.cu): float32 rows of up to 64 features against a centre pack
 int km_launch_cdist_tc(const float *X, int64_t n, int d, int64_t ldx, const void *pack, int k, float *out, int64_t ldo,
-                       int mode, float gamma, cudaStream_t st);
+                       int mode, float gamma, cudaStream_t st, double *cost, int init);
 extern "C" int b200km_cdist_pack_f32(const float *X, int64_t n, int d, int64_t ldx, const void *pack, int k, float *out,
                                      int64_t ldo, int mode, double gamma, void *stream) {
     KM_CHECK_ARG(X && pack && out && n > 0 && d > 0 && k > 0 && ldx >= d && ldo >= k, B200KM_EINVAL);
     KM_CHECK_ARG(mode >= B200KM_CDIST_SQUARED && mode <= B200KM_CDIST_RBF, B200KM_EINVAL);
     KM_CHECK_ARG(k <= B200KM_MAX_K, B200KM_ETOOBIG);
     KM_CHECK_ARG((reinterpret_cast<uintptr_t>(pack) & 255) == 0, B200KM_EALIGN);
-    return km_launch_cdist_tc(X, n, d, ldx, pack, k, out, ldo, mode, (float)gamma, km_stream(stream));
+    return km_launch_cdist_tc(X, n, d, ldx, pack, k, out, ldo, mode, (float)gamma, km_stream(stream), nullptr, 0);
+}
+
+// K4 against up to 128 new candidates at once, on the same kernel (mode 3: min over the candidates, merged into the running
+// minimum, nothing else stored)
+extern "C" int b200km_mindist_tc_f32(const float *X, int64_t n, int d, int64_t ldx, const void *pack, int m, float *mind2,
+                                     int init, double *cost_out, void *stream) {
+    KM_CHECK_ARG(X && pack && mind2 && cost_out && n > 0 && d > 0 && m > 0 && ldx >= d, B200KM_EINVAL);
+    KM_CHECK_ARG(m <= 128 && d <= 128, B200KM_ETOOBIG);
+    KM_CHECK_ARG((reinterpret_cast<uintptr_t>(pack) & 255) == 0, B200KM_EALIGN);
+    return km_launch_cdist_tc(X, n, d, ldx, pack, m, mind2, 0, 3, 0.f, km_stream(stream), cost_out, init);
 }
 
 // pairwise kernels on the same tile kernel (the SpectralClustering tail)

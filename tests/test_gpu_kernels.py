@@ -360,6 +360,40 @@ def test_mindist_tma_ring_equals_register_path(eng, n, d):
     npt.assert_allclose(out[2][0][:20000], d2, rtol=1e-4, atol=3e-5 * d2.max())
 
 
+@pytest.mark.parametrize("n,d,m,pad", [(50000, 64, 5, 0), (20001, 64, 8, 0), (30000, 32, 20, 0), (9000, 128, 128, 0),
+                                       (7000, 7, 47, 0), (12345, 100, 33, 4), (300, 64, 6, 0), (4000, 16, 129, 0)])
+def test_mindist_many_candidates_on_tensor_cores(eng, n, d, m, pad):
+    """K4 against 9 .. 128 new candidates in one tensor-core pass (b200km_mindist_tc_f32: K7's kernel with a min-merge
+    epilogue) against float64 numpy, first pass and update, far from the origin; fewer / more candidates take the other
+    routes and meet the same bounds."""
+    import torch
+
+    rs = np.random.RandomState(n + m)
+    C = rs.uniform(-10, 10, size=(12, d)) + 300.0
+    X = (C[rs.randint(0, 12, size=n)] + rs.standard_normal((n, d))).astype(np.float32)
+    full = eng.to_device(np.concatenate([X, np.zeros((n, pad), np.float32)], axis=1)) if pad else eng.to_device(X)
+    Xd = full[:, :d]
+    cand_rows = rs.choice(n, size=m + 3, replace=False)
+    mind2 = torch.empty(n, dtype=torch.float32, device=eng.device)
+    launches0 = eng.launches
+    cost0 = eng.mindist_update(Xd, Xd[cand_rows[:3]].contiguous(), mind2, init=True).item()
+    eng.trace = []
+    cost1 = eng.mindist_update(Xd, Xd[cand_rows[3:]].contiguous(), mind2, init=False).item()
+    names = [nm for nm, _ in eng.trace]
+    eng.trace = None
+    assert ("b200km_mindist_tc_f32" in names) == (9 <= m <= 128)
+    X64 = X.astype(np.float64)
+    d2a = sklearn.metrics.pairwise_distances(X64, X64[cand_rows[:3]], metric="sqeuclidean").min(1)
+    d2b = np.minimum(d2a, sklearn.metrics.pairwise_distances(X64, X64[cand_rows[3:]], metric="sqeuclidean").min(1))
+    npt.assert_allclose(cost0, d2a.sum(), rtol=3e-5)
+    npt.assert_allclose(cost1, d2b.sum(), rtol=3e-5)
+    # centred expanded form: absolute error ~2^-21 of the spread squared (NOT of the offset 300)
+    spread2 = ((X64 - X64.mean(0)) ** 2).sum(1).max()
+    npt.assert_allclose(mind2.cpu().numpy(), d2b, rtol=1e-4, atol=4e-6 * spread2)
+    # the candidates themselves: distance (numerically) zero
+    assert mind2.cpu().numpy()[cand_rows].max() <= 4e-6 * spread2
+
+
 def test_bernoulli_matches_oracle_philox(eng):
     import torch
 

@@ -29,3 +29,8 @@ for name, ev in tr:
 print(f"rows {n} k {k}: wall {wall*1e3:.1f} ms, rounds {len(rs.picks)}, gpu-timeline total {e0.elapsed_time(prev):.1f} ms")
 for name, v in sorted(agg.items(), key=lambda kv: -sum(kv[1])):
     print(f"  {name:34s} x{len(v):3d}  total {sum(v):8.2f} ms  median {statistics.median(v):7.3f}  max {max(v):7.3f}")
+k4 = agg.get("b200km_mindist_update_f32", [])
+if k4:   # one K4 launch per round that found new candidates: its time against the number of candidates it took
+    m_of = [len(set(int(v) for v in p)) for p in rs.picks]
+    print("  K4 launches (ms):", " ".join(f"{t:.1f}" for t in k4))
+    print("  picks per round :", " ".join(str(m) for m in m_of))

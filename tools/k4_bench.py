@@ -1,5 +1,5 @@
-"""K4 (b200km_mindist_update_f32) per launch: the register-path kernel (B200KM_OPT_K4_VARIANT = 1) against auto (TMA
-ring), 1 / 2 / 3 / 4 / 8 new candidates.  argv: [rows d]"""
+"""K4 per pass over X: B200KM_OPT_K4_VARIANT = 1 (register-path kernel, 8 candidates per launch; K1 route from 48
+candidates on) against auto (TMA ring up to 4 candidates, one tensor-core pass for 9 .. 128).  argv: [rows d]"""
 import os, sys
 import torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -10,9 +10,9 @@ n = int(float(sys.argv[1])) if len(sys.argv) > 1 else 60_000_000
 d = int(sys.argv[2]) if len(sys.argv) > 2 else 64
 X = torch.randn(n, d, device=eng.device)
 mind2 = torch.full((n,), 1e30, device=eng.device)
-for m in (1, 2, 3, 4, 8):
+for m in (1, 2, 3, 4, 5, 8, 16, 40, 128):
     cand = X[100 : 100 + m].contiguous()
-    for variant, name in ((1, "registers"), (2, "TMA ring ")):
+    for variant, name in ((1, "registers / K1 route "), (0, "auto (ring, TC >= 9) ")):
         eng.lib.b200km_set_option(_lib.OPT_K4_VARIANT, variant)
         for _ in range(2):
             eng.mindist_update(X, cand, mind2, init=False)
