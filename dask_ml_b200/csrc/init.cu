@@ -373,6 +373,120 @@ mindist_tma_kernel(const float *__restrict__ X, int64_t n, int d, const float *_
     km_block_atomic_add(cost, cost_out, sh.red);
 }
 
+// ---------------------------------------------------------------------------------------------
+// K4 for 3 .. 8 new candidates (float32 rows of 128 / 256 / 512 bytes): one THREAD per row.
+// With LPR lanes per row (the kernels above) every candidate's partial sums must be reduced across the lanes: from three
+// candidates on that reduction and its bookkeeping are most of the instruction stream (88 instructions per row at 8
+// candidates, 36 of them arithmetic) and the pass is bound by its issue slots, not by HBM.  Here a warp stages ITS 32
+// rows with cp.async into one of two private shared-memory buffers (16-byte chunks XOR-swizzled by the row, so that
+// the 32 lanes reading chunk c of 32 different rows hit different banks), each lane then walks its own row chunk by
+// chunk against the candidates (broadcast loads) with one accumulator per candidate -- no cross-lane step at all, and
+// lane = row makes the minima one coalesced load and store.  No block barrier in the loop.
+// The sum of a row runs over its elements in order, whatever the shard or the launch shape: every row's result
+// depends on the row and the candidates alone.
+// ---------------------------------------------------------------------------------------------
+// warps per CTA (one CTA per SM): 24, 12 for 512-byte rows -- ONE 32-row buffer per warp (192 KB in all at d = 64 and
+// 128): a warp's copy is not overlapped with its own arithmetic but with the other warps', and six warps per scheduler
+// cover the latencies of the walk better than three with two buffers each did (5.4 -> ms per 6e7 rows at 8 candidates)
+__host__ __device__ constexpr int mr_nw(int dv) { return dv <= 16 ? 24 : 12; }
+
+template <int MM, int DV>
+__global__ void __launch_bounds__(32 * mr_nw(DV), 1)
+mindist_rows_kernel(const float *__restrict__ X, int64_t n, int64_t ldx, const float *__restrict__ cand, int m,
+                    float *__restrict__ mind2, int init, double *__restrict__ cost_out) {
+    constexpr int D = DV * 4;
+    constexpr int RB = DV * 16;                // row bytes
+    constexpr int MR_NW = mr_nw(DV);
+    extern __shared__ __align__(128) unsigned char mr_smem[];
+    float *cs = reinterpret_cast<float *>(mr_smem);                              // [m][D]
+    unsigned char *bufs = mr_smem + (((size_t)MM * D * 4 + 127) & ~(size_t)127); // [MR_NW][32][RB]
+    __shared__ double red[32];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    for (int e = tid; e < m * D; e += 32 * MR_NW) cs[e] = cand[e];
+    __syncthreads();
+    unsigned char *mine = bufs + (size_t)warp * 32 * RB;
+    const uint32_t mine32 = km_smem_u32(mine);
+    // staging: lane l moves chunks l, l + 32, ... of the slice (consecutive lanes -> consecutive 16-byte pieces of a row)
+    auto issue = [&](int64_t base) {
+        const int64_t left = n - base;
+#pragma unroll
+        for (int i = 0; i < DV; ++i) {
+            const int e = lane + 32 * i, r = e / DV, c = e % DV;
+            if (r < left)
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(mine32 + (uint32_t)(r * RB + ((c ^ (r & 7)) << 4))),
+                             "l"(X + (base + r) * ldx + c * 4) : "memory");
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    const int64_t nslices = (n + 31) / 32;
+    const int64_t stride = (int64_t)gridDim.x * MR_NW;
+    double cost = 0.0;
+    const unsigned char *xr = mine + (size_t)lane * RB;
+    const uint32_t my_sw = (uint32_t)(lane & 7);
+    for (int64_t sl = (int64_t)blockIdx.x * MR_NW + warp; sl < nslices; sl += stride) {
+        const int64_t row = sl * 32 + lane;
+        issue(sl * 32);
+        float oldv = INFINITY;
+        if (!init && row < n) oldv = mind2[row];
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+        __syncwarp();                       // the slice has landed for every lane
+        float acc[MM];
+#pragma unroll
+        for (int j = 0; j < MM; ++j) acc[j] = 0.f;
+#pragma unroll 4
+        for (int c = 0; c < DV; ++c) {
+            const float4 xv = *reinterpret_cast<const float4 *>(xr + ((c ^ my_sw) << 4));
+#pragma unroll
+            for (int j = 0; j < MM; ++j) {
+                if (j < m) {
+                    const float4 cv = *reinterpret_cast<const float4 *>(cs + j * D + c * 4);
+                    float df;
+                    df = xv.x - cv.x; acc[j] = fmaf(df, df, acc[j]);
+                    df = xv.y - cv.y; acc[j] = fmaf(df, df, acc[j]);
+                    df = xv.z - cv.z; acc[j] = fmaf(df, df, acc[j]);
+                    df = xv.w - cv.w; acc[j] = fmaf(df, df, acc[j]);
+                }
+            }
+        }
+        __syncwarp();                       // every lane has read its row: the buffer can be refilled
+        if (row < n) {
+            float best = oldv;
+#pragma unroll
+            for (int j = 0; j < MM; ++j) best = (j < m && acc[j] < best) ? acc[j] : best;
+            mind2[row] = best;
+            cost += (double)best;
+        }
+    }
+    km_block_atomic_add(cost, cost_out, red);
+}
+
+// (or -1: not for this shape).  Taken for EVERY n when it fits, so that a row's minimum does not depend on which
+// kernel the size of its shard would otherwise select.
+static int mindist_rows(const float *X, int64_t n, int d, int64_t ldx, const float *cand, int m, float *mind2, int init,
+                        double *cost_out, cudaStream_t st) {
+    if (m < 3 || m > MD_MAXM || d % 4 != 0 || ldx % 4 != 0 || (reinterpret_cast<uintptr_t>(X) & 15) != 0) return -1;
+    if (km_k4_variant() == 1) return -1;
+    const int dv = d / 4;
+    if (dv != 8 && dv != 16 && dv != 32) return -1;
+#define MR_LAUNCH(MM_, DV_)                                                                                      \
+    {                                                                                                            \
+        constexpr int NW_ = mr_nw(DV_);                                                                          \
+        int64_t blocks = ((n + 31) / 32 + NW_ - 1) / NW_;                                                        \
+        if (blocks > km_num_sms()) blocks = km_num_sms();                                                        \
+        auto kern = mindist_rows_kernel<MM_, DV_>;                                                               \
+        static bool attr_set[KM_MAX_DEVICES] = {};                                                               \
+        if (int rc = km_set_smem_once(kern, 216 * 1024, attr_set)) return rc;                                    \
+        const size_t smem = (((size_t)MM_ * DV_ * 16 + 127) & ~(size_t)127) + (size_t)NW_ * 32 * DV_ * 16;       \
+        kern<<<(unsigned)blocks, 32 * NW_, smem, st>>>(X, n, ldx, cand, m, mind2, init, cost_out);               \
+    }
+#define MR_LAUNCH_D(MM_)                                                                                         \
+    if (dv == 8) MR_LAUNCH(MM_, 8) else if (dv == 16) MR_LAUNCH(MM_, 16) else MR_LAUNCH(MM_, 32)
+    if (m <= 4) { MR_LAUNCH_D(4) } else { MR_LAUNCH_D(8) }
+#undef MR_LAUNCH_D
+#undef MR_LAUNCH
+    return (int)cudaGetLastError();
+}
+
 template <typename T>
 static int mindist_impl(const T *X, int64_t n, int d, int64_t ldx, const T *cand, int m, T *mind2, int init,
                         double *cost_out, void *stream) {
@@ -386,6 +500,11 @@ static int mindist_impl(const T *X, int64_t n, int d, int64_t ldx, const T *cand
     if (d % VECW == 0 && ldx % VECW == 0 && (reinterpret_cast<uintptr_t>(X) & 15) == 0) {
         const int dv = d / VECW;
         int64_t cap = (int64_t)km_num_sms() * 8;
+        if constexpr (sizeof(T) == 4) {
+            const int rc_rows = mindist_rows(reinterpret_cast<const float *>(X), n, d, ldx, reinterpret_cast<const float *>(cand), m,
+                                             reinterpret_cast<float *>(mind2), init, cost_out, st);
+            if (rc_rows >= 0) return rc_rows;
+        }
         if constexpr (sizeof(T) == 4) {
             // the TMA ring (B200KM_OPT_K4_VARIANT = 1 keeps the register path): contiguous rows, a row group size that
             // divides a warp's slice of a stage, and enough rows to fill the ring on every SM

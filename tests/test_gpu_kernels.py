@@ -329,7 +329,8 @@ def test_mindist_and_cost(eng, n, d, dtype):
 def test_mindist_tma_ring_equals_register_path(eng, n, d):
     """K4 fed by the TMA ring (B200KM_OPT_K4_VARIANT = 2: wherever it fits, from 1024 rows per SM on) against the
     register-path kernel (= 1): the same per-row arithmetic, so the running minima are equal bit for bit; the
-    float64 cost differs only in the order of the additions.  1 .. 8 new candidates, first pass and update."""
+    float64 cost differs only in the order of the additions.  One or two new candidates (more take the row kernel
+    whatever the size), first pass and update."""
     import torch
 
     from dask_ml_b200 import _lib
@@ -344,7 +345,7 @@ def test_mindist_tma_ring_equals_register_path(eng, n, d):
             mind2 = torch.empty(n, dtype=torch.float32, device=eng.device)
             costs = [eng.mindist_update(Xd, Xd[:1], mind2, init=True).item()]
             first = 1
-            for m in (2, 3, 1, 5, 8, 4):
+            for m in (2, 1, 2, 1, 2, 2):
                 cand = Xd[first * 37 : first * 37 + m].contiguous()
                 costs.append(eng.mindist_update(Xd, cand, mind2, init=False).item())
                 first += m
@@ -354,7 +355,7 @@ def test_mindist_tma_ring_equals_register_path(eng, n, d):
     npt.assert_array_equal(out[2][0], out[1][0])
     npt.assert_allclose(out[2][1], out[1][1], rtol=1e-13)
     picked = np.concatenate([[0]] + [np.arange(f * 37, f * 37 + m) for f, m in
-                                     zip(np.cumsum([1, 2, 3, 1, 5, 8]), (2, 3, 1, 5, 8, 4))])
+                                     zip(np.cumsum([1, 2, 1, 2, 1, 2]), (2, 1, 2, 1, 2, 2))])
     d2 = sklearn.metrics.pairwise_distances(X[:20000].astype(np.float64), X[picked].astype(np.float64),
                                             metric="sqeuclidean").min(1)
     npt.assert_allclose(out[2][0][:20000], d2, rtol=1e-4, atol=3e-5 * d2.max())
@@ -392,6 +393,44 @@ def test_mindist_many_candidates_on_tensor_cores(eng, n, d, m, pad):
     npt.assert_allclose(mind2.cpu().numpy(), d2b, rtol=1e-4, atol=4e-6 * spread2)
     # the candidates themselves: distance (numerically) zero
     assert mind2.cpu().numpy()[cand_rows].max() <= 4e-6 * spread2
+
+
+@pytest.mark.parametrize("n,d,pad", [(200001, 64, 0), (100, 64, 0), (33, 32, 0), (50017, 128, 0), (70000, 32, 4), (9999, 64, 8)])
+def test_mindist_row_kernel(eng, n, d, pad):
+    """K4 with 3 .. 8 new candidates: one thread per row behind warp-private cp.async buffers.  Against float64 numpy
+    (direct-form float32 accuracy), and: the result of a row does not depend on where the row sits -- the same rows
+    handed over as a shifted slice give the same minima bit for bit (what makes the picks independent of the sharding)."""
+    import torch
+
+    rs = np.random.RandomState(n + d)
+    X = (rs.standard_normal((n, d)) * 3 + rs.uniform(-10, 10, size=(1, d))).astype(np.float32)
+    full = eng.to_device(np.concatenate([X, np.zeros((n, pad), np.float32)], axis=1)) if pad else eng.to_device(X)
+    Xd = full[:, :d]
+    mind2 = torch.empty(n, dtype=torch.float32, device=eng.device)
+    eng.mindist_update(Xd, Xd[:1].contiguous(), mind2, init=True)
+    cands = []
+    first = 1
+    eng.trace = []
+    for m in (3, 8, 5, 4, 7, 6):
+        c = np.arange(first * 3, first * 3 + m) % n
+        cands.append(c)
+        eng.mindist_update(Xd, Xd[torch.as_tensor(c, device=eng.device)].contiguous(), mind2, init=False)
+        first += m
+    names = [nm for nm, _ in eng.trace]
+    eng.trace = None
+    assert names.count("b200km_mindist_update_f32") == 6
+    allc = np.concatenate([[0]] + cands)
+    X64 = X.astype(np.float64)
+    d2 = sklearn.metrics.pairwise_distances(X64[:20000], X64[allc], metric="sqeuclidean").min(1)
+    got = mind2.cpu().numpy()
+    npt.assert_allclose(got[:20000], d2, rtol=2e-5, atol=1e-5 * d2.max())
+    if n > 100:
+        off = 37                                  # a slice that starts mid-warp: other lanes, other CTAs, same answers
+        m2 = torch.empty(n - off, dtype=torch.float32, device=eng.device)
+        eng.mindist_update(Xd[off:], Xd[:1].contiguous(), m2, init=True)
+        for c in cands:
+            eng.mindist_update(Xd[off:], Xd[torch.as_tensor(c, device=eng.device)].contiguous(), m2, init=False)
+        npt.assert_array_equal(m2.cpu().numpy(), got[off:])
 
 
 def test_bernoulli_matches_oracle_philox(eng):

@@ -12,7 +12,7 @@ X = torch.randn(n, d, device=eng.device)
 mind2 = torch.full((n,), 1e30, device=eng.device)
 for m in (1, 2, 3, 4, 5, 8, 16, 40, 128):
     cand = X[100 : 100 + m].contiguous()
-    for variant, name in ((1, "registers / K1 route "), (0, "auto (ring, TC >= 9) ")):
+    for variant, name in ((1, "registers / K1 route "), (0, "auto (ring, rows, TC) ")):
         eng.lib.b200km_set_option(_lib.OPT_K4_VARIANT, variant)
         for _ in range(2):
             eng.mindist_update(X, cand, mind2, init=False)
