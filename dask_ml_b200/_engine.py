@@ -416,9 +416,10 @@ class CudaEngine:
     # ---- K4 .. K6 -------------------------------------------------------------------------
     MINDIST_MAX_M = 8
     MINDIST_K1_MIN_M = 48        # from this many new candidates on, one K1 pass beats m / 8 passes of K4
-    # b200km_mindist_tc_f32 (float32, d <= 128): one pass for up to 128 candidates; it pays from nine on (two launches of
-    # the 8-candidate kernel: 12.4 ms against 11.0 ms per 6e7 x 64 rows; 40 candidates 31 -> 11.3 ms)
-    MINDIST_TC_MIN_M, MINDIST_TC_MAX_M = 9, 128
+    # b200km_mindist_tc_f32 (float32, d <= 128): one pass for up to 128 candidates at 11 ms per 6e7 x 64 rows whatever
+    # their number; a pass of the 8-candidate kernel is 3.7 ms (one thread per row), so the tensor-core pass pays from
+    # 25 candidates on (40 candidates: 18.7 -> 11.3 ms)
+    MINDIST_TC_MIN_M, MINDIST_TC_MAX_M = 25, 128
 
     def mindist_update(self, X: torch.Tensor, cand: torch.Tensor, mind2: torch.Tensor, init: bool) -> torch.Tensor:
         """Running min of squared distances to ``cand`` rows; returns the (1,) float64 local cost."""
@@ -431,7 +432,7 @@ class CudaEngine:
                 and d <= self.CDIST_TC_MAX_D and hasattr(self.lib, "b200km_mindist_tc_f32")
                 and self.lib.b200km_get_option(_lib.OPT_K1_VARIANT) in (_lib.K1_AUTO, _lib.K1_TCGEN05)
                 and self.lib.b200km_get_option(_lib.OPT_K4_VARIANT) != 1):
-            # 9 .. 128 new candidates: ONE pass on the tensor cores (K7's kernel with a min-merge epilogue) instead of
+            # 25 .. 128 new candidates: ONE pass on the tensor cores (K7's kernel with a min-merge epilogue) instead of
             # m / 8 passes of an FFMA kernel that is bound by its arithmetic from three candidates on
             pack = self.pack(cand.to(torch.float64).contiguous())
             for r0 in range(0, n, _MAX_ROWS_PER_CALL):

@@ -280,7 +280,7 @@ int b200km_mindist_update_f64(const double *X, int64_t n, int d, int64_t ldx, co
  * b200km_pack_centers (one-CTA layout), are the M side of K7's 3xTF32 kernel (b200km_cdist_pack_f32), whose epilogue
  * here keeps only the minimum over the candidates and merges it into mind2; distances in the centred expanded form
  * (error ~2^-21 of the data's spread squared).  The FFMA kernel above takes 8 candidates per launch; this one costs the
- * same whatever their number (11 ms per 6e7 x 64 rows: the 128-lane MMA is the bound) and wins from 9 candidates on. */
+ * same whatever their number (11 ms per 6e7 x 64 rows: the 128-lane MMA is the bound) and wins from 25 candidates on. */
 int b200km_mindist_tc_f32(const float *X, int64_t n, int d, int64_t ldx, const void *pack, int m, float *mind2,
                           int init, double *cost_out, void *stream);
 /* The same update when the distances to the new candidates come from somewhere else (K1 against MANY candidates at

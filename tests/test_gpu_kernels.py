@@ -361,10 +361,10 @@ def test_mindist_tma_ring_equals_register_path(eng, n, d):
     npt.assert_allclose(out[2][0][:20000], d2, rtol=1e-4, atol=3e-5 * d2.max())
 
 
-@pytest.mark.parametrize("n,d,m,pad", [(50000, 64, 5, 0), (20001, 64, 8, 0), (30000, 32, 20, 0), (9000, 128, 128, 0),
+@pytest.mark.parametrize("n,d,m,pad", [(50000, 64, 5, 0), (20001, 64, 8, 0), (30000, 32, 20, 0), (30000, 32, 25, 0), (9000, 128, 128, 0),
                                        (7000, 7, 47, 0), (12345, 100, 33, 4), (300, 64, 6, 0), (4000, 16, 129, 0)])
 def test_mindist_many_candidates_on_tensor_cores(eng, n, d, m, pad):
-    """K4 against 9 .. 128 new candidates in one tensor-core pass (b200km_mindist_tc_f32: K7's kernel with a min-merge
+    """K4 against 25 .. 128 new candidates in one tensor-core pass (b200km_mindist_tc_f32: K7's kernel with a min-merge
     epilogue) against float64 numpy, first pass and update, far from the origin; fewer / more candidates take the other
     routes and meet the same bounds."""
     import torch
@@ -382,7 +382,7 @@ def test_mindist_many_candidates_on_tensor_cores(eng, n, d, m, pad):
     cost1 = eng.mindist_update(Xd, Xd[cand_rows[3:]].contiguous(), mind2, init=False).item()
     names = [nm for nm, _ in eng.trace]
     eng.trace = None
-    assert ("b200km_mindist_tc_f32" in names) == (9 <= m <= 128)
+    assert ("b200km_mindist_tc_f32" in names) == (25 <= m <= 128)
     X64 = X.astype(np.float64)
     d2a = sklearn.metrics.pairwise_distances(X64, X64[cand_rows[:3]], metric="sqeuclidean").min(1)
     d2b = np.minimum(d2a, sklearn.metrics.pairwise_distances(X64, X64[cand_rows[3:]], metric="sqeuclidean").min(1))

@@ -1,5 +1,5 @@
 """K4 per pass over X: B200KM_OPT_K4_VARIANT = 1 (register-path kernel, 8 candidates per launch; K1 route from 48
-candidates on) against auto (TMA ring up to 4 candidates, one tensor-core pass for 9 .. 128).  argv: [rows d]"""
+candidates on) against auto (TMA ring up to 4 candidates, one thread per row for 3 .. 8 per launch, one tensor-core pass for 25 .. 128).  argv: [rows d]"""
 import os, sys
 import torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
