@@ -55,9 +55,10 @@ extern "C" {
 #define B200KM_OPT_K2_VARIANT 2 /* 0 = auto, 1 = shared-memory owner table, 2 = chunk sort + run sums, 3 = global atomics */
 #define B200KM_OPT_FUSED_VARIANT 3 /* fused K1+K2 (k <= 16, d <= 32): 0 = auto, 1 = the sorted-tile kernel always,
                                      * 2 = same as auto (the cp.async kernel for 16-byte aligned rows of 64 / 128 bytes) */
-#define B200KM_OPT_K4_VARIANT 4 /* K4 (b200km_mindist_update_f32): 0 = auto (rows streamed through a TMA ring when they are contiguous,
-                                  * 128 .. 2048 bytes long, there are enough of them and the pass is HBM-bound), 1 = the register-path kernel
-                                  * always, 2 = the ring wherever it fits.  Same results bit for bit. */
+#define B200KM_OPT_K4_VARIANT 4 /* K4 (b200km_mindist_update_f32): 0 = auto (1-2 candidates: rows streamed through a TMA ring when
+                                  * they are contiguous, 128 .. 2048 bytes long and there are enough of them; 3-8 candidates: one
+                                  * thread per row), 1 = the register-path kernel always, 2 = the ring wherever it fits (the row
+                                  * kernel still takes 3-8 candidates).  Ring and register path: same results bit for bit. */
 int b200km_set_option(int key, int value);
 int b200km_get_option(int key);
 
@@ -271,6 +272,10 @@ int b200km_finalize(const double *acc, int k, int d, const double *centers_old,
  *     cost_out += sum_i mind2[i] (float64; caller zeroes).  init != 0 ignores the old mind2.
  * Replaces: evaluate_cost (R/dask_ml/cluster/k_means.py:516-519) and the first half of
  *           _sample_points (:533-534); `cand` (m x d, X dtype, m <= B200KM_MINDIST_MAX_M).
+ * float32, 16-byte aligned rows: 1-2 candidates stream X through a TMA ring (contiguous rows, >= 1024 rows per SM; the
+ * register-path kernel otherwise -- bit-identical results), 3-8 candidates run one thread per row behind cp.async
+ * buffers (rows of 128 / 256 / 512 bytes, any n).  A row's result depends on the row and the candidates alone, never
+ * on n, the launch shape or where the row sits in X.  B200KM_OPT_K4_VARIANT = 1: the register-path kernel always.
  * ---------------------------------------------------------------------------------------- */
 int b200km_mindist_update_f32(const float *X, int64_t n, int d, int64_t ldx, const float *cand,
                               int m, float *mind2, int init, double *cost_out, void *stream);
